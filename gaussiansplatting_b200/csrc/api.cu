@@ -1,0 +1,918 @@
+// api.cu — the C ABI of include/gs_abi.h: handles, device memory, and the host-side orchestration that the
+// reference keeps in tiled_rasterizer.mm / gpu_sort.mm / optimizer.mm / density_control.mm.
+#include "../../include/gs_abi.h"
+#include "gs_kernels.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+struct gs_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    uint32_t* h_pinned = nullptr;   // small pinned read-back area
+};
+static std::string g_create_err;
+
+#define GS_SETDEV(c) cudaSetDevice((c)->device)
+#define GS_CUDA(c, expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t e__ = (expr);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            (c)->err = std::string(#expr) + ": " + cudaGetErrorString(e__);                       \
+            return e__ == cudaErrorMemoryAllocation ? GS_ERR_OOM : GS_ERR_CUDA;                   \
+        }                                                                                         \
+    } while (0)
+#define GS_ARG(c, cond, msg)                                                                      \
+    do { if (!(cond)) { (c)->err = std::string("bad argument: ") + msg; return GS_ERR_ARG; } } while (0)
+#define GS_LAUNCH_CHECK(c) GS_CUDA(c, cudaGetLastError())
+
+template <typename T>
+static int dalloc(gs_ctx* c, T** p, size_t count) {
+    *p = nullptr;
+    if (count == 0) count = 1;
+    GS_CUDA(c, cudaMalloc((void**)p, count * sizeof(T)));
+    return GS_OK;
+}
+#define GS_TRY(expr) do { int r__ = (expr); if (r__ != GS_OK) return r__; } while (0)
+
+extern "C" {
+
+int gs_version(void) { return 100; }
+
+static int ctx_create_common(int device, cudaStream_t st, bool own, gs_ctx** out) {
+    if (!out) return GS_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) {
+        g_create_err = e != cudaSuccess ? std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e)
+                                        : "no such CUDA device";
+        return GS_ERR_CUDA;
+    }
+    gs_ctx* c = new (std::nothrow) gs_ctx();
+    if (!c) return GS_ERR_OOM;
+    c->device = device;
+    cudaSetDevice(device);
+    if (own) {
+        e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { g_create_err = cudaGetErrorString(e); delete c; return GS_ERR_CUDA; }
+        c->own_stream = true;
+    } else c->stream = st;
+    e = cudaMallocHost((void**)&c->h_pinned, 256);
+    if (e != cudaSuccess) { g_create_err = cudaGetErrorString(e); delete c; return GS_ERR_CUDA; }
+    *out = c;
+    return GS_OK;
+}
+int gs_ctx_create(int device, gs_ctx** out) { return ctx_create_common(device, nullptr, true, out); }
+int gs_ctx_create_on_stream(int device, void* s, gs_ctx** out) { return ctx_create_common(device, (cudaStream_t)s, false, out); }
+int gs_ctx_destroy(gs_ctx* c) {
+    if (!c) return GS_OK;
+    GS_SETDEV(c);
+    cudaStreamSynchronize(c->stream);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    cudaFreeHost(c->h_pinned);
+    delete c;
+    return GS_OK;
+}
+int gs_ctx_sync(gs_ctx* c) { GS_SETDEV(c); GS_CUDA(c, cudaStreamSynchronize(c->stream)); return GS_OK; }
+const char* gs_last_error(gs_ctx* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
+void* gs_ctx_stream(gs_ctx* c) { return (void*)c->stream; }
+
+int gs_dev_alloc(gs_ctx* c, size_t bytes, void** p) { GS_SETDEV(c); GS_CUDA(c, cudaMalloc(p, bytes ? bytes : 1)); return GS_OK; }
+int gs_dev_free(gs_ctx* c, void* p) { GS_SETDEV(c); GS_CUDA(c, cudaStreamSynchronize(c->stream)); GS_CUDA(c, cudaFree(p)); return GS_OK; }
+int gs_dev_upload(gs_ctx* c, void* d, const void* h, size_t bytes) {
+    GS_SETDEV(c);
+    GS_CUDA(c, cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_dev_download(gs_ctx* c, void* h, const void* d, size_t bytes) {
+    GS_SETDEV(c);
+    GS_CUDA(c, cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_dev_memset(gs_ctx* c, void* d, int v, size_t bytes) { GS_SETDEV(c); GS_CUDA(c, cudaMemsetAsync(d, v, bytes, c->stream)); return GS_OK; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// model state
+// ------------------------------------------------------------------------------------------------------
+struct gs_gaussians {
+    gs_ctx* c;
+    float* base = nullptr;      // 19 float planes (pos 3, scale 3, opacity 1, sh 12) of stride cap, then rot float4[cap]
+    uint32_t cap = 0, n = 0;
+    void* staging = nullptr;    // AoS staging for upload/download
+    size_t staging_bytes = 0;
+    GsParams view() const {
+        GsParams P;
+        P.cap = cap;
+        P.pos = base; P.scale = base + 3 * (size_t)cap; P.opacity = base + 6 * (size_t)cap; P.sh = base + 7 * (size_t)cap;
+        P.rot = reinterpret_cast<float4*>(base + 19 * (size_t)cap);
+        return P;
+    }
+};
+static int params_alloc(gs_ctx* c, uint32_t cap, float** base) {
+    cap = (cap + 63u) & ~63u;   // keeps the float4 plane 16-B aligned
+    return dalloc(c, base, (size_t)cap * 23);
+}
+static int staging_reserve(gs_ctx* c, void** p, size_t* have, size_t need) {
+    if (*have >= need) return GS_OK;
+    if (*p) { GS_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(*p); *p = nullptr; *have = 0; }
+    GS_CUDA(c, cudaMalloc(p, need));
+    *have = need;
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_gaussians_create(gs_ctx* c, uint32_t capacity, gs_gaussians** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_gaussians* g = new (std::nothrow) gs_gaussians();
+    if (!g) return GS_ERR_OOM;
+    g->c = c;
+    g->cap = (std::max(capacity, 64u) + 63u) & ~63u;
+    int r = params_alloc(c, g->cap, &g->base);
+    if (r != GS_OK) { delete g; return r; }
+    *out = g;
+    return GS_OK;
+}
+int gs_gaussians_destroy(gs_gaussians* g) {
+    if (!g) return GS_OK;
+    cudaSetDevice(g->c->device);
+    cudaStreamSynchronize(g->c->stream);
+    cudaFree(g->base); cudaFree(g->staging);
+    delete g;
+    return GS_OK;
+}
+static int gaussians_reserve(gs_gaussians* g, uint32_t n) {   // contents are NOT preserved
+    if (n <= g->cap) return GS_OK;
+    gs_ctx* c = g->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(g->base); g->base = nullptr;
+    g->cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    return params_alloc(c, g->cap, &g->base);
+}
+int gs_gaussians_upload(gs_gaussians* g, const gs_gaussian* host, uint32_t n) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_ARG(c, host || n == 0, "host");
+    GS_TRY(gaussians_reserve(g, n));
+    GS_TRY(staging_reserve(c, &g->staging, &g->staging_bytes, (size_t)n * sizeof(gs_gaussian)));
+    GS_CUDA(c, cudaMemcpyAsync(g->staging, host, (size_t)n * sizeof(gs_gaussian), cudaMemcpyHostToDevice, c->stream));
+    gs_launch_params_from_aos(g->staging, n, g->view(), c->stream);
+    GS_LAUNCH_CHECK(c);
+    g->n = n;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_gaussians_download(gs_gaussians* g, gs_gaussian* host, uint32_t n) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_ARG(c, n <= g->n, "n exceeds the live count");
+    GS_TRY(staging_reserve(c, &g->staging, &g->staging_bytes, (size_t)n * sizeof(gs_gaussian)));
+    gs_launch_params_to_aos(g->view(), n, g->staging, c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(host, g->staging, (size_t)n * sizeof(gs_gaussian), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+uint32_t gs_gaussians_count(const gs_gaussians* g) { return g->n; }
+uint32_t gs_gaussians_capacity(const gs_gaussians* g) { return g->cap; }
+int gs_gaussians_clamp_opacity(gs_gaussians* g, float max_raw) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    gs_launch_clamp_opacity(g->view(), g->n, max_raw, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// gradient buffer, images
+// ------------------------------------------------------------------------------------------------------
+struct gs_grads {
+    gs_ctx* c;
+    float* g = nullptr;         // 16 planes of `stride` floats
+    uint32_t cap = 0, stride = 0;
+    int stat_mode = 0;
+    void* staging = nullptr;
+    size_t staging_bytes = 0;
+    GsGradPack view() const { GsGradPack G; G.g = g; G.stride = stride; return G; }
+};
+struct gs_image {
+    gs_ctx* c;
+    uint32_t w = 0, h = 0;
+    float4* px = nullptr;
+    uint32_t* rgba8 = nullptr;  // staging for 8-bit transfers
+};
+
+static int grads_reserve(gs_grads* g, uint32_t n) {   // contents are NOT preserved on growth
+    if (n <= g->cap) return GS_OK;
+    gs_ctx* c = g->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(g->g); g->g = nullptr;
+    g->cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    g->stride = g->cap;
+    return dalloc(c, &g->g, (size_t)g->cap * 16);
+}
+
+extern "C" {
+
+int gs_gaussians_positions(gs_gaussians* g, void* dptr) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_ARG(c, dptr, "dptr");
+    gs_launch_positions(g->view(), g->n, (float4*)dptr, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+int gs_grads_create(gs_ctx* c, uint32_t capacity, gs_grads** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_grads* g = new (std::nothrow) gs_grads();
+    if (!g) return GS_ERR_OOM;
+    g->c = c;
+    int r = grads_reserve(g, std::max(capacity, 64u));
+    if (r != GS_OK) { delete g; return r; }
+    *out = g;
+    return GS_OK;
+}
+int gs_grads_destroy(gs_grads* g) {
+    if (!g) return GS_OK;
+    cudaSetDevice(g->c->device);
+    cudaStreamSynchronize(g->c->stream);
+    cudaFree(g->g); cudaFree(g->staging);
+    delete g;
+    return GS_OK;
+}
+int gs_grads_zero(gs_grads* g, uint32_t n) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_TRY(grads_reserve(g, n));
+    GS_CUDA(c, cudaMemsetAsync(g->g, 0, (size_t)g->stride * 16 * sizeof(float), c->stream));
+    return GS_OK;
+}
+int gs_grads_upload(gs_grads* g, const gs_gradients* host, uint32_t n) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_TRY(grads_reserve(g, n));
+    GS_TRY(staging_reserve(c, &g->staging, &g->staging_bytes, (size_t)n * sizeof(gs_gradients)));
+    GS_CUDA(c, cudaMemcpyAsync(g->staging, host, (size_t)n * sizeof(gs_gradients), cudaMemcpyHostToDevice, c->stream));
+    gs_launch_grads_from_aos(g->staging, n, g->view(), c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_grads_download(gs_grads* g, gs_gradients* host, uint32_t n) {
+    gs_ctx* c = g->c; GS_SETDEV(c);
+    GS_ARG(c, n <= g->cap, "n exceeds capacity");
+    GS_TRY(staging_reserve(c, &g->staging, &g->staging_bytes, (size_t)n * sizeof(gs_gradients)));
+    gs_launch_grads_to_aos(g->view(), n, g->staging, c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(host, g->staging, (size_t)n * sizeof(gs_gradients), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_grads_set_stat_mode(gs_grads* g, int m) { g->stat_mode = m ? 1 : 0; return GS_OK; }
+int gs_grads_packed(gs_grads* g, void** dptr, uint64_t* num_floats, uint32_t* stride) {
+    if (dptr) *dptr = g->g;
+    if (num_floats) *num_floats = (uint64_t)g->stride * 16;
+    if (stride) *stride = g->stride;
+    return GS_OK;
+}
+
+int gs_image_create(gs_ctx* c, uint32_t w, uint32_t h, gs_image** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out && w && h, "image size");
+    gs_image* im = new (std::nothrow) gs_image();
+    if (!im) return GS_ERR_OOM;
+    im->c = c; im->w = w; im->h = h;
+    int r = dalloc(c, &im->px, (size_t)w * h);
+    if (r == GS_OK) r = dalloc(c, &im->rgba8, (size_t)w * h);
+    if (r != GS_OK) { cudaFree(im->px); delete im; return r; }
+    *out = im;
+    return GS_OK;
+}
+int gs_image_destroy(gs_image* im) {
+    if (!im) return GS_OK;
+    cudaSetDevice(im->c->device);
+    cudaStreamSynchronize(im->c->stream);
+    cudaFree(im->px); cudaFree(im->rgba8);
+    delete im;
+    return GS_OK;
+}
+int gs_image_upload_rgba32f(gs_image* im, const float* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_CUDA(c, cudaMemcpyAsync(im->px, host, (size_t)im->w * im->h * 16, cudaMemcpyHostToDevice, c->stream));
+    return GS_OK;
+}
+int gs_image_upload_rgba8(gs_image* im, const uint8_t* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_CUDA(c, cudaMemcpyAsync(im->rgba8, host, (size_t)im->w * im->h * 4, cudaMemcpyHostToDevice, c->stream));
+    gs_launch_rgba8_to_rgba32f(im->rgba8, im->w * im->h, im->px, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+int gs_image_download_rgba32f(gs_image* im, float* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_CUDA(c, cudaMemcpyAsync(host, im->px, (size_t)im->w * im->h * 16, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_image_download_rgba8(gs_image* im, uint8_t* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    gs_launch_rgba32f_to_rgba8(im->px, im->w * im->h, im->rgba8, c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(host, im->rgba8, (size_t)im->w * im->h * 4, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+void* gs_image_devptr(gs_image* im) { return im->px; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// TiledRasterizer — host orchestration of tiled_rasterizer.mm:275-722
+// ------------------------------------------------------------------------------------------------------
+struct gs_rast {
+    gs_ctx* c;
+    uint32_t cap_g = 0, cap_tiles = 0, cap_pix = 0;
+    uint64_t cap_pairs = 0;
+    GsProjected proj{};
+    uint32_t* meta = nullptr;
+    void* scan_scratch = nullptr; size_t scan_scratch_bytes = 0;
+    uint64_t *keys_in = nullptr, *kbuf[2] = {nullptr, nullptr};
+    uint32_t *vals_in = nullptr, *vbuf[2] = {nullptr, nullptr};
+    void* sort_scratch = nullptr;
+    uint2* ranges = nullptr;
+    uint32_t* last_idx = nullptr;
+    float* tfinal = nullptr;
+    float* acc = nullptr;
+    void* staging = nullptr; size_t staging_bytes = 0;
+    // state left behind by forward for backward / inspection (tiled_rasterizer.hpp:94-106)
+    uint32_t W = 0, H = 0, ntx = 0, nty = 0, n = 0;
+    uint64_t pairs = 0;
+    int result = 0, passes = 0;
+};
+
+static void rast_free_gaussian_arrays(gs_rast* r) {
+    cudaFree(r->proj.rec); cudaFree(r->proj.bbox); cudaFree(r->proj.aux); cudaFree(r->proj.covc); cudaFree(r->proj.offs);
+    cudaFree(r->acc); cudaFree(r->scan_scratch);
+    r->proj.rec = nullptr; r->proj.bbox = nullptr; r->proj.aux = nullptr; r->proj.covc = nullptr; r->proj.offs = nullptr;
+    r->acc = nullptr; r->scan_scratch = nullptr;
+}
+static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
+    if (n <= r->cap_g) return GS_OK;
+    gs_ctx* c = r->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    rast_free_gaussian_arrays(r);
+    const uint32_t cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    GS_TRY(dalloc(c, &r->proj.rec, (size_t)cap * 3));
+    GS_TRY(dalloc(c, &r->proj.bbox, cap));
+    GS_TRY(dalloc(c, &r->proj.aux, cap));
+    GS_TRY(dalloc(c, &r->proj.covc, cap));
+    GS_TRY(dalloc(c, &r->proj.offs, (size_t)cap + 1));
+    GS_TRY(dalloc(c, &r->acc, (size_t)cap * 12));
+    r->scan_scratch_bytes = gs_scan_scratch_bytes(cap);
+    GS_CUDA(c, cudaMalloc(&r->scan_scratch, r->scan_scratch_bytes));
+    r->cap_g = cap;
+    return GS_OK;
+}
+static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureBufferCapacity, tiled_rasterizer.mm:210-239
+    gs_ctx* c = r->c;
+    const uint32_t ntx = (W + GS_TILE - 1) / GS_TILE, nty = (H + GS_TILE - 1) / GS_TILE;
+    if (ntx * nty > r->cap_tiles) {
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(r->ranges); cudaFree(r->proj.tile_flags);
+        r->cap_tiles = ntx * nty;
+        GS_TRY(dalloc(c, &r->ranges, r->cap_tiles));
+        GS_TRY(dalloc(c, &r->proj.tile_flags, r->cap_tiles));
+    }
+    if (W * H > r->cap_pix) {
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(r->last_idx); cudaFree(r->tfinal);
+        r->cap_pix = W * H;
+        GS_TRY(dalloc(c, &r->last_idx, r->cap_pix));
+        GS_TRY(dalloc(c, &r->tfinal, r->cap_pix));
+    }
+    r->W = W; r->H = H; r->ntx = ntx; r->nty = nty;
+    return GS_OK;
+}
+static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapacity, tiled_rasterizer.mm:242-272 (no 100 M clamp: note C)
+    if (need <= r->cap_pairs) return GS_OK;
+    gs_ctx* c = r->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch);
+    for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); r->kbuf[i] = nullptr; r->vbuf[i] = nullptr; }
+    r->keys_in = nullptr; r->vals_in = nullptr; r->sort_scratch = nullptr;
+    const uint64_t cap = std::max<uint64_t>(need, (uint64_t)(r->cap_pairs * 1.5));
+    GS_TRY(dalloc(c, &r->keys_in, cap));
+    GS_TRY(dalloc(c, &r->vals_in, cap));
+    for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->kbuf[i], cap)); GS_TRY(dalloc(c, &r->vbuf[i], cap)); }
+    GS_CUDA(c, cudaMalloc(&r->sort_scratch, gs_sort_scratch_bytes(cap, 8)));
+    r->cap_pairs = cap;
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_rast_create(gs_ctx* c, uint32_t max_gaussians, gs_rast** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_rast* r = new (std::nothrow) gs_rast();
+    if (!r) return GS_ERR_OOM;
+    r->c = c;
+    int rc = dalloc(c, &r->meta, GS_META_COUNT);
+    if (rc == GS_OK) rc = rast_reserve_gaussians(r, std::max(max_gaussians, 64u));
+    if (rc == GS_OK) rc = rast_reserve_pairs(r, (uint64_t)std::max(max_gaussians, 64u) * 8);   // AVG_TILES_PER_GAUSSIAN, tiled_rasterizer.hpp:80
+    if (rc != GS_OK) { gs_rast_destroy(r); return rc; }
+    *out = r;
+    return GS_OK;
+}
+int gs_rast_destroy(gs_rast* r) {
+    if (!r) return GS_OK;
+    cudaSetDevice(r->c->device);
+    cudaStreamSynchronize(r->c->stream);
+    rast_free_gaussian_arrays(r);
+    cudaFree(r->meta); cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch);
+    for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); }
+    cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
+    delete r;
+    return GS_OK;
+}
+
+int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    GS_ARG(c, g && u && out, "null handle");
+    cudaStream_t st = c->stream;
+    const uint32_t n = g->n, W = out->w, H = out->h;
+    GS_TRY(rast_reserve_gaussians(r, n));
+    GS_TRY(rast_reserve_image(r, W, H));
+    r->n = n; r->pairs = 0; r->passes = 0;
+    // meta: total = 0, key OR = 0, key AND = ~0
+    GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
+    GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
+    // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
+    gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
+                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
+    gs_launch_exclusive_scan(r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaStreamSynchronize(st));                            // the reference's read of pairCounter (:379-380,454)
+    const uint64_t P = c->h_pinned[GS_META_TOTAL_PAIRS];
+    const uint32_t kor = c->h_pinned[GS_META_KEY_OR], kand = c->h_pinned[GS_META_KEY_AND];
+    if (P >= (1ull << 30)) { c->err = "pair count exceeds 2^30"; return GS_ERR_CAPACITY; }
+    GS_TRY(rast_reserve_pairs(r, P));
+    r->pairs = P;
+    const uint32_t tiles = r->ntx * r->nty;
+    const uint64_t* skeys = r->kbuf[0];
+    const uint32_t* svals = r->vbuf[0];
+    if (P > 0) {
+        gs_launch_emit_pairs(r->proj, n, r->ntx, r->keys_in, r->vals_in, st);
+        int tile_bits = 0;
+        while ((1u << tile_bits) < tiles) tile_bits++;
+        const uint64_t varying = (uint64_t)(kor ^ kand) | (tile_bits ? (((1ull << tile_bits) - 1ull) << 32) : 0ull);
+        const GsSortPlan plan = gs_sort_plan(0, 32 + tile_bits, varying);
+        r->passes = plan.num_passes;
+        r->result = gs_launch_sort64(r->keys_in, r->vals_in, r->kbuf, r->vbuf, P, plan, r->sort_scratch, st);
+        skeys = r->kbuf[r->result]; svals = r->vbuf[r->result];
+    }
+    gs_launch_tile_ranges(skeys, (uint32_t)P, tiles, nullptr, r->ranges, st);
+    gs_launch_blend_forward(r->proj, svals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniforms* u, gs_image* rendered, gs_image* gt, int flags) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    GS_ARG(c, g && gr && u && rendered && gt, "null handle");
+    GS_ARG(c, rendered->w == r->W && rendered->h == r->H && gt->w == r->W && gt->h == r->H, "image size differs from the last forward");
+    GS_ARG(c, g->n == r->n, "gaussian count differs from the last forward");
+    cudaStream_t st = c->stream;
+    const uint32_t n = r->n;
+    if (!(flags & GS_BWD_ACCUMULATE)) GS_TRY(gs_grads_zero(gr, n));   // :687
+    else GS_ARG(c, n <= gr->cap, "gradient buffer too small to accumulate into");
+    GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)n * 12 * sizeof(float), st));
+    const uint32_t* svals = r->vbuf[r->pairs ? r->result : 0];
+    gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
+                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, st);
+    gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,
+                                  gr->view(), gr->stat_mode, st);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    cudaStream_t st = c->stream;
+    const void* src = nullptr; size_t need = 0;
+    const int res = r->pairs ? r->result : 0;
+    switch (which) {
+        case GS_RAST_PROJECTED:
+            need = (size_t)r->n * sizeof(gs_projected);
+            GS_TRY(staging_reserve(c, &r->staging, &r->staging_bytes, need));
+            gs_launch_projected_to_aos(r->proj, r->n, r->staging, st);
+            GS_LAUNCH_CHECK(c);
+            src = r->staging; break;
+        case GS_RAST_KEYS: src = r->keys_in; need = r->pairs * 8; break;
+        case GS_RAST_VALUES: src = r->vals_in; need = r->pairs * 4; break;
+        case GS_RAST_SORTED_KEYS: src = r->kbuf[res]; need = r->pairs * 8; break;
+        case GS_RAST_SORTED_VALUES: src = r->vbuf[res]; need = r->pairs * 4; break;
+        case GS_RAST_TILE_RANGES: src = r->ranges; need = (size_t)r->ntx * r->nty * 8; break;
+        case GS_RAST_LAST_IDX: src = r->last_idx; need = (size_t)r->W * r->H * 4; break;
+        case GS_RAST_TFINAL: src = r->tfinal; need = (size_t)r->W * r->H * 4; break;
+        default: GS_ARG(c, false, "which");
+    }
+    GS_ARG(c, bytes >= need, "host buffer too small");
+    if (need) GS_CUDA(c, cudaMemcpyAsync(host, src, need, cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaStreamSynchronize(st));
+    return GS_OK;
+}
+uint64_t gs_rast_pair_count(const gs_rast* r) { return r->pairs; }
+int gs_rast_sort_passes(const gs_rast* r) { return r->passes; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// GPURadixSort64 / GPURadixSort32 (gpu_sort.hpp:14-107)
+// ------------------------------------------------------------------------------------------------------
+template <typename KeyT>
+struct sort_obj {
+    gs_ctx* c;
+    uint64_t cap = 0;
+    KeyT* kbuf[2] = {nullptr, nullptr};
+    uint32_t* vbuf[2] = {nullptr, nullptr};
+    KeyT* kin = nullptr;            // sort32_depth: generated keys
+    uint32_t* vin = nullptr;
+    void* scratch = nullptr;
+    int result = 0;
+};
+struct gs_sort64 : sort_obj<uint64_t> {};
+struct gs_sort32 : sort_obj<uint32_t> {};
+
+template <typename S>
+static void sort_free(S* s) {
+    for (int i = 0; i < 2; i++) { cudaFree(s->kbuf[i]); cudaFree(s->vbuf[i]); s->kbuf[i] = nullptr; s->vbuf[i] = nullptr; }
+    cudaFree(s->kin); cudaFree(s->vin); cudaFree(s->scratch);
+    s->kin = nullptr; s->vin = nullptr; s->scratch = nullptr;
+}
+template <typename S>
+static int sort_reserve(S* s, uint64_t n, bool gen_inputs) {   // ensureCapacity, gpu_sort.mm
+    gs_ctx* c = s->c;
+    if (n <= s->cap && (!gen_inputs || s->kin)) return GS_OK;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint64_t cap = std::max<uint64_t>(std::max<uint64_t>(n, s->cap), 1024);
+    sort_free(s);
+    for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &s->kbuf[i], cap)); GS_TRY(dalloc(c, &s->vbuf[i], cap)); }
+    if (gen_inputs) { GS_TRY(dalloc(c, &s->kin, cap)); GS_TRY(dalloc(c, &s->vin, cap)); }
+    GS_CUDA(c, cudaMalloc(&s->scratch, gs_sort_scratch_bytes(cap, sizeof(*s->kbuf[0]))));
+    s->cap = cap;
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_sort64_create(gs_ctx* c, uint64_t max_elements, gs_sort64** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_sort64* s = new (std::nothrow) gs_sort64();
+    if (!s) return GS_ERR_OOM;
+    s->c = c;
+    int r = sort_reserve(s, max_elements, false);
+    if (r != GS_OK) { sort_free(s); delete s; return r; }
+    *out = s;
+    return GS_OK;
+}
+int gs_sort64_destroy(gs_sort64* s) {
+    if (!s) return GS_OK;
+    cudaSetDevice(s->c->device); cudaStreamSynchronize(s->c->stream);
+    sort_free(s); delete s;
+    return GS_OK;
+}
+int gs_sort64_sort(gs_sort64* s, const uint64_t* d_keys, const uint32_t* d_vals, uint64_t n, int begin_bit, int end_bit) {
+    gs_ctx* c = s->c; GS_SETDEV(c);
+    GS_ARG(c, begin_bit >= 0 && end_bit <= 64 && begin_bit <= end_bit, "bit range");
+    GS_ARG(c, (d_keys && d_vals) || n == 0, "null input");
+    if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
+    GS_TRY(sort_reserve(s, n, false));
+    const GsSortPlan plan = gs_sort_plan(begin_bit, end_bit, ~0ull);
+    s->result = gs_launch_sort64(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, s->scratch, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+const uint64_t* gs_sort64_sorted_keys(gs_sort64* s) { return s->kbuf[s->result]; }
+const uint32_t* gs_sort64_sorted_values(gs_sort64* s) { return s->vbuf[s->result]; }
+
+int gs_sort32_create(gs_ctx* c, uint64_t max_elements, gs_sort32** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_sort32* s = new (std::nothrow) gs_sort32();
+    if (!s) return GS_ERR_OOM;
+    s->c = c;
+    int r = sort_reserve(s, max_elements, true);
+    if (r != GS_OK) { sort_free(s); delete s; return r; }
+    *out = s;
+    return GS_OK;
+}
+int gs_sort32_destroy(gs_sort32* s) {
+    if (!s) return GS_OK;
+    cudaSetDevice(s->c->device); cudaStreamSynchronize(s->c->stream);
+    sort_free(s); delete s;
+    return GS_OK;
+}
+int gs_sort32_sort(gs_sort32* s, const uint32_t* d_keys, const uint32_t* d_vals, uint64_t n) {
+    gs_ctx* c = s->c; GS_SETDEV(c);
+    if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
+    GS_TRY(sort_reserve(s, n, true));
+    const GsSortPlan plan = gs_sort_plan(0, 32, ~0ull);               // 4 passes x 8 bits, gpu_sort.hpp:34
+    s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, s->scratch, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+int gs_sort32_sort_depth(gs_sort32* s, const void* d_pos4, const float cam[3], uint64_t n) {
+    gs_ctx* c = s->c; GS_SETDEV(c);
+    GS_ARG(c, n < (1ull << 30), "too many elements");
+    GS_TRY(sort_reserve(s, n, true));
+    gs_launch_depth_keys32((const float4*)d_pos4, cam[0], cam[1], cam[2], (uint32_t)n, s->kin, s->vin, c->stream);
+    return gs_sort32_sort(s, s->kin, s->vin, n);
+}
+const uint32_t* gs_sort32_sorted_keys(gs_sort32* s) { return s->kbuf[s->result]; }
+const uint32_t* gs_sort32_sorted_indices(gs_sort32* s) { return s->vbuf[s->result]; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// AdamOptimizer (optimizer.hpp:23-95, optimizer.mm)
+// ------------------------------------------------------------------------------------------------------
+struct gs_adam {
+    gs_ctx* c;
+    float* base = nullptr;      // 38 float planes of stride cap (m: pos3 scale3 op1 sh12, v: same), then m_rot, v_rot float4[cap]
+    uint32_t cap = 0;           // allocation stride
+    uint32_t num = 0;           // the reference's numGaussians (state covers [0, num))
+    uint32_t timestep = 0;
+    GsAdamState view() const {
+        GsAdamState S;
+        const size_t s = cap;
+        S.cap = cap;
+        S.m_pos = base; S.m_scale = base + 3 * s; S.m_op = base + 6 * s; S.m_sh = base + 7 * s;
+        S.v_pos = base + 19 * s; S.v_scale = base + 22 * s; S.v_op = base + 25 * s; S.v_sh = base + 26 * s;
+        S.m_rot = reinterpret_cast<float4*>(base + 38 * s); S.v_rot = reinterpret_cast<float4*>(base + 42 * s);
+        return S;
+    }
+};
+// plane index / width (floats per Gaussian) of a moment group inside the float-plane block; rotation handled apart
+static const int kAdamPlane[5] = {0, 3, -1, 6, 7};
+static const int kAdamWidth[5] = {3, 3, 4, 1, 12};
+
+static int adam_zero_range(gs_adam* a, uint32_t lo, uint32_t hi, int group_mask) {   // zero [lo,hi) of the selected groups (m and v)
+    gs_ctx* c = a->c;
+    if (hi <= lo) return GS_OK;
+    for (int g = 0; g < 5; g++) {
+        if (!(group_mask & (1 << g))) continue;
+        if (g == 2) {
+            GS_CUDA(c, cudaMemsetAsync(a->base + 38 * (size_t)a->cap + 4 * (size_t)lo, 0, (size_t)(hi - lo) * 16, c->stream));
+            GS_CUDA(c, cudaMemsetAsync(a->base + 42 * (size_t)a->cap + 4 * (size_t)lo, 0, (size_t)(hi - lo) * 16, c->stream));
+            continue;
+        }
+        for (int mv = 0; mv < 2; mv++)
+            GS_CUDA(c, cudaMemset2DAsync(a->base + (size_t)(kAdamPlane[g] + 19 * mv) * a->cap + lo, (size_t)a->cap * 4, 0,
+                                         (size_t)(hi - lo) * 4, kAdamWidth[g], c->stream));
+    }
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_adam_create(gs_ctx* c, uint32_t num, gs_adam** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_adam* a = new (std::nothrow) gs_adam();
+    if (!a) return GS_ERR_OOM;
+    a->c = c;
+    a->num = num;
+    a->cap = (std::max(num, 64u) + 63u) & ~63u;
+    int r = dalloc(c, &a->base, (size_t)a->cap * 46);
+    if (r != GS_OK) { delete a; return r; }
+    *out = a;
+    return gs_adam_reset(a);
+}
+int gs_adam_destroy(gs_adam* a) {
+    if (!a) return GS_OK;
+    cudaSetDevice(a->c->device); cudaStreamSynchronize(a->c->stream);
+    cudaFree(a->base); delete a;
+    return GS_OK;
+}
+int gs_adam_reset(gs_adam* a) {                                        // optimizer.mm:80-93
+    gs_ctx* c = a->c; GS_SETDEV(c);
+    a->timestep = 0;
+    GS_CUDA(c, cudaMemsetAsync(a->base, 0, (size_t)a->cap * 46 * sizeof(float), c->stream));
+    return GS_OK;
+}
+int gs_adam_resize_if_needed(gs_adam* a, uint32_t n) {                 // optimizer.mm:95-134: grow only, zero-filled tail
+    gs_ctx* c = a->c; GS_SETDEV(c);
+    if (n <= a->num) return GS_OK;
+    if (n > a->cap) {
+        const uint32_t ncap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+        float* nb = nullptr;
+        GS_TRY(dalloc(c, &nb, (size_t)ncap * 46));
+        GS_CUDA(c, cudaMemsetAsync(nb, 0, (size_t)ncap * 46 * sizeof(float), c->stream));
+        if (a->num) {
+            GS_CUDA(c, cudaMemcpy2DAsync(nb, (size_t)ncap * 4, a->base, (size_t)a->cap * 4, (size_t)a->num * 4, 38, cudaMemcpyDeviceToDevice, c->stream));
+            GS_CUDA(c, cudaMemcpyAsync(nb + 38 * (size_t)ncap, a->base + 38 * (size_t)a->cap, (size_t)a->num * 16, cudaMemcpyDeviceToDevice, c->stream));
+            GS_CUDA(c, cudaMemcpyAsync(nb + 42 * (size_t)ncap, a->base + 42 * (size_t)a->cap, (size_t)a->num * 16, cudaMemcpyDeviceToDevice, c->stream));
+        }
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(a->base);
+        a->base = nb; a->cap = ncap;
+    } else {
+        GS_TRY(adam_zero_range(a, a->num, n, 31));
+    }
+    a->num = n;
+    return GS_OK;
+}
+int gs_adam_reset_opacity_momentum(gs_adam* a) { GS_SETDEV(a->c); return adam_zero_range(a, 0, a->num, 1 << 3); }   // :137-140
+int gs_adam_reset_scale_momentum(gs_adam* a) { GS_SETDEV(a->c); return adam_zero_range(a, 0, a->num, 1 << 1); }     // :143-147
+int gs_adam_reset_state_for_new(gs_adam* a, uint32_t start) {          // :150-188
+    GS_SETDEV(a->c);
+    if (start >= a->num) return GS_OK;
+    return adam_zero_range(a, start, a->num, 31);
+}
+uint32_t gs_adam_timestep(const gs_adam* a) { return a->timestep; }
+
+int gs_adam_step(gs_adam* a, gs_gaussians* g, gs_grads* gr, const float lrs[5]) {
+    gs_ctx* c = a->c; GS_SETDEV(c);
+    GS_ARG(c, g && gr && lrs, "null argument");
+    a->timestep++;                                                     // optimizer.mm:237
+    const uint32_t n = std::min(g->n, a->num);                         // live count, bounded by the state size (note A)
+    GS_ARG(c, n <= gr->cap, "gradient buffer smaller than the gaussian count");
+    const float beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;             // optimizer.mm:272-274
+    const float bc1 = 1.0f - powf(beta1, (float)a->timestep);          // shaders.metal:579-580
+    const float bc2 = 1.0f - powf(beta2, (float)a->timestep);
+    gs_launch_adam(g->view(), gr->view(), a->view(), n, lrs, beta1, beta2, eps, bc1, bc2, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+static int adam_xfer(gs_adam* a, int group, int mv, float* host, const float* src_host, uint32_t n) {
+    gs_ctx* c = a->c; GS_SETDEV(c);
+    GS_ARG(c, group >= 0 && group < 5 && (mv == 0 || mv == 1) && n <= a->cap, "group / moment / n");
+    const int w = kAdamWidth[group];
+    if (group == 2) {
+        float* d = a->base + (size_t)(38 + 4 * mv) * a->cap;
+        if (host) GS_CUDA(c, cudaMemcpyAsync(host, d, (size_t)n * 16, cudaMemcpyDeviceToHost, c->stream));
+        else GS_CUDA(c, cudaMemcpyAsync(d, src_host, (size_t)n * 16, cudaMemcpyHostToDevice, c->stream));
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        return GS_OK;
+    }
+    float* d = a->base + (size_t)(kAdamPlane[group] + 19 * mv) * a->cap;
+    std::vector<float> tmp((size_t)n * w);
+    if (host) {     // planes -> the reference's packed [n][w]
+        GS_CUDA(c, cudaMemcpy2DAsync(tmp.data(), (size_t)n * 4, d, (size_t)a->cap * 4, (size_t)n * 4, w, cudaMemcpyDeviceToHost, c->stream));
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (uint32_t i = 0; i < n; i++) for (int k = 0; k < w; k++) host[(size_t)i * w + k] = tmp[(size_t)k * n + i];
+    } else {
+        for (uint32_t i = 0; i < n; i++) for (int k = 0; k < w; k++) tmp[(size_t)k * n + i] = src_host[(size_t)i * w + k];
+        GS_CUDA(c, cudaMemcpy2DAsync(d, (size_t)a->cap * 4, tmp.data(), (size_t)n * 4, (size_t)n * 4, w, cudaMemcpyHostToDevice, c->stream));
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return GS_OK;
+}
+int gs_adam_download(gs_adam* a, int group, int mv, float* host, uint32_t n) { return adam_xfer(a, group, mv, host, nullptr, n); }
+int gs_adam_upload(gs_adam* a, int group, int mv, const float* host, uint32_t n) { return adam_xfer(a, group, mv, nullptr, host, n); }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// DensityController (density_control.hpp:20-62, density_control.mm)
+// ------------------------------------------------------------------------------------------------------
+struct gs_dens {
+    gs_ctx* c;
+    uint32_t max_gaussians = 1500000;   // MAX_GAUSSIANS, density_control.mm:27
+    float scene_extent = 1.0f;          // :41
+    uint32_t seed = 0x5EEDu;
+    uint32_t cap = 0;                   // per-Gaussian arrays
+    float* accum = nullptr;
+    uint32_t *count = nullptr, *markers = nullptr, *rank = nullptr, *out_off = nullptr, *small = nullptr;   // small: counts3 + stats4
+    void* scan_scratch = nullptr;
+    float* spare = nullptr; uint32_t spare_cap = 0;   // ping-pong target for the rebuilt model state
+};
+static int dens_reserve(gs_dens* d, uint32_t n) {
+    if (n <= d->cap) return GS_OK;
+    gs_ctx* c = d->c;
+    const uint32_t cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    float* na = nullptr; uint32_t* nc = nullptr;
+    GS_TRY(dalloc(c, &na, cap)); GS_TRY(dalloc(c, &nc, cap));
+    GS_CUDA(c, cudaMemsetAsync(na, 0, (size_t)cap * 4, c->stream));
+    GS_CUDA(c, cudaMemsetAsync(nc, 0, (size_t)cap * 4, c->stream));
+    if (d->cap) {
+        GS_CUDA(c, cudaMemcpyAsync(na, d->accum, (size_t)d->cap * 4, cudaMemcpyDeviceToDevice, c->stream));
+        GS_CUDA(c, cudaMemcpyAsync(nc, d->count, (size_t)d->cap * 4, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(d->accum); cudaFree(d->count); cudaFree(d->markers); cudaFree(d->rank); cudaFree(d->out_off); cudaFree(d->scan_scratch);
+    d->accum = na; d->count = nc;
+    GS_TRY(dalloc(c, &d->markers, cap)); GS_TRY(dalloc(c, &d->rank, (size_t)cap + 1)); GS_TRY(dalloc(c, &d->out_off, (size_t)cap + 1));
+    GS_CUDA(c, cudaMalloc(&d->scan_scratch, gs_scan_scratch_bytes(cap)));
+    d->cap = cap;
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_dens_create(gs_ctx* c, uint32_t max_gaussians, gs_dens** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out && max_gaussians > 0, "out / max_gaussians");
+    gs_dens* d = new (std::nothrow) gs_dens();
+    if (!d) return GS_ERR_OOM;
+    d->c = c; d->max_gaussians = max_gaussians;
+    int r = dalloc(c, &d->small, 8);
+    if (r == GS_OK) r = dens_reserve(d, 1024);
+    if (r != GS_OK) { gs_dens_destroy(d); return r; }
+    *out = d;
+    return GS_OK;
+}
+int gs_dens_destroy(gs_dens* d) {
+    if (!d) return GS_OK;
+    cudaSetDevice(d->c->device); cudaStreamSynchronize(d->c->stream);
+    cudaFree(d->accum); cudaFree(d->count); cudaFree(d->markers); cudaFree(d->rank); cudaFree(d->out_off);
+    cudaFree(d->small); cudaFree(d->scan_scratch); cudaFree(d->spare);
+    delete d;
+    return GS_OK;
+}
+int gs_dens_set_scene_extent(gs_dens* d, float e) { d->scene_extent = e; return GS_OK; }   // density_control.mm:79-84
+int gs_dens_set_seed(gs_dens* d, uint32_t s) { d->seed = s; return GS_OK; }
+int gs_dens_reset_accumulator(gs_dens* d, uint32_t n) {                // :113-118
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_TRY(dens_reserve(d, n));
+    GS_CUDA(c, cudaMemsetAsync(d->accum, 0, (size_t)n * 4, c->stream));
+    GS_CUDA(c, cudaMemsetAsync(d->count, 0, (size_t)n * 4, c->stream));
+    return GS_OK;
+}
+int gs_dens_accumulate(gs_dens* d, gs_grads* gr, uint32_t n) {         // :121-185
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, gr && n <= gr->cap, "gradient buffer");
+    GS_TRY(dens_reserve(d, n));
+    gs_launch_accumulate_stats(gr->view(), gr->stat_mode, n, d->accum, d->count, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+int gs_dens_apply(gs_dens* d, gs_gaussians* g, uint32_t iteration, float focal, float image_width, float avg_depth,
+                  gs_density_stats* stats) {                           // :188-501
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, g, "gaussians");
+    gs_density_stats s = {0, 0, 0};
+    if (stats) *stats = s;
+    const uint32_t n = g->n;
+    GS_TRY(dens_reserve(d, n));
+    if (iteration >= 15000u) return gs_dens_reset_accumulator(d, n);   // :216-220
+    cudaStream_t st = c->stream;
+    GsDensifyArgs a;
+    a.n = n; a.iteration = iteration; a.seed = d->seed; a.max_gaussians = d->max_gaussians;
+    a.scene_extent = d->scene_extent; a.focal = focal; a.image_width = image_width; a.avg_depth = avg_depth;
+    const uint64_t bound = std::min<uint64_t>(2ull * n, std::max<uint64_t>(n, d->max_gaussians));
+    if (bound > d->spare_cap) {
+        GS_CUDA(c, cudaStreamSynchronize(st));
+        cudaFree(d->spare); d->spare = nullptr;
+        d->spare_cap = ((uint32_t)std::min<uint64_t>(bound * 5 / 4, 0xFFFFFF00ull) + 63u) & ~63u;
+        GS_TRY(dalloc(c, &d->spare, (size_t)d->spare_cap * 23));
+    }
+    gs_launch_densify_mark(g->view(), d->accum, d->count, a, d->markers, d->small, st);
+    gs_launch_densify_plan(d->markers, n, d->max_gaussians, d->small, d->rank, d->out_off, d->small + 4, d->scan_scratch, st);
+    gs_gaussians tmp = *g;
+    tmp.base = d->spare; tmp.cap = d->spare_cap;
+    gs_launch_densify_scatter(g->view(), tmp.view(), d->markers, d->out_off, a, st);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, d->small + 4, 4 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaStreamSynchronize(st));
+    s.numPruned = c->h_pinned[0]; s.numCloned = c->h_pinned[1]; s.numSplit = c->h_pinned[2];
+    const uint32_t newCount = c->h_pinned[3];
+    std::swap(g->base, d->spare); std::swap(g->cap, d->spare_cap);      // :486-490
+    g->n = newCount;
+    if (stats) *stats = s;
+    return gs_dens_reset_accumulator(d, newCount);                      // :493
+}
+int gs_dens_download(gs_dens* d, float* accum, uint32_t* count, uint32_t* markers, uint32_t n) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, n <= d->cap, "n");
+    if (accum) GS_CUDA(c, cudaMemcpyAsync(accum, d->accum, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (count) GS_CUDA(c, cudaMemcpyAsync(count, d->count, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (markers) GS_CUDA(c, cudaMemcpyAsync(markers, d->markers, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+int gs_dens_upload(gs_dens* d, const float* accum, const uint32_t* count, uint32_t n) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_TRY(dens_reserve(d, n));
+    if (accum) GS_CUDA(c, cudaMemcpyAsync(d->accum, accum, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    if (count) GS_CUDA(c, cudaMemcpyAsync(d->count, count, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+
+}  // extern "C"

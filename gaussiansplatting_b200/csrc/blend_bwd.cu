@@ -1,0 +1,290 @@
+// blend_bwd.cu — K7: reverse-order per-tile backward blend (tiledBackward's per-pixel part,
+// tiled_shaders.metal:388-536, 567-573) and K8: the per-Gaussian linear tail (:538-736).
+//
+// The reference does the whole chain per (pixel, Gaussian) and issues 16 float atomics each.  Everything
+// after dL/dalpha is LINEAR in nine per-(pixel,Gaussian) quantities with per-Gaussian coefficients, so K7 only
+// accumulates those nine moments
+//     m0..2 = sum dLdp_c * w      m3 = sum q      m4,5 = sum q*dx, q*dy      m6,7,8 = sum q*dx^2, q*dx*dy, q*dy^2
+// (w = alpha*T, q = dL/dalpha * G), reduced across the warp by a transposed butterfly (14 shuffles for 9
+// values), across the CTA's warps in shared memory, and flushed with one global float atomic per
+// (tile, Gaussian, moment); K8 then applies the chain once per Gaussian.  The decisions (power, G, alpha
+// tests) use the pinned arithmetic so K7 walks exactly the entries the oracle walks.
+#include "gs_common.cuh"
+#include "gs_kernels.h"
+
+namespace {
+
+constexpr int BB = 128;   // staged entries per round
+
+// sum of v[0..7] over the warp; afterwards lane L holds (in v[0]) the total of value ((L>>2)&7 bit-reversed order below)
+__device__ __forceinline__ float warp_reduce8_transposed(float v[8], uint32_t lane) {
+    const bool b4 = lane & 16u, b3 = lane & 8u, b2 = lane & 4u;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const float send = b4 ? v[i] : v[i + 4], keep = b4 ? v[i + 4] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        const float send = b3 ? v[i] : v[i + 2], keep = b3 ? v[i + 2] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 8);
+    }
+    {
+        const float send = b2 ? v[0] : v[1], keep = b2 ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, 4);
+    }
+    v[0] += __shfl_xor_sync(0xFFFFFFFFu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xFFFFFFFFu, v[0], 1);
+    return v[0];
+}
+// which of the 8 values a lane ends up holding
+__device__ __forceinline__ uint32_t reduce8_index(uint32_t lane) {
+    return ((lane >> 4) & 1u) * 4u + ((lane >> 3) & 1u) * 2u + ((lane >> 2) & 1u);
+}
+
+__global__ void __launch_bounds__(256) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
+                                                             const float4* __restrict__ rendered, const float4* __restrict__ gt,
+                                                             int quantize, const uint32_t* __restrict__ last_idx,
+                                                             const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
+                                                             float* __restrict__ acc) {
+    __shared__ float4 s_r0[BB], s_r1[BB];
+    __shared__ float s_b[BB];
+    __shared__ uint32_t s_gid[BB];
+    __shared__ float s_acc[BB * 9];
+    __shared__ uint32_t s_wmax[8];
+    const uint32_t tile = blockIdx.x;
+    const uint32_t tX = tile % ntx, tY = tile / ntx;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t px = tX * 16u + (warp & 1u) * 8u + (lane & 7u);
+    const uint32_t py = tY * 16u + (warp >> 1) * 4u + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px + 0.5f, pyf = (float)py + 0.5f;      // :416
+    const uint2 range = ranges[tile];                                // :410-413
+
+    uint32_t e = 0;                                                  // entries [0, e) of the tile list concern this pixel
+    float T = 1.0f, dr = 0.f, dg = 0.f, db = 0.f;
+    if (inside) {
+        const size_t pix = (size_t)py * W + px;
+        const uint32_t li = last_idx[pix];                           // :404-407
+        if (li != 0xFFFFFFFFu) {
+            e = min(li + 1u, range.x + range.y) - range.x;           // :427
+            const float4 r = rendered[pix], t = gt[pix];             // :418-423
+            float rr[3] = {r.x, r.y, r.z};
+            const float tt[3] = {t.x, t.y, t.z};
+            float s[3];
+#pragma unroll
+            for (int c = 0; c < 3; c++) {
+                if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
+                const float diff = rr[c] - tt[c];
+                s[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
+            }
+            dr = s[0]; dg = s[1]; db = s[2];
+            T = tfinal[pix];
+            if (tile_flags[tile]) {
+                // Rare path (a conic-degenerate entry was walked): redo the reference's first pass (:430-460), which,
+                // unlike the forward, does not skip such entries.
+                float Tf = 1.0f;
+                for (uint32_t k = 0; k < e; k++) {
+                    const uint32_t g = svals[range.x + k];
+                    const float4 a = rec[3 * (size_t)g], b = rec[3 * (size_t)g + 1];
+                    const float dx = gs::fsub(pxf, a.x), dy = gs::fsub(pyf, a.y);
+                    const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
+                    if (!(power <= 0.0f) || power < -4.5f) continue;
+                    const float alpha = fminf(gs::fmul(b.y, gs::exp_blend(power)), GS_ALPHA_MAX);
+                    if (alpha < GS_ALPHA_MIN) continue;
+                    const float test_T = gs::fmul(Tf, gs::fsub(1.0f, alpha));
+                    if (test_T < GS_T_EPS) break;                    // :458
+                    Tf = test_T;
+                }
+                T = Tf;
+            }
+        }
+    }
+    // CTA-wide and warp-wide extent of the walk
+    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, e);
+    if (lane == 0) s_wmax[warp] = wmax;
+    __syncthreads();
+    uint32_t bmax = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) bmax = max(bmax, s_wmax[w]);
+
+    float ar = 1.0f, ag = 1.0f, ab = 1.0f;                           // accum_rec starts at the white background :468-470
+    for (uint32_t hi = bmax; hi > 0;) {
+        const uint32_t lo = hi > (uint32_t)BB ? hi - BB : 0u;
+        const uint32_t cnt = hi - lo;
+        if (threadIdx.x < cnt) {
+            const uint32_t g = svals[range.x + lo + threadIdx.x];
+            const float4 r0 = rec[3 * (size_t)g], r1 = rec[3 * (size_t)g + 1];
+            s_r0[threadIdx.x] = r0; s_r1[threadIdx.x] = r1; s_b[threadIdx.x] = rec[3 * (size_t)g + 2].x;
+            s_gid[threadIdx.x] = g;
+        }
+        for (uint32_t i = threadIdx.x; i < cnt * 9u; i += 256u) s_acc[i] = 0.f;
+        __syncthreads();
+        if (wmax > lo) {
+            for (int k = (int)min(hi, wmax) - 1 - (int)lo; k >= 0; k--) {    // :473 back to front
+                const float4 a = s_r0[k];
+                const float4 b = s_r1[k];
+                const float dx = gs::fsub(pxf, a.x), dy = gs::fsub(pyf, a.y);   // :483
+                const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
+                bool c = (lo + (uint32_t)k < e) && (power <= 0.0f) && !(power < -4.5f);   // :489
+                float G = 0.f, alpha = 0.f;
+                if (c) {
+                    G = gs::exp_blend(power);                         // :492
+                    alpha = fminf(gs::fmul(b.y, G), GS_ALPHA_MAX);
+                    c = !(alpha < GS_ALPHA_MIN);                      // :495
+                }
+                if (!__any_sync(0xFFFFFFFFu, c)) continue;
+                float v[8], v8 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[i] = 0.f;
+                if (c) {
+                    const float cb = s_b[k];
+                    const float om = 1.0f - alpha;
+                    T = T / fmaxf(om, 0.0001f);                       // :498
+                    const float w = alpha * T;                        // :500
+                    const float dLdA = T * ((dr * (b.z - ar) + dg * (b.w - ag)) + db * (cb - ab));   // :510
+                    ar = alpha * b.z + om * ar; ag = alpha * b.w + om * ag; ab = alpha * cb + om * ab;   // :514
+                    const float q = dLdA * G;
+                    const float qx = q * dx, qy = q * dy;
+                    v[0] = dr * w; v[1] = dg * w; v[2] = db * w; v[3] = q;
+                    v[4] = qx; v[5] = qy; v[6] = qx * dx; v[7] = qx * dy; v8 = qy * dy;
+                }
+                const float tot = warp_reduce8_transposed(v, lane);
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v8 += __shfl_xor_sync(0xFFFFFFFFu, v8, d);
+                if ((lane & 3u) == 0u) atomicAdd(&s_acc[k * 9 + reduce8_index(lane)], tot);
+                if (lane == 1u) atomicAdd(&s_acc[k * 9 + 8], v8);
+            }
+        }
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < cnt * 9u; i += 256u) {
+            const float x = s_acc[i];
+            if (x != 0.f) atomicAdd(&acc[(size_t)s_gid[i / 9u] * 12u + (i % 9u)], x);
+        }
+        __syncthreads();
+        hi = lo;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K8: per-Gaussian tail of tiledBackward (:517-736) applied to the nine moments.  HBM-bound (196 B/Gaussian).
+// Not pinned arithmetic: gradients are graded at 1e-3 relative.
+// ---------------------------------------------------------------------------------------------------
+struct V9 { float V[9]; };   // upper 3x3 of the view matrix, V[c*3+r] = viewMatrix[c][r]
+
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, GsProjected O, const float* __restrict__ acc,
+                                                                  const __grid_constant__ V9 vm, float fx, float fy, uint32_t n,
+                                                                  GsGradPack Gp, int stat_mode) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 m0 = *reinterpret_cast<const float4*>(acc + (size_t)i * 12);
+    const float4 m1 = *reinterpret_cast<const float4*>(acc + (size_t)i * 12 + 4);
+    const float m8 = acc[(size_t)i * 12 + 8];
+    const bool any = (m0.x != 0.f) | (m0.y != 0.f) | (m0.z != 0.f) | (m0.w != 0.f) | (m1.x != 0.f) | (m1.y != 0.f) |
+                     (m1.z != 0.f) | (m1.w != 0.f) | (m8 != 0.f);
+    if (!any) return;                                   // no pixel contributed: every gradient term is +0
+    const float4 r0 = O.rec[3 * (size_t)i], r1 = O.rec[3 * (size_t)i + 1], r2 = O.rec[3 * (size_t)i + 2];
+    const float4 ax = O.aux[i];
+    const float A = -2.0f * r0.z, B = -r0.w, C = -2.0f * r1.x;       // conic
+    const float sig = r1.y;
+    const float col[3] = {r1.z, r1.w, r2.x};
+    float g[16];
+    // colour (:503-507, 699-704): gate per channel, then SH_C0
+    const float mc[3] = {m0.x, m0.y, m0.z};
+#pragma unroll
+    for (int c = 0; c < 3; c++) g[11 + c] = (col[c] <= 0.01f || col[c] >= 0.99f) ? 0.f : mc[c] * GS_SH_C0;
+    g[3] = sig * (1.0f - sig) * m0.w;                                // :517-519
+    // dL/dScreenPos = sig * (A*Sqdx + B*Sqdy, C*Sqdy + B*Sqdx)  (:523-536)
+    const float sx = sig * (A * m1.x + B * m1.y), sy = sig * (C * m1.y + B * m1.x);
+    const float z = r2.y, vx = ax.x, vy = ax.y;
+    const float txtz = vx / z, tytz = vy / z;                        // unclamped (note I) :546-547
+    const float dv0 = sx * fx / z, dv1 = sy * fy / z;                // :551-554
+    const float dv2 = -sx * fx * txtz / z - sy * fy * tytz / z;
+    // dL/dWorld = W^T * dL/dView, W(r,c) = V[c*3+r]  (:558-565)
+#pragma unroll
+    for (int c = 0; c < 3; c++) g[c] = (vm.V[c * 3 + 0] * dv0 + vm.V[c * 3 + 1] * dv1) + vm.V[c * 3 + 2] * dv2;
+    // dL/dConic (:570-573)
+    const float k5 = -0.5f * sig;
+    const float dA = k5 * m1.z, dB = k5 * 2.0f * m1.w, dC = k5 * m8;
+    // conic -> cov2D (:577-596)
+    const float ca = ax.z, cb = ax.w, cc = O.covc[i];
+    const float denom = ca * cc - cb * cb;
+    const float d2i = 1.0f / ((denom * denom) + 0.0000001f);
+    const float Ga = d2i * (-cc * cc * dA + 2.0f * cb * cc * dB + (denom - ca * cc) * dC);
+    const float Gc = d2i * (-ca * ca * dC + 2.0f * ca * cb * dB + (denom - ca * cc) * dA);
+    const float Gb = d2i * 2.0f * (cb * cc * dA - (denom + 2.0f * cb * cb) * dB + ca * cb * dC);
+    // T = J*W (rows 0,1; row 2 is zero), J from the unclamped ratios (:602-620)
+    const float J00 = fx / z, J02 = -fx * txtz / z, J11 = fy / z, J12 = -fy * tytz / z;
+    float T0[3], T1[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        T0[c] = J00 * vm.V[c * 3 + 0] + J02 * vm.V[c * 3 + 2];
+        T1[c] = J11 * vm.V[c * 3 + 1] + J12 * vm.V[c * 3 + 2];
+    }
+    // dL/dSigma = T^T * [[Ga,Gb],[Gb,Gc]] * T  (:624-631; Gb on BOTH off-diagonals, as the reference)
+    float dS[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const float u0 = T0[r] * Ga + T1[r] * Gb, u1 = T0[r] * Gb + T1[r] * Gc;
+#pragma unroll
+        for (int c = 0; c < 3; c++) dS[r][c] = u0 * T0[c] + u1 * T1[c];
+    }
+    // scale / rotation (:635-696): exp(clamp(logs,+-5)) WITHOUT the 20:1 clamp, RAW quaternion
+    const uint32_t cap = P.cap;
+    const float s[3] = {gs::exp_pinned(gs::clampf(P.scale[i], -GS_MAX_SCALE, GS_MAX_SCALE)),
+                        gs::exp_pinned(gs::clampf(P.scale[cap + i], -GS_MAX_SCALE, GS_MAX_SCALE)),
+                        gs::exp_pinned(gs::clampf(P.scale[2 * cap + i], -GS_MAX_SCALE, GS_MAX_SCALE))};
+    const float4 qq = P.rot[i];
+    const float qr = qq.x, qx = qq.y, qy = qq.z, qz = qq.w;
+    float R[3][3];   // R[row][col]
+    R[0][0] = 1.0f - 2.0f * (qy * qy + qz * qz); R[1][0] = 2.0f * (qx * qy + qr * qz); R[2][0] = 2.0f * (qx * qz - qr * qy);
+    R[0][1] = 2.0f * (qx * qy - qr * qz); R[1][1] = 1.0f - 2.0f * (qx * qx + qz * qz); R[2][1] = 2.0f * (qy * qz + qr * qx);
+    R[0][2] = 2.0f * (qx * qz + qr * qy); R[1][2] = 2.0f * (qy * qz - qr * qx); R[2][2] = 1.0f - 2.0f * (qx * qx + qy * qy);
+    // dL/dM = 2 * dL/dSigma * M, M = R*S  (:655-658)
+    float dM[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++)
+            dM[r][c] = 2.0f * ((dS[r][0] * R[0][c] + dS[r][1] * R[1][c]) + dS[r][2] * R[2][c]) * s[c];
+    // dL/ds_k = (R^T dM)_kk ; dL/dlog s = dL/ds * s  (:661-666)
+#pragma unroll
+    for (int k = 0; k < 3; k++) g[4 + k] = ((R[0][k] * dM[0][k] + R[1][k] * dM[1][k]) + R[2][k] * dM[2][k]) * s[k];
+    // D(i,j) = dL_dMt_scaled[i][j] = dL/dR(row i, col j) = dM[i][j]*s[j]  (:669-675)
+    float D[3][3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 3; c++) D[r][c] = dM[r][c] * s[c];
+    g[7] = 2.0f * (qz * (D[0][1] - D[1][0]) + qy * (D[2][0] - D[0][2]) + qx * (D[1][2] - D[2][1]));   // :679-696
+    g[8] = 2.0f * (qy * (D[1][0] + D[0][1]) + qz * (D[2][0] + D[0][2]) + qr * (D[1][2] - D[2][1]) - 2.0f * qx * (D[2][2] + D[1][1]));
+    g[9] = 2.0f * (qx * (D[1][0] + D[0][1]) + qr * (D[2][0] - D[0][2]) + qz * (D[1][2] + D[2][1]) - 2.0f * qy * (D[2][2] + D[0][0]));
+    g[10] = 2.0f * (qr * (D[0][1] - D[1][0]) + qx * (D[2][0] + D[0][2]) + qy * (D[1][2] + D[2][1]) - 2.0f * qz * (D[1][1] + D[0][0]));
+    if (stat_mode) {   // per-view densify statistic (density_control.mm:157-168), so it survives a sum over views
+        float mag = fminf(sqrtf(sx * sx + sy * sy), 1.0f);
+        const bool ok = !isnan(mag) && !isinf(mag) && mag > 0.f;
+        g[14] = ok ? mag : 0.f; g[15] = ok ? 1.0f : 0.f;
+    } else { g[14] = sx; g[15] = sy; }
+    const uint32_t st = Gp.stride;
+#pragma unroll
+    for (int k = 0; k < 16; k++) Gp.g[(size_t)k * st + i] += g[k];
+}
+
+}  // namespace
+
+void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
+                              uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
+                              const uint32_t* last_idx, const float* tfinal, float* acc, cudaStream_t st) {
+    if (ntx * nty == 0) return;
+    blend_backward_kernel<<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, last_idx,
+                                                     tfinal, O.tile_flags, acc);
+}
+
+void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,
+                                   float fy, uint32_t n, GsGradPack G, int stat_mode, cudaStream_t st) {
+    if (n == 0) return;
+    V9 vm;
+    for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) vm.V[c * 3 + r] = V[c * 4 + r];
+    preprocess_backward_kernel<<<(n + 255) / 256, 256, 0, st>>>(P, O, acc, vm, fx, fy, n, G, stat_mode);
+}

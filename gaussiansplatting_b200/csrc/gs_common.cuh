@@ -1,0 +1,114 @@
+// gs_common.cuh — shared device helpers: pinned fp32 arithmetic, constants, error plumbing.
+//
+// "Pinned arithmetic" (DESIGN.md): the kernels that decide sort keys, tile lists, tile ranges,
+// lastContribIdx and the forward image spell every rounding explicitly with __f*_rn intrinsics
+// (never contracted by nvcc) so they reproduce the CPU oracle bit for bit.  The exp() used there is
+// gs_exp2_poly(): exp2(x*log2e) by a degree-5 polynomial built from + * fma and one integer add.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GS_TILE 16u
+#define GS_SH_C0 0.28209479177387814f      // tiled_shaders.metal:83
+#define GS_MAX_RADIUS 512.0f               // tiled_shaders.metal:85
+#define GS_MAX_SCALE 5.0f                  // tiled_shaders.metal:87
+#define GS_MAX_SCALE_TRAIN 4.0f            // shaders.metal:55
+#define GS_MIN_OPACITY 0.005f              // tiled_shaders.metal:742
+#define GS_MAX_TILES_PER_GAUSSIAN 256u     // tiled_shaders.metal:743
+#define GS_ALPHA_MIN (1.0f / 255.0f)       // tiled_shaders.metal:366
+#define GS_ALPHA_MAX 0.99f                 // tiled_shaders.metal:363
+#define GS_T_EPS 0.0001f                   // tiled_shaders.metal:334,458
+
+#define GS_LOG2E 1.44269504088896340736f
+#define GS_EXP2_C1 0x1.62e42ap-1f
+#define GS_EXP2_C2 0x1.ebf9bcp-3f
+#define GS_EXP2_C3 0x1.c6b752p-5f
+#define GS_EXP2_C4 0x1.3cea88p-7f
+#define GS_EXP2_C5 0x1.5bba14p-10f
+#define GS_EXP2_MAGIC 12582912.0f          // 1.5 * 2^23
+
+namespace gs {
+
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float ffma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+// MSL clamp == min(max(x, lo), hi); fminf/fmaxf return the non-NaN operand, like C.
+__device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// 2^t, |t| < 126: r's low mantissa bits hold round(t); f = t - round(t) in [-0.5, 0.5].
+__device__ __forceinline__ float exp2_poly(float t) {
+    float r = fadd(t, GS_EXP2_MAGIC);
+    float nf = fsub(r, GS_EXP2_MAGIC);
+    float f = fsub(t, nf);
+    float p = GS_EXP2_C5;
+    p = ffma(p, f, GS_EXP2_C4);
+    p = ffma(p, f, GS_EXP2_C3);
+    p = ffma(p, f, GS_EXP2_C2);
+    p = ffma(p, f, GS_EXP2_C1);
+    p = ffma(p, f, 1.0f);
+    return __uint_as_float(__float_as_uint(p) + (__float_as_uint(r) << 23));
+}
+// blend exponent already known to lie in [-4.5, 0]
+__device__ __forceinline__ float exp_blend(float x) { return exp2_poly(fmul(x, GS_LOG2E)); }
+// general exp, exponent clamped to [-125, 125] (NaN -> -125)
+__device__ __forceinline__ float exp_pinned(float x) {
+    return exp2_poly(fminf(fmaxf(fmul(x, GS_LOG2E), -125.0f), 125.0f));
+}
+
+// pinned blend exponent: power = fma(dx, fma(Ah, dx, Bn*dy), (Ch*dy)*dy); Ah=-A/2, Bn=-B, Ch=-C/2
+__device__ __forceinline__ float blend_power(float Ah, float Bn, float Ch, float dx, float dy) {
+    float u = ffma(Ah, dx, fmul(Bn, dy));
+    float v = fmul(fmul(Ch, dy), dy);
+    return ffma(dx, u, v);
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// relaxed gpu-scope load/store for look-back status words
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+}  // namespace gs
+
+// ---------------------------------------------------------------------------------------------
+// Device-resident layouts (DESIGN.md "Data layout in HBM")
+// ---------------------------------------------------------------------------------------------
+// Model state, SoA with plane stride = capacity (floats):
+//   pos[3] scale[3] opacity[1] sh[12] planes, and rotation as float4[capacity] (16-B vector loads).
+struct GsParams {
+    float* pos;      // 3 planes
+    float* scale;    // 3 planes (log scale)
+    float4* rot;     // (w,x,y,z)
+    float* opacity;  // raw
+    float* sh;       // 12 planes
+    uint32_t cap;    // plane stride
+};
+
+// Per-Gaussian projection record.  rec: 3 x float4 per Gaussian (48-B gather unit for the blend kernels)
+//   rec[3i+0] = {sx, sy, Ah, Bn}   rec[3i+1] = {Ch, opacity, r, g}   rec[3i+2] = {b, depth, radius, flags}
+// flags bit0: |A|+|B|+|C| < 1e-4 (forward-only skip, tiled_shaders.metal:350-351)
+struct GsProjected {
+    float4* rec;
+    uint4* bbox;     // tileMinX, tileMinY, tileMaxX, tileMaxY
+    float4* aux;     // viewPos.x, viewPos.y, cov2D.a, cov2D.b
+    float* covc;     // cov2D.c
+    uint32_t* offs;  // tile count per Gaussian, then (after the scan) exclusive offsets; [n] = total
+    uint32_t* tile_flags;  // per TILE: 1 if the forward walked a conic-degenerate entry (backward then redoes pass 1)
+};
+
+// Packed gradient buffer: 16 planes of stride `stride` floats:
+//   0-2 position, 3 opacity, 4-6 scale, 7-10 rotation, 11-13 SH-DC (R,G,B), 14-15 view-space x,y
+//   (or, in per-view-stat mode, 14 = sum of clamped |viewspace grad|, 15 = number of views counted).
+struct GsGradPack {
+    float* g;
+    uint32_t stride;
+};

@@ -1,0 +1,94 @@
+// gs_kernels.h — internal launcher interface between the kernel translation units and the C ABI (api.cu).
+// Every launcher enqueues on the given stream and returns; none synchronises.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "gs_common.cuh"
+
+// meta words written by preprocess / scan (one small device array per rasterizer)
+enum { GS_META_TOTAL_PAIRS = 0, GS_META_KEY_OR = 1, GS_META_KEY_AND = 2, GS_META_COUNT = 4 };
+
+// K1 ------------------------------------------------------------------------------------------------
+void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* V, const float* VP, float sw, float sh,
+                          float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, cudaStream_t st);
+
+// K2: in-place exclusive scan of v[0..n) ; v[n] and *total receive the sum.  scratch: gs_scan_scratch_bytes(n).
+size_t gs_scan_scratch_bytes(uint32_t n);
+void gs_launch_exclusive_scan(uint32_t* v, uint32_t n, uint32_t* total, void* scratch, cudaStream_t st);
+
+// K3: emit (tile<<32 | depthKey, gaussian) pairs at the scanned offsets (Gaussian order, ty-major, tx-minor)
+void gs_launch_emit_pairs(const GsProjected& O, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals, cudaStream_t st);
+
+// K4: onesweep LSD radix sort -------------------------------------------------------------------------
+struct GsSortPlan {
+    int num_passes;
+    int shifts[8];
+    int bits[8];
+};
+// passes over [begin_bit, end_bit) in 8-bit digits, skipping digits in which `varying_mask` has no bit set
+GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask);
+size_t gs_sort_scratch_bytes(uint64_t n, int key_bytes);
+// Sorts (keys_in, vals_in) stably.  keys_in/vals_in are not modified; the result lands in buffer
+// (plan.num_passes odd ? 0 : 1) of {kbuf,vbuf}; with 0 passes the input is copied to buffer 0.
+// Returns the index (0/1) of the buffer holding the result.
+int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
+                     const GsSortPlan& plan, void* scratch, cudaStream_t st);
+int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
+                     const GsSortPlan& plan, void* scratch, cudaStream_t st);
+// viewer depth keys (computeDepths, sort.metal:36-72)
+void gs_launch_depth_keys32(const float4* positions, float cx, float cy, float cz, uint32_t n, uint32_t* keys,
+                            uint32_t* vals, cudaStream_t st);
+
+// K5: tile ranges from sorted keys (buildTileRanges semantics, sort.metal:553-589).  lb: numTiles+1 scratch words.
+void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* lb,
+                           uint2* ranges, cudaStream_t st);
+
+// K6: forward blend.  image: W*H float4 RGBA; last_idx/tfinal: W*H.
+void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
+                             uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st);
+
+// K7: backward blend -> per-Gaussian 9-moment accumulators acc[12*n] (zeroed by the caller)
+//   acc[12i+0..2] = sum dLdp_c * w            acc[12i+3] = sum q          (q = dL/dalpha * G)
+//   acc[12i+4..5] = sum q*dx, q*dy            acc[12i+6..8] = sum q*dx^2, q*dx*dy, q*dy^2
+void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
+                              uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
+                              const uint32_t* last_idx, const float* tfinal, float* acc, cudaStream_t st);
+
+// K8: per-Gaussian chain: moments -> parameter gradients, accumulated (+=) into the packed gradient planes
+void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,
+                                   float fy, uint32_t n, GsGradPack G, int stat_mode, cudaStream_t st);
+
+// layout conversion between the reference's AoS wire structs and the device SoA
+void gs_launch_params_from_aos(const void* aos112, uint32_t n, GsParams P, cudaStream_t st);
+void gs_launch_params_to_aos(GsParams P, uint32_t n, void* aos112, cudaStream_t st);
+void gs_launch_grads_to_aos(GsGradPack G, uint32_t n, void* aos112, cudaStream_t st);
+void gs_launch_grads_from_aos(const void* aos112, uint32_t n, GsGradPack G, cudaStream_t st);
+void gs_launch_projected_to_aos(const GsProjected& O, uint32_t n, void* aos88, cudaStream_t st);
+void gs_launch_rgba32f_to_rgba8(const float4* img, uint32_t npix, uint32_t* out, cudaStream_t st);
+void gs_launch_rgba8_to_rgba32f(const uint32_t* img, uint32_t npix, float4* out, cudaStream_t st);
+void gs_launch_clamp_opacity(GsParams P, uint32_t n, float max_raw, cudaStream_t st);
+void gs_launch_positions(GsParams P, uint32_t n, float4* out, cudaStream_t st);
+
+// K9: Adam -------------------------------------------------------------------------------------------
+struct GsAdamState {   // the reference's 10 moment buffers (optimizer.mm:34-60), SoA planes of stride cap
+    float *m_pos, *m_scale, *m_op, *m_sh, *v_pos, *v_scale, *v_op, *v_sh;
+    float4 *m_rot, *v_rot;
+    uint32_t cap;
+};
+void gs_launch_adam(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const float lrs[5], float beta1, float beta2,
+                    float eps, float bc1, float bc2, cudaStream_t st);
+
+// A13 / K10-K11: density control ----------------------------------------------------------------------
+void gs_launch_accumulate_stats(GsGradPack G, int stat_mode, uint32_t n, float* accum, uint32_t* count, cudaStream_t st);
+struct GsDensifyArgs {
+    uint32_t n, iteration, seed, max_gaussians;
+    float scene_extent, focal, image_width, avg_depth;
+};
+// mark: markers[n] in {0 keep,1 prune,2 clone,3 split}; counts[0..2] = pruned, cloned, split (pre-cap)
+void gs_launch_densify_mark(GsParams P, const float* accum, const uint32_t* count, GsDensifyArgs a, uint32_t* markers,
+                            uint32_t* counts3, cudaStream_t st);
+// cap (density_control.mm:360-382) + output offsets: out_off[n+1]; stats[0..2] final pruned/cloned/split, stats[3]=new count
+void gs_launch_densify_plan(uint32_t* markers, uint32_t n, uint32_t max_gaussians, uint32_t* counts3, uint32_t* rankbuf,
+                            uint32_t* out_off, uint32_t* stats4, void* scan_scratch, cudaStream_t st);
+void gs_launch_densify_scatter(GsParams Pin, GsParams Pout, const uint32_t* markers, const uint32_t* out_off,
+                               GsDensifyArgs a, cudaStream_t st);

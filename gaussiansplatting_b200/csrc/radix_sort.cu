@@ -1,0 +1,248 @@
+// radix_sort.cu — K4: onesweep-style least-significant-digit radix sort of (key, u32 value) pairs.
+//
+// Replaces what the reference ships for the tile|depth sort — the 8-thread CPU LSD sort
+// (tiled_rasterizer.mm:27-102) — and the disabled Metal path behind GPURadixSort64::sort
+// (gpu_sort.mm:456-676; histogram64 + scatter64WithAtomicRank, sort.metal:222-270, whose atomic rank is not
+// order preserving).  Same contract: stable ascending sort of u64 keys carrying u32 values; also
+// instantiated for u32 keys (GPURadixSort32, gpu_sort.mm:196-338).
+//
+// Design (HBM-bound; per pass every pair is read once and written once, 12 B + 12 B for u64 keys):
+//   * one up-front kernel builds the digit histograms of ALL passes in a single read of the keys;
+//   * one kernel per pass: a CTA takes a tile of 256 x 16 keys in warp-striped order, ranks them with
+//     warp-level match_any (stable: warp, row, lane order), publishes its per-digit counts, resolves its
+//     global digit offsets by decoupled look-back over the preceding tiles' status words, reorders the tile
+//     through shared memory so global stores are digit-contiguous, and scatters keys then values;
+//   * tile ids are handed out by an atomic ticket so a tile only ever waits on tiles that already started.
+#include "gs_common.cuh"
+#include "gs_kernels.h"
+
+namespace {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_IPT = 16;
+constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 pairs per CTA
+constexpr uint32_t ST_AGG = 0x40000000u, ST_INC = 0x80000000u, ST_VAL = 0x3FFFFFFFu;
+
+struct PassList { int n; int shift[8]; uint32_t mask[8]; };
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict__ keys, uint64_t n, PassList pl,
+                                                         uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t sh[8][256];
+    for (int i = threadIdx.x; i < 8 * 256; i += blockDim.x) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const KeyT k = keys[i];
+#pragma unroll
+        for (int p = 0; p < 8; p++)
+            if (p < pl.n) atomicAdd(&sh[p][(uint32_t)(k >> pl.shift[p]) & pl.mask[p]], 1u);
+    }
+    __syncthreads();
+    for (int p = 0; p < pl.n; p++)
+        for (int d = threadIdx.x; d < 256; d += blockDim.x)
+            if (sh[p][d]) atomicAdd(&ghist[p * 256 + d], sh[p][d]);
+}
+
+// exclusive scan of one value per thread over a 256-thread CTA
+__device__ __forceinline__ uint32_t block_excl_scan256(uint32_t x, uint32_t* s_w /*[8]*/) {
+    uint32_t inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (gs::lane_id() >= d) inc += t; }
+    if (gs::lane_id() == 31) s_w[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t off = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) if (w < (int)(threadIdx.x >> 5)) off += s_w[w];
+    __syncthreads();
+    return off + inc - x;
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
+                                                              KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n,
+                                                              int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
+                                                              uint32_t* counter, uint32_t* status) {
+    __shared__ uint32_t s_wh[RS_WARPS][256];       // per-warp digit counts, then per-warp offsets within the digit
+    __shared__ uint32_t s_binstart[256];           // first slot of digit d in the tile-local sorted order
+    __shared__ uint32_t s_gbase[256];              // global position of slot i with digit d  =  s_gbase[d] + i
+    __shared__ uint32_t s_scan[RS_WARPS];
+    __shared__ uint32_t s_tile;
+    __shared__ __align__(16) KeyT s_keys[RS_TILE]; // reused for values
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
+
+    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_wh[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t warp = threadIdx.x >> 5, lane = gs::lane_id();
+    const uint64_t tile_base = (uint64_t)tile * RS_TILE;
+    const uint32_t valid = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
+    const uint32_t wbase = warp * (32 * RS_IPT) + lane;    // warp-striped: item j at wbase + 32*j
+
+    KeyT key[RS_IPT];
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) {
+        const uint32_t li = wbase + 32 * j;
+        key[j] = (li < valid) ? kin[tile_base + li] : (KeyT)~(KeyT)0;
+    }
+    // stable ranking inside the warp's chunk
+    uint32_t rank[RS_IPT];
+    uint32_t* wh = s_wh[warp];
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) {
+        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+        const uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
+        const int leader = 31 - __clz(m);
+        uint32_t prev = 0;
+        if ((int)lane == leader) { prev = wh[d]; wh[d] = prev + __popc(m); }
+        prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+        rank[j] = prev + __popc(m & lt);
+        __syncwarp();
+    }
+    __syncthreads();
+    // thread d: per-warp exclusive offsets of digit d, and the tile's count
+    const uint32_t d_own = threadIdx.x;
+    uint32_t cnt = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; w++) { uint32_t c = s_wh[w][d_own]; s_wh[w][d_own] = cnt; cnt += c; }
+    if (tile == 0) gs::st_relaxed(&status[d_own], ST_INC | cnt);
+    else gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_AGG | cnt);
+    const uint32_t binstart = block_excl_scan256(cnt, s_scan);
+    const uint32_t gstart = block_excl_scan256(ghist[d_own], s_scan);
+    uint32_t excl = 0;
+    if (tile > 0) {
+        int t = (int)tile - 1;
+        while (true) {
+            uint32_t s;
+            do { s = gs::ld_relaxed(&status[(size_t)t * 256 + d_own]); } while ((s & (ST_AGG | ST_INC)) == 0u);
+            excl += s & ST_VAL;
+            if (s & ST_INC) break;
+            t--;
+        }
+        gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_INC | (excl + cnt));
+    }
+    s_binstart[d_own] = binstart;
+    s_gbase[d_own] = gstart + excl - binstart;
+    __syncthreads();
+    // tile-local reorder of keys
+    uint32_t slot[RS_IPT];
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) {
+        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+        slot[j] = s_binstart[d] + wh[d] + rank[j];
+        s_keys[slot[j]] = key[j];
+    }
+    __syncthreads();
+    uint32_t pos[RS_IPT];
+#pragma unroll
+    for (int k = 0; k < RS_IPT; k++) {
+        const uint32_t i = threadIdx.x + k * RS_THREADS;
+        if (i < valid) {
+            const KeyT kk = s_keys[i];
+            pos[k] = s_gbase[(uint32_t)(kk >> shift) & mask] + i;
+            kout[pos[k]] = kk;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) {
+        const uint32_t li = wbase + 32 * j;
+        if (li < valid) s_vals[slot[j]] = vin[tile_base + li];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_IPT; k++) {
+        const uint32_t i = threadIdx.x + k * RS_THREADS;
+        if (i < valid) vout[pos[k]] = s_vals[i];
+    }
+}
+
+__global__ void depth_keys32_kernel(const float4* __restrict__ pos, float cx, float cy, float cz, uint32_t n,
+                                    uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 p = pos[i];
+    vals[i] = i;
+    uint32_t key = 0xFFFFFFFFu;                                       // sort.metal:50-54, 63-67
+    if (!(isnan(p.x) || isnan(p.y) || isnan(p.z) || isinf(p.x) || isinf(p.y) || isinf(p.z))) {
+        const float dx = gs::fsub(p.x, cx), dy = gs::fsub(p.y, cy), dz = gs::fsub(p.z, cz);
+        const float depth = gs::fadd(gs::fadd(gs::fmul(dx, dx), gs::fmul(dy, dy)), gs::fmul(dz, dz));   // :58-60
+        if (!(isnan(depth) || isinf(depth) || depth < 0.0f)) {
+            const uint32_t u = __float_as_uint(depth);
+            const uint32_t m = (uint32_t)(-(int32_t)(u >> 31)) | 0x80000000u;   // :28-33
+            key = ~(u ^ m);                                           // :70
+        }
+    }
+    keys[i] = key;
+}
+
+constexpr size_t RS_HIST_BYTES = 8 * 256 * 4;
+constexpr size_t RS_CTR_BYTES = 64;
+
+template <typename KeyT>
+int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
+              const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+    if (n == 0) return 0;
+    if (plan.num_passes == 0) {
+        cudaMemcpyAsync(kbuf[0], keys_in, n * sizeof(KeyT), cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(vbuf[0], vals_in, n * 4, cudaMemcpyDeviceToDevice, st);
+        return 0;
+    }
+    const uint32_t tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+    const size_t status_bytes = (size_t)tiles * 256 * 4;
+    uint32_t* ghist = (uint32_t*)scratch;
+    uint32_t* counters = (uint32_t*)((char*)scratch + RS_HIST_BYTES);
+    uint32_t* status = (uint32_t*)((char*)scratch + RS_HIST_BYTES + RS_CTR_BYTES);
+    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + status_bytes * plan.num_passes, st);
+    PassList pl;
+    pl.n = plan.num_passes;
+    for (int p = 0; p < 8; p++) { pl.shift[p] = p < pl.n ? plan.shifts[p] : 0; pl.mask[p] = p < pl.n ? ((1u << plan.bits[p]) - 1u) : 0u; }
+    uint64_t hb = (n + 2047) / 2048; int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
+    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, pl, ghist);
+    const KeyT* kin = keys_in;
+    const uint32_t* vin = vals_in;
+    int dst = 0;
+    for (int p = 0; p < plan.num_passes; p++) {
+        onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, pl.shift[p], pl.mask[p],
+                                                            ghist + p * 256, counters + p, status + (size_t)p * tiles * 256);
+        kin = kbuf[dst]; vin = vbuf[dst];
+        dst ^= 1;
+    }
+    return dst ^ 1;
+}
+
+}  // namespace
+
+GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
+    GsSortPlan pl;
+    pl.num_passes = 0;
+    for (int s = begin_bit; s < end_bit; s += 8) {
+        int bits = (end_bit - s) < 8 ? (end_bit - s) : 8;
+        uint64_t m = ((bits == 64 ? ~0ull : ((1ull << bits) - 1ull)) << s);
+        if ((varying_mask & m) == 0) continue;
+        pl.shifts[pl.num_passes] = s; pl.bits[pl.num_passes] = bits; pl.num_passes++;
+    }
+    return pl;
+}
+
+size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
+    size_t tiles = (size_t)((n + RS_TILE - 1) / RS_TILE) + 1;
+    return RS_HIST_BYTES + RS_CTR_BYTES + tiles * 256 * 4 * 8;
+}
+
+int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
+                     const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+    return sort_impl<uint64_t>(keys_in, vals_in, kbuf, vbuf, n, plan, scratch, st);
+}
+int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
+                     const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+    return sort_impl<uint32_t>(keys_in, vals_in, kbuf, vbuf, n, plan, scratch, st);
+}
+void gs_launch_depth_keys32(const float4* positions, float cx, float cy, float cz, uint32_t n, uint32_t* keys,
+                            uint32_t* vals, cudaStream_t st) {
+    if (n == 0) return;
+    depth_keys32_kernel<<<(n + 255) / 256, 256, 0, st>>>(positions, cx, cy, cz, n, keys, vals);
+}

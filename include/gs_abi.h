@@ -1,0 +1,204 @@
+/*
+ * gs_abi.h — C ABI of the B200-native tiled Gaussian-splatting hot path (libgs_b200.so).
+ *
+ * This is the drop-in boundary: it replaces mtl_engine.mm's device plumbing and the metal-cpp dependency of
+ * ctaylo41/GaussianSplatting.  The reference's host classes (TiledRasterizer, GPURadixSort32/64, AdamOptimizer,
+ * DensityController) keep their names and methods and forward to these entry points
+ * (gaussiansplatting_b200/host/).  Reference paths below are relative to
+ * /root/reference/GuassianSplatting/.
+ *
+ * Conventions
+ *   - every call returns int: 0 = GS_OK, negative = error; text via gs_last_error().  No exceptions, no aborts.
+ *   - one CUDA stream per gs_ctx; calls ENQUEUE and return unless they hand data back to the host
+ *     (download / get / apply / anything documented as synchronising).
+ *   - host pointers are never retained.  Handles are created/destroyed by the caller; a handle is not
+ *     thread-safe; different gs_ctx are independent (one per GPU / rank).
+ *   - wire structs are the reference's, byte for byte (static_asserts below).  On the device the library keeps
+ *     its own SoA layouts; conversion happens only in upload/download calls.
+ */
+#ifndef GS_ABI_H
+#define GS_ABI_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { GS_OK = 0, GS_ERR_CUDA = -1, GS_ERR_OOM = -2, GS_ERR_ARG = -3, GS_ERR_NCCL = -4, GS_ERR_CAPACITY = -5 };
+
+/* ---- wire structs ------------------------------------------------------------------------------------ */
+typedef struct {               /* Gaussian — ply_loader.hpp:14-20, tiled_shaders.metal:11-22 */
+    float position[3]; float _pad0;
+    float scale[3];    float _pad1;          /* LOG scale */
+    float rotation[4];                       /* (w,x,y,z) */
+    float opacity;                           /* raw, pre-sigmoid */
+    float sh[12];                            /* R 0-3, G 4-7, B 8-11 (DC at 0,4,8) */
+    float _pad2[3];
+} gs_gaussian;
+
+typedef struct {               /* GaussianGradients — gradients.hpp:11-31 */
+    float position_x, position_y, position_z, opacity;
+    float scale_x, scale_y, scale_z, _pad1;
+    float rotation[4];
+    float sh[12];
+    float viewspace_grad_x, viewspace_grad_y, _pad2, _pad3;
+} gs_gradients;
+
+typedef struct {               /* ProjectedGaussian — tiled_rasterizer.hpp:24-39 */
+    float screenPos[2]; float conic[3]; float depth; float opacity; float color[3]; float radius;
+    uint32_t tileMinX, tileMinY, tileMaxX, tileMaxY; float _pad1;
+    float viewPos_xy[2]; float cov2D[3]; float _pad2;
+} gs_projected;
+
+typedef struct { uint32_t start, count; } gs_tile_range;     /* TileRange — tiled_rasterizer.hpp:16-19 */
+
+typedef struct {               /* TiledUniforms — tiled_rasterizer.hpp:42-53 (column-major 4x4, m[c*4+r]) */
+    float viewMatrix[16], projectionMatrix[16], viewProjectionMatrix[16];
+    float screenSize[2], focalLength[2];
+    float cameraPos[4];
+    uint32_t numTilesX, numTilesY, numGaussians, _pad2;
+} gs_uniforms;
+
+typedef struct { uint32_t numPruned, numCloned, numSplit; } gs_density_stats;   /* DensityStats — density_control.hpp:13-17 */
+
+#if defined(__cplusplus)
+static_assert(sizeof(gs_gaussian) == 112 && sizeof(gs_gradients) == 112 && sizeof(gs_projected) == 88, "wire layout");
+static_assert(sizeof(gs_tile_range) == 8 && sizeof(gs_uniforms) == 240, "wire layout");
+#endif
+
+typedef struct gs_ctx gs_ctx;
+typedef struct gs_gaussians gs_gaussians;   /* device-resident model state (the reference's gaussianBuffer) */
+typedef struct gs_grads gs_grads;           /* device-resident gradient buffer (the reference's gaussianGradients) */
+typedef struct gs_image gs_image;           /* device-resident RGBA image (render target / ground-truth texture) */
+typedef struct gs_rast gs_rast;             /* TiledRasterizer */
+typedef struct gs_sort64 gs_sort64;         /* GPURadixSort64 */
+typedef struct gs_sort32 gs_sort32;         /* GPURadixSort32 */
+typedef struct gs_adam gs_adam;             /* AdamOptimizer */
+typedef struct gs_dens gs_dens;             /* DensityController */
+
+/* ---- context (replaces MTL::Device + MTL::CommandQueue, mtl_engine.mm:79-86) ----------------------------- */
+int gs_ctx_create(int device, gs_ctx** out);
+/* share an existing CUDA stream (e.g. torch's current stream) instead of creating one */
+int gs_ctx_create_on_stream(int device, void* cuda_stream, gs_ctx** out);
+int gs_ctx_destroy(gs_ctx*);
+int gs_ctx_sync(gs_ctx*);                               /* waitUntilCompleted */
+const char* gs_last_error(gs_ctx*);                     /* ctx may be NULL: last creation error */
+void* gs_ctx_stream(gs_ctx*);
+int gs_version(void);
+
+/* raw device memory (MTL::Buffer with no typed role: sort inputs, positions) */
+int gs_dev_alloc(gs_ctx*, size_t bytes, void** dptr);
+int gs_dev_free(gs_ctx*, void* dptr);
+int gs_dev_upload(gs_ctx*, void* dptr, const void* host, size_t bytes);      /* synchronises */
+int gs_dev_download(gs_ctx*, void* host, const void* dptr, size_t bytes);    /* synchronises */
+int gs_dev_memset(gs_ctx*, void* dptr, int value, size_t bytes);
+
+/* ---- model state --------------------------------------------------------------------------------------- */
+int gs_gaussians_create(gs_ctx*, uint32_t capacity, gs_gaussians** out);
+int gs_gaussians_destroy(gs_gaussians*);
+int gs_gaussians_upload(gs_gaussians*, const gs_gaussian* host, uint32_t n);   /* sets count = n; grows capacity */
+int gs_gaussians_download(gs_gaussians*, gs_gaussian* host, uint32_t n);       /* synchronises */
+uint32_t gs_gaussians_count(const gs_gaussians*);
+uint32_t gs_gaussians_capacity(const gs_gaussians*);
+/* opacity reset, mtl_engine.mm:1179-1185: opacity = min(opacity, max_raw) */
+int gs_gaussians_clamp_opacity(gs_gaussians*, float max_raw);
+/* xyz + pad float4 positions for the viewer sort (updatePositionBuffer, mtl_engine.mm:1028-1036); dptr: n*16 B */
+int gs_gaussians_positions(gs_gaussians*, void* dptr_float4);
+
+/* ---- gradient buffer ------------------------------------------------------------------------------------ */
+int gs_grads_create(gs_ctx*, uint32_t capacity, gs_grads** out);
+int gs_grads_destroy(gs_grads*);
+int gs_grads_zero(gs_grads*, uint32_t n);
+int gs_grads_upload(gs_grads*, const gs_gradients* host, uint32_t n);     /* SH-rest gradients must be 0 (never produced) */
+int gs_grads_download(gs_grads*, gs_gradients* host, uint32_t n);         /* synchronises */
+/* 0 (default): columns 14-15 hold raw summed view-space x,y (reference semantics, one view per buffer).
+ * 1: columns 14-15 hold sum over views of min(|viewspace|,1) and the number of views counted, so that the
+ *    statistic survives accumulation over several views / an all-reduce over ranks. */
+int gs_grads_set_stat_mode(gs_grads*, int per_view_stats);
+/* the packed fp32 device buffer (16 planes of `stride` floats) — hand this to ncclAllReduce / torch.distributed */
+int gs_grads_packed(gs_grads*, void** dptr, uint64_t* num_floats, uint32_t* stride);
+
+/* ---- images ------------------------------------------------------------------------------------------- */
+int gs_image_create(gs_ctx*, uint32_t width, uint32_t height, gs_image** out);
+int gs_image_destroy(gs_image*);
+int gs_image_upload_rgba32f(gs_image*, const float* host);                /* enqueue on the ctx stream (host should be pinned) */
+int gs_image_upload_rgba8(gs_image*, const uint8_t* host);
+int gs_image_download_rgba32f(gs_image*, float* host);                    /* synchronises */
+int gs_image_download_rgba8(gs_image*, uint8_t* host);                    /* synchronises; RGBA8Unorm rounding */
+void* gs_image_devptr(gs_image*);                                          /* float4[width*height] */
+
+/* ---- TiledRasterizer (tiled_rasterizer.hpp:56-124) ------------------------------------------------------ */
+int gs_rast_create(gs_ctx*, uint32_t max_gaussians, gs_rast** out);
+int gs_rast_destroy(gs_rast*);
+/* forward(queue, gaussianBuffer, gaussianCount, uniforms, outputTexture) — tiled_rasterizer.mm:275-672.
+ * numTilesX/Y/numGaussians in *u are overwritten from the image size and the live count (:308-311).
+ * Synchronises once internally (pair count read-back, as the reference does at :379-380,454). */
+int gs_rast_forward(gs_rast*, gs_gaussians*, const gs_uniforms* u, gs_image* out);
+/* backward(queue, gaussianBuffer, gradientBuffer, gaussianCount, uniforms, rendered, groundTruth) —
+ * tiled_rasterizer.mm:675-722.  Zeroes the gradient buffer first (:687) unless GS_BWD_ACCUMULATE is set.
+ * Must follow a forward with the same uniforms (tiled_rasterizer.hpp:94-106). */
+enum { GS_BWD_QUANTIZE_RGBA8 = 1, GS_BWD_ACCUMULATE = 2 };
+int gs_rast_backward(gs_rast*, gs_gaussians*, gs_grads*, const gs_uniforms* u, gs_image* rendered, gs_image* gt, int flags);
+/* inspection of the state forward leaves behind (parity tests); all synchronise and copy to host */
+enum { GS_RAST_PROJECTED = 0,   /* gs_projected[n] */
+       GS_RAST_KEYS = 1,        /* uint64[pairs]  pre-sort   */
+       GS_RAST_VALUES = 2,      /* uint32[pairs]  pre-sort   */
+       GS_RAST_SORTED_KEYS = 3, /* uint64[pairs] */
+       GS_RAST_SORTED_VALUES = 4,/* uint32[pairs] */
+       GS_RAST_TILE_RANGES = 5, /* gs_tile_range[tiles] */
+       GS_RAST_LAST_IDX = 6,    /* uint32[w*h] */
+       GS_RAST_TFINAL = 7 };    /* float[w*h] */
+int gs_rast_get(gs_rast*, int which, void* host, size_t bytes);
+uint64_t gs_rast_pair_count(const gs_rast*);
+int gs_rast_sort_passes(const gs_rast*);                /* digit passes the last forward ran */
+
+/* ---- GPURadixSort64 / GPURadixSort32 (gpu_sort.hpp:14-107) ---------------------------------------------- */
+int gs_sort64_create(gs_ctx*, uint64_t max_elements, gs_sort64** out);
+int gs_sort64_destroy(gs_sort64*);
+/* sort(queue, keysIn, valuesIn, numElements): device pointers; inputs are left untouched; stable; bits [begin,end) */
+int gs_sort64_sort(gs_sort64*, const uint64_t* d_keys, const uint32_t* d_vals, uint64_t n, int begin_bit, int end_bit);
+const uint64_t* gs_sort64_sorted_keys(gs_sort64*);      /* borrowed, valid until the next sort */
+const uint32_t* gs_sort64_sorted_values(gs_sort64*);
+int gs_sort32_create(gs_ctx*, uint64_t max_elements, gs_sort32** out);
+int gs_sort32_destroy(gs_sort32*);
+/* sort(queue, positionBuffer, cameraPos, n): float4 positions -> back-to-front indices (computeDepths, sort.metal:36-72) */
+int gs_sort32_sort_depth(gs_sort32*, const void* d_positions_float4, const float cam[3], uint64_t n);
+int gs_sort32_sort(gs_sort32*, const uint32_t* d_keys, const uint32_t* d_vals, uint64_t n);
+const uint32_t* gs_sort32_sorted_keys(gs_sort32*);
+const uint32_t* gs_sort32_sorted_indices(gs_sort32*);
+
+/* ---- AdamOptimizer (optimizer.hpp:23-95) ---------------------------------------------------------------- */
+int gs_adam_create(gs_ctx*, uint32_t num_gaussians, gs_adam** out);
+int gs_adam_destroy(gs_adam*);
+/* step(queue, gaussians, gradients, lr_position, lr_scale, lr_rotation, lr_opacity, lr_sh): ++timestep, then the
+ * fused update over the LIVE count (SURVEY note A), beta1 .9, beta2 .999, eps 1e-8 (optimizer.mm:228-296) */
+int gs_adam_step(gs_adam*, gs_gaussians*, gs_grads*, const float lrs[5]);
+int gs_adam_reset(gs_adam*);
+int gs_adam_resize_if_needed(gs_adam*, uint32_t new_num_gaussians);
+int gs_adam_reset_opacity_momentum(gs_adam*);
+int gs_adam_reset_scale_momentum(gs_adam*);
+int gs_adam_reset_state_for_new(gs_adam*, uint32_t start_idx);
+uint32_t gs_adam_timestep(const gs_adam*);
+/* moments in the reference's layout: group 0 position [n*3], 1 scale [n*3], 2 rotation [n*4], 3 opacity [n], 4 sh [n*12];
+ * which_moment 0 = m, 1 = v.  Synchronise. */
+int gs_adam_download(gs_adam*, int group, int which_moment, float* host, uint32_t n);
+int gs_adam_upload(gs_adam*, int group, int which_moment, const float* host, uint32_t n);
+
+/* ---- DensityController (density_control.hpp:20-62) ------------------------------------------------------ */
+int gs_dens_create(gs_ctx*, uint32_t max_gaussians, gs_dens** out);      /* reference: 1,500,000 */
+int gs_dens_destroy(gs_dens*);
+int gs_dens_set_scene_extent(gs_dens*, float extent);
+int gs_dens_set_seed(gs_dens*, uint32_t seed);
+int gs_dens_accumulate(gs_dens*, gs_grads*, uint32_t n);
+int gs_dens_reset_accumulator(gs_dens*, uint32_t n);
+/* apply(...): may replace the device storage inside *g and changes its count; synchronises (new count read-back) */
+int gs_dens_apply(gs_dens*, gs_gaussians* g, uint32_t iteration, float focal_length, float image_width,
+                  float avg_depth, gs_density_stats* stats);
+int gs_dens_download(gs_dens*, float* accum, uint32_t* count, uint32_t* markers, uint32_t n);   /* any may be NULL */
+int gs_dens_upload(gs_dens*, const float* accum, const uint32_t* count, uint32_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS_ABI_H */

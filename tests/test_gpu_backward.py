@@ -1,0 +1,122 @@
+"""GPU parity of the backward path (K7 + K8) through the C ABI against the CPU oracle.
+
+Bar (north_star): gradients within 1e-3 relative (atomic order differs).  The comparison is per component against
+the oracle's double-accumulated value: |a-b| <= 1e-3 * max(|a|,|b|) + atol, where atol = 1e-5 * (largest |value| of
+that parameter group) absorbs components that are the tiny remainder of large cancelling terms (their float
+accumulation noise is relative to the terms, not to the remainder).
+"""
+import numpy as np
+import pytest
+from gaussiansplatting_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+GROUPS = ["position", "opacity", "scale", "rotation", "sh", "viewspace"]
+
+
+def compare_grads(got, ref, rtol=1e-3, atol_rel=1e-5):
+    worst = {}
+    for f in GROUPS:
+        a, b = got[f].astype(np.float64), ref[f].astype(np.float64)
+        scale = max(np.abs(b).max(), 1e-30)
+        err = np.abs(a - b) - (rtol * np.maximum(np.abs(a), np.abs(b)) + atol_rel * scale)
+        worst[f] = float(err.max())
+        assert err.max() <= 0, (f, float(err.max()), float(scale))
+    return worst
+
+
+def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False):
+    ref = orc.render(g, u)
+    gt = orc.render(gt_g, u)["image"]
+    ref_gr = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, quantize=quantize)
+    G = gs.Gaussians(ctx, len(g)); G.upload(g)
+    R = gs.Rasterizer(ctx, len(g))
+    img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
+    gti.upload(gt)
+    D = gs.Grads(ctx, len(g))
+    try:
+        R.forward(G, u, img)
+        R.backward(G, D, u, img, gti, gs.GS_BWD_QUANTIZE_RGBA8 if quantize else 0)
+        got = D.download(len(g))
+    finally:
+        D.close(); gti.close(); img.close(); R.close(); G.close()
+    return got, ref_gr
+
+
+@pytest.mark.parametrize("n,W,H,s0,seed", [
+    (300, 64, 64, 0.05, 7),
+    (2000, 100, 70, 0.03, 8),
+    (10000, 256, 256, 0.012, synth.CONFIG_SEED["C1"]),
+])
+def test_backward_parity(gs, ctx, orc, n, W, H, s0, seed):
+    g = synth.make_scene(n, seed, s0)
+    gt_g = synth.make_scene(n, seed ^ 0xA5A5, s0)
+    u = synth.make_camera(1, 8, W, H, n)
+    got, ref = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    assert np.abs(ref["opacity"]).max() > 0
+    compare_grads(got, ref)
+    # SH-rest gradients are never written (tiled_shaders.metal:699-704)
+    for k in (1, 2, 3, 5, 6, 7, 9, 10, 11):
+        assert np.all(got["sh"][:, k] == 0)
+
+
+def test_backward_quantized_and_saturated(gs, ctx, orc):
+    """RGBA8 render-target mode (note G) on a dense scene where many pixels hit the T < 1e-4 cut (note I)"""
+    n, W, H = 6000, 128, 96
+    g = synth.make_scene(n, 31, 0.03); g["opacity"] += 2.0
+    gt_g = synth.make_scene(n, 32, 0.03)
+    u = synth.make_camera(5, 8, W, H, n)
+    got, ref = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=True)
+    compare_grads(got, ref)
+
+
+def test_backward_degenerate_conic_tiles(gs, ctx, orc):
+    """giant splats whose conic magnitude is < 1e-4 are skipped by the forward but not by the backward's first
+    pass (note I): exercises the per-tile recompute path"""
+    n, W, H = 3000, 256, 256
+    g = synth.make_scene(n, 41, 0.02)
+    g["scale"][:150] = np.log(3.0)
+    gt_g = synth.make_scene(n, 42, 0.02)
+    u = synth.make_camera(2, 8, W, H, n)
+    ref = orc.render(g, u)
+    p = ref["proj"]
+    mag = np.abs(p["conic"]).sum(1)
+    assert ((mag < 1e-4) & (p["radius"] > 0)).sum() > 0, "fixture must contain conic-degenerate visible splats"
+    got, refg = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    compare_grads(got, refg)
+
+
+def test_backward_accumulate_two_views(gs, ctx, orc):
+    """GS_BWD_ACCUMULATE sums views (the data-parallel step) and per-view stat mode feeds density control"""
+    n, W, H = 2000, 96, 64
+    g = synth.make_scene(n, 51, 0.04)
+    gt_g = synth.make_scene(n, 52, 0.04)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    R = gs.Rasterizer(ctx, n)
+    img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
+    D = gs.Grads(ctx, n); D.set_stat_mode(True)
+    total = None
+    accum, count = np.zeros(n, np.float32), np.zeros(n, np.uint32)
+    try:
+        for v in range(2):
+            u = synth.make_camera(v, 2, W, H, n)
+            ref = orc.render(g, u)
+            gt = orc.render(gt_g, u)["image"]
+            rg = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt)
+            orc.accumulate_gradients(rg, accum, count)
+            total = rg.copy() if total is None else total
+            if v:
+                for f in GROUPS:
+                    total[f] = total[f] + rg[f]
+            gti.upload(gt)
+            R.forward(G, u, img)
+            R.backward(G, D, u, img, gti, gs.GS_BWD_ACCUMULATE if v else 0)
+        got = D.download(n)
+        for f in GROUPS[:-1]:
+            a, b = got[f].astype(np.float64), total[f].astype(np.float64)
+            assert np.all(np.abs(a - b) <= 1e-3 * np.maximum(np.abs(a), np.abs(b)) + 1e-5 * np.abs(b).max()), f
+        # columns 14/15 = sum of per-view clamped norms, number of views counted
+        assert np.array_equal(got["viewspace"][:, 1].astype(np.uint32), count)
+        assert np.allclose(got["viewspace"][:, 0], accum, rtol=1e-3, atol=1e-6)
+    finally:
+        D.close(); gti.close(); img.close(); R.close(); G.close()

@@ -1,0 +1,184 @@
+"""GPU parity of the radix sorts (K4), Adam (K9) and density control (A13, K10/K11) through the C ABI."""
+import numpy as np
+import pytest
+from gaussiansplatting_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def rand_u64(seed, n):
+    return synth.splitmix64(seed, n, 77)
+
+
+# ---- GPURadixSort64 / GPURadixSort32 ------------------------------------------------------------------------
+@pytest.mark.parametrize("n", [0, 1, 31, 1000, 4096, 4097, 100003, 1 << 20])
+def test_sort64_matches_reference_cpu_sort(gs, ctx, orc, n):
+    keys = rand_u64(n + 1, n)
+    vals = np.arange(n, dtype=np.uint32)
+    S = gs.Sort64(ctx, max(n, 1))
+    try:
+        k, v = S.sort_host(keys, vals)
+    finally:
+        S.close()
+    rk, rv = orc.sort_pairs(keys, vals, threads=4)
+    assert np.array_equal(k, rk) and np.array_equal(v, rv)
+
+
+def test_sort64_is_stable_and_respects_bit_range(gs, ctx, orc):
+    n = 300000
+    keys = rand_u64(5, n) & np.uint64(0x0000000F000000FF)      # many ties -> stability matters
+    vals = np.arange(n, dtype=np.uint32)
+    S = gs.Sort64(ctx, n)
+    try:
+        k, v = S.sort_host(keys, vals)
+        rk, rv = orc.sort_pairs(keys, vals)
+        assert np.array_equal(k, rk) and np.array_equal(v, rv)
+        # only bits [32,40): order by that digit, ties in input order
+        k2, v2 = S.sort_host(keys, vals, 32, 40)
+        order = np.argsort((keys >> np.uint64(32)) & np.uint64(0xFF), kind="stable")
+        assert np.array_equal(v2, vals[order]) and np.array_equal(k2, keys[order])
+    finally:
+        S.close()
+
+
+def test_sort64_checksum_at_full_size(gs, ctx):
+    """BASELINE-size property test (no oracle needed): sortedness, permutation validity, key/value pairing"""
+    n = 1 << 23
+    keys = rand_u64(99, n)
+    vals = np.arange(n, dtype=np.uint32)
+    S = gs.Sort64(ctx, n)
+    try:
+        k, v = S.sort_host(keys, vals)
+    finally:
+        S.close()
+    assert np.all(k[:-1] <= k[1:])
+    assert np.array_equal(keys[v], k)
+    assert np.array_equal(np.sort(v), vals)
+
+
+def test_sort32_depth_back_to_front(gs, ctx, orc):
+    n = 50000
+    pos = np.zeros((n, 4), np.float32)
+    pos[:, :3] = synth.make_scene(n, 3, 0.01)["position"]
+    pos[7, 0] = np.nan; pos[9, 2] = np.inf
+    cam = np.array([0.5, -3.0, 1.0], np.float32)
+    rk, rv = orc.depth_keys32(pos, cam)
+    rk, rv = orc.sort_pairs32(rk, rv)
+    d = ctx.alloc(n * 16)
+    S = gs.Sort32(ctx, n)
+    try:
+        ctx.upload(d, pos)
+        S.sort_depth(d, cam, n)
+        ctx.sync()
+        assert np.array_equal(ctx.download(S.sorted_keys, n, np.uint32), rk)
+        assert np.array_equal(ctx.download(S.sorted_indices, n, np.uint32), rv)
+    finally:
+        S.close(); ctx.free(d)
+
+
+# ---- AdamOptimizer ----------------------------------------------------------------------------------------
+def make_grads(orc_mod, n, seed):
+    from gaussiansplatting_b200.layouts import GRADIENTS
+    g = np.zeros(n, GRADIENTS)
+    u = lambda s, k=1: (synth.uniform01(seed, n * k, s).reshape(n, k) * 2 - 1).astype(np.float32)
+    g["position"] = u(1, 3) * 0.8
+    g["opacity"] = u(2)[:, 0] * 0.8
+    g["scale"] = u(3, 3) * 0.3
+    g["rotation"] = u(4, 4) * 1e-3
+    for c in range(3):
+        g["sh"][:, 4 * c] = u(5 + c)[:, 0] * 1e-2
+    g["viewspace"] = u(9, 2) * 1e-3
+    g["position"][3, 0] = np.nan          # skipped Gaussian (shaders.metal:567-570)
+    g["opacity"][5] = np.inf
+    return g
+
+
+def test_adam_parity_three_steps(gs, ctx, orc):
+    n = 5000
+    g = synth.make_scene(n, 61, 0.02)
+    g["position"][11, 0] = 2e6            # corrupted Gaussian is skipped (:573-576)
+    lrs = [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3]
+    ref = g.copy()
+    st = orc.AdamState(n)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    A = gs.Adam(ctx, n)
+    D = gs.Grads(ctx, n)
+    try:
+        for step in range(3):
+            gr = make_grads(orc, n, 100 + step)
+            orc.adam_step(ref, gr, st, lrs)
+            D.upload(gr)
+            A.step(G, D, lrs)
+        assert A.timestep == 3
+        got = G.download()
+        for f in ("position", "scale", "rotation", "opacity", "sh"):
+            assert np.array_equal(got[f], ref[f], equal_nan=True), f
+        for grp in range(5):
+            assert np.array_equal(A.download(grp, 0, n), st.m[grp], equal_nan=True), grp
+            assert np.array_equal(A.download(grp, 1, n), st.v[grp], equal_nan=True), grp
+        # state helpers (optimizer.mm:137-188)
+        A.reset_opacity_momentum(); A.reset_scale_momentum()
+        assert not A.download(3, 0, n).any() and not A.download(1, 1, n).any()
+        assert A.download(0, 0, n).any()
+        A.reset_state_for_new(n - 100)
+        assert not A.download(0, 0, n)[3 * (n - 100):].any() and A.download(0, 0, n)[:3 * (n - 100)].any()
+        A.resize_if_needed(3 * n)
+        assert np.array_equal(A.download(0, 0, n), np.concatenate([st.m[0][:3 * (n - 100)], np.zeros(300, np.float32)]))
+        assert not A.download(4, 1, 3 * n)[12 * n:].any()
+    finally:
+        D.close(); A.close(); G.close()
+
+
+# ---- DensityController ------------------------------------------------------------------------------------
+def test_accumulate_gradients_parity(gs, ctx, orc):
+    n = 4000
+    gr = make_grads(orc, n, 7)
+    gr["position"][3, 0] = 0; gr["opacity"][5] = 0
+    gr["viewspace"][10] = [3.0, 4.0]      # clamped to 1
+    gr["viewspace"][11] = 0               # not counted
+    gr["viewspace"][12, 0] = np.nan       # not counted
+    accum, count = np.zeros(n, np.float32), np.zeros(n, np.uint32)
+    D = gs.Grads(ctx, n); Dn = gs.Density(ctx)
+    try:
+        D.upload(gr)
+        for _ in range(2):
+            orc.accumulate_gradients(gr, accum, count)
+            Dn.accumulate(D, n)
+        a, c = Dn.download(n)
+        assert np.array_equal(c, count) and np.array_equal(a, accum)
+    finally:
+        Dn.close(); D.close()
+
+
+@pytest.mark.parametrize("iteration,max_g", [(700, 1500000), (3500, 1500000), (700, 2600), (700, 2000), (200, 1500000),
+                                             (15000, 1500000)])
+def test_densify_apply_parity(gs, ctx, orc, iteration, max_g):
+    n = 2000
+    g = synth.make_scene(n, 71, 0.02)
+    g["scale"][:400] = np.log(0.2)         # big: split candidates
+    g["scale"][:100] = np.log(0.5)         # world-space / screen-space prune once iteration > 3000
+    g["opacity"][400:500] = -7.0           # pruned
+    accum = (synth.uniform01(5, n, 1) * 1e-3).astype(np.float32)
+    count = (synth.uniform01(5, n, 2) * 3).astype(np.uint32)
+    extent, focal, width, depth, seed = 3.3, 230.0, 256.0, 6.6, 1234
+    ref, rmark, rstats = orc.densify_apply(g, accum, count, iteration, extent, focal, width, depth, seed, max_g)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    Dn = gs.Density(ctx, max_g)
+    try:
+        Dn.set_scene_extent(extent); Dn.set_seed(seed)
+        Dn.upload(accum, count)
+        stats = Dn.apply(G, iteration, focal, width, depth)
+        assert stats == tuple(int(x) for x in rstats)
+        assert G.count == len(ref)
+        got = G.download()
+        if iteration < 15000:                               # past DENSIFY_UNTIL_ITER apply() returns before marking
+            _, _, m = Dn.download(n, markers=True)
+            assert np.array_equal(m, rmark)
+        for f in ("position", "scale", "rotation", "opacity", "sh"):
+            assert np.array_equal(got[f], ref[f]), f
+        a, c = Dn.download(G.count)
+        assert not a.any() and not c.any()                 # resetAccumulator(newCount), density_control.mm:493
+    finally:
+        Dn.close(); G.close()
+    if max_g < 3000:
+        assert len(ref) <= max_g and rstats[2] < 190 + (max_g > 2000) * 1000
