@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the tiled-splatting hot path (BASELINE.json metric).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path through the C ABI
+  python bench.py --impl reference --gpus N --steps K ...   # the CPU oracle (the reference is Metal-only) on host cores
+
+One "step" = one fwd+bwd pass of the hot path over one synthetic view of config C2 (1M Gaussians, 1920x1080).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from gaussiansplatting_b200 import synth  # noqa: E402
+
+METRIC = "fwd+bwd ms/frame @1M Gaussians 1080p"
+LRS = [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3]          # mtl_engine.mm:1063-1068
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                       "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: [self.rows.append(l) for l in self.p.stdout], daemon=True).start()
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        for l in self.rows:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def workload(name):
+    n = synth.CONFIG_N[name]
+    W, H = synth.CONFIG_RES[name]
+    return n, W, H, synth.CONFIG_S0[name], synth.CONFIG_SEED[name], synth.CONFIG_ORBIT[name]
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reference arm: the reference's own algorithm on the host cores (oracle port; Metal cannot run here)
+# ---------------------------------------------------------------------------------------------------------
+def oracle_frame(orc, g, u, gt, threads, timing=None):
+    t0 = time.perf_counter()
+    r = orc.render(g, u, threads)
+    t1 = time.perf_counter()
+    if gt is None:
+        gt = np.full_like(r["image"], 0.5)
+    orc.backward(g, r["proj"], r["svals"], r["ranges"], u, r["last"], r["image"], gt, threads=threads)
+    t2 = time.perf_counter()
+    if timing is not None:
+        timing.append((t1 - t0, t2 - t1))
+    return t2 - t0
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import orc
+    orc.build()
+    n, W, H, s0, seed, orbit = workload(args.workload)
+    threads = orc.max_threads()
+    g = synth.make_scene(n, seed, s0)
+    steps, warm = max(1, args.steps), max(0, min(args.warmup, 1))
+    # a full 1M-Gaussian 1080p frame costs several seconds of CPU: bound the run to ~a few minutes
+    steps = min(steps, 5)
+    times = []
+    for i in range(warm + steps):
+        u = synth.make_camera(i, 64, W, H, n, orbit)
+        t = oracle_frame(orc, g, u, None, threads)
+        if i >= warm:
+            times.append(t)
+    ms = 1e3 * float(np.mean(times))
+    sample = f"{len(times)} full frames (project+pairs+CPU LSD sort+ranges+forward+backward), {threads} OpenMP threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": ms, "unit": "ms/frame", "n_gpus": args.gpus, "steps": len(times),
+        "warmup": warm, "ms_per_step": ms, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": f"{args.workload}: {n} Gaussians, {W}x{H}, 1 view per step"},
+        "cpu_baseline": {"value": ms, "unit": "ms/frame", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ms, "unit": "ms/frame", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference is Metal/Objective-C++ and cannot run on Linux: this arm times oracle/ (scalar C++ restatement of "
+                "its kernels + its own CPU radix sort) on the host cores"}))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# this repo's arm
+# ---------------------------------------------------------------------------------------------------------
+class CudaArrayView:
+    """zero-copy torch view of a raw device pointer (for torch.distributed on the packed gradient buffer)"""
+    def __init__(self, ptr, nfloats):
+        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+
+
+def run_ours(args):
+    import torch
+    from gaussiansplatting_b200 import capi as gs
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    n, W, H, s0, seed, orbit = workload(args.workload)
+    K, Wm = max(1, args.steps), max(3, args.warmup)
+    hbm_peak, sm_max_mhz, peak_kind = measured_peaks()
+
+    ctx = gs.Context(local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local)
+    g_host = synth.make_scene(n, seed, s0)
+    G = gs.Gaussians(ctx, n); G.upload(g_host)
+    R = gs.Rasterizer(ctx, n)
+    img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
+    D = gs.Grads(ctx, n)
+    A = gs.Adam(ctx, n)
+    Dn = gs.Density(ctx); Dn.set_scene_extent(synth.scene_extent(orbit))
+    NV = 64
+    cams = [synth.make_camera(v, NV, W, H, n, orbit) for v in range(NV)]
+    # ground truth: render of a different scene seed through this same path, kept as RGBA8 in pinned memory
+    Ggt = gs.Gaussians(ctx, n); Ggt.upload(synth.make_scene(n, seed ^ 0xA5A5, s0))
+    gt_pinned = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    out_pinned = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    R.forward(Ggt, cams[rank % NV], gti)
+    gti.download_rgba8_ptr(gt_pinned.data_ptr())
+    Ggt.close()
+    gti.upload_rgba8_ptr(gt_pinned.data_ptr()); ctx.sync()
+
+    def view(i):
+        return cams[(i * world + rank) % NV]
+
+    def barrier():
+        ctx.sync()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """device time of `steps` calls, CUDA events on the launching stream, max over ranks"""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            fn(i)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        barrier()
+        return ms
+
+    def fwd_bwd(i):
+        R.forward(G, view(i), img)
+        R.backward(G, D, view(i), img, gti)
+
+    for i in range(Wm):
+        fwd_bwd(i)
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_total = timed(fwd_bwd, K)
+    clocks = sampler.stop()
+    ms_step = ms_total / K                       # one view per rank per step
+    value = ms_total / (K * world)               # whole-job ms per frame
+    pairs, passes = R.pair_count, R.sort_passes
+
+    out = {"metric": METRIC, "value": value, "unit": "ms/frame", "n_gpus": world, "steps": K, "warmup": Wm,
+           "ms_per_step": ms_step, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+           "data": "synthetic", "clocks": clocks,
+           "config": {"workload": f"{args.workload}: {n} Gaussians, {W}x{H}, 1 view per GPU per step, {pairs} tile pairs",
+                      "parallelism": f"views sharded over {world} GPU(s), no data-path collective for fwd+bwd",
+                      "l2": "per-step working set (~0.6 GB: params, records, pair buffers, images) exceeds the 126 MB L2"}}
+
+    # ---- end to end through the C ABI with host buffers: H2D ground truth (pinned RGBA8) + uniforms, D2H rendered RGBA8
+    def e2e_step(i):
+        gti.upload_rgba8_ptr(gt_pinned.data_ptr())
+        R.forward(G, view(i), img)
+        R.backward(G, D, view(i), img, gti)
+        img.download_rgba8_ptr(out_pinned.data_ptr())      # synchronises
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        e2e_step(i)
+    ctx.sync()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    if dist is not None:
+        t = torch.tensor([e2e_ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); e2e_ms = float(t.item())
+    out["e2e"] = {"value": e2e_ms / (K * world), "unit": "ms/frame", "h2d_bytes_per_step": W * H * 4 + 240,
+                  "d2h_bytes_per_step": W * H * 4,
+                  "what": "per step: pinned RGBA8 ground truth + TiledUniforms H2D, forward, backward, rendered RGBA8 D2H; "
+                          "Gaussians/gradients stay device-resident (model state), wall clock incl. all syncs"}
+
+    # ---- training iterations (fwd + bwd + accumulateGradients + Adam), with the gradient all-reduce when N > 1
+    D.set_stat_mode(world > 1)
+    ptr, nfl, _ = D.packed()
+    gbuf = torch.as_tensor(CudaArrayView(ptr, nfl), device="cuda") if dist is not None else None
+
+    def train_step(i):
+        R.forward(G, view(i), img)
+        R.backward(G, D, view(i), img, gti)
+        if dist is not None:
+            ctx.sync()
+            dist.all_reduce(gbuf)
+            torch.cuda.current_stream().synchronize()
+        Dn.accumulate(D, n)
+        A.step(G, D, LRS)
+    g_backup = G.download() if rank == 0 and False else None
+    for i in range(2):
+        train_step(i)
+    ms_train = timed(train_step, K)
+    out["train_iters_per_s"] = 1e3 * K / ms_train
+    out["train_views_per_s"] = 1e3 * K * world / ms_train
+    G.upload(g_host)                                 # undo the training steps for the measurements below
+    launches_fb = 9 + passes                         # preprocess scan emit hist passes ranges blend_fwd blend_bwd chain
+    out["gpu_launches"] = K * launches_fb
+
+    if rank == 0:
+        # ---- per-kernel device times (CUDA events around every stage, same stream) and rooflines
+        R.set_profiling(True)
+        acc = None
+        for i in range(K):
+            fwd_bwd(i)
+            t = R.timings()
+            acc = t if acc is None else {k: acc[k] + t[k] for k in t}
+        R.set_profiling(False)
+        stage = {k: v / K for k, v in acc.items()}
+        R.forward(G, view(0), img)
+        E, C = R.count_evals()
+        last = R.get(gs.RAST_LAST_IDX); rng = R.get(gs.RAST_TILE_RANGES)
+        P = R.pair_count
+        tiles = len(rng)
+        sm_mhz = clocks.get("sm_mhz") or sm_max_mhz
+        fp32_peak = 2 * 128 * 148 * sm_max_mhz * 1e6 / 1e12          # TFLOP/s at max clock
+        bytes_alg = {"preprocess": 136.0 * n, "scan": 8.0 * n, "emit": 12.0 * P + 32.0 * n,
+                     "sort": P * (8.0 + 24.0 * passes), "ranges": 8.0 * P + 8.0 * tiles,
+                     "preprocess_bwd": 196.0 * n}
+        flops_alg = {"blend_fwd": 25.0 * C + 14.0 * (E - C), "blend_bwd": 70.0 * C + 14.0 * (E - C)}
+        roofs = {}
+        for k, b in bytes_alg.items():
+            a = b / (stage[k] * 1e-3) / 1e9 if stage[k] > 0 else 0.0
+            roofs[k] = {"bound": "hbm", "ms": stage[k], "achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak}
+        for k, f in flops_alg.items():
+            a = f / (stage[k] * 1e-3) / 1e12 if stage[k] > 0 else 0.0
+            roofs[k] = {"bound": "fp32", "ms": stage[k], "achieved": a, "peak": fp32_peak, "unit": "TFLOP/s",
+                        "frac": a / fp32_peak}
+        dom = max((k for k in roofs), key=lambda k: stage[k])
+        out["roofline"] = dict(roofs[dom], kernel=dom, traffic=None, peak_kind=peak_kind,
+                               note="algorithmic bytes/flops per SURVEY 8(d); fp32 peak = 2*128*148*sm_max_mhz")
+        out["rooflines"] = roofs
+        out["stage_ms"] = stage
+        out["evals"] = {"E": E, "C": C, "pairs": P, "sort_passes": passes}
+
+        # ---- radix sort Gkeys/s: standalone GPURadixSort64 on full-entropy keys (8 passes) and the real tile|depth keys
+        sort_res = {}
+        for logn in (20, 24):
+            m = 1 << logn
+            keys = synth.splitmix64(1234 + logn, m, 5)
+            dk, dv = ctx.alloc(m * 8), ctx.alloc(m * 4)
+            ctx.upload(dk, keys); ctx.upload(dv, np.arange(m, dtype=np.uint32))
+            S = gs.Sort64(ctx, m)
+            for _ in range(3):
+                S.sort(dk, dv, m)
+            reps = 20
+            ms = timed(lambda i: S.sort(dk, dv, m), reps) / reps
+            gk = m / (ms * 1e-3) / 1e9
+            bts = m * (8.0 + 24.0 * 8)
+            sort_res[f"random_u64_2^{logn}"] = {"gkeys_per_s": gk, "ms": ms, "passes": 8, "GB/s": bts / (ms * 1e-3) / 1e9,
+                                                "frac_of_hbm": bts / (ms * 1e-3) / 1e9 / hbm_peak}
+            S.close(); ctx.free(dk); ctx.free(dv)
+        sort_res["tile_depth_keys_C2"] = {"gkeys_per_s": P / (stage["sort"] * 1e-3) / 1e9, "ms": stage["sort"], "passes": passes,
+                                          "n": P}
+        out["sort"] = sort_res
+        out["sort_gkeys_per_s"] = sort_res["random_u64_2^24"]["gkeys_per_s"]
+
+        # ---- CPU baseline beside it: the oracle on the host cores, one full frame of the same workload
+        if world == 1 and not args.no_cpu:
+            from oracle import orc
+            orc.build()
+            th = orc.max_threads()
+            gt_f = gt_pinned.numpy().astype(np.float32) / 255.0
+            tm = []
+            t = oracle_frame(orc, g_host, view(0), gt_f, th, tm)
+            out["cpu_baseline"] = {"value": t * 1e3, "unit": "ms/frame", "cores": th, "kind": "port",
+                                   "sample": f"1 full frame of the same workload (forward {tm[0][0]:.2f} s incl. the reference's "
+                                             f"CPU LSD sort, backward {tm[0][1]:.2f} s)"}
+        print(json.dumps(out))
+    barrier()
+    for o in (Dn, A, D, gti, img, R, G):
+        o.close()
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=list(synth.CONFIG_N))
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

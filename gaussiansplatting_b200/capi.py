@@ -213,6 +213,21 @@ class Rasterizer:
     def backward(self, gaussians, grads, uniforms, rendered, gt, flags=0):
         self.ctx.check(lib().gs_rast_backward(self.h, gaussians.h, grads.h, _p(uniforms), rendered.h, gt.h, C.c_int(flags)))
 
+    def set_profiling(self, on=True):
+        self.ctx.check(lib().gs_rast_set_profiling(self.h, C.c_int(int(on))))
+
+    STAGES = ("preprocess", "scan", "readback", "emit", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
+
+    def timings(self, include_backward=True):
+        ms = (C.c_float * 9)()
+        self.ctx.check(lib().gs_rast_get_timings(self.h, ms, C.c_int(int(include_backward))))
+        return dict(zip(self.STAGES, [float(x) for x in ms]))
+
+    def count_evals(self):
+        e, c = C.c_uint64(), C.c_uint64()
+        self.ctx.check(lib().gs_rast_count_evals(self.h, C.byref(e), C.byref(c)))
+        return int(e.value), int(c.value)
+
     @property
     def pair_count(self):
         return int(lib().gs_rast_pair_count(self.h))

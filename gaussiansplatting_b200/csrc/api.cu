@@ -19,6 +19,7 @@ struct gs_ctx {
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
 };
 static std::string g_create_err;
+#define GS_PROF_EVENTS 11
 
 #define GS_SETDEV(c) cudaSetDevice((c)->device)
 #define GS_CUDA(c, expr)                                                                          \
@@ -359,6 +360,11 @@ struct gs_rast {
     uint32_t W = 0, H = 0, ntx = 0, nty = 0, n = 0;
     uint64_t pairs = 0;
     int result = 0, passes = 0;
+    // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
+    bool prof = false;
+    cudaEvent_t ev[GS_PROF_EVENTS] = {};
+    unsigned long long* counters = nullptr;
+    void mark(int i) { if (prof) cudaEventRecord(ev[i], c->stream); }
 };
 
 static void rast_free_gaussian_arrays(gs_rast* r) {
@@ -443,6 +449,8 @@ int gs_rast_destroy(gs_rast* r) {
     cudaFree(r->meta); cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch);
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); }
     cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
+    cudaFree(r->counters);
+    for (int i = 0; i < GS_PROF_EVENTS; i++) if (r->ev[i]) cudaEventDestroy(r->ev[i]);
     delete r;
     return GS_OK;
 }
@@ -458,10 +466,13 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     // meta: total = 0, key OR = 0, key AND = ~0
     GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
     GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
+    r->mark(0);
     // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
     gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
                          u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
+    r->mark(1);
     gs_launch_exclusive_scan(r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
+    r->mark(2);
     GS_LAUNCH_CHECK(c);
     GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     GS_CUDA(c, cudaStreamSynchronize(st));                            // the reference's read of pairCounter (:379-380,454)
@@ -473,8 +484,10 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     const uint32_t tiles = r->ntx * r->nty;
     const uint64_t* skeys = r->kbuf[0];
     const uint32_t* svals = r->vbuf[0];
+    r->mark(3);
     if (P > 0) {
         gs_launch_emit_pairs(r->proj, n, r->ntx, r->keys_in, r->vals_in, st);
+        r->mark(4);
         int tile_bits = 0;
         while ((1u << tile_bits) < tiles) tile_bits++;
         const uint64_t varying = (uint64_t)(kor ^ kand) | (tile_bits ? (((1ull << tile_bits) - 1ull) << 32) : 0ull);
@@ -482,9 +495,12 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
         r->passes = plan.num_passes;
         r->result = gs_launch_sort64(r->keys_in, r->vals_in, r->kbuf, r->vbuf, P, plan, r->sort_scratch, st);
         skeys = r->kbuf[r->result]; svals = r->vbuf[r->result];
-    }
+    } else r->mark(4);
+    r->mark(5);
     gs_launch_tile_ranges(skeys, (uint32_t)P, tiles, nullptr, r->ranges, st);
+    r->mark(6);
     gs_launch_blend_forward(r->proj, svals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+    r->mark(7);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }
@@ -496,15 +512,53 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     GS_ARG(c, g->n == r->n, "gaussian count differs from the last forward");
     cudaStream_t st = c->stream;
     const uint32_t n = r->n;
+    r->mark(8);
     if (!(flags & GS_BWD_ACCUMULATE)) GS_TRY(gs_grads_zero(gr, n));   // :687
     else GS_ARG(c, n <= gr->cap, "gradient buffer too small to accumulate into");
     GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)n * 12 * sizeof(float), st));
     const uint32_t* svals = r->vbuf[r->pairs ? r->result : 0];
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
                              (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, st);
+    r->mark(9);
     gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,
                                   gr->view(), gr->stat_mode, st);
+    r->mark(10);
     GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+
+int gs_rast_set_profiling(gs_rast* r, int on) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    if (on) for (int i = 0; i < GS_PROF_EVENTS; i++) if (!r->ev[i]) GS_CUDA(c, cudaEventCreate(&r->ev[i]));
+    r->prof = on != 0;
+    return GS_OK;
+}
+// ms of the last forward (+ backward): [0] preprocess [1] scan [2] pair-count read-back (host sync) [3] emit
+// [4] sort (all passes) [5] tile ranges [6] blend forward [7] backward memsets + blend backward [8] per-Gaussian backward
+int gs_rast_get_timings(gs_rast* r, float* ms9, int include_backward) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    GS_ARG(c, r->prof && ms9, "profiling is off");
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    static const int from[9] = {0, 1, 2, 3, 4, 5, 6, 8, 9}, to[9] = {1, 2, 3, 4, 5, 6, 7, 9, 10};
+    for (int i = 0; i < 9; i++) {
+        ms9[i] = 0.f;
+        if (i >= 7 && !include_backward) continue;
+        GS_CUDA(c, cudaEventElapsedTime(&ms9[i], r->ev[from[i]], r->ev[to[i]]));
+    }
+    return GS_OK;
+}
+// E = list entries the forward walk visits, C = contributing evaluations, for the last forward
+int gs_rast_count_evals(gs_rast* r, uint64_t* E, uint64_t* C) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    if (!r->counters) GS_TRY(dalloc(c, &r->counters, 2));
+    GS_CUDA(c, cudaMemsetAsync(r->counters, 0, 16, c->stream));
+    gs_launch_blend_count(r->proj, r->vbuf[r->pairs ? r->result : 0], r->ranges, r->W, r->H, r->ntx, r->nty, r->counters, c->stream);
+    GS_LAUNCH_CHECK(c);
+    unsigned long long h[2];
+    GS_CUDA(c, cudaMemcpyAsync(h, r->counters, 16, cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (E) *E = h[0];
+    if (C) *C = h[1];
     return GS_OK;
 }
 

@@ -30,10 +30,12 @@ __global__ void tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n
 
 constexpr int FB = 256;   // staged entries per round
 
+template <bool COUNT>
 __global__ void __launch_bounds__(256) blend_forward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                             float4* __restrict__ image, uint32_t* __restrict__ last_idx,
-                                                            float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags) {
+                                                            float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags,
+                                                            unsigned long long* __restrict__ counters) {
     __shared__ float4 s_r0[FB], s_r1[FB];
     __shared__ float s_b[FB];
     __shared__ uint32_t s_degen;
@@ -48,6 +50,7 @@ __global__ void __launch_bounds__(256) blend_forward_kernel(const float4* __rest
     if (threadIdx.x == 0) s_degen = 0;
 
     float Cr = 0.f, Cg = 0.f, Cb = 0.f, T = 1.0f, Tp = 1.0f;
+    uint32_t nE = 0, nC = 0;   // COUNT only: list entries visited / contributing evaluations (roofline accounting)
     uint32_t last = 0xFFFFFFFFu;
     bool done = !inside;
     for (uint32_t base = 0; base < range.y; base += FB) {
@@ -66,6 +69,7 @@ __global__ void __launch_bounds__(256) blend_forward_kernel(const float4* __rest
             for (uint32_t k = 0; k < cnt; k++) {                     // :334
                 const float4 a = s_r0[k];
                 const float4 b = s_r1[k];
+                if (COUNT) nE++;
                 const float dx = gs::fsub(pxf, a.x), dy = gs::fsub(pyf, a.y);   // :347
                 const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
                 if (!(power <= 0.0f) || power < -4.5f) continue;      // :359
@@ -75,11 +79,18 @@ __global__ void __launch_bounds__(256) blend_forward_kernel(const float4* __rest
                 const float w = gs::fmul(alpha, T);                   // :369
                 Cr = gs::ffma(b.z, w, Cr); Cg = gs::ffma(b.w, w, Cg); Cb = gs::ffma(s_b[k], w, Cb);
                 Tp = T;
+                if (COUNT) nC++;
                 T = gs::fmul(T, gs::fsub(1.0f, alpha));               // :370
                 last = range.x + base + k;                            // :372
                 if (!(T > GS_T_EPS)) { done = true; break; }          // :334 loop condition
             }
         }
+    }
+    if (COUNT) {
+        unsigned long long e = nE, c = nC;
+        for (int d = 16; d >= 1; d >>= 1) { e += __shfl_xor_sync(0xFFFFFFFFu, e, d); c += __shfl_xor_sync(0xFFFFFFFFu, c, d); }
+        if (lane == 0) { atomicAdd(&counters[0], e); atomicAdd(&counters[1], c); }
+        return;
     }
     if (inside) {
         const size_t pix = (size_t)py * W + px;
@@ -104,5 +115,14 @@ void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st) {
     if (ntx * nty == 0) return;
-    blend_forward_kernel<<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, tfinal, O.tile_flags);
+    blend_forward_kernel<false><<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, tfinal,
+                                                           O.tile_flags, nullptr);
+}
+
+// counts E (entries visited) and C (contributing evaluations) of the forward walk; counters[2] zeroed by the caller
+void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
+                           uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st) {
+    if (ntx * nty == 0) return;
+    blend_forward_kernel<true><<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
+                                                          O.tile_flags, counters);
 }

@@ -47,6 +47,9 @@ void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st);
 
+void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
+                           uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st);
+
 // K7: backward blend -> per-Gaussian 9-moment accumulators acc[12*n] (zeroed by the caller)
 //   acc[12i+0..2] = sum dLdp_c * w            acc[12i+3] = sum q          (q = dL/dalpha * G)
 //   acc[12i+4..5] = sum q*dx, q*dy            acc[12i+6..8] = sum q*dx^2, q*dx*dy, q*dy^2

@@ -12,9 +12,17 @@ from .layouts import GAUSSIAN, UNIFORMS
 SH_C0 = 0.28209479177387814
 TILE = 16
 
-# per-config base scale s0 and scene seeds
-CONFIG_S0 = {"C1": 0.012, "C2": 0.010, "C3": 0.010, "C4": 0.006, "C5": 0.010}
+# per-config base scale s0, calibrated ONCE with the oracle so that the mean number of tiles per visible
+# Gaussian is ~7-9 (the reference's sizing assumption AVG_TILES_PER_GAUSSIAN = 8, tiled_rasterizer.hpp:80) and frozen:
+#   C1 256^2  orbit 3: s0 0.040 -> 6.7 tiles      C2 1080p orbit 3: s0 0.006 -> 7.9 tiles
+#   C4 4K     orbit 3: s0 0.006 -> 20.8 tiles (log-scale is clamped at -5, tiled_shaders.metal:87,160, so no s0 goes lower)
+#   C3/C5 (training) use s0 0.03 seen from orbit 12: Adam clamps log-scale to +-4 (shaders.metal:55,655), so a trainable
+#   scene cannot hold scales below e^-4 = 0.018.
+CONFIG_S0 = {"C1": 0.040, "C2": 0.006, "C3": 0.030, "C4": 0.006, "C5": 0.030}
+CONFIG_ORBIT = {"C1": 3.0, "C2": 3.0, "C3": 12.0, "C4": 3.0, "C5": 12.0}
 CONFIG_SEED = {"C1": 0x5EED0001, "C2": 0x5EED0002, "C3": 0x5EED0003, "C4": 0x5EED0004, "C5": 0x5EED0005}
+CONFIG_N = {"C1": 10000, "C2": 1000000, "C3": 500000, "C4": 3000000, "C5": 1000000}
+CONFIG_RES = {"C1": (256, 256), "C2": (1920, 1080), "C3": (1920, 1080), "C4": (3840, 2160), "C5": (1920, 1080)}
 
 
 def splitmix64(seed, n, stream=0):

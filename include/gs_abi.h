@@ -150,6 +150,12 @@ enum { GS_RAST_PROJECTED = 0,   /* gs_projected[n] */
        GS_RAST_LAST_IDX = 6,    /* uint32[w*h] */
        GS_RAST_TFINAL = 7 };    /* float[w*h] */
 int gs_rast_get(gs_rast*, int which, void* host, size_t bytes);
+/* per-stage CUDA-event timing of the last forward/backward (replaces the chrono prints of tiled_rasterizer.mm:639-671):
+ * ms9 = preprocess, scan, pair-count read-back, emit, sort, tile ranges, blend fwd, blend bwd (+memsets), per-Gaussian bwd */
+int gs_rast_set_profiling(gs_rast*, int on);
+int gs_rast_get_timings(gs_rast*, float* ms9, int include_backward);
+/* E = list entries the forward walk visits, C = contributing (pixel, Gaussian) evaluations of the last forward */
+int gs_rast_count_evals(gs_rast*, uint64_t* E, uint64_t* C);
 uint64_t gs_rast_pair_count(const gs_rast*);
 int gs_rast_sort_passes(const gs_rast*);                /* digit passes the last forward ran */
 
