@@ -8,7 +8,8 @@
 //
 // Design (HBM-bound; per pass every pair is read once and written once, 12 B + 12 B for u64 keys):
 //   * one up-front kernel builds the digit histograms of ALL passes in a single read of the keys;
-//   * one kernel per pass: a CTA takes a tile of 256 x 16 keys in warp-striped order, ranks them with
+//   * one kernel per pass: a CTA stages a tile of 256 x 16 pairs into shared memory with two TMA bulk copies
+//     (cp.async.bulk + mbarrier: the whole 48 KB is in flight from one instruction, no registers), ranks them with
 //     warp-level match_any (stable: warp, row, lane order), publishes its per-digit counts, resolves its
 //     global digit offsets by decoupled look-back over the preceding tiles' status words, reorders the tile
 //     through shared memory so global stores are digit-contiguous, and scatters keys then values;
@@ -59,37 +60,81 @@ __device__ __forceinline__ uint32_t block_excl_scan256(uint32_t x, uint32_t* s_w
     return off + inc - x;
 }
 
-template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
-                                                              KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n,
-                                                              int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
-                                                              uint32_t* counter, uint32_t* status) {
-    __shared__ uint32_t s_wh[RS_WARPS][256];       // per-warp digit counts, then per-warp offsets within the digit
-    __shared__ uint32_t s_binstart[256];           // first slot of digit d in the tile-local sorted order
-    __shared__ uint32_t s_gbase[256];              // global position of slot i with digit d  =  s_gbase[d] + i
-    __shared__ uint32_t s_scan[RS_WARPS];
-    __shared__ uint32_t s_tile;
-    __shared__ __align__(16) KeyT s_keys[RS_TILE]; // reused for values
-    uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys);
+// ---- TMA 1-D bulk copy + mbarrier (sm_90+/sm_100a): one thread stages the whole tile, no registers involved ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
 
-    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
-    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_wh[0][0])[i] = 0;
+constexpr int RS_LOOKBACK = 8;   // predecessor status words fetched per round (independent loads)
+
+template <typename KeyT>
+struct OnesweepSmem {
+    alignas(128) KeyT keys[RS_TILE];          // TMA-staged input keys, then the tile-sorted keys
+    alignas(128) uint32_t vals[RS_TILE];      // TMA-staged input values, then the tile-sorted values
+    uint16_t wh[RS_WARPS][256];               // per-warp digit counts, then per-warp offsets within the digit
+    uint32_t binstart[256];                   // first slot of digit d in the tile-local sorted order
+    uint32_t gbase[256];                      // global position of slot i holding digit d = gbase[d] + i
+    uint32_t scan[RS_WARPS];
+    uint32_t tile;
+    alignas(8) uint64_t bar;
+};
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
+                                                                 KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n,
+                                                                 int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
+                                                                 uint32_t* counter, uint32_t* status, int aligned16) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    OnesweepSmem<KeyT>& S = *reinterpret_cast<OnesweepSmem<KeyT>*>(smem_raw);
+
+    if (threadIdx.x == 0) { S.tile = atomicAdd(counter, 1u); mbar_init(&S.bar, 1); }
+    for (int i = threadIdx.x; i < RS_WARPS * 256 / 2; i += RS_THREADS) reinterpret_cast<uint32_t*>(&S.wh[0][0])[i] = 0;
     __syncthreads();
-    const uint32_t tile = s_tile;
+    const uint32_t tile = S.tile;
     const uint32_t warp = threadIdx.x >> 5, lane = gs::lane_id();
     const uint64_t tile_base = (uint64_t)tile * RS_TILE;
     const uint32_t valid = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
     const uint32_t wbase = warp * (32 * RS_IPT) + lane;    // warp-striped: item j at wbase + 32*j
-
+    const bool bulk = aligned16 && valid == RS_TILE;
+    if (bulk) {
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(&S.bar, RS_TILE * (sizeof(KeyT) + 4));
+            bulk_g2s(S.keys, kin + tile_base, RS_TILE * sizeof(KeyT), &S.bar);
+            bulk_g2s(S.vals, vin + tile_base, RS_TILE * 4, &S.bar);
+        }
+        mbar_wait(&S.bar, 0);
+    } else {   // ragged last tile / unaligned caller buffers: plain coalesced loads, padded with all-ones keys
+#pragma unroll
+        for (int k = 0; k < RS_IPT; k++) {
+            const uint32_t i = threadIdx.x + k * RS_THREADS;
+            S.keys[i] = (i < valid) ? kin[tile_base + i] : (KeyT)~(KeyT)0;
+            S.vals[i] = (i < valid) ? vin[tile_base + i] : 0u;
+        }
+        __syncthreads();
+    }
     KeyT key[RS_IPT];
 #pragma unroll
-    for (int j = 0; j < RS_IPT; j++) {
-        const uint32_t li = wbase + 32 * j;
-        key[j] = (li < valid) ? kin[tile_base + li] : (KeyT)~(KeyT)0;
-    }
-    // stable ranking inside the warp's chunk
+    for (int j = 0; j < RS_IPT; j++) key[j] = S.keys[wbase + 32 * j];
+    // stable ranking inside the warp's chunk: match_any groups equal digits, the highest lane bumps the warp counter
     uint32_t rank[RS_IPT];
-    uint32_t* wh = s_wh[warp];
+    uint16_t* wh = S.wh[warp];
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (int j = 0; j < RS_IPT; j++) {
@@ -97,7 +142,7 @@ __global__ void __launch_bounds__(RS_THREADS) onesweep_kernel(const KeyT* __rest
         const uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
         const int leader = 31 - __clz(m);
         uint32_t prev = 0;
-        if ((int)lane == leader) { prev = wh[d]; wh[d] = prev + __popc(m); }
+        if ((int)lane == leader) { prev = wh[d]; wh[d] = (uint16_t)(prev + __popc(m)); }
         prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
         rank[j] = prev + __popc(m & lt);
         __syncwarp();
@@ -107,56 +152,59 @@ __global__ void __launch_bounds__(RS_THREADS) onesweep_kernel(const KeyT* __rest
     const uint32_t d_own = threadIdx.x;
     uint32_t cnt = 0;
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; w++) { uint32_t c = s_wh[w][d_own]; s_wh[w][d_own] = cnt; cnt += c; }
+    for (int w = 0; w < RS_WARPS; w++) { uint32_t c = S.wh[w][d_own]; S.wh[w][d_own] = (uint16_t)cnt; cnt += c; }
     if (tile == 0) gs::st_relaxed(&status[d_own], ST_INC | cnt);
     else gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_AGG | cnt);
-    const uint32_t binstart = block_excl_scan256(cnt, s_scan);
-    const uint32_t gstart = block_excl_scan256(ghist[d_own], s_scan);
+    const uint32_t binstart = block_excl_scan256(cnt, S.scan);
+    const uint32_t gstart = block_excl_scan256(ghist[d_own], S.scan);
+    // decoupled look-back, RS_LOOKBACK predecessors per round trip
     uint32_t excl = 0;
     if (tile > 0) {
         int t = (int)tile - 1;
-        while (true) {
-            uint32_t s;
-            do { s = gs::ld_relaxed(&status[(size_t)t * 256 + d_own]); } while ((s & (ST_AGG | ST_INC)) == 0u);
-            excl += s & ST_VAL;
-            if (s & ST_INC) break;
-            t--;
+        bool done = false;
+        while (!done) {
+            uint32_t s[RS_LOOKBACK];
+#pragma unroll
+            for (int k = 0; k < RS_LOOKBACK; k++)
+                s[k] = (t - k >= 0) ? gs::ld_relaxed(&status[(size_t)(t - k) * 256 + d_own]) : ST_INC;
+            int k = 0;
+#pragma unroll
+            for (; k < RS_LOOKBACK; k++) {
+                if ((s[k] & (ST_AGG | ST_INC)) == 0u) break;           // not published yet: retry from here
+                excl += s[k] & ST_VAL;
+                if (s[k] & ST_INC) { done = true; break; }
+            }
+            t -= k;
         }
         gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_INC | (excl + cnt));
     }
-    s_binstart[d_own] = binstart;
-    s_gbase[d_own] = gstart + excl - binstart;
+    S.binstart[d_own] = binstart;
+    S.gbase[d_own] = gstart + excl - binstart;
     __syncthreads();
-    // tile-local reorder of keys
+    // tile-local reorder: keys into their sorted slots (every thread holds its keys in registers by now)
     uint32_t slot[RS_IPT];
 #pragma unroll
     for (int j = 0; j < RS_IPT; j++) {
         const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
-        slot[j] = s_binstart[d] + wh[d] + rank[j];
-        s_keys[slot[j]] = key[j];
+        slot[j] = S.binstart[d] + wh[d] + rank[j];
     }
+    uint32_t v[RS_IPT];
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) { S.keys[slot[j]] = key[j]; v[j] = S.vals[wbase + 32 * j]; }
     __syncthreads();
-    uint32_t pos[RS_IPT];
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) S.vals[slot[j]] = v[j];
+    __syncthreads();
+    // digit-contiguous global stores
 #pragma unroll
     for (int k = 0; k < RS_IPT; k++) {
         const uint32_t i = threadIdx.x + k * RS_THREADS;
         if (i < valid) {
-            const KeyT kk = s_keys[i];
-            pos[k] = s_gbase[(uint32_t)(kk >> shift) & mask] + i;
-            kout[pos[k]] = kk;
+            const KeyT kk = S.keys[i];
+            const uint32_t pos = S.gbase[(uint32_t)(kk >> shift) & mask] + i;
+            kout[pos] = kk;
+            vout[pos] = S.vals[i];
         }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < RS_IPT; j++) {
-        const uint32_t li = wbase + 32 * j;
-        if (li < valid) s_vals[slot[j]] = vin[tile_base + li];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < RS_IPT; k++) {
-        const uint32_t i = threadIdx.x + k * RS_THREADS;
-        if (i < valid) vout[pos[k]] = s_vals[i];
     }
 }
 
@@ -205,9 +253,14 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
     int dst = 0;
+    const size_t smem = sizeof(OnesweepSmem<KeyT>);
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; }
     for (int p = 0; p < plan.num_passes; p++) {
-        onesweep_kernel<KeyT><<<tiles, RS_THREADS, 0, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, pl.shift[p], pl.mask[p],
-                                                            ghist + p * 256, counters + p, status + (size_t)p * tiles * 256);
+        const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
+        onesweep_kernel<KeyT><<<tiles, RS_THREADS, smem, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, pl.shift[p], pl.mask[p],
+                                                               ghist + p * 256, counters + p, status + (size_t)p * tiles * 256,
+                                                               aligned16);
         kin = kbuf[dst]; vin = vbuf[dst];
         dst ^= 1;
     }
