@@ -1,0 +1,351 @@
+"""CPU tests of the oracle (oracle/, the scalar C++ restatement of the reference's kernels).
+
+The reference ships no golden vectors or tests, so the oracle is pinned by
+  (1) the committed fixtures in tests/golden/ (regression: the oracle must keep producing them bit for bit),
+  (2) hand-computed single-Gaussian cases (conic, radius, tile bbox, colour, depth key) evaluated in float64 numpy,
+  (3) the run-time invariants the reference itself checks (tiled_rasterizer.mm:577-636, gpu_sort.mm:602-675),
+  (4) an independent numpy restatement of the forward blend and of one Adam step,
+  (5) finite differences of the oracle's own forward against its analytic backward (colour and opacity columns, the
+      ones the reference's backward computes without approximation).
+"""
+import glob
+import os
+import numpy as np
+import pytest
+from gaussiansplatting_b200 import synth
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+LRS = [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3]
+
+
+def eq_struct(a, b, skip=("_pad",)):
+    for f in a.dtype.names:
+        if f.startswith(skip):
+            continue
+        assert np.array_equal(a[f], b[f], equal_nan=True), f
+
+
+# ---- (1) golden regression --------------------------------------------------------------------------------------
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
+def test_oracle_reproduces_golden(orc, path):
+    d = np.load(path)
+    g, u = d["gaussians"], d["uniforms"]
+    r = orc.render(g, u, threads=1)
+    eq_struct(r["proj"], d["proj"])
+    for k in ("keys", "vals", "skeys", "svals", "image", "last"):
+        assert np.array_equal(r[k], d[k]), k
+    eq_struct(r["ranges"], d["ranges"])
+    assert (r["E"], r["C"]) == tuple(int(x) for x in d["evals"])
+    grads, tf = orc.backward(g, r["proj"], r["svals"], r["ranges"], u, r["last"], r["image"], d["gt"], want_tfinal=True)
+    eq_struct(grads, d["grads"])
+    assert np.array_equal(tf, d["tfinal"], equal_nan=True)          # NaN marks pixels without a contribution
+    st = orc.AdamState(len(g))
+    g1 = g.copy()
+    orc.adam_step(g1, grads, st, LRS)
+    eq_struct(g1, d["adam_gaussians"])
+    assert np.array_equal(np.concatenate(st.m), d["adam_m"]) and np.array_equal(np.concatenate(st.v), d["adam_v"])
+    acc, cnt = np.zeros(len(g), np.float32), np.zeros(len(g), np.uint32)
+    orc.accumulate_gradients(grads, acc, cnt)
+    assert np.array_equal(acc, d["dens_accum"]) and np.array_equal(cnt, d["dens_counts"])
+    W = int(u["screenSize"][0][0])
+    out, markers, stats = orc.densify_apply(d["dens_in"], d["dens_accum_in"], d["dens_counts"], int(d["dens_iter"]),
+                                            synth.scene_extent(3.0), 0.9 * W, float(W), 2.0 * synth.scene_extent(3.0), 0x5EED)
+    eq_struct(out, d["dens_out"])
+    assert np.array_equal(markers, d["dens_markers"]) and np.array_equal(stats, d["dens_stats"])
+
+
+def test_oracle_threads_do_not_change_results(orc):
+    """the OpenMP (timed-baseline) mode must give the same integers and image as the single-thread golden mode"""
+    n, W, H = 3000, 128, 96
+    g = synth.make_scene(n, 5, 0.03)
+    u = synth.make_camera(2, 8, W, H, n)
+    a, b = orc.render(g, u, threads=1), orc.render(g, u, threads=4)
+    for k in ("keys", "vals", "skeys", "svals", "image", "last"):
+        assert np.array_equal(a[k], b[k]), k
+
+
+# ---- (2) hand-computed single Gaussian --------------------------------------------------------------------------
+def test_single_gaussian_hand_computed(orc):
+    """identity rotation, isotropic scale s, on the optical axis at depth z: cov2D = (f s / z)^2 + 0.3 on the diagonal,
+    conic = 1/that, radius = ceil(3 sqrt(lambda)), centre pixel, bbox from the radius  (tiled_shaders.metal:180-290)"""
+    W = H = 128
+    g = np.zeros(1, orc.GAUSSIAN)
+    s, z = 0.05, 3.0
+    g["scale"][0] = np.log(s)
+    g["rotation"][0] = [1, 0, 0, 0]
+    g["opacity"][0] = 1.0
+    g["sh"][0][[0, 4, 8]] = [(0.8 - 0.5) / synth.SH_C0, (0.2 - 0.5) / synth.SH_C0, (0.5 - 0.5) / synth.SH_C0]
+    u = synth.build_uniforms([1, 0, 0, 0], [0, 0, z], 0.9 * W, 0.9 * W, W / 2, H / 2, W, H, 1)
+    p = orc.project(g, u)[0]
+    f = 0.9 * W
+    var = (f * s / z) ** 2 + 0.3
+    assert np.allclose(p["screenPos"], [W / 2, H / 2], atol=1e-4)
+    assert abs(p["depth"] - z) < 1e-6
+    assert np.allclose(p["cov2D"], [var, 0, var], rtol=1e-5, atol=1e-6)
+    assert np.allclose(p["conic"], [1 / var, 0, 1 / var], rtol=1e-5, atol=1e-7)
+    lam = var + np.sqrt(max(0.1, 0.0))               # mid + sqrt(max(0.1, mid^2 - det)), det = var^2
+    radius = min(np.ceil(3 * np.sqrt(lam)), 512)
+    assert p["radius"] == radius
+    lo, hi = int(W / 2 - radius) // 16, min(int(W / 2 + radius), W - 1) // 16
+    assert (p["tileMinX"], p["tileMinY"], p["tileMaxX"], p["tileMaxY"]) == (lo, lo, hi, hi)
+    assert abs(p["opacity"] - 1 / (1 + np.exp(-1.0))) < 1e-6
+    assert np.allclose(p["color"], [0.8, 0.2, 0.5], atol=1e-6)
+    keys, vals = orc.generate_pairs(np.array([p]), W // 16)
+    assert len(keys) == (hi - lo + 1) ** 2 and np.all(vals == 0)
+    dk = np.float32(z).view(np.uint32) | np.uint32(0x80000000)      # tiled_shaders.metal:773-774
+    tiles = [(ty * (W // 16) + tx) for ty in range(lo, hi + 1) for tx in range(lo, hi + 1)]
+    assert np.array_equal(keys, (np.array(tiles, np.uint64) << np.uint64(32)) | np.uint64(dk))
+    # the centre pixel sees alpha = min(sigma * exp(-0.5 * 0.25/var * 2) ...) -> compare the blended colour
+    r = orc.render(g, u)
+    px = r["image"][H // 2, W // 2]
+    d2 = 0.5 ** 2 + 0.5 ** 2
+    alpha = min(float(p["opacity"]) * np.exp(-0.5 * d2 / var), 0.99)
+    want = np.array([0.8, 0.2, 0.5]) * alpha + (1 - alpha)
+    assert np.allclose(px[:3], want, atol=2e-6) and px[3] == 1.0
+
+
+def test_culls(orc):
+    """every cull of projectGaussians writes radius 0 and emits no pairs (tiled_shaders.metal:120-147, 240-290)"""
+    W = H = 64
+    g = synth.make_scene(8, 3, 0.05)
+    g["position"][:] = 0
+    g["position"][0, 0] = np.nan
+    g["position"][1, 1] = 2e6
+    g["scale"][2, 0] = np.nan
+    g["position"][3, 2] = -10.0            # behind the camera
+    g["position"][4, 0] = 50.0             # |ndc| > 1.2
+    g["scale"][5] = 5.0                    # giant: > 256 tiles? (64x64 has only 16 tiles) -> stays visible
+    g["opacity"][6] = -9.0                 # clamped to -8 -> sigma = 3.3e-4 < 0.005: projected but no pairs
+    u = synth.build_uniforms([1, 0, 0, 0], [0, 0, 3.0], 0.9 * W, 0.9 * W, W / 2, H / 2, W, H, 8)
+    p = orc.project(g, u)
+    assert np.all(p["radius"][:5] == 0) and p["radius"][5] > 0 and p["radius"][6] > 0 and p["radius"][7] > 0
+    assert np.all(p["tileMinX"][:5] == 0xFFFFFFFF) and np.all(p["tileMaxX"][:5] == 0)
+    keys, vals = orc.generate_pairs(p, 4)
+    assert set(vals.tolist()) == {5, 7}
+
+
+# ---- (3) the reference's own run-time invariants ----------------------------------------------------------------
+@pytest.mark.parametrize("n,W,H,s0,seed", [(2000, 100, 70, 0.03, 11), (10000, 256, 256, 0.012, synth.CONFIG_SEED["C1"])])
+def test_invariants(orc, n, W, H, s0, seed):
+    g = synth.make_scene(n, seed, s0)
+    u = synth.make_camera(1, 8, W, H, n)
+    r = orc.render(g, u, threads=2)
+    P = len(r["keys"])
+    assert P > 0
+    # sort: ascending, a permutation, identical to numpy's stable sort (gpu_sort.mm:602-675)
+    assert np.all(r["skeys"][1:] >= r["skeys"][:-1])
+    order = np.argsort(r["keys"], kind="stable")
+    assert np.array_equal(r["skeys"], r["keys"][order]) and np.array_equal(r["svals"], r["vals"][order])
+    # pre-sort pair order: Gaussian index, then ty-major / tx-minor (SURVEY note K)
+    assert np.all(np.diff(r["vals"].astype(np.int64)) >= 0)
+    same = r["vals"][1:] == r["vals"][:-1]
+    assert np.all((r["keys"][1:] >> np.uint64(32))[same] > (r["keys"][:-1] >> np.uint64(32))[same])
+    # tile ranges: contiguous, disjoint, covering every pair (tiled_rasterizer.mm:577-636)
+    rg = r["ranges"]
+    assert int(rg["count"].sum()) == P
+    assert np.array_equal(rg["start"][1:], (rg["start"] + rg["count"])[:-1]) and rg["start"][0] == 0
+    tile_of = (r["skeys"] >> np.uint64(32)).astype(np.int64)
+    assert np.array_equal(np.bincount(tile_of, minlength=len(rg)), rg["count"])
+    # lastContribIdx points inside the pixel's own tile range
+    ntx = int(u["numTilesX"][0])
+    ys, xs = np.nonzero(r["last"] != 0xFFFFFFFF)
+    t = (ys // 16) * ntx + xs // 16
+    li = r["last"][ys, xs]
+    assert np.all(li >= rg["start"][t]) and np.all(li < rg["start"][t] + rg["count"][t])
+    # image in [0,1], alpha channel 1, untouched pixels are the white background
+    assert r["image"].min() >= 0 and r["image"].max() <= 1.0 + 1e-6 and np.all(r["image"][..., 3] == 1)
+    assert np.all(r["image"][r["last"] == 0xFFFFFFFF][:, :3] == 1.0)
+    assert r["C"] <= r["E"] <= P * 256
+
+
+def test_sh_colour_round_trip():
+    """main.mm:327-339: colour = 0.2820948 * sh + 0.5"""
+    c = np.linspace(0.05, 0.95, 19)
+    sh = (c - 0.5) / synth.SH_C0
+    assert np.allclose(synth.SH_C0 * sh + 0.5, c, atol=1e-12)
+
+
+def test_sort_is_stable_on_ties(orc):
+    keys = (synth.splitmix64(7, 5000) & np.uint64(0x7)) << np.uint64(32)     # 8 distinct keys -> massive ties
+    vals = np.arange(5000, dtype=np.uint32)
+    for th in (1, 3):
+        sk, sv = orc.sort_pairs(keys, vals, th)
+        o = np.argsort(keys, kind="stable")
+        assert np.array_equal(sk, keys[o]) and np.array_equal(sv, vals[o])
+    sk, sv = orc.sort_pairs(keys[:0], vals[:0])
+    assert len(sk) == 0
+
+
+def test_depth_keys32_back_to_front(orc):
+    """computeDepths (sort.metal:36-72): ascending key order == far-to-near; invalid positions sort last"""
+    rng = synth.uniform01(3, 4000, 0).reshape(1000, 4).astype(np.float32) * 10 - 5
+    rng[5, 0] = np.nan
+    rng[6, 1] = np.inf
+    cam = np.array([0.5, -1.0, 2.0], np.float32)
+    keys, vals = orc.depth_keys32(rng, cam)
+    sk, sv = orc.sort_pairs32(keys, vals)
+    d2 = ((rng[:, :3] - cam) ** 2).sum(1)
+    d_sorted = d2[sv[:-2]]
+    assert np.all(np.diff(d_sorted) <= 1e-4) and set(sv[-2:].tolist()) == {5, 6}
+
+
+# ---- (4) independent numpy restatements -------------------------------------------------------------------------
+def test_pinned_exp_accuracy(orc):
+    """the pinned degree-5 polynomial exp the oracle and the kernels share is within 1e-6 relative of the real exp (x*log2e is rounded once before the polynomial)"""
+    xs = np.linspace(-4.5, 0.0, 4001, dtype=np.float32)
+    got = np.array([orc.lib().orc_test_exp_blend(float(x)) for x in xs], np.float32)
+    ref = np.exp(xs.astype(np.float64))
+    assert np.max(np.abs(got - ref) / ref) <= 1e-6
+    xs = np.linspace(-8.0, 5.0, 2001, dtype=np.float32)
+    got = np.array([orc.lib().orc_test_expf(float(x)) for x in xs], np.float32)
+    ref = np.exp(xs.astype(np.float64))
+    assert np.max(np.abs(got - ref) / ref) <= 1e-6
+
+
+def numpy_forward(proj, svals, ranges, W, H, ntx):
+    """tiledForward (tiled_shaders.metal:307-385) in float64 numpy, one tile at a time"""
+    img = np.ones((H, W, 3))
+    for t, (start, count) in enumerate(zip(ranges["start"], ranges["count"])):
+        if count == 0:
+            continue
+        tx, ty = t % ntx, t // ntx
+        ys, xs = np.mgrid[ty * 16:min(ty * 16 + 16, H), tx * 16:min(tx * 16 + 16, W)]
+        px, py = xs + 0.5, ys + 0.5
+        C = np.zeros(px.shape + (3,))
+        T = np.ones(px.shape)
+        alive = np.ones(px.shape, bool)
+        for gi in svals[start:start + count]:
+            p = proj[gi]
+            A, B, Cc = [float(v) for v in p["conic"]]
+            if p["radius"] <= 0 or abs(A) + abs(B) + abs(Cc) < 1e-4:
+                continue
+            dx, dy = px - float(p["screenPos"][0]), py - float(p["screenPos"][1])
+            power = -0.5 * (A * dx * dx + 2 * B * dx * dy + Cc * dy * dy)
+            alpha = np.minimum(float(p["opacity"]) * np.exp(power), 0.99)
+            ok = alive & (power <= 0) & (power >= -4.5) & (alpha >= 1 / 255)
+            w = np.where(ok, alpha * T, 0.0)
+            C += w[..., None] * p["color"].astype(np.float64)
+            T = np.where(ok, T * (1 - alpha), T)
+            alive &= T > 1e-4
+        img[ys, xs] = C + T[..., None]
+    return img
+
+
+def test_forward_matches_numpy_float64(orc):
+    n, W, H = 600, 64, 48
+    g = synth.make_scene(n, 31, 0.04)
+    u = synth.make_camera(4, 8, W, H, n)
+    r = orc.render(g, u)
+    ref = numpy_forward(r["proj"], r["svals"], r["ranges"], W, H, int(u["numTilesX"][0]))
+    # threshold tests can flip for values within rounding of a threshold: allow a handful of pixels
+    err = np.abs(r["image"][..., :3] - ref).max(axis=2)
+    assert np.quantile(err, 0.995) < 5e-6 and (err > 1e-3).sum() <= 3
+
+
+def test_adam_first_step_numpy(orc):
+    """adamStep (shaders.metal:536-713): first step moves every parameter with a non-zero gradient by ~lr*sign(g),
+    position capped to |update| <= 0.1, log-scale clamped to +-4, quaternion renormalised, opacity +-8, SH +-2"""
+    n = 256
+    g = synth.make_scene(n, 77, 0.05)
+    gr = np.zeros(n, orc.GRADIENTS)
+    u = synth.uniform01(5, n * 23, 0).reshape(n, 23) - 0.5
+    gr["position"], gr["opacity"], gr["scale"], gr["rotation"] = u[:, :3], u[:, 3], u[:, 4:7] * 3.0, u[:, 7:11]
+    gr["sh"][:, [0, 4, 8]] = u[:, 11:14]
+    g0 = g.copy()
+    st = orc.AdamState(n)
+    orc.adam_step(g, gr, st, LRS)
+    assert st.t == 1
+    sgn = np.sign(gr["position"])
+    assert np.allclose(g["position"] - g0["position"], -LRS[0] * sgn, rtol=1e-3, atol=1e-9)
+    assert np.allclose(g["opacity"] - g0["opacity"], -LRS[3] * np.sign(gr["opacity"]), rtol=1e-3, atol=1e-7)
+    want_scale = np.clip(g0["scale"] - LRS[1] * np.sign(gr["scale"]), -4.0, 4.0)
+    assert np.allclose(g["scale"], want_scale, rtol=1e-4, atol=1e-6)
+    assert np.allclose(np.linalg.norm(g["rotation"], axis=1), 1.0, atol=1e-5)
+    clipped = np.clip(gr["scale"], -0.5, 0.5)                       # gradient clip +-0.5 (shaders.metal:582)
+    assert np.allclose(st.m[1].reshape(n, 3), 0.1 * clipped, rtol=1e-5, atol=1e-9)
+    assert np.allclose(st.v[1].reshape(n, 3), 0.001 * clipped ** 2, rtol=1e-4, atol=1e-12)
+    # SH components that never receive gradient keep a zero moment and an unchanged value
+    assert np.all(g["sh"][:, 1] == g0["sh"][:, 1]) and np.all(st.m[4].reshape(n, 12)[:, 1] == 0)
+    # NaN gradient in position_x skips the whole Gaussian (shaders.metal:567-570)
+    g2 = g0.copy()
+    gr2 = gr.copy()
+    gr2["position"][3, 0] = np.nan
+    orc.adam_step(g2, gr2, orc.AdamState(n), LRS)
+    for f in ("position", "scale", "rotation", "opacity", "sh"):
+        assert np.array_equal(g2[f][3], g0[f][3]), f
+
+
+def test_lr_decay_closed_form(orc):
+    """exponentialLRDecay (mtl_engine.mm:1039-1045): lr_init * (lr_final/lr_init)^(iter/max)"""
+    for it, mx in ((0, 1000), (500, 1000), (1000, 1000), (29999, 30000)):
+        got = orc.lib().orc_lr_decay(orc.C.c_float(1.6e-4), orc.C.c_float(1.6e-6), orc.C.c_uint64(it), orc.C.c_uint64(mx))
+        assert abs(got - 1.6e-4 * (1.6e-6 / 1.6e-4) ** (it / mx)) < 1e-9
+
+
+def test_densify_layout(orc):
+    """DensityController::apply (density_control.mm:188-501): keep -> 1, clone -> 2 adjacent identical, split -> 2
+    children replacing the parent with log-scale + ln(1/1.6), prune -> 0; cap un-marks clones then splits"""
+    n = 500
+    g = synth.make_scene(n, 13, 0.01)            # maxScale < 0.01 * extent -> clone
+    g["opacity"][::5] = -7.0
+    g["scale"][1::5] = np.log(0.2)
+    accum = np.full(n, 1e-2, np.float32)
+    counts = np.ones(n, np.uint32)
+    out, markers, stats = orc.densify_apply(g, accum, counts, 700, 3.3, 100.0, 128.0, 6.6, 1)
+    assert np.all(markers[::5] == 1) and np.all(markers[1::5] == 3) and np.all(markers[2::5] == 2)
+    assert len(out) == n - stats[0] + stats[1] + stats[2]
+    w = 0
+    for i in range(n):
+        if markers[i] == 1:
+            continue
+        if markers[i] == 0:
+            assert out[w].tobytes() == g[i].tobytes(); w += 1
+        elif markers[i] == 2:
+            assert out[w].tobytes() == g[i].tobytes() and out[w + 1].tobytes() == g[i].tobytes(); w += 2
+        else:
+            for k in (0, 1):
+                assert np.allclose(out[w + k]["scale"], g[i]["scale"] + np.log(1 / 1.6), atol=1e-6)
+                assert np.array_equal(out[w + k]["rotation"], g[i]["rotation"])
+            mid = 0.5 * (out[w]["position"] + out[w + 1]["position"])
+            assert np.allclose(mid, g[i]["position"], atol=1e-5)    # children at pos +- offset
+            w += 2
+    assert w == len(out)
+    # cap: with max 520 only 20 more may be added: clones are un-marked first, in index order
+    out2, markers2, stats2 = orc.densify_apply(g, accum, counts, 700, 3.3, 100.0, 128.0, 6.6, 1, max_gaussians=n - 100 + 20)
+    assert len(out2) <= n - 100 + 20 + 1 and stats2[1] + stats2[2] < stats[1] + stats[2]
+    # outside the densify window nothing is cloned or split
+    _, m3, s3 = orc.densify_apply(g, accum, counts, 200, 3.3, 100.0, 128.0, 6.6, 1)
+    assert s3[1] == 0 and s3[2] == 0
+
+
+# ---- (5) finite differences of the oracle's own forward vs its backward ---------------------------------------
+def test_backward_finite_differences(orc):
+    """L = sum |render - gt| / 3 has dL/dpixel = sign/3, exactly what tiledBackward uses (:418-423).  The colour and
+    opacity gradients are computed by the reference without approximation, so central differences of the oracle's
+    forward must agree with them away from the non-differentiable tests."""
+    n, W, H = 40, 48, 48
+    g = synth.make_scene(n, 41, 0.12)
+    g["opacity"] = np.clip(g["opacity"], -1.0, 1.0)
+    gt_img = np.zeros((H, W, 4), np.float32)                       # render > gt everywhere -> sign = +1, L smooth
+    u = synth.make_camera(0, 8, W, H, n)
+
+    def loss(gg):
+        return float(orc.render(gg, u)["image"][..., :3].astype(np.float64).sum() / 3.0)
+
+    r = orc.render(g, u)
+    grads = orc.backward(g, r["proj"], r["svals"], r["ranges"], u, r["last"], r["image"], gt_img)
+    checked = 0
+    for i in range(n):
+        for field, idx, eps in (("sh", 0, 2e-2), ("sh", 4, 2e-2), ("opacity", None, 2e-2)):
+            ana = float(grads[field][i][idx]) if idx is not None else float(grads[field][i])
+            if abs(ana) < 0.5:
+                continue
+            gp, gm = g.copy(), g.copy()
+            if idx is None:
+                gp[field][i] += eps; gm[field][i] -= eps
+            else:
+                gp[field][i][idx] += eps; gm[field][i][idx] -= eps
+            fd = (loss(gp) - loss(gm)) / (2 * eps)
+            assert abs(fd - ana) <= 0.05 * max(abs(fd), abs(ana)) + 0.05, (i, field, idx, fd, ana)
+            checked += 1
+    assert checked >= 20
