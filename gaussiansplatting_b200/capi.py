@@ -48,6 +48,11 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
 
+def tune(name, value):
+    if lib().gs_tune(name.encode(), C.c_int(value)) != 0:
+        raise GsError(f"unknown tuning knob {name}")
+
+
 class Context:
     def __init__(self, device=0, stream=None):
         self.h = C.c_void_p()
@@ -216,7 +221,7 @@ class Rasterizer:
     def set_profiling(self, on=True):
         self.ctx.check(lib().gs_rast_set_profiling(self.h, C.c_int(int(on))))
 
-    STAGES = ("preprocess", "scan", "readback", "emit", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
+    STAGES = ("preprocess", "depth_sort", "scan", "emit", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
 
     def timings(self, include_backward=True):
         ms = (C.c_float * 9)()

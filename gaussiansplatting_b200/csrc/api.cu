@@ -19,6 +19,7 @@ struct gs_ctx {
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
 };
 static std::string g_create_err;
+static void gs_set_sort_mode(int v);
 #define GS_PROF_EVENTS 11
 
 #define GS_SETDEV(c) cudaSetDevice((c)->device)
@@ -46,6 +47,14 @@ static int dalloc(gs_ctx* c, T** p, size_t count) {
 extern "C" {
 
 int gs_version(void) { return 100; }
+
+int gs_tune(const char* name, int value) {
+    if (!name) return GS_ERR_ARG;
+    if (!strcmp(name, "fwd_ppt")) { gs_tune_fwd_ppt(value); return GS_OK; }
+    if (!strcmp(name, "bwd_ppt")) { gs_tune_bwd_ppt(value); return GS_OK; }
+    if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
+    return GS_ERR_ARG;
+}
 
 static int ctx_create_common(int device, cudaStream_t st, bool own, gs_ctx** out) {
     if (!out) return GS_ERR_ARG;
@@ -348,9 +357,14 @@ struct gs_rast {
     GsProjected proj{};
     uint32_t* meta = nullptr;
     void* scan_scratch = nullptr; size_t scan_scratch_bytes = 0;
+    // pair buffers.  64-bit mode: keys_in/kbuf hold u64 (tile|depth) keys.  Hoisted mode: the same allocations hold
+    // u32 tile ids (first half used).
     uint64_t *keys_in = nullptr, *kbuf[2] = {nullptr, nullptr};
     uint32_t *vals_in = nullptr, *vbuf[2] = {nullptr, nullptr};
     void* sort_scratch = nullptr;
+    // hoisted mode: depth order of the Gaussians (the low-word passes of the LSD sort, run on N keys instead of P)
+    uint32_t *iota = nullptr, *dk_buf[2] = {nullptr, nullptr}, *perm_buf[2] = {nullptr, nullptr};
+    void* dsort_scratch = nullptr;
     uint2* ranges = nullptr;
     uint32_t* last_idx = nullptr;
     float* tfinal = nullptr;
@@ -359,7 +373,12 @@ struct gs_rast {
     // state left behind by forward for backward / inspection (tiled_rasterizer.hpp:94-106)
     uint32_t W = 0, H = 0, ntx = 0, nty = 0, n = 0;
     uint64_t pairs = 0;
+    int mode = 0;                       // sort mode of the last forward: 0 hoisted, 1 full 64-bit pair sort
     int result = 0, passes = 0;
+    const uint32_t* sorted_vals = nullptr;   // per-tile lists (bit 31 = GS_CULL_BIT)
+    const uint32_t* sorted_tiles = nullptr;  // hoisted mode: sorted u32 tile ids
+    const uint64_t* sorted_keys = nullptr;   // 64-bit mode: sorted keys
+    cudaEvent_t ev_pairs = nullptr;     // recorded after the pair count landed in pinned memory
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
@@ -367,11 +386,19 @@ struct gs_rast {
     void mark(int i) { if (prof) cudaEventRecord(ev[i], c->stream); }
 };
 
+__global__ void iota_kernel(uint32_t* v, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
+}
+
 static void rast_free_gaussian_arrays(gs_rast* r) {
     cudaFree(r->proj.rec); cudaFree(r->proj.bbox); cudaFree(r->proj.aux); cudaFree(r->proj.covc); cudaFree(r->proj.offs);
-    cudaFree(r->acc); cudaFree(r->scan_scratch);
+    cudaFree(r->proj.cnt); cudaFree(r->proj.dkey);
+    cudaFree(r->acc); cudaFree(r->scan_scratch); cudaFree(r->iota); cudaFree(r->dsort_scratch);
+    for (int i = 0; i < 2; i++) { cudaFree(r->dk_buf[i]); cudaFree(r->perm_buf[i]); r->dk_buf[i] = nullptr; r->perm_buf[i] = nullptr; }
     r->proj.rec = nullptr; r->proj.bbox = nullptr; r->proj.aux = nullptr; r->proj.covc = nullptr; r->proj.offs = nullptr;
-    r->acc = nullptr; r->scan_scratch = nullptr;
+    r->proj.cnt = nullptr; r->proj.dkey = nullptr;
+    r->acc = nullptr; r->scan_scratch = nullptr; r->iota = nullptr; r->dsort_scratch = nullptr;
 }
 static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     if (n <= r->cap_g) return GS_OK;
@@ -384,7 +411,13 @@ static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     GS_TRY(dalloc(c, &r->proj.aux, cap));
     GS_TRY(dalloc(c, &r->proj.covc, cap));
     GS_TRY(dalloc(c, &r->proj.offs, (size_t)cap + 1));
+    GS_TRY(dalloc(c, &r->proj.cnt, cap));
+    GS_TRY(dalloc(c, &r->proj.dkey, cap));
     GS_TRY(dalloc(c, &r->acc, (size_t)cap * 12));
+    GS_TRY(dalloc(c, &r->iota, cap));
+    for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->dk_buf[i], cap)); GS_TRY(dalloc(c, &r->perm_buf[i], cap)); }
+    GS_CUDA(c, cudaMalloc(&r->dsort_scratch, gs_sort_scratch_bytes(cap, 4)));
+    iota_kernel<<<(cap + 255) / 256, 256, 0, c->stream>>>(r->iota, cap);
     r->scan_scratch_bytes = gs_scan_scratch_bytes(cap);
     GS_CUDA(c, cudaMalloc(&r->scan_scratch, r->scan_scratch_bytes));
     r->cap_g = cap;
@@ -437,6 +470,7 @@ int gs_rast_create(gs_ctx* c, uint32_t max_gaussians, gs_rast** out) {
     int rc = dalloc(c, &r->meta, GS_META_COUNT);
     if (rc == GS_OK) rc = rast_reserve_gaussians(r, std::max(max_gaussians, 64u));
     if (rc == GS_OK) rc = rast_reserve_pairs(r, (uint64_t)std::max(max_gaussians, 64u) * 8);   // AVG_TILES_PER_GAUSSIAN, tiled_rasterizer.hpp:80
+    if (rc == GS_OK && cudaEventCreateWithFlags(&r->ev_pairs, cudaEventDisableTiming) != cudaSuccess) rc = GS_ERR_CUDA;
     if (rc != GS_OK) { gs_rast_destroy(r); return rc; }
     *out = r;
     return GS_OK;
@@ -450,29 +484,21 @@ int gs_rast_destroy(gs_rast* r) {
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); }
     cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
     cudaFree(r->counters);
+    if (r->ev_pairs) cudaEventDestroy(r->ev_pairs);
     for (int i = 0; i < GS_PROF_EVENTS; i++) if (r->ev[i]) cudaEventDestroy(r->ev[i]);
     delete r;
     return GS_OK;
 }
 
-int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
-    gs_ctx* c = r->c; GS_SETDEV(c);
-    GS_ARG(c, g && u && out, "null handle");
+// Full 64-bit pair sort (the reference's structure: duplicate keys, sort P pairs on tile|depth).  Needs the pair count on
+// the host before the pair kernels can be sized, i.e. one mid-frame synchronisation like the reference's (:379-380,454).
+static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
+    gs_ctx* c = r->c;
     cudaStream_t st = c->stream;
-    const uint32_t n = g->n, W = out->w, H = out->h;
-    GS_TRY(rast_reserve_gaussians(r, n));
-    GS_TRY(rast_reserve_image(r, W, H));
-    r->n = n; r->pairs = 0; r->passes = 0;
-    // meta: total = 0, key OR = 0, key AND = ~0
-    GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
-    GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
-    r->mark(0);
-    // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
-    gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
-                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
-    r->mark(1);
-    gs_launch_exclusive_scan(r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
+    const uint32_t n = r->n, W = r->W, H = r->H;
     r->mark(2);
+    gs_launch_exclusive_scan(r->proj.cnt, nullptr, r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
+    r->mark(3);
     GS_LAUNCH_CHECK(c);
     GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     GS_CUDA(c, cudaStreamSynchronize(st));                            // the reference's read of pairCounter (:379-380,454)
@@ -482,11 +508,9 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     GS_TRY(rast_reserve_pairs(r, P));
     r->pairs = P;
     const uint32_t tiles = r->ntx * r->nty;
-    const uint64_t* skeys = r->kbuf[0];
-    const uint32_t* svals = r->vbuf[0];
-    r->mark(3);
+    r->sorted_keys = r->kbuf[0]; r->sorted_vals = r->vbuf[0]; r->sorted_tiles = nullptr;
     if (P > 0) {
-        gs_launch_emit_pairs(r->proj, n, r->ntx, r->keys_in, r->vals_in, st);
+        gs_launch_emit_pairs(r->proj, r->proj.offs, n, r->ntx, r->keys_in, r->vals_in, (uint32_t)r->cap_pairs, st);
         r->mark(4);
         int tile_bits = 0;
         while ((1u << tile_bits) < tiles) tile_bits++;
@@ -494,15 +518,91 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
         const GsSortPlan plan = gs_sort_plan(0, 32 + tile_bits, varying);
         r->passes = plan.num_passes;
         r->result = gs_launch_sort64(r->keys_in, r->vals_in, r->kbuf, r->vbuf, P, plan, r->sort_scratch, st);
-        skeys = r->kbuf[r->result]; svals = r->vbuf[r->result];
+        r->sorted_keys = r->kbuf[r->result]; r->sorted_vals = r->vbuf[r->result];
     } else r->mark(4);
     r->mark(5);
-    gs_launch_tile_ranges(skeys, (uint32_t)P, tiles, nullptr, r->ranges, st);
+    gs_launch_tile_ranges(r->sorted_keys, (uint32_t)P, tiles, nullptr, r->ranges, st);
     r->mark(6);
-    gs_launch_blend_forward(r->proj, svals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
     r->mark(7);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
+}
+
+// Hoisted mode (default).  The LSD radix sort on (tile<<32 | depth) is: the low-word (depth) passes, then the
+// high-word (tile) passes, each stable.  Every duplicate of a Gaussian carries the same depth word, so the low-word
+// passes are run on the N Gaussians BEFORE duplication (N keys instead of P ~ 7N), pairs are emitted in that order, and
+// only the ceil(log2 tiles) tile bits are sorted on the P pairs (2 passes of u32+u32 instead of 6 of u64+u32).  The
+// resulting order is, element for element, the stable sort of the reference's 64-bit keys.  Nothing waits for the
+// host: pair kernels read the pair count from device memory and their grids are sized from the buffer capacity; the
+// host blocks only on the event after the scan (while the GPU keeps working) to validate the capacity.
+static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
+    gs_ctx* c = r->c;
+    cudaStream_t st = c->stream;
+    const uint32_t n = r->n, W = r->W, H = r->H;
+    const uint32_t tiles = r->ntx * r->nty;
+    int tile_bits = 0;
+    while ((1u << tile_bits) < tiles) tile_bits++;
+    // depth order of the Gaussians: keys = depth bits (bit 31 is always set: depth > 0.1), values = index
+    const GsSortPlan dplan = gs_sort_plan(0, 31, ~0ull);
+    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, r->dsort_scratch, st);
+    const uint32_t* perm = r->perm_buf[dres];
+    r->mark(2);
+    gs_launch_exclusive_scan(r->proj.cnt, perm, r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
+    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaEventRecord(r->ev_pairs, st));
+    r->mark(3);
+    const GsSortPlan tplan = gs_sort_plan_even(0, tile_bits);
+    r->passes = dplan.num_passes + tplan.num_passes;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        uint32_t* tk_in = reinterpret_cast<uint32_t*>(r->keys_in);
+        uint32_t* tk[2] = {reinterpret_cast<uint32_t*>(r->kbuf[0]), reinterpret_cast<uint32_t*>(r->kbuf[1])};
+        const uint32_t cap = (uint32_t)std::min<uint64_t>(r->cap_pairs, 0x3FFFFFFFull);
+        const uint32_t* d_total = r->meta + GS_META_TOTAL_PAIRS;
+        gs_launch_emit_tile_pairs(r->proj, perm, r->proj.offs, n, r->ntx, tk_in, r->vals_in, cap, st);
+        r->mark(4);
+        r->result = gs_launch_sort32(tk_in, r->vals_in, tk, r->vbuf, cap, d_total, tplan, r->sort_scratch, st);
+        r->sorted_tiles = tplan.num_passes ? tk[r->result] : tk_in;
+        r->sorted_vals = tplan.num_passes ? r->vbuf[r->result] : r->vals_in;
+        r->sorted_keys = nullptr;
+        r->mark(5);
+        gs_launch_tile_ranges32(r->sorted_tiles, cap, d_total, tiles, r->ranges, st);
+        r->mark(6);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+        r->mark(7);
+        GS_LAUNCH_CHECK(c);
+        if (attempt == 0) GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));   // the GPU is still busy with the kernels above
+        const uint64_t P = c->h_pinned[GS_META_TOTAL_PAIRS];
+        if (P >= (1ull << 30)) { c->err = "pair count exceeds 2^30"; return GS_ERR_CAPACITY; }
+        r->pairs = P;
+        if (P <= r->cap_pairs) break;
+        GS_TRY(rast_reserve_pairs(r, P));                              // rare: grow (synchronises) and redo the pair stages
+    }
+    return GS_OK;
+}
+
+static int g_sort_mode = 0;
+}  // extern "C"
+static void gs_set_sort_mode(int v) { g_sort_mode = v ? 1 : 0; }
+extern "C" {
+
+int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    GS_ARG(c, g && u && out, "null handle");
+    cudaStream_t st = c->stream;
+    const uint32_t n = g->n, W = out->w, H = out->h;
+    GS_TRY(rast_reserve_gaussians(r, n));
+    GS_TRY(rast_reserve_image(r, W, H));
+    r->n = n; r->pairs = 0; r->passes = 0; r->mode = g_sort_mode;
+    // meta: total = 0, key OR = 0, key AND = ~0
+    GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
+    GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
+    r->mark(0);
+    // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
+    gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
+                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
+    r->mark(1);
+    return r->mode == 1 ? forward_pairs64(r, g, u, out) : forward_hoisted(r, g, u, out);
 }
 
 int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniforms* u, gs_image* rendered, gs_image* gt, int flags) {
@@ -516,7 +616,7 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     if (!(flags & GS_BWD_ACCUMULATE)) GS_TRY(gs_grads_zero(gr, n));   // :687
     else GS_ARG(c, n <= gr->cap, "gradient buffer too small to accumulate into");
     GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)n * 12 * sizeof(float), st));
-    const uint32_t* svals = r->vbuf[r->pairs ? r->result : 0];
+    const uint32_t* svals = r->sorted_vals;
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
                              (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, st);
     r->mark(9);
@@ -533,8 +633,9 @@ int gs_rast_set_profiling(gs_rast* r, int on) {
     r->prof = on != 0;
     return GS_OK;
 }
-// ms of the last forward (+ backward): [0] preprocess [1] scan [2] pair-count read-back (host sync) [3] emit
-// [4] sort (all passes) [5] tile ranges [6] blend forward [7] backward memsets + blend backward [8] per-Gaussian backward
+// ms of the last forward (+ backward): [0] preprocess [1] depth sort of the Gaussians (hoisted mode; 0 otherwise) [2] scan
+// [3] emit (64-bit mode: includes the host's pair-count read-back) [4] pair sort (all passes) [5] tile ranges
+// [6] blend forward [7] backward memsets + blend backward [8] per-Gaussian backward
 int gs_rast_get_timings(gs_rast* r, float* ms9, int include_backward) {
     gs_ctx* c = r->c; GS_SETDEV(c);
     GS_ARG(c, r->prof && ms9, "profiling is off");
@@ -552,7 +653,7 @@ int gs_rast_count_evals(gs_rast* r, uint64_t* E, uint64_t* C) {
     gs_ctx* c = r->c; GS_SETDEV(c);
     if (!r->counters) GS_TRY(dalloc(c, &r->counters, 2));
     GS_CUDA(c, cudaMemsetAsync(r->counters, 0, 16, c->stream));
-    gs_launch_blend_count(r->proj, r->vbuf[r->pairs ? r->result : 0], r->ranges, r->W, r->H, r->ntx, r->nty, r->counters, c->stream);
+    gs_launch_blend_count(r->proj, r->sorted_vals, r->ranges, r->W, r->H, r->ntx, r->nty, r->counters, c->stream);
     GS_LAUNCH_CHECK(c);
     unsigned long long h[2];
     GS_CUDA(c, cudaMemcpyAsync(h, r->counters, 16, cudaMemcpyDeviceToHost, c->stream));
@@ -566,7 +667,8 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
     gs_ctx* c = r->c; GS_SETDEV(c);
     cudaStream_t st = c->stream;
     const void* src = nullptr; size_t need = 0;
-    const int res = r->pairs ? r->result : 0;
+    void* tmp[3] = {nullptr, nullptr, nullptr};
+    int rc = GS_OK;
     switch (which) {
         case GS_RAST_PROJECTED:
             need = (size_t)r->n * sizeof(gs_projected);
@@ -574,19 +676,42 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
             gs_launch_projected_to_aos(r->proj, r->n, r->staging, st);
             GS_LAUNCH_CHECK(c);
             src = r->staging; break;
-        case GS_RAST_KEYS: src = r->keys_in; need = r->pairs * 8; break;
-        case GS_RAST_VALUES: src = r->vals_in; need = r->pairs * 4; break;
-        case GS_RAST_SORTED_KEYS: src = r->kbuf[res]; need = r->pairs * 8; break;
-        case GS_RAST_SORTED_VALUES: src = r->vbuf[res]; need = r->pairs * 4; break;
+        case GS_RAST_KEYS:
+        case GS_RAST_VALUES:
+            if (r->mode == 1) { src = which == GS_RAST_KEYS ? (const void*)r->keys_in : (const void*)r->vals_in; }
+            else if (r->pairs) {
+                // hoisted mode never materialises the reference's pre-sort list: rebuild it (Gaussian order, u64 keys) on demand
+                GS_CUDA(c, cudaMalloc(&tmp[0], ((size_t)r->n + 1) * 4));
+                GS_CUDA(c, cudaMalloc(&tmp[1], r->pairs * 8));
+                GS_CUDA(c, cudaMalloc(&tmp[2], r->pairs * 4));
+                gs_launch_exclusive_scan(r->proj.cnt, nullptr, (uint32_t*)tmp[0], r->n, r->meta + GS_META_COUNT - 1, r->scan_scratch, st);
+                gs_launch_emit_pairs(r->proj, (const uint32_t*)tmp[0], r->n, r->ntx, (uint64_t*)tmp[1], (uint32_t*)tmp[2], (uint32_t)r->pairs, st);
+                src = which == GS_RAST_KEYS ? tmp[1] : tmp[2];
+            }
+            need = r->pairs * (which == GS_RAST_KEYS ? 8 : 4); break;
+        case GS_RAST_SORTED_KEYS:
+            if (r->mode == 1) src = r->sorted_keys;
+            else if (r->pairs) {
+                GS_CUDA(c, cudaMalloc(&tmp[0], r->pairs * 8));
+                gs_launch_rebuild_keys64(r->sorted_tiles, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
+                src = tmp[0];
+            }
+            need = r->pairs * 8; break;
+        case GS_RAST_SORTED_VALUES: src = r->sorted_vals; need = r->pairs * 4; break;
         case GS_RAST_TILE_RANGES: src = r->ranges; need = (size_t)r->ntx * r->nty * 8; break;
         case GS_RAST_LAST_IDX: src = r->last_idx; need = (size_t)r->W * r->H * 4; break;
         case GS_RAST_TFINAL: src = r->tfinal; need = (size_t)r->W * r->H * 4; break;
         default: GS_ARG(c, false, "which");
     }
-    GS_ARG(c, bytes >= need, "host buffer too small");
-    if (need) GS_CUDA(c, cudaMemcpyAsync(host, src, need, cudaMemcpyDeviceToHost, st));
-    GS_CUDA(c, cudaStreamSynchronize(st));
-    return GS_OK;
+    if (bytes < need) { c->err = "bad argument: host buffer too small"; rc = GS_ERR_ARG; }
+    if (rc == GS_OK && need && cudaMemcpyAsync(host, src, need, cudaMemcpyDeviceToHost, st) != cudaSuccess) { c->err = "cudaMemcpyAsync"; rc = GS_ERR_CUDA; }
+    if (cudaStreamSynchronize(st) != cudaSuccess && rc == GS_OK) { c->err = "cudaStreamSynchronize"; rc = GS_ERR_CUDA; }
+    for (void* t : tmp) cudaFree(t);
+    if (rc == GS_OK && (which == GS_RAST_VALUES || which == GS_RAST_SORTED_VALUES)) {   // bit 31 is the library's "cannot contribute" mark (pairs.cu)
+        uint32_t* v = (uint32_t*)host;
+        for (uint64_t i = 0; i < r->pairs; i++) v[i] &= GS_ID_MASK;
+    }
+    return rc;
 }
 uint64_t gs_rast_pair_count(const gs_rast* r) { return r->pairs; }
 int gs_rast_sort_passes(const gs_rast* r) { return r->passes; }
@@ -685,7 +810,7 @@ int gs_sort32_sort(gs_sort32* s, const uint32_t* d_keys, const uint32_t* d_vals,
     if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
     GS_TRY(sort_reserve(s, n, true));
     const GsSortPlan plan = gs_sort_plan(0, 32, ~0ull);               // 4 passes x 8 bits, gpu_sort.hpp:34
-    s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, s->scratch, c->stream);
+    s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, nullptr, plan, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }

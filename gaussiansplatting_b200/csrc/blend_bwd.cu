@@ -14,7 +14,10 @@
 
 namespace {
 
-constexpr int BB = 128;   // staged entries per round
+#ifndef GS_BWD_PPT
+#define GS_BWD_PPT 2
+#endif
+constexpr int BB = 128;   // raw list entries staged per round
 
 // sum of v[0..7] over the warp; afterwards lane L holds (in v[0]) the total of value ((L>>2)&7 bit-reversed order below)
 __device__ __forceinline__ float warp_reduce8_transposed(float v[8], uint32_t lane) {
@@ -42,125 +45,169 @@ __device__ __forceinline__ uint32_t reduce8_index(uint32_t lane) {
     return ((lane >> 4) & 1u) * 4u + ((lane >> 3) & 1u) * 2u + ((lane >> 2) & 1u);
 }
 
-__global__ void __launch_bounds__(256) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+// PPT pixels per thread, NT = 256/PPT threads (NW warps) per tile.  Each round stages BB raw list entries (those flagged
+// GS_CULL_BIT by pairs.cu are dropped, order kept).  A warp reduces the nine moments of an entry over its lanes and
+// stores them in ITS OWN row of shared memory (a warp meets an entry once per round, so no atomics and no conflicts);
+// the rows are summed and flushed with one global float atomic per (tile, Gaussian, moment).
+template <int PPT>
+__global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                              const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                              const float4* __restrict__ rendered, const float4* __restrict__ gt,
                                                              int quantize, const uint32_t* __restrict__ last_idx,
                                                              const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
                                                              float* __restrict__ acc) {
-    __shared__ float4 s_r0[BB], s_r1[BB];
-    __shared__ float s_b[BB];
-    __shared__ uint32_t s_gid[BB];
-    __shared__ float s_acc[BB * 9];
-    __shared__ uint32_t s_wmax[8];
+    constexpr int NT = 256 / PPT, NW = NT / 32, K = (BB + NT - 1) / NT;
+    __shared__ float4 s_r0[BB], s_r1[BB], s_r2[BB];     // r2 = {blue, list index (bits), gaussian id (bits), -}
+    __shared__ float s_acc[NW][BB * 9];
+    __shared__ uint32_t s_w[NW];
+    __shared__ uint32_t s_wmax[NW];
     const uint32_t tile = blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-    const uint32_t px = tX * 16u + (warp & 1u) * 8u + (lane & 7u);
-    const uint32_t py = tY * 16u + (warp >> 1) * 4u + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px + 0.5f, pyf = (float)py + 0.5f;      // :416
     const uint2 range = ranges[tile];                                // :410-413
+    const bool redo = tile_flags[tile] != 0u;
 
-    uint32_t e = 0;                                                  // entries [0, e) of the tile list concern this pixel
-    float T = 1.0f, dr = 0.f, dg = 0.f, db = 0.f;
-    if (inside) {
-        const size_t pix = (size_t)py * W + px;
-        const uint32_t li = last_idx[pix];                           // :404-407
-        if (li != 0xFFFFFFFFu) {
-            e = min(li + 1u, range.x + range.y) - range.x;           // :427
-            const float4 r = rendered[pix], t = gt[pix];             // :418-423
-            float rr[3] = {r.x, r.y, r.z};
-            const float tt[3] = {t.x, t.y, t.z};
-            float s[3];
+    float pxf[PPT], pyf[PPT], T[PPT], dr[PPT], dg[PPT], db[PPT], ar[PPT], ag[PPT], ab[PPT];
+    uint32_t e[PPT];                                                 // entries [0, e) of the tile list concern pixel j
+    uint32_t emax = 0;
 #pragma unroll
-            for (int c = 0; c < 3; c++) {
-                if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
-                const float diff = rr[c] - tt[c];
-                s[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
-            }
-            dr = s[0]; dg = s[1]; db = s[2];
-            T = tfinal[pix];
-            if (tile_flags[tile]) {
-                // Rare path (a conic-degenerate entry was walked): redo the reference's first pass (:430-460), which,
-                // unlike the forward, does not skip such entries.
-                float Tf = 1.0f;
-                for (uint32_t k = 0; k < e; k++) {
-                    const uint32_t g = svals[range.x + k];
-                    const float4 a = rec[3 * (size_t)g], b = rec[3 * (size_t)g + 1];
-                    const float dx = gs::fsub(pxf, a.x), dy = gs::fsub(pyf, a.y);
-                    const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
-                    if (!(power <= 0.0f) || power < -4.5f) continue;
-                    const float alpha = fminf(gs::fmul(b.y, gs::exp_blend(power)), GS_ALPHA_MAX);
-                    if (alpha < GS_ALPHA_MIN) continue;
-                    const float test_T = gs::fmul(Tf, gs::fsub(1.0f, alpha));
-                    if (test_T < GS_T_EPS) break;                    // :458
-                    Tf = test_T;
+    for (int j = 0; j < PPT; j++) {
+        uint32_t x, y;
+        gs::tile_pixel<PPT>(warp, lane, j, x, y);
+        const uint32_t px = tX * 16u + x, py = tY * 16u + y;
+        pxf[j] = (float)px + 0.5f; pyf[j] = (float)py + 0.5f;        // :416
+        e[j] = 0; T[j] = 1.0f; dr[j] = 0.f; dg[j] = 0.f; db[j] = 0.f;
+        ar[j] = 1.0f; ag[j] = 1.0f; ab[j] = 1.0f;                    // accum_rec starts at the white background :468-470
+        if (px < W && py < H) {
+            const size_t pix = (size_t)py * W + px;
+            const uint32_t li = last_idx[pix];                       // :404-407
+            if (li != 0xFFFFFFFFu) {
+                e[j] = min(li + 1u, range.x + range.y) - range.x;    // :427
+                const float4 r = rendered[pix], t = gt[pix];         // :418-423
+                float rr[3] = {r.x, r.y, r.z};
+                const float tt[3] = {t.x, t.y, t.z};
+                float s[3];
+#pragma unroll
+                for (int c = 0; c < 3; c++) {
+                    if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
+                    const float diff = rr[c] - tt[c];
+                    s[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
                 }
-                T = Tf;
+                dr[j] = s[0]; dg[j] = s[1]; db[j] = s[2];
+                T[j] = tfinal[pix];
+                if (redo) {
+                    // Rare path (a conic-degenerate entry was walked): redo the reference's first pass (:430-460), which,
+                    // unlike the forward, does not skip such entries.
+                    float Tf = 1.0f;
+                    for (uint32_t k = 0; k < e[j]; k++) {
+                        const uint32_t g = svals[range.x + k] & GS_ID_MASK;
+                        const float4 a = rec[3 * (size_t)g], b = rec[3 * (size_t)g + 1];
+                        const float dx = gs::fsub(pxf[j], a.x), dy = gs::fsub(pyf[j], a.y);
+                        const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
+                        if (!(power <= 0.0f) || power < -4.5f) continue;
+                        const float alpha = fminf(gs::fmul(b.y, gs::exp_blend(power)), GS_ALPHA_MAX);
+                        if (alpha < GS_ALPHA_MIN) continue;
+                        const float test_T = gs::fmul(Tf, gs::fsub(1.0f, alpha));
+                        if (test_T < GS_T_EPS) break;                // :458
+                        Tf = test_T;
+                    }
+                    T[j] = Tf;
+                }
             }
         }
+        emax = max(emax, e[j]);
     }
     // CTA-wide and warp-wide extent of the walk
-    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, e);
+    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, emax);
     if (lane == 0) s_wmax[warp] = wmax;
     __syncthreads();
     uint32_t bmax = 0;
 #pragma unroll
-    for (int w = 0; w < 8; w++) bmax = max(bmax, s_wmax[w]);
+    for (int w = 0; w < NW; w++) bmax = max(bmax, s_wmax[w]);
 
-    float ar = 1.0f, ag = 1.0f, ab = 1.0f;                           // accum_rec starts at the white background :468-470
+    float* my_acc = s_acc[warp];
     for (uint32_t hi = bmax; hi > 0;) {
         const uint32_t lo = hi > (uint32_t)BB ? hi - BB : 0u;
-        const uint32_t cnt = hi - lo;
-        if (threadIdx.x < cnt) {
-            const uint32_t g = svals[range.x + lo + threadIdx.x];
-            const float4 r0 = rec[3 * (size_t)g], r1 = rec[3 * (size_t)g + 1];
-            s_r0[threadIdx.x] = r0; s_r1[threadIdx.x] = r1; s_b[threadIdx.x] = rec[3 * (size_t)g + 2].x;
-            s_gid[threadIdx.x] = g;
+        const uint32_t cntraw = hi - lo;
+        // ---- stage (compacting out culled pairs, list order kept) and clear this warp's moment rows
+        uint32_t v[K], nl = 0;
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            const uint32_t j = threadIdx.x * K + q;
+            v[q] = (j < cntraw) ? svals[range.x + lo + j] : GS_CULL_BIT;
+            nl += (v[q] >> 31) ^ 1u;
         }
-        for (uint32_t i = threadIdx.x; i < cnt * 9u; i += 256u) s_acc[i] = 0.f;
+        uint32_t total;
+        uint32_t slot = gs::cta_excl_scan<NW>(nl, s_w, &total);
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            if (v[q] >> 31) continue;
+            const uint32_t g = v[q];
+            s_r0[slot] = rec[3 * (size_t)g]; s_r1[slot] = rec[3 * (size_t)g + 1];
+            s_r2[slot] = make_float4(rec[3 * (size_t)g + 2].x, __uint_as_float(lo + threadIdx.x * K + q), __uint_as_float(g), 0.f);
+            slot++;
+        }
+        for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
         __syncthreads();
         if (wmax > lo) {
-            for (int k = (int)min(hi, wmax) - 1 - (int)lo; k >= 0; k--) {    // :473 back to front
+            // staged list indices ascend: entries at or beyond this warp's extent are of no interest to it
+            uint32_t kend = total;
+            if (wmax < hi) {
+                uint32_t a = 0, b = total;
+                while (a < b) { const uint32_t m = (a + b) >> 1; if (__float_as_uint(s_r2[m].y) < wmax) a = m + 1; else b = m; }
+                kend = a;
+            }
+            for (int k = (int)kend - 1; k >= 0; k--) {                // :473 back to front
                 const float4 a = s_r0[k];
                 const float4 b = s_r1[k];
-                const float dx = gs::fsub(pxf, a.x), dy = gs::fsub(pyf, a.y);   // :483
-                const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
-                bool c = (lo + (uint32_t)k < e) && (power <= 0.0f) && !(power < -4.5f);   // :489
-                float G = 0.f, alpha = 0.f;
-                if (c) {
-                    G = gs::exp_blend(power);                         // :492
-                    alpha = fminf(gs::fmul(b.y, G), GS_ALPHA_MAX);
-                    c = !(alpha < GS_ALPHA_MIN);                      // :495
-                }
-                if (!__any_sync(0xFFFFFFFFu, c)) continue;
-                float v[8], v8 = 0.f;
+                const float4 c2 = s_r2[k];
+                const uint32_t idx = __float_as_uint(c2.y);
+                bool c[PPT], anyc = false;
+                float G[PPT], alpha[PPT], dx[PPT], dy[PPT];
 #pragma unroll
-                for (int i = 0; i < 8; i++) v[i] = 0.f;
-                if (c) {
-                    const float cb = s_b[k];
-                    const float om = 1.0f - alpha;
-                    T = T / fmaxf(om, 0.0001f);                       // :498
-                    const float w = alpha * T;                        // :500
-                    const float dLdA = T * ((dr * (b.z - ar) + dg * (b.w - ag)) + db * (cb - ab));   // :510
-                    ar = alpha * b.z + om * ar; ag = alpha * b.w + om * ag; ab = alpha * cb + om * ab;   // :514
-                    const float q = dLdA * G;
-                    const float qx = q * dx, qy = q * dy;
-                    v[0] = dr * w; v[1] = dg * w; v[2] = db * w; v[3] = q;
-                    v[4] = qx; v[5] = qy; v[6] = qx * dx; v[7] = qx * dy; v8 = qy * dy;
+                for (int j = 0; j < PPT; j++) {
+                    dx[j] = gs::fsub(pxf[j], a.x); dy[j] = gs::fsub(pyf[j], a.y);   // :483
+                    const float power = gs::blend_power(a.z, a.w, b.x, dx[j], dy[j]);
+                    c[j] = (idx < e[j]) && (power <= 0.0f) && !(power < -4.5f);     // :489
+                    G[j] = 0.f; alpha[j] = 0.f;
+                    if (c[j]) {
+                        G[j] = gs::exp_blend(power);                  // :492
+                        alpha[j] = fminf(gs::fmul(b.y, G[j]), GS_ALPHA_MAX);
+                        c[j] = !(alpha[j] < GS_ALPHA_MIN);            // :495
+                    }
+                    anyc |= c[j];
                 }
-                const float tot = warp_reduce8_transposed(v, lane);
+                if (!__any_sync(0xFFFFFFFFu, anyc)) continue;
+                float v8[8], v9 = 0.f;
 #pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v8 += __shfl_xor_sync(0xFFFFFFFFu, v8, d);
-                if ((lane & 3u) == 0u) atomicAdd(&s_acc[k * 9 + reduce8_index(lane)], tot);
-                if (lane == 1u) atomicAdd(&s_acc[k * 9 + 8], v8);
+                for (int i = 0; i < 8; i++) v8[i] = 0.f;
+#pragma unroll
+                for (int j = 0; j < PPT; j++) {
+                    if (c[j]) {
+                        const float om = 1.0f - alpha[j];
+                        T[j] = __fdividef(T[j], fmaxf(om, 0.0001f));  // :498
+                        const float w = alpha[j] * T[j];              // :500
+                        const float dLdA = T[j] * ((dr[j] * (b.z - ar[j]) + dg[j] * (b.w - ag[j])) + db[j] * (c2.x - ab[j]));   // :510
+                        ar[j] = alpha[j] * b.z + om * ar[j]; ag[j] = alpha[j] * b.w + om * ag[j]; ab[j] = alpha[j] * c2.x + om * ab[j];   // :514
+                        const float q = dLdA * G[j];
+                        const float qx = q * dx[j], qy = q * dy[j];
+                        v8[0] += dr[j] * w; v8[1] += dg[j] * w; v8[2] += db[j] * w; v8[3] += q;
+                        v8[4] += qx; v8[5] += qy; v8[6] += qx * dx[j]; v8[7] += qx * dy[j]; v9 += qy * dy[j];
+                    }
+                }
+                const float tot = warp_reduce8_transposed(v8, lane);
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
+                if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
+                if (lane == 1u) my_acc[k * 9 + 8] = v9;
             }
         }
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < cnt * 9u; i += 256u) {
-            const float x = s_acc[i];
-            if (x != 0.f) atomicAdd(&acc[(size_t)s_gid[i / 9u] * 12u + (i % 9u)], x);
+        for (uint32_t i = threadIdx.x; i < total * 9u; i += NT) {
+            float x = 0.f;
+#pragma unroll
+            for (int w = 0; w < NW; w++) x += s_acc[w][i];
+            if (x != 0.f) atomicAdd(&acc[(size_t)__float_as_uint(s_r2[i / 9u].z) * 12u + (i % 9u)], x);
         }
         __syncthreads();
         hi = lo;
@@ -273,12 +320,19 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, Gs
 
 }  // namespace
 
+static int g_bwd_ppt = GS_BWD_PPT;
+void gs_tune_bwd_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_bwd_ppt = v; }
+
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
                               const uint32_t* last_idx, const float* tfinal, float* acc, cudaStream_t st) {
     if (ntx * nty == 0) return;
-    blend_backward_kernel<<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, last_idx,
-                                                     tfinal, O.tile_flags, acc);
+#define GS_BWD_LAUNCH(PPT)                                                                                          \
+    blend_backward_kernel<PPT><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
+                                                                 last_idx, tfinal, O.tile_flags, acc)
+    if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4);
+    else if (g_bwd_ppt == 2) GS_BWD_LAUNCH(2);
+    else GS_BWD_LAUNCH(1);
 }
 
 void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,

@@ -164,12 +164,12 @@ void gs_launch_densify_plan(uint32_t* markers, uint32_t n, uint32_t max_gaussian
     if (n) {
         for (uint32_t which = 2; which <= 3; which++) {               // clones first, then splits (:364-379)
             flag_marker_kernel<<<blocks, 256, 0, st>>>(markers, n, which, rankbuf);
-            gs_launch_exclusive_scan(rankbuf, n, stats4 + 3, scan_scratch, st);
+            gs_launch_exclusive_scan(rankbuf, nullptr, rankbuf, n, stats4 + 3, scan_scratch, st);
             unmark_kernel<<<blocks, 256, 0, st>>>(markers, n, max_gaussians, counts3, rankbuf, which);
         }
         out_count_kernel<<<blocks, 256, 0, st>>>(markers, n, out_off);
     }
-    gs_launch_exclusive_scan(out_off, n, stats4 + 3, scan_scratch, st);
+    gs_launch_exclusive_scan(out_off, nullptr, out_off, n, stats4 + 3, scan_scratch, st);
     densify_stats_kernel<<<1, 1, 0, st>>>(counts3, n, max_gaussians, out_off, stats4);
 }
 

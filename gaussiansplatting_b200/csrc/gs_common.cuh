@@ -18,6 +18,8 @@
 #define GS_ALPHA_MIN (1.0f / 255.0f)       // tiled_shaders.metal:366
 #define GS_ALPHA_MAX 0.99f                 // tiled_shaders.metal:363
 #define GS_T_EPS 0.0001f                   // tiled_shaders.metal:334,458
+#define GS_CULL_BIT 0x80000000u            // pair value bit 31: this (tile, Gaussian) pair can never contribute (pairs.cu)
+#define GS_ID_MASK 0x7FFFFFFFu
 
 #define GS_LOG2E 1.44269504088896340736f
 #define GS_EXP2_C1 0x1.62e42ap-1f
@@ -67,6 +69,32 @@ __device__ __forceinline__ float blend_power(float Ah, float Bn, float Ch, float
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
+// Pixel (within the 16x16 tile) of slot j of a thread, for PPT pixels per thread (256/PPT threads per tile):
+//   PPT 1: 8 warps, each an 8x4 patch;  PPT 2: 4 warps, each an 8x8 block, a lane owns a vertical pair;
+//   PPT 4: 2 warps, each a 16x8 strip, a lane owns a 2x2 quad.
+template <int PPT>
+__device__ __forceinline__ void tile_pixel(uint32_t warp, uint32_t lane, int j, uint32_t& x, uint32_t& y) {
+    if (PPT == 1) { x = (warp & 1u) * 8u + (lane & 7u); y = (warp >> 1) * 4u + (lane >> 3); }
+    else if (PPT == 2) { x = (warp & 1u) * 8u + (lane & 7u); y = (warp >> 1) * 8u + (lane >> 3) * 2u + (uint32_t)j; }
+    else { x = (lane & 7u) * 2u + ((uint32_t)j & 1u); y = warp * 8u + (lane >> 3) * 2u + ((uint32_t)j >> 1); }
+}
+
+// exclusive scan of one small count per thread over a CTA of NW warps; returns the exclusive prefix, *total = CTA sum.
+// s_w: NW words of shared scratch; contains one __syncthreads().
+template <int NW>
+__device__ __forceinline__ uint32_t cta_excl_scan(uint32_t x, uint32_t* s_w, uint32_t* total) {
+    uint32_t inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane_id() >= (uint32_t)d) inc += t; }
+    if (lane_id() == 31u) s_w[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    uint32_t off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) { const uint32_t c = s_w[w]; if (w < (int)(threadIdx.x >> 5)) off += c; tot += c; }
+    *total = tot;
+    return off + inc - x;
+}
+
 // relaxed gpu-scope load/store for look-back status words
 __device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
     uint32_t v;
@@ -101,7 +129,9 @@ struct GsProjected {
     uint4* bbox;     // tileMinX, tileMinY, tileMaxX, tileMaxY
     float4* aux;     // viewPos.x, viewPos.y, cov2D.a, cov2D.b
     float* covc;     // cov2D.c
-    uint32_t* offs;  // tile count per Gaussian, then (after the scan) exclusive offsets; [n] = total
+    uint32_t* cnt;   // tiles this Gaussian emits (0 = culled / fails generateTilePairs' admission tests)
+    uint32_t* dkey;  // sortable depth bits (tiled_shaders.metal:773-774); 0xFFFFFFFF when cnt == 0
+    uint32_t* offs;  // exclusive scan of cnt in emission order (Gaussian order, or depth order in hoisted mode); [n] = total
     uint32_t* tile_flags;  // per TILE: 1 if the forward walked a conic-degenerate entry (backward then redoes pass 1)
 };
 

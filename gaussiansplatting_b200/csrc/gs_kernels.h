@@ -12,12 +12,19 @@ enum { GS_META_TOTAL_PAIRS = 0, GS_META_KEY_OR = 1, GS_META_KEY_AND = 2, GS_META
 void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* V, const float* VP, float sw, float sh,
                           float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, cudaStream_t st);
 
-// K2: in-place exclusive scan of v[0..n) ; v[n] and *total receive the sum.  scratch: gs_scan_scratch_bytes(n).
+// K2: exclusive scan: out[j] = sum_{j'<j} in[perm ? perm[j'] : j']; out[n] and *total receive the sum (in == out allowed
+// when perm is null).  scratch: gs_scan_scratch_bytes(n).
 size_t gs_scan_scratch_bytes(uint32_t n);
-void gs_launch_exclusive_scan(uint32_t* v, uint32_t n, uint32_t* total, void* scratch, cudaStream_t st);
+void gs_launch_exclusive_scan(const uint32_t* in, const uint32_t* perm, uint32_t* out, uint32_t n, uint32_t* total,
+                              void* scratch, cudaStream_t st);
 
-// K3: emit (tile<<32 | depthKey, gaussian) pairs at the scanned offsets (Gaussian order, ty-major, tx-minor)
-void gs_launch_emit_pairs(const GsProjected& O, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals, cudaStream_t st);
+// K3: emit (tile<<32 | depthKey, gaussian) pairs at the scanned offsets O.offs (Gaussian order, ty-major, tx-minor).
+// Bit 31 of a value (GS_CULL_BIT) marks a pair that can never contribute; writes are bounded by cap_pairs.
+void gs_launch_emit_pairs(const GsProjected& O, const uint32_t* offs, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals,
+                          uint32_t cap_pairs, cudaStream_t st);
+// hoisted-depth mode: list position j is Gaussian perm[j] (depth order), offs[j] its scanned offset; key = tile id only
+void gs_launch_emit_tile_pairs(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
+                               uint32_t* tile_keys, uint32_t* vals, uint32_t cap_pairs, cudaStream_t st);
 
 // K4: onesweep LSD radix sort -------------------------------------------------------------------------
 struct GsSortPlan {
@@ -33,8 +40,12 @@ size_t gs_sort_scratch_bytes(uint64_t n, int key_bytes);
 // Returns the index (0/1) of the buffer holding the result.
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
                      const GsSortPlan& plan, void* scratch, cudaStream_t st);
+// n is a host-side BOUND (grid, scratch); when d_n is non-null the true count is read from the device (min(*d_n, n)),
+// so the caller needs no host synchronisation to learn it.
 int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const GsSortPlan& plan, void* scratch, cudaStream_t st);
+                     const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st);
+// passes over [begin_bit, end_bit) with the bits split evenly over ceil(bits/8) digits (13 bits -> 7 + 6)
+GsSortPlan gs_sort_plan_even(int begin_bit, int end_bit);
 // viewer depth keys (computeDepths, sort.metal:36-72)
 void gs_launch_depth_keys32(const float4* positions, float cx, float cy, float cz, uint32_t n, uint32_t* keys,
                             uint32_t* vals, cudaStream_t st);
@@ -42,6 +53,13 @@ void gs_launch_depth_keys32(const float4* positions, float cx, float cy, float c
 // K5: tile ranges from sorted keys (buildTileRanges semantics, sort.metal:553-589).  lb: numTiles+1 scratch words.
 void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* lb,
                            uint2* ranges, cudaStream_t st);
+// same result from sorted u32 tile ids by run-boundary detection (O(P) coalesced reads); the pair count is read from
+// the device (min(*d_n, max_pairs)); the grid is sized from max_pairs
+void gs_launch_tile_ranges32(const uint32_t* sorted_tiles, uint32_t max_pairs, const uint32_t* d_n, uint32_t num_tiles,
+                             uint2* ranges, cudaStream_t st);
+// inspection: rebuild the reference's 64-bit sorted keys (tile<<32 | depthKey) from sorted tile ids + values
+void gs_launch_rebuild_keys64(const uint32_t* sorted_tiles, const uint32_t* sorted_vals, const uint32_t* dkey, uint32_t n,
+                              uint64_t* keys, cudaStream_t st);
 
 // K6: forward blend.  image: W*H float4 RGBA; last_idx/tfinal: W*H.
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
@@ -95,3 +113,7 @@ void gs_launch_densify_plan(uint32_t* markers, uint32_t n, uint32_t max_gaussian
                             uint32_t* out_off, uint32_t* stats4, void* scan_scratch, cudaStream_t st);
 void gs_launch_densify_scatter(GsParams Pin, GsParams Pout, const uint32_t* markers, const uint32_t* out_off,
                                GsDensifyArgs a, cudaStream_t st);
+
+// tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
+void gs_tune_fwd_ppt(int v);
+void gs_tune_bwd_ppt(int v);

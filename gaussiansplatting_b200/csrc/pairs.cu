@@ -21,7 +21,9 @@ __device__ __forceinline__ void st_relaxed64(unsigned long long* p, unsigned lon
 }
 
 // scratch layout: [0] dynamic tile counter (u32, + pad to 8 B), then one u64 status word per tile
-__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(uint32_t* __restrict__ v, uint32_t n, uint32_t* __restrict__ total,
+// out[j] = sum_{j'<j} in[perm ? perm[j'] : j'] ; out[n] = *total = the sum.  in == out (perm == nullptr) is allowed.
+__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, const uint32_t* __restrict__ perm, uint32_t* out,
+                                                            uint32_t n, uint32_t* __restrict__ total,
                                                             uint32_t* counter, unsigned long long* status) {
     __shared__ uint32_t s_tile, s_warp[SCAN_THREADS / 32], s_prefix;
     if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
@@ -31,7 +33,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(uint32_t* __restrict
     uint32_t x[SCAN_IPT];
     uint32_t sum = 0;
 #pragma unroll
-    for (int k = 0; k < SCAN_IPT; k++) { x[k] = (base + k < n) ? v[base + k] : 0u; sum += x[k]; }
+    for (int k = 0; k < SCAN_IPT; k++) { x[k] = (base + k < n) ? in[perm ? perm[base + k] : base + k] : 0u; sum += x[k]; }
     // block exclusive scan of per-thread sums
     uint32_t inc = sum;
 #pragma unroll
@@ -59,34 +61,78 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(uint32_t* __restrict
             st_relaxed64(&status[tile], FLAG_INC | (unsigned long long)(excl + block_sum));
         }
         s_prefix = excl;
-        if ((uint64_t)(tile + 1) * SCAN_TILE >= n) { v[n] = excl + block_sum; *total = excl + block_sum; }
+        if ((uint64_t)(tile + 1) * SCAN_TILE >= n) { out[n] = excl + block_sum; *total = excl + block_sum; }
     }
     __syncthreads();
     uint32_t run = s_prefix + warp_off + (inc - sum);
 #pragma unroll
-    for (int k = 0; k < SCAN_IPT; k++) { if (base + k < n) v[base + k] = run; run += x[k]; }
+    for (int k = 0; k < SCAN_IPT; k++) { if (base + k < n) out[base + k] = run; run += x[k]; }
 }
 
-// K3.  One block = 256 consecutive Gaussians; the block's pairs form one contiguous output run, written
-// cooperatively (coalesced 8-B / 4-B lanes); the owner of an output slot is found by binary search in smem.
-__global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, uint32_t n, uint32_t ntx, uint64_t* __restrict__ keys,
-                                                         uint32_t* __restrict__ vals) {
+// Exact-conservative footprint test (not in the reference): can Gaussian g contribute to ANY pixel centre of tile
+// (tx,ty)?  tiledForward/tiledBackward drop an entry when power < -4.5 or alpha = sigma*exp(power) < 1/255
+// (tiled_shaders.metal:359-366,489-495), i.e. when q = A dx^2 + 2B dx dy + C dy^2 = -2 power exceeds
+// qthr = min(9, 2 ln(255 sigma)).  q is a convex quadratic centred on the splat, so its minimum over the tile's
+// pixel-centre box lies on an edge FACING the centre (<= 2 edges, each a clamped 1-D minimum).  A pair whose minimum
+// exceeds qthr by more than the rounding noise of the pinned power arithmetic can never contribute: it stays in the
+// list (so lists, ranges and lastContribIdx remain those of the reference) but is emitted with bit 31 of its value
+// set, and the blend kernels drop it while staging.
+struct CullRec { float sx, sy, A, B, C, qthr; };
+__device__ __forceinline__ CullRec cull_rec(const float4 r0, const float4 r1) {
+    CullRec c;
+    c.sx = r0.x; c.sy = r0.y; c.A = -2.0f * r0.z; c.B = -r0.w; c.C = -2.0f * r1.x;
+    c.qthr = fminf(9.0f, 2.0f * __logf(255.0f * r1.y)) + 2e-3f;
+    if (!(c.qthr == c.qthr)) c.qthr = 9.002f;
+    return c;
+}
+__device__ __forceinline__ float edge_min_q(float A, float B, float C, float cx, float ylo, float yhi) {
+    // min over dy in [ylo,yhi] of A cx^2 + 2 B cx dy + C dy^2
+    const float dy = fminf(fmaxf(-B * cx / C, ylo), yhi);
+    return A * cx * cx + 2.0f * B * cx * dy + C * dy * dy;
+}
+__device__ __forceinline__ bool tile_cannot_contribute(const CullRec& c, uint32_t tx, uint32_t ty) {
+    const float x0 = (float)(tx * GS_TILE) + 0.5f - c.sx, x1 = x0 + 15.0f;      // dx range of the pixel centres
+    const float y0 = (float)(ty * GS_TILE) + 0.5f - c.sy, y1 = y0 + 15.0f;
+    const bool inx = x0 <= 0.f && x1 >= 0.f, iny = y0 <= 0.f && y1 >= 0.f;
+    if (inx && iny) return false;                                              // centre inside the box: q_min = 0
+    if (!(c.A > 0.f) || !(c.C > 0.f)) return false;                            // degenerate / non-finite conic: keep
+    float q = 3.0e38f;
+    if (!inx) q = fminf(q, edge_min_q(c.A, c.B, c.C, x0 > 0.f ? x0 : x1, y0, y1));
+    if (!iny) q = fminf(q, edge_min_q(c.C, c.B, c.A, y0 > 0.f ? y0 : y1, x0, x1));
+    const float Dx = fmaxf(fabsf(x0), fabsf(x1)), Dy = fmaxf(fabsf(y0), fabsf(y1));
+    const float noise = 4e-6f * (c.A * Dx * Dx + 2.0f * fabsf(c.B) * Dx * Dy + c.C * Dy * Dy);   // ~32 ulp of the largest term
+    return q > c.qthr + noise;                                                 // NaN compares false: keep
+}
+
+// K3.  One block = 256 consecutive list positions (Gaussian order, or depth order through `perm`); the block's pairs
+// form one contiguous output run, written cooperatively (coalesced lanes); the owner of an output slot is found by
+// binary search in smem.  KeyT = u64: (tile<<32 | depthKey) keys of the reference; KeyT = u32: the tile id alone
+// (hoisted-depth mode, see api.cu).
+template <typename KeyT>
+__global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, const uint32_t* __restrict__ perm,
+                                                         const uint32_t* __restrict__ offs, uint32_t n, uint32_t ntx,
+                                                         KeyT* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap_pairs) {
     __shared__ uint32_t s_off[257];
-    __shared__ uint32_t s_minx[256], s_miny[256], s_tx[256], s_dkey[256];
+    __shared__ uint32_t s_minx[256], s_miny[256], s_tx[256], s_dkey[256], s_gid[256];
+    __shared__ CullRec s_cull[256];
     const uint32_t g0 = blockIdx.x * 256u;
     const uint32_t i = g0 + threadIdx.x;
     if (i < n) {
-        s_off[threadIdx.x] = O.offs[i];
-        const uint4 bb = O.bbox[i];
+        const uint32_t g = perm ? perm[i] : i;
+        s_gid[threadIdx.x] = g;
+        s_off[threadIdx.x] = offs[i];
+        const uint4 bb = O.bbox[g];
         s_minx[threadIdx.x] = bb.x; s_miny[threadIdx.x] = bb.y; s_tx[threadIdx.x] = bb.z - bb.x + 1u;
-        const uint32_t k = __float_as_uint(O.rec[3 * (size_t)i + 2].y);        // depth
+        const float4 r0 = O.rec[3 * (size_t)g], r1 = O.rec[3 * (size_t)g + 1];
+        const uint32_t k = __float_as_uint(O.rec[3 * (size_t)g + 2].y);        // depth
         s_dkey[threadIdx.x] = (k & 0x80000000u) ? ~k : (k | 0x80000000u);       // tiled_shaders.metal:773-774
+        s_cull[threadIdx.x] = cull_rec(r0, r1);
     }
     const uint32_t last = min(g0 + 256u, n);
     const uint32_t cnt = last - g0;
-    if (threadIdx.x == 0) s_off[cnt] = O.offs[last];          // offs[n] holds the total
+    if (threadIdx.x == 0) s_off[cnt] = offs[last];            // offs[n] holds the total
     __syncthreads();
-    const uint32_t begin = s_off[0], stop = s_off[cnt];
+    const uint32_t begin = s_off[0], stop = min(s_off[cnt], cap_pairs);
     for (uint32_t j = begin + threadIdx.x; j < stop; j += 256u) {
         // largest g in [0,cnt) with s_off[g] <= j   (offsets are non-decreasing; empty Gaussians are skipped)
         uint32_t lo = 0, hi = cnt;
@@ -94,8 +140,9 @@ __global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, uint32_t
         const uint32_t k = j - s_off[lo];
         const uint32_t tw = s_tx[lo];
         const uint32_t ty = s_miny[lo] + k / tw, tx = s_minx[lo] + k % tw;        // :784-786
-        keys[j] = ((uint64_t)(ty * ntx + tx) << 32) | (uint64_t)s_dkey[lo];       // :787
-        vals[j] = g0 + lo;
+        if (sizeof(KeyT) == 8) keys[j] = (KeyT)(((uint64_t)(ty * ntx + tx) << 32) | (uint64_t)s_dkey[lo]);   // :787
+        else keys[j] = (KeyT)(ty * ntx + tx);
+        vals[j] = s_gid[lo] | (tile_cannot_contribute(s_cull[lo], tx, ty) ? GS_CULL_BIT : 0u);
     }
 }
 
@@ -106,14 +153,22 @@ size_t gs_scan_scratch_bytes(uint32_t n) {
     return 8 + tiles * 8;
 }
 
-void gs_launch_exclusive_scan(uint32_t* v, uint32_t n, uint32_t* total, void* scratch, cudaStream_t st) {
-    if (n == 0) { cudaMemsetAsync(v, 0, 4, st); cudaMemsetAsync(total, 0, 4, st); return; }
+void gs_launch_exclusive_scan(const uint32_t* in, const uint32_t* perm, uint32_t* out, uint32_t n, uint32_t* total,
+                              void* scratch, cudaStream_t st) {
+    if (n == 0) { cudaMemsetAsync(out, 0, 4, st); cudaMemsetAsync(total, 0, 4, st); return; }
     uint32_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     cudaMemsetAsync(scratch, 0, 8 + (size_t)tiles * 8, st);
-    scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(v, n, total, (uint32_t*)scratch, (unsigned long long*)((char*)scratch + 8));
+    scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(in, perm, out, n, total, (uint32_t*)scratch,
+                                                (unsigned long long*)((char*)scratch + 8));
 }
 
-void gs_launch_emit_pairs(const GsProjected& O, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals, cudaStream_t st) {
+void gs_launch_emit_pairs(const GsProjected& O, const uint32_t* offs, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals,
+                          uint32_t cap_pairs, cudaStream_t st) {
     if (n == 0) return;
-    emit_pairs_kernel<<<(n + 255) / 256, 256, 0, st>>>(O, n, ntx, keys, vals);
+    emit_pairs_kernel<uint64_t><<<(n + 255) / 256, 256, 0, st>>>(O, nullptr, offs, n, ntx, keys, vals, cap_pairs);
+}
+void gs_launch_emit_tile_pairs(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
+                               uint32_t* tile_keys, uint32_t* vals, uint32_t cap_pairs, cudaStream_t st) {
+    if (n == 0) return;
+    emit_pairs_kernel<uint32_t><<<(n + 255) / 256, 256, 0, st>>>(O, perm, offs, n, ntx, tile_keys, vals, cap_pairs);
 }

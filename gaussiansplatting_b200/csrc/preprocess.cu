@@ -139,7 +139,8 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
         } while (0);
         O.rec[3 * (size_t)i + 0] = r0; O.rec[3 * (size_t)i + 1] = r1; O.rec[3 * (size_t)i + 2] = r2;
         O.bbox[i] = bb; O.aux[i] = ax; O.covc[i] = cc;
-        O.offs[i] = count;
+        O.cnt[i] = count;
+        O.dkey[i] = count ? dkey : 0xFFFFFFFFu;
     }
     // depth-key OR / AND over Gaussians that emit pairs: digits whose bits never vary need no sort pass
     const uint32_t kor = __reduce_or_sync(0xFFFFFFFFu, count ? dkey : 0u);

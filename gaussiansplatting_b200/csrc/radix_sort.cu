@@ -28,9 +28,11 @@ constexpr uint32_t ST_AGG = 0x40000000u, ST_INC = 0x80000000u, ST_VAL = 0x3FFFFF
 struct PassList { int n; int shift[8]; uint32_t mask[8]; };
 
 template <typename KeyT>
-__global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict__ keys, uint64_t n, PassList pl,
+__global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict__ keys, uint64_t n_max,
+                                                         const uint32_t* __restrict__ d_n, PassList pl,
                                                          uint32_t* __restrict__ ghist) {
     __shared__ uint32_t sh[8][256];
+    const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;   // element count may live on the device (no host sync)
     for (int i = threadIdx.x; i < 8 * 256; i += blockDim.x) (&sh[0][0])[i] = 0;
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -98,11 +100,13 @@ struct OnesweepSmem {
 
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
-                                                                 KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n,
+                                                                 KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n_max,
+                                                                 const uint32_t* __restrict__ d_n,
                                                                  int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
                                                                  uint32_t* counter, uint32_t* status, int aligned16) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     OnesweepSmem<KeyT>& S = *reinterpret_cast<OnesweepSmem<KeyT>*>(smem_raw);
+    const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;
 
     if (threadIdx.x == 0) { S.tile = atomicAdd(counter, 1u); mbar_init(&S.bar, 1); }
     for (int i = threadIdx.x; i < RS_WARPS * 256 / 2; i += RS_THREADS) reinterpret_cast<uint32_t*>(&S.wh[0][0])[i] = 0;
@@ -110,6 +114,7 @@ __global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __r
     const uint32_t tile = S.tile;
     const uint32_t warp = threadIdx.x >> 5, lane = gs::lane_id();
     const uint64_t tile_base = (uint64_t)tile * RS_TILE;
+    if (tile_base >= n) return;                              // grid was sized from a host-side bound
     const uint32_t valid = (uint32_t)min((uint64_t)RS_TILE, n - tile_base);
     const uint32_t wbase = warp * (32 * RS_IPT) + lane;    // warp-striped: item j at wbase + 32*j
     const bool bulk = aligned16 && valid == RS_TILE;
@@ -232,7 +237,7 @@ constexpr size_t RS_CTR_BYTES = 64;
 
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-              const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+              const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st) {
     if (n == 0) return 0;
     if (plan.num_passes == 0) {
         cudaMemcpyAsync(kbuf[0], keys_in, n * sizeof(KeyT), cudaMemcpyDeviceToDevice, st);
@@ -249,7 +254,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     pl.n = plan.num_passes;
     for (int p = 0; p < 8; p++) { pl.shift[p] = p < pl.n ? plan.shifts[p] : 0; pl.mask[p] = p < pl.n ? ((1u << plan.bits[p]) - 1u) : 0u; }
     uint64_t hb = (n + 2047) / 2048; int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
-    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, pl, ghist);
+    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pl, ghist);
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
     int dst = 0;
@@ -258,7 +263,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     if (!attr_set) { cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; }
     for (int p = 0; p < plan.num_passes; p++) {
         const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
-        onesweep_kernel<KeyT><<<tiles, RS_THREADS, smem, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, pl.shift[p], pl.mask[p],
+        onesweep_kernel<KeyT><<<tiles, RS_THREADS, smem, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[p], pl.mask[p],
                                                                ghist + p * 256, counters + p, status + (size_t)p * tiles * 256,
                                                                aligned16);
         kin = kbuf[dst]; vin = vbuf[dst];
@@ -288,11 +293,22 @@ size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
 
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
                      const GsSortPlan& plan, void* scratch, cudaStream_t st) {
-    return sort_impl<uint64_t>(keys_in, vals_in, kbuf, vbuf, n, plan, scratch, st);
+    return sort_impl<uint64_t>(keys_in, vals_in, kbuf, vbuf, n, nullptr, plan, scratch, st);
 }
 int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const GsSortPlan& plan, void* scratch, cudaStream_t st) {
-    return sort_impl<uint32_t>(keys_in, vals_in, kbuf, vbuf, n, plan, scratch, st);
+                     const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+    return sort_impl<uint32_t>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, scratch, st);
+}
+GsSortPlan gs_sort_plan_even(int begin_bit, int end_bit) {
+    GsSortPlan pl;
+    const int bits = end_bit - begin_bit;
+    pl.num_passes = (bits + 7) / 8;
+    int s = begin_bit;
+    for (int p = 0; p < pl.num_passes; p++) {
+        const int b = (bits - (s - begin_bit) + (pl.num_passes - p) - 1) / (pl.num_passes - p);
+        pl.shifts[p] = s; pl.bits[p] = b; s += b;
+    }
+    return pl;
 }
 void gs_launch_depth_keys32(const float4* positions, float cx, float cy, float cz, uint32_t n, uint32_t* keys,
                             uint32_t* vals, cudaStream_t st) {

@@ -86,6 +86,8 @@ int gs_ctx_sync(gs_ctx*);                               /* waitUntilCompleted */
 const char* gs_last_error(gs_ctx*);                     /* ctx may be NULL: last creation error */
 void* gs_ctx_stream(gs_ctx*);
 int gs_version(void);
+/* process-wide tuning knobs for benchmarking kernel variants: "fwd_ppt" / "bwd_ppt" = pixels per thread (1, 2, 4) */
+int gs_tune(const char* name, int value);
 
 /* raw device memory (MTL::Buffer with no typed role: sort inputs, positions) */
 int gs_dev_alloc(gs_ctx*, size_t bytes, void** dptr);

@@ -9,6 +9,7 @@ from gaussiansplatting_b200 import capi as gs, synth
 wl = sys.argv[1] if len(sys.argv) > 1 else "C2"
 warm = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
+adam = not (len(sys.argv) > 4 and sys.argv[4] == "noadam")
 n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
 ctx = gs.Context(0)
 G = gs.Gaussians(ctx, n); G.upload(synth.make_scene(n, synth.CONFIG_SEED[wl], synth.CONFIG_S0[wl]))
@@ -21,6 +22,7 @@ R.forward(Gt, cams[0], gti)
 for i in range(warm + steps):
     R.forward(G, cams[i + 1], img)
     R.backward(G, D, cams[i + 1], img, gti)
-    A.step(G, D, [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3])
+    if adam:
+        A.step(G, D, [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3])
 ctx.sync()
 print("ok pairs", R.pair_count, "passes", R.sort_passes)
