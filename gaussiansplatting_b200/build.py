@@ -17,7 +17,8 @@ SOURCES = ["preprocess.cu", "pairs.cu", "radix_sort.cu", "blend_fwd.cu", "blend_
 HEADERS = ["gs_common.cuh", "gs_kernels.h", os.path.join("..", "..", "include", "gs_abi.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
-         "-ccbin", "/usr/bin/g++", "--expt-relaxed-constexpr"]
+         "-ccbin", "/usr/bin/g++", "--expt-relaxed-constexpr"] + os.environ.get("GS_NVCC_EXTRA", "").split()
+LIB = os.environ.get("GS_LIB_OUT", LIB)          # experiments: build a variant library next to the default one
 
 
 def _stale(target, deps):

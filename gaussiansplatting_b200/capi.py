@@ -10,7 +10,7 @@ import numpy as np
 from .layouts import GAUSSIAN, GRADIENTS, PROJECTED, TILERANGE, UNIFORMS
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
+LIB_PATH = os.environ.get("GS_LIB", os.path.join(_HERE, "libgs_b200.so"))
 _lib = None
 
 GS_BWD_QUANTIZE_RGBA8 = 1

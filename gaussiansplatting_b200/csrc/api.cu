@@ -19,6 +19,8 @@ struct gs_ctx {
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
 };
 static std::string g_create_err;
+static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
+static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
 static void gs_set_sort_mode(int v);
 #define GS_PROF_EVENTS 11
 
@@ -53,6 +55,8 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "fwd_ppt")) { gs_tune_fwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "bwd_ppt")) { gs_tune_bwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
+    if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
+    if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     return GS_ERR_ARG;
 }
 
@@ -517,7 +521,7 @@ static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         const uint64_t varying = (uint64_t)(kor ^ kand) | (tile_bits ? (((1ull << tile_bits) - 1ull) << 32) : 0ull);
         const GsSortPlan plan = gs_sort_plan(0, 32 + tile_bits, varying);
         r->passes = plan.num_passes;
-        r->result = gs_launch_sort64(r->keys_in, r->vals_in, r->kbuf, r->vbuf, P, plan, r->sort_scratch, st);
+        r->result = gs_launch_sort64(r->keys_in, r->vals_in, r->kbuf, r->vbuf, P, plan, 0, r->sort_scratch, st);
         r->sorted_keys = r->kbuf[r->result]; r->sorted_vals = r->vbuf[r->result];
     } else r->mark(4);
     r->mark(5);
@@ -545,7 +549,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     while ((1u << tile_bits) < tiles) tile_bits++;
     // depth order of the Gaussians: keys = depth bits (bit 31 is always set: depth > 0.1), values = index
     const GsSortPlan dplan = gs_sort_plan(0, 31, ~0ull);
-    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, r->dsort_scratch, st);
+    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, GS_SORT_HINT_DISTINCT, r->dsort_scratch, st);
     const uint32_t* perm = r->perm_buf[dres];
     r->mark(2);
     gs_launch_exclusive_scan(r->proj.cnt, perm, r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
@@ -561,7 +565,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         const uint32_t* d_total = r->meta + GS_META_TOTAL_PAIRS;
         gs_launch_emit_tile_pairs(r->proj, perm, r->proj.offs, n, r->ntx, tk_in, r->vals_in, cap, st);
         r->mark(4);
-        r->result = gs_launch_sort32(tk_in, r->vals_in, tk, r->vbuf, cap, d_total, tplan, r->sort_scratch, st);
+        r->result = gs_launch_sort32(tk_in, r->vals_in, tk, r->vbuf, cap, d_total, tplan, g_tile_sort_hint, r->sort_scratch, st);
         r->sorted_tiles = tplan.num_passes ? tk[r->result] : tk_in;
         r->sorted_vals = tplan.num_passes ? r->vbuf[r->result] : r->vals_in;
         r->sorted_keys = nullptr;
@@ -781,7 +785,7 @@ int gs_sort64_sort(gs_sort64* s, const uint64_t* d_keys, const uint32_t* d_vals,
     if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
     GS_TRY(sort_reserve(s, n, false));
     const GsSortPlan plan = gs_sort_plan(begin_bit, end_bit, ~0ull);
-    s->result = gs_launch_sort64(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, s->scratch, c->stream);
+    s->result = gs_launch_sort64(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, g_sort_api_hint, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }
@@ -810,7 +814,7 @@ int gs_sort32_sort(gs_sort32* s, const uint32_t* d_keys, const uint32_t* d_vals,
     if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
     GS_TRY(sort_reserve(s, n, true));
     const GsSortPlan plan = gs_sort_plan(0, 32, ~0ull);               // 4 passes x 8 bits, gpu_sort.hpp:34
-    s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, nullptr, plan, s->scratch, c->stream);
+    s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, nullptr, plan, g_sort_api_hint, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }

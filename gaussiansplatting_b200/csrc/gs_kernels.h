@@ -38,12 +38,15 @@ size_t gs_sort_scratch_bytes(uint64_t n, int key_bytes);
 // Sorts (keys_in, vals_in) stably.  keys_in/vals_in are not modified; the result lands in buffer
 // (plan.num_passes odd ? 0 : 1) of {kbuf,vbuf}; with 0 passes the input is copied to buffer 0.
 // Returns the index (0/1) of the buffer holding the result.
+// hints: GS_SORT_HINT_DISTINCT = the digits met in a warp row (32 consecutive elements) are mostly distinct (random keys,
+// tile ids of a Gaussian's neighbouring tiles): rank with ballots; otherwise with match.any (runs of equal digits).
+enum { GS_SORT_HINT_DISTINCT = 1 };
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const GsSortPlan& plan, void* scratch, cudaStream_t st);
+                     const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st);
 // n is a host-side BOUND (grid, scratch); when d_n is non-null the true count is read from the device (min(*d_n, n)),
 // so the caller needs no host synchronisation to learn it.
 int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st);
+                     const uint32_t* d_n, const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st);
 // passes over [begin_bit, end_bit) with the bits split evenly over ceil(bits/8) digits (13 bits -> 7 + 6)
 GsSortPlan gs_sort_plan_even(int begin_bit, int end_bit);
 // viewer depth keys (computeDepths, sort.metal:36-72)

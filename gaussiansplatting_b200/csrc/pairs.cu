@@ -44,24 +44,34 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, 
     uint32_t warp_off = 0, block_sum = 0;
 #pragma unroll
     for (int w = 0; w < SCAN_THREADS / 32; w++) { if (w < (int)warp) warp_off += s_warp[w]; block_sum += s_warp[w]; }
-    if (threadIdx.x == 0) {
+    if (warp == 0) {
+        // decoupled look-back by one warp: 32 predecessors per round, the nearest inclusive prefix ends the walk
         uint32_t excl = 0;
+        const uint32_t lane = gs::lane_id();
         if (tile == 0) {
-            st_relaxed64(&status[0], FLAG_INC | block_sum);
+            if (lane == 0) st_relaxed64(&status[0], FLAG_INC | block_sum);
         } else {
-            st_relaxed64(&status[tile], FLAG_AGG | block_sum);
-            int t = (int)tile - 1;
+            if (lane == 0) st_relaxed64(&status[tile], FLAG_AGG | block_sum);
+            int base = (int)tile - 1;
             while (true) {
-                unsigned long long s;
-                do { s = ld_relaxed64(&status[t]); } while ((s >> 32) == 0ull);
-                excl += (uint32_t)s;
-                if (s & FLAG_INC) break;
-                t--;
+                const int idx = base - (int)lane;
+                unsigned long long s = FLAG_INC;                       // before the first tile: inclusive prefix 0
+                if (idx >= 0) do { s = ld_relaxed64(&status[idx]); } while ((s >> 32) == 0ull);
+                const uint32_t incmask = __ballot_sync(0xFFFFFFFFu, (s & FLAG_INC) != 0ull);
+                const int first = incmask ? (__ffs(incmask) - 1) : 31;
+                uint32_t v = ((int)lane <= first) ? (uint32_t)s : 0u;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+                excl += v;
+                if (incmask) break;
+                base -= 32;
             }
-            st_relaxed64(&status[tile], FLAG_INC | (unsigned long long)(excl + block_sum));
+            if (lane == 0) st_relaxed64(&status[tile], FLAG_INC | (unsigned long long)(excl + block_sum));
         }
-        s_prefix = excl;
-        if ((uint64_t)(tile + 1) * SCAN_TILE >= n) { out[n] = excl + block_sum; *total = excl + block_sum; }
+        if (lane == 0) {
+            s_prefix = excl;
+            if ((uint64_t)(tile + 1) * SCAN_TILE >= n) { out[n] = excl + block_sum; *total = excl + block_sum; }
+        }
     }
     __syncthreads();
     uint32_t run = s_prefix + warp_off + (inc - sum);
@@ -77,17 +87,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, 
 // exceeds qthr by more than the rounding noise of the pinned power arithmetic can never contribute: it stays in the
 // list (so lists, ranges and lastContribIdx remain those of the reference) but is emitted with bit 31 of its value
 // set, and the blend kernels drop it while staging.
-struct CullRec { float sx, sy, A, B, C, qthr; };
+struct CullRec { float sx, sy, A, B, C, qthr, iA, iC; };
 __device__ __forceinline__ CullRec cull_rec(const float4 r0, const float4 r1) {
     CullRec c;
     c.sx = r0.x; c.sy = r0.y; c.A = -2.0f * r0.z; c.B = -r0.w; c.C = -2.0f * r1.x;
     c.qthr = fminf(9.0f, 2.0f * __logf(255.0f * r1.y)) + 2e-3f;
     if (!(c.qthr == c.qthr)) c.qthr = 9.002f;
+    c.iA = 1.0f / c.A; c.iC = 1.0f / c.C;       // only steer where on an edge q is sampled; the margin absorbs their rounding
     return c;
 }
-__device__ __forceinline__ float edge_min_q(float A, float B, float C, float cx, float ylo, float yhi) {
+__device__ __forceinline__ float edge_min_q(float A, float B, float C, float iC, float cx, float ylo, float yhi) {
     // min over dy in [ylo,yhi] of A cx^2 + 2 B cx dy + C dy^2
-    const float dy = fminf(fmaxf(-B * cx / C, ylo), yhi);
+    const float dy = fminf(fmaxf(-B * cx * iC, ylo), yhi);
     return A * cx * cx + 2.0f * B * cx * dy + C * dy * dy;
 }
 __device__ __forceinline__ bool tile_cannot_contribute(const CullRec& c, uint32_t tx, uint32_t ty) {
@@ -97,8 +108,8 @@ __device__ __forceinline__ bool tile_cannot_contribute(const CullRec& c, uint32_
     if (inx && iny) return false;                                              // centre inside the box: q_min = 0
     if (!(c.A > 0.f) || !(c.C > 0.f)) return false;                            // degenerate / non-finite conic: keep
     float q = 3.0e38f;
-    if (!inx) q = fminf(q, edge_min_q(c.A, c.B, c.C, x0 > 0.f ? x0 : x1, y0, y1));
-    if (!iny) q = fminf(q, edge_min_q(c.C, c.B, c.A, y0 > 0.f ? y0 : y1, x0, x1));
+    if (!inx) q = fminf(q, edge_min_q(c.A, c.B, c.C, c.iC, x0 > 0.f ? x0 : x1, y0, y1));
+    if (!iny) q = fminf(q, edge_min_q(c.C, c.B, c.A, c.iA, y0 > 0.f ? y0 : y1, x0, x1));
     const float Dx = fmaxf(fabsf(x0), fabsf(x1)), Dy = fmaxf(fabsf(y0), fabsf(y1));
     const float noise = 4e-6f * (c.A * Dx * Dx + 2.0f * fabsf(c.B) * Dx * Dy + c.C * Dy * Dy);   // ~32 ulp of the largest term
     return q > c.qthr + noise;                                                 // NaN compares false: keep

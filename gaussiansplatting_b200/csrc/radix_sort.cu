@@ -19,10 +19,14 @@
 
 namespace {
 
-constexpr int RS_THREADS = 256;
+#ifndef GS_RS_THREADS
+#define GS_RS_THREADS 256
+#endif
+#ifndef GS_RS_CTAS
+#define GS_RS_CTAS 4
+#endif
+constexpr int RS_THREADS = GS_RS_THREADS;   // >= 256: threads 0..255 also own one digit each
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_IPT = 16;
-constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 pairs per CTA
 constexpr uint32_t ST_AGG = 0x40000000u, ST_INC = 0x80000000u, ST_VAL = 0x3FFFFFFFu;
 
 struct PassList { int n; int shift[8]; uint32_t mask[8]; };
@@ -48,7 +52,7 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict_
             if (sh[p][d]) atomicAdd(&ghist[p * 256 + d], sh[p][d]);
 }
 
-// exclusive scan of one value per thread over a 256-thread CTA
+// exclusive scan of one value per thread over the CTA (only the first 256 threads carry non-zero values)
 __device__ __forceinline__ uint32_t block_excl_scan256(uint32_t x, uint32_t* s_w /*[8]*/) {
     uint32_t inc = x;
 #pragma unroll
@@ -85,9 +89,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 constexpr int RS_LOOKBACK = 8;   // predecessor status words fetched per round (independent loads)
+constexpr int RS_GROUP = 32;     // tiles per second-level group
+constexpr int RS_GLOOK = 4;      // groups inspected per round
+__device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
 
-template <typename KeyT>
+template <typename KeyT, int RS_IPT>
 struct OnesweepSmem {
+    static constexpr int RS_TILE = RS_THREADS * RS_IPT;
     alignas(128) KeyT keys[RS_TILE];          // TMA-staged input keys, then the tile-sorted keys
     alignas(128) uint32_t vals[RS_TILE];      // TMA-staged input values, then the tile-sorted values
     uint16_t wh[RS_WARPS][256];               // per-warp digit counts, then per-warp offsets within the digit
@@ -98,14 +110,18 @@ struct OnesweepSmem {
     alignas(8) uint64_t bar;
 };
 
-template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
+// RS_IPT items per thread (tile = 256 * RS_IPT pairs: 4096 for large inputs, 2048 when the whole input then fits in one
+// resident wave); BALLOT selects the peer-finding primitive of the ranking step.
+template <typename KeyT, int RS_IPT, bool BALLOT>
+__global__ void __launch_bounds__(RS_THREADS, GS_RS_CTAS) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                                  KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n_max,
                                                                  const uint32_t* __restrict__ d_n,
-                                                                 int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
-                                                                 uint32_t* counter, uint32_t* status, int aligned16) {
+                                                                 int shift, uint32_t mask, int nbits, const uint32_t* __restrict__ ghist,
+                                                                 uint32_t* counter, uint32_t* status, unsigned long long* agg2,
+                                                                 int aligned16) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    OnesweepSmem<KeyT>& S = *reinterpret_cast<OnesweepSmem<KeyT>*>(smem_raw);
+    constexpr int RS_TILE = RS_THREADS * RS_IPT;
+    OnesweepSmem<KeyT, RS_IPT>& S = *reinterpret_cast<OnesweepSmem<KeyT, RS_IPT>*>(smem_raw);
     const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;
 
     if (threadIdx.x == 0) { S.tile = atomicAdd(counter, 1u); mbar_init(&S.bar, 1); }
@@ -137,41 +153,68 @@ __global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __r
     KeyT key[RS_IPT];
 #pragma unroll
     for (int j = 0; j < RS_IPT; j++) key[j] = S.keys[wbase + 32 * j];
-    // stable ranking inside the warp's chunk: match_any groups equal digits, the highest lane bumps the warp counter
+    // Stable ranking inside the warp's chunk.  All match_any of the chunk are issued first (they depend only on the
+    // keys, so they pipeline instead of heading a 16-long dependent chain); then, row by row, every lane reads the
+    // warp's running count of its digit and the highest lane of each group stores count + group size.  Shared-memory
+    // accesses of one warp complete in order, so row j+1's reads see row j's stores without a shuffle.
     uint32_t rank[RS_IPT];
     uint16_t* wh = S.wh[warp];
     const uint32_t lt = (1u << lane) - 1u;
+    uint32_t mm[RS_IPT];
 #pragma unroll
     for (int j = 0; j < RS_IPT; j++) {
         const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
-        const uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
-        const int leader = 31 - __clz(m);
-        uint32_t prev = 0;
-        if ((int)lane == leader) { prev = wh[d]; wh[d] = (uint16_t)(prev + __popc(m)); }
-        prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+        if (BALLOT) {   // one ballot per digit bit: constant cost, wins when the digits of a warp row are mostly distinct
+            uint32_t m = 0xFFFFFFFFu;
+#pragma unroll
+            for (int b = 0; b < 8; b++) {   // bits at or above the digit width are 0 in every lane: those ballots are no-ops
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, (d >> b) & 1u);
+                m &= ((d >> b) & 1u) ? bal : ~bal;
+            }
+            mm[j] = m;
+        } else mm[j] = __match_any_sync(0xFFFFFFFFu, d);   // cost grows with the distinct values: wins on runs of equal digits
+    }
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) {
+        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+        const uint32_t m = mm[j];
+        const uint32_t prev = wh[d];
         rank[j] = prev + __popc(m & lt);
+        __syncwarp();
+        if ((m >> lane) == 1u) wh[d] = (uint16_t)(prev + __popc(m));   // highest lane of its group
         __syncwarp();
     }
     __syncthreads();
     // thread d: per-warp exclusive offsets of digit d, and the tile's count
-    const uint32_t d_own = threadIdx.x;
+    const uint32_t d_own = threadIdx.x & 255u;
+    const bool owner = threadIdx.x < 256u;
     uint32_t cnt = 0;
+    if (owner) {
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; w++) { uint32_t c = S.wh[w][d_own]; S.wh[w][d_own] = (uint16_t)cnt; cnt += c; }
-    if (tile == 0) gs::st_relaxed(&status[d_own], ST_INC | cnt);
-    else gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_AGG | cnt);
+        for (int w = 0; w < RS_WARPS; w++) { uint32_t c = S.wh[w][d_own]; S.wh[w][d_own] = (uint16_t)cnt; cnt += c; }
+        if (tile == 0) gs::st_relaxed(&status[d_own], ST_INC | cnt);
+        else gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_AGG | cnt);
+        // second level: the tile adds its count to its group's aggregate; the upper bits count arrivals, so one
+        // 64-bit load tells a reader both the sum and whether all RS_GROUP tiles of the group are in it
+        atomicAdd(&agg2[(size_t)(tile / RS_GROUP) * 256 + d_own], (1ull << 40) | (unsigned long long)cnt);
+    }
     const uint32_t binstart = block_excl_scan256(cnt, S.scan);
-    const uint32_t gstart = block_excl_scan256(ghist[d_own], S.scan);
-    // decoupled look-back, RS_LOOKBACK predecessors per round trip
+    const uint32_t gstart = block_excl_scan256(owner ? ghist[d_own] : 0u, S.scan);
+    // Two-level decoupled look-back.  With ~600 tiles in flight a flat look-back walks hundreds of predecessors that
+    // have only published their own counts (measured: the walk, not the ranking, set the pass time).  Here a tile
+    // sums the counts of the earlier tiles of ITS group (< RS_GROUP words), then steps back a whole group at a time:
+    // the inclusive prefix of the group's last tile if that is out already, else the group aggregate.
     uint32_t excl = 0;
-    if (tile > 0) {
-        int t = (int)tile - 1;
+    if (tile > 0 && owner) {
         bool done = false;
-        while (!done) {
+        const int g0 = (int)(tile / RS_GROUP);
+        int t = (int)tile - 1;
+        const int lo = g0 * RS_GROUP;
+        while (!done && t >= lo) {
             uint32_t s[RS_LOOKBACK];
 #pragma unroll
             for (int k = 0; k < RS_LOOKBACK; k++)
-                s[k] = (t - k >= 0) ? gs::ld_relaxed(&status[(size_t)(t - k) * 256 + d_own]) : ST_INC;
+                s[k] = (t - k >= lo) ? gs::ld_relaxed(&status[(size_t)(t - k) * 256 + d_own]) : ST_AGG;
             int k = 0;
 #pragma unroll
             for (; k < RS_LOOKBACK; k++) {
@@ -181,10 +224,32 @@ __global__ void __launch_bounds__(RS_THREADS, 4) onesweep_kernel(const KeyT* __r
             }
             t -= k;
         }
+        int gg = g0 - 1;
+        while (!done && gg >= 0) {
+            uint32_t s[RS_GLOOK];
+            unsigned long long a[RS_GLOOK];
+#pragma unroll
+            for (int k = 0; k < RS_GLOOK; k++) {
+                const int q = gg - k;
+                s[k] = (q >= 0) ? gs::ld_relaxed(&status[((size_t)q * RS_GROUP + RS_GROUP - 1) * 256 + d_own]) : ST_INC;
+                a[k] = (q >= 0) ? ld_relaxed64(&agg2[(size_t)q * 256 + d_own]) : 0ull;
+            }
+            int k = 0;
+#pragma unroll
+            for (; k < RS_GLOOK; k++) {
+                if (s[k] & ST_INC) { excl += s[k] & ST_VAL; done = true; break; }
+                if ((a[k] >> 40) != (unsigned long long)RS_GROUP) break;   // group not complete yet: retry from here
+                excl += (uint32_t)(a[k] & 0xFFFFFFFFFFull);
+            }
+            gg -= k;
+        }
         gs::st_relaxed(&status[(size_t)tile * 256 + d_own], ST_INC | (excl + cnt));
     }
-    S.binstart[d_own] = binstart;
-    S.gbase[d_own] = gstart + excl - binstart;
+    if (owner) { S.binstart[d_own] = binstart; S.gbase[d_own] = gstart + excl - binstart; }
+    // the keys are not kept in registers across the look-back (they would spill): fetch them again before the
+    // barrier after which the tile is permuted in place
+#pragma unroll
+    for (int j = 0; j < RS_IPT; j++) key[j] = S.keys[wbase + 32 * j];
     __syncthreads();
     // tile-local reorder: keys into their sorted slots (every thread holds its keys in registers by now)
     uint32_t slot[RS_IPT];
@@ -232,44 +297,65 @@ __global__ void depth_keys32_kernel(const float4* __restrict__ pos, float cx, fl
     keys[i] = key;
 }
 
+constexpr uint32_t RS_BIG_TILE = RS_THREADS * 16, RS_SMALL_TILE = RS_THREADS * 8;
 constexpr size_t RS_HIST_BYTES = 8 * 256 * 4;
 constexpr size_t RS_CTR_BYTES = 64;
 
+template <typename KeyT, int IPT, bool BALLOT>
+void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n, const uint32_t* d_n,
+                   const GsSortPlan& plan, const PassList& pl, uint32_t tiles, uint32_t* ghist, uint32_t* counters,
+                   uint32_t* status, unsigned long long* agg2, size_t groups, cudaStream_t st) {
+    const size_t smem = sizeof(OnesweepSmem<KeyT, IPT>);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+    }
+    const KeyT* kin = keys_in;
+    const uint32_t* vin = vals_in;
+    int dst = 0;
+    for (int p = 0; p < plan.num_passes; p++) {
+        const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
+        onesweep_kernel<KeyT, IPT, BALLOT><<<tiles, RS_THREADS, smem, st>>>(
+            kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[p], pl.mask[p], plan.bits[p], ghist + p * 256, counters + p,
+            status + (size_t)p * tiles * 256, agg2 + (size_t)p * groups * 256, aligned16);
+        kin = kbuf[dst]; vin = vbuf[dst];
+        dst ^= 1;
+    }
+}
+
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-              const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+              const uint32_t* d_n, const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st) {
     if (n == 0) return 0;
     if (plan.num_passes == 0) {
         cudaMemcpyAsync(kbuf[0], keys_in, n * sizeof(KeyT), cudaMemcpyDeviceToDevice, st);
         cudaMemcpyAsync(vbuf[0], vals_in, n * 4, cudaMemcpyDeviceToDevice, st);
         return 0;
     }
-    const uint32_t tiles = (uint32_t)((n + RS_TILE - 1) / RS_TILE);
+    // small inputs: 2048-pair tiles so that every tile is resident at once (one wave) instead of 1.x waves of 4096
+    const bool small = n <= (uint64_t)RS_SMALL_TILE * 148 * GS_RS_CTAS;
+    const uint32_t tile_elems = small ? RS_SMALL_TILE : RS_BIG_TILE;
+    const uint32_t tiles = (uint32_t)((n + tile_elems - 1) / tile_elems);
     const size_t status_bytes = (size_t)tiles * 256 * 4;
     uint32_t* ghist = (uint32_t*)scratch;
     uint32_t* counters = (uint32_t*)((char*)scratch + RS_HIST_BYTES);
     uint32_t* status = (uint32_t*)((char*)scratch + RS_HIST_BYTES + RS_CTR_BYTES);
-    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + status_bytes * plan.num_passes, st);
+    const size_t groups = (tiles + RS_GROUP - 1) / RS_GROUP;
+    const size_t agg_bytes = groups * 256 * 8;
+    unsigned long long* agg2 = (unsigned long long*)((char*)status + status_bytes * plan.num_passes);
+    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (status_bytes + agg_bytes) * plan.num_passes, st);
     PassList pl;
     pl.n = plan.num_passes;
     for (int p = 0; p < 8; p++) { pl.shift[p] = p < pl.n ? plan.shifts[p] : 0; pl.mask[p] = p < pl.n ? ((1u << plan.bits[p]) - 1u) : 0u; }
     uint64_t hb = (n + 2047) / 2048; int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
     radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pl, ghist);
-    const KeyT* kin = keys_in;
-    const uint32_t* vin = vals_in;
-    int dst = 0;
-    const size_t smem = sizeof(OnesweepSmem<KeyT>);
-    static bool attr_set = false;
-    if (!attr_set) { cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; }
-    for (int p = 0; p < plan.num_passes; p++) {
-        const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
-        onesweep_kernel<KeyT><<<tiles, RS_THREADS, smem, st>>>(kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[p], pl.mask[p],
-                                                               ghist + p * 256, counters + p, status + (size_t)p * tiles * 256,
-                                                               aligned16);
-        kin = kbuf[dst]; vin = vbuf[dst];
-        dst ^= 1;
-    }
-    return dst ^ 1;
+    const bool ballot = (hints & GS_SORT_HINT_DISTINCT) != 0;
+#define GS_RS_GO(IPT, B) launch_passes<KeyT, IPT, B>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, pl, tiles, ghist, counters, status, agg2, groups, st)
+    if (small) { if (ballot) GS_RS_GO(8, true); else GS_RS_GO(8, false); }
+    else { if (ballot) GS_RS_GO(16, true); else GS_RS_GO(16, false); }
+#undef GS_RS_GO
+    return (plan.num_passes & 1) ? 0 : 1;
 }
 
 }  // namespace
@@ -287,17 +373,17 @@ GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
 }
 
 size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
-    size_t tiles = (size_t)((n + RS_TILE - 1) / RS_TILE) + 1;
-    return RS_HIST_BYTES + RS_CTR_BYTES + tiles * 256 * 4 * 8;
+    size_t tiles = (size_t)((n + RS_SMALL_TILE - 1) / RS_SMALL_TILE) + 1;
+    return RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + (tiles / RS_GROUP + 1) * 256 * 8) * 8;
 }
 
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const GsSortPlan& plan, void* scratch, cudaStream_t st) {
-    return sort_impl<uint64_t>(keys_in, vals_in, kbuf, vbuf, n, nullptr, plan, scratch, st);
+                     const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st) {
+    return sort_impl<uint64_t>(keys_in, vals_in, kbuf, vbuf, n, nullptr, plan, hints, scratch, st);
 }
 int gs_launch_sort32(const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
-                     const uint32_t* d_n, const GsSortPlan& plan, void* scratch, cudaStream_t st) {
-    return sort_impl<uint32_t>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, scratch, st);
+                     const uint32_t* d_n, const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st) {
+    return sort_impl<uint32_t>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, hints, scratch, st);
 }
 GsSortPlan gs_sort_plan_even(int begin_bit, int end_bit) {
     GsSortPlan pl;

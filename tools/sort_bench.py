@@ -10,7 +10,9 @@ import torch
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 ctx = gs.Context(0)
 stream = torch.cuda.ExternalStream(ctx.stream, device=0)
-for logn in (20, 23, 24, 26):
+sizes = [int(x) for x in sys.argv[2].split(',')] if len(sys.argv) > 2 else (20, 23, 24, 26)
+for ballot, logn in [(b, l) for l in sizes for b in (0, 1)]:
+    gs.tune("sort_api_ballot", ballot)
     m = 1 << logn
     keys = synth.splitmix64(1234 + logn, m, 5)
     dk, dv = ctx.alloc(m * 8), ctx.alloc(m * 4)
@@ -25,5 +27,5 @@ for logn in (20, 23, 24, 26):
         S.sort(dk, dv, m)
     e1.record(stream); e1.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    print(f"u64+u32 n=2^{logn}: {ms:.3f} ms  {m / ms / 1e6:.2f} Gkeys/s  {m * 200 / ms / 1e6:.0f} GB/s algorithmic (8 passes)")
+    print(f"ballot={ballot} u64+u32 n=2^{logn}: {ms:.3f} ms  {m / ms / 1e6:.2f} Gkeys/s  {m * 200 / ms / 1e6:.0f} GB/s algorithmic (8 passes)")
     S.close(); ctx.free(dk); ctx.free(dv)
