@@ -64,7 +64,7 @@ __global__ void rebuild_keys64_kernel(const uint32_t* __restrict__ tiles, const 
 }
 
 #ifndef GS_FWD_PPT
-#define GS_FWD_PPT 1
+#define GS_FWD_PPT 2
 #endif
 constexpr int FB = 256;   // raw list entries staged per round
 
