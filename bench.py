@@ -377,6 +377,26 @@ def run_ours(args):
         out["sort"] = sort_res
         out["sort_gkeys_per_s"] = sort_res["random_u64_2^24"]["gkeys_per_s"]
 
+        # ---- BASELINE config 3: training loop with Adam + densify/prune through the C++ host layer (Engine::train,
+        # the reference's mtl_engine.mm:1047-1221 schedule time-compressed so that densify / opacity-reset events occur)
+        if world == 1 and not args.no_c3:
+            from gaussiansplatting_b200 import host
+            n3, (W3, H3) = synth.CONFIG_N["C3"], synth.CONFIG_RES["C3"]
+            o3, s3, seed3 = synth.CONFIG_ORBIT["C3"], synth.CONFIG_S0["C3"], synth.CONFIG_SEED["C3"]
+            V3, ep3 = 16, args.c3_epochs
+            poses = [synth.orbit_pose(v, V3, o3) for v in range(V3)]
+            cfg = host.TrainConfig(width=W3, height=H3, num_views=V3, epochs=ep3, fx=0.9 * W3, fy=0.9 * W3, cx=W3 / 2, cy=H3 / 2,
+                                   scene_extent=synth.scene_extent(o3), densify_from=100, densify_until=10 ** 6,
+                                   densify_interval=100, opacity_reset_interval=600, seed=0x5EED, quantize_rgba8=1)
+            res, _ = host.train(synth.make_scene(n3, seed3, s3), synth.make_scene(n3, seed3 ^ 0xA5A5, s3),
+                                np.array([p[0] for p in poses], np.float32), np.array([p[1] for p in poses], np.float32), cfg, local)
+            out["c3"] = {"iters_per_s": res["iterations"] / res["seconds"], "iterations": res["iterations"], "start_gaussians": n3,
+                         "final_gaussians": res["final_count"], "densify_events": res["densify_events"],
+                         "ms_per_densify_event": 1e3 * res["densify_seconds"] / max(res["densify_events"], 1),
+                         "opacity_resets": res["opacity_resets"], "pruned": res["pruned"], "cloned": res["cloned"], "split": res["split"],
+                         "what": "500k-Gaussian 1080p training loop (fwd, bwd, accumulateGradients, Adam, densify every 100 its, "
+                                 "opacity reset every 600) through the C++ Engine::train; wall clock incl. densify read-backs"}
+
         # ---- CPU baseline beside it: the oracle on the host cores, one full frame of the same workload
         if world == 1 and not args.no_cpu:
             from oracle import orc
@@ -405,6 +425,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=list(synth.CONFIG_N))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-c3", action="store_true", help="skip the config-3 training loop")
+    ap.add_argument("--c3-epochs", type=int, default=100, help="epochs of 16 views for the config-3 loop")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -55,7 +55,24 @@ def build(force=False, verbose=False):
         p = subprocess.run(cmd, capture_output=True, text=True)
         if p.returncode != 0:
             raise RuntimeError("link failed:\n" + p.stdout + p.stderr)
+    build_host(force or bool(jobs))
     return LIB
+
+
+HOST_LIB = os.path.join(HERE, "libgs_host.so")
+HOST_SRCS = [os.path.join(HERE, "host", f) for f in ("gs_host_capi.cpp", "engine.hpp", "gs_host.hpp", "metal_shim.hpp")]
+
+
+def build_host(force=False):
+    """libgs_host.so: the C++ host layer (the reference's class interfaces over the C ABI) + its C entry points"""
+    if not (force or _stale(HOST_LIB, HOST_SRCS + [LIB, os.path.join(HERE, "..", "include", "gs_abi.h")])):
+        return HOST_LIB
+    cmd = ["/usr/bin/g++", "-std=c++17", "-O2", "-fPIC", "-Wall", "-Wextra", "-shared", "-o", HOST_LIB, HOST_SRCS[0],
+           "-L" + HERE, "-l:" + os.path.basename(LIB), "-Wl,-rpath,$ORIGIN"]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    if p.returncode != 0:
+        raise RuntimeError("host layer build failed:\n" + p.stdout + p.stderr)
+    return HOST_LIB
 
 
 if __name__ == "__main__":

@@ -1,0 +1,70 @@
+"""ctypes binding of libgs_host.so — the C++ host layer (gaussiansplatting_b200/host/: the reference's TiledRasterizer /
+GPURadixSort / AdamOptimizer / DensityController class interfaces and the headless train loop of mtl_engine.mm) driven
+from Python.  No CPU fallback: a missing library or CUDA device raises GsError."""
+import ctypes as C
+import os
+import numpy as np
+from .capi import GsError
+from .layouts import GAUSSIAN
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgs_host.so")
+_lib = None
+
+
+class TrainConfig(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("num_views", C.c_uint32), ("epochs", C.c_uint32),
+                ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("scene_extent", C.c_float),
+                ("densify_from", C.c_uint32), ("densify_until", C.c_uint32), ("densify_interval", C.c_uint32),
+                ("opacity_reset_interval", C.c_uint32), ("seed", C.c_uint32), ("quantize_rgba8", C.c_int)]
+
+
+class TrainResult(C.Structure):
+    _fields_ = [("seconds", C.c_double), ("densify_seconds", C.c_double), ("iterations", C.c_uint64),
+                ("densify_events", C.c_uint64), ("opacity_resets", C.c_uint64), ("pruned", C.c_uint64),
+                ("cloned", C.c_uint64), ("split", C.c_uint64), ("final_count", C.c_uint32), ("adam_timestep", C.c_uint32),
+                ("last_pairs", C.c_uint64)]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GsError(f"{LIB_PATH} is missing: run `python -m gaussiansplatting_b200.build`")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.gs_host_last_error.restype = C.c_char_p
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def train(gaussians, gt_gaussians, quats, trans, cfg, device=0, want_output=False):
+    """Engine::train (mtl_engine.mm:1047-1221) on synthetic views; returns (TrainResult dict, trained Gaussians or None)"""
+    g = np.ascontiguousarray(gaussians, GAUSSIAN)
+    gt = np.ascontiguousarray(gt_gaussians, GAUSSIAN)
+    q = np.ascontiguousarray(quats, np.float32)
+    t = np.ascontiguousarray(trans, np.float32)
+    res = TrainResult()
+    cap = 1500000 + len(g)
+    out = np.zeros(cap, GAUSSIAN) if want_output else None
+    rc = lib().gs_host_train(C.c_int(device), _p(g), C.c_uint32(len(g)), _p(gt), C.c_uint32(len(gt)), _p(q), _p(t),
+                             C.byref(cfg), C.byref(res), _p(out) if want_output else None, C.c_uint32(cap))
+    if rc != 0:
+        raise GsError("gs_host_train: " + lib().gs_host_last_error().decode())
+    return res.asdict(), (out[:res.final_count] if want_output else None)
+
+
+def sort64(keys, vals, device=0):
+    """GPURadixSort64::sort through the C++ class"""
+    k = np.ascontiguousarray(keys, np.uint64)
+    v = np.ascontiguousarray(vals, np.uint32)
+    ko, vo = np.zeros_like(k), np.zeros_like(v)
+    rc = lib().gs_host_sort64(C.c_int(device), _p(k), _p(v), C.c_uint64(len(k)), _p(ko), _p(vo))
+    if rc != 0:
+        raise GsError("gs_host_sort64: " + lib().gs_host_last_error().decode())
+    return ko, vo

@@ -1,0 +1,183 @@
+// engine.hpp — headless training driver: the parts of MTLEngine (mtl_engine.hpp / mtl_engine.mm) that call the hot path.
+//
+//   loadGaussians   mtl_engine.mm:278-330   upload + construct the four operator objects
+//   trainStep       mtl_engine.mm:856-1025  uniforms from the COLMAP pose -> forward -> backward -> accumulateGradients -> Adam
+//   train           mtl_engine.mm:1047-1221 LR schedule, densify every 100 iterations in (500, 15000), opacity reset every 3000
+//   viewMatrixFromColmap / projectionFromColmap  mtl_engine.mm:637-682;  exponentialLRDecay  :1039-1045
+// Window, GLFW, the instanced-quad viewer and the logging-only loss kernels are not here (DESIGN.md "Out of scope").
+#pragma once
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "gs_host.hpp"
+
+struct TrainingView {              // TrainingImage + ColmapImage/ColmapCamera of the reference, reduced to what trainStep reads
+    float qw, qx, qy, qz;          // world -> camera rotation (COLMAP)
+    float tx, ty, tz;              // translation
+    float fx, fy, cx, cy;          // intrinsics in pixels of `texture`
+    MTL::Texture* texture;         // ground truth
+};
+
+struct TrainSchedule {             // the constants of MTLEngine::train (mtl_engine.mm:1053-1068, mtl_engine.hpp:167)
+    size_t opacityResetInterval = 3000, densifyFromIter = 500, densifyUntilIter = 15000, densityControlInterval = 100;
+    float opacityResetValue = -4.6f;
+    float positionLRInit = 0.00016f, positionLRFinal = 0.0000016f, scaleLR = 0.005f, rotationLR = 0.001f,
+          opacityLR = 0.025f, shLR = 0.0025f;
+};
+
+struct TrainStats {
+    size_t iterations = 0, densifyEvents = 0, opacityResets = 0;
+    uint64_t pruned = 0, cloned = 0, split = 0;
+    double seconds = 0, densifySeconds = 0;
+    size_t finalCount = 0;
+};
+
+class Engine {
+public:
+    explicit Engine(int deviceOrdinal = 0) {                                    // initHeadless, mtl_engine.mm:79-86
+        device = MTL::Device::CreateSystemDefaultDevice(deviceOrdinal);
+        if (!device) throw std::runtime_error("no CUDA device");
+        commandQueue = device->newCommandQueue();
+        library = device->newDefaultLibrary();
+    }
+    ~Engine() {
+        delete tiledRasterizer; delete optimizer; delete densityController;
+        if (gaussianBuffer) gaussianBuffer->release();
+        if (gaussianGradients) gaussianGradients->release();
+        if (renderTarget) renderTarget->release();
+        commandQueue->release(); delete library; device->release();
+    }
+
+    void loadGaussians(const std::vector<Gaussian>& gaussians, float extent) {   // mtl_engine.mm:278-330
+        sceneExtent = extent;
+        gaussianCount = gaussians.size();
+        const size_t capacity = std::max<size_t>(gaussianCount, 1);
+        gaussianBuffer = device->newGaussianBuffer(reinterpret_cast<const gs_gaussian*>(gaussians.data()), gaussianCount, capacity);
+        gaussianGradients = device->newGradientBuffer(capacity);
+        optimizer = new AdamOptimizer(device, library, capacity);
+        DensityController::setSceneExtent(extent);
+        densityController = new DensityController(device, library);
+        tiledRasterizer = new TiledRasterizer(device, library, (uint32_t)capacity);
+    }
+
+    static simd_float4x4 viewMatrixFromColmap(const TrainingView& v) {           // mtl_engine.mm:637-660: V = [R(q) | t]
+        const float w = v.qw, x = v.qx, y = v.qy, z = v.qz;
+        simd_float4x4 m{};
+        m.columns[0] = {1 - 2 * (y * y + z * z), 2 * (x * y + w * z), 2 * (x * z - w * y), 0};
+        m.columns[1] = {2 * (x * y - w * z), 1 - 2 * (x * x + z * z), 2 * (y * z + w * x), 0};
+        m.columns[2] = {2 * (x * z + w * y), 2 * (y * z - w * x), 1 - 2 * (x * x + y * y), 0};
+        m.columns[3] = {v.tx, v.ty, v.tz, 1};
+        return m;
+    }
+    static simd_float4x4 projectionFromColmap(const TrainingView& v, float width, float height, float nearZ = 0.1f, float farZ = 1000.0f) {
+        simd_float4x4 p{};                                                       // mtl_engine.mm:662-682
+        p.columns[0] = {2 * v.fx / width, 0, 0, 0};
+        p.columns[1] = {0, 2 * v.fy / height, 0, 0};
+        p.columns[2] = {2 * v.cx / width - 1, 2 * v.cy / height - 1, farZ / (farZ - nearZ), 1};
+        p.columns[3] = {0, 0, -(farZ * nearZ) / (farZ - nearZ), 0};
+        return p;
+    }
+    static float exponentialLRDecay(float lrInit, float lrFinal, size_t iter, size_t maxIter) {   // mtl_engine.mm:1039-1045
+        if (maxIter == 0) return lrInit;
+        const float t = std::min(1.0f, (float)iter / (float)maxIter);
+        return lrInit * std::pow(lrFinal / lrInit, t);
+    }
+
+    TiledUniforms uniformsFor(const TrainingView& v) const {                     // mtl_engine.mm:912-924
+        const float W = (float)v.texture->width(), H = (float)v.texture->height();
+        TiledUniforms u{};
+        u.viewMatrix = viewMatrixFromColmap(v);
+        u.projectionMatrix = projectionFromColmap(v, W, H);
+        for (int c = 0; c < 4; c++) {                                            // VP = P * V (column-major)
+            const float* vc = &u.viewMatrix.columns[c].x;
+            float out[4] = {0, 0, 0, 0};
+            for (int k = 0; k < 4; k++) { const float* pk = &u.projectionMatrix.columns[k].x; for (int r = 0; r < 4; r++) out[r] += pk[r] * vc[k]; }
+            u.viewProjectionMatrix.columns[c] = {out[0], out[1], out[2], out[3]};
+        }
+        u.screenSize = {W, H};
+        u.focalLength = {v.fx, v.fy};
+        const simd_float4* R = u.viewMatrix.columns;                             // cameraPos = -R^T t
+        u.cameraPos = {-(R[0].x * v.tx + R[0].y * v.ty + R[0].z * v.tz), -(R[1].x * v.tx + R[1].y * v.ty + R[1].z * v.tz),
+                       -(R[2].x * v.tx + R[2].y * v.ty + R[2].z * v.tz), 0};
+        u.numTilesX = (v.texture->width() + 15) / 16; u.numTilesY = (v.texture->height() + 15) / 16;
+        u.numGaussians = (uint32_t)gaussianCount;
+        return u;
+    }
+
+    // one training iteration on view imgIdx (the reference returns the logging loss; that kernel is off the gradient path)
+    float trainStep(size_t imgIdx, float lrPos, float lrScale, float lrRot, float lrOpacity, float lrSH) {
+        const TrainingView& v = trainingImages[imgIdx];
+        if (!renderTarget || renderTarget->width() != v.texture->width() || renderTarget->height() != v.texture->height()) {
+            if (renderTarget) renderTarget->release();
+            renderTarget = device->newTexture(v.texture->width(), v.texture->height());   // mtl_engine.mm:715-727
+        }
+        const TiledUniforms u = uniformsFor(v);
+        tiledRasterizer->forward(commandQueue, gaussianBuffer, gaussianCount, u, renderTarget);                       // :973
+        tiledRasterizer->backward(commandQueue, gaussianBuffer, gaussianGradients, gaussianCount, u, renderTarget, v.texture);   // :994
+        densityController->accumulateGradients(commandQueue, gaussianGradients, gaussianCount);                       // :998
+        optimizer->step(commandQueue, gaussianBuffer, gaussianGradients, lrPos, lrScale, lrRot, lrOpacity, lrSH);     // :1001
+        return 0.0f;
+    }
+
+    TrainStats train(size_t numEpochs, const TrainSchedule& S = TrainSchedule()) {   // mtl_engine.mm:1047-1221
+        TrainStats st;
+        const size_t totalExpectedIters = numEpochs * trainingImages.size();
+        size_t totalIterations = 0;
+        device->waitUntilCompleted();
+        const auto t0 = std::chrono::high_resolution_clock::now();
+        for (size_t epoch = 0; epoch < numEpochs; epoch++) {
+            for (size_t imgIdx = 0; imgIdx < trainingImages.size(); imgIdx++) {
+                const float lrPos = exponentialLRDecay(S.positionLRInit, S.positionLRFinal, totalIterations, totalExpectedIters);
+                trainStep(imgIdx, lrPos, S.scaleLR, S.rotationLR, S.opacityLR, S.shLR);
+                totalIterations++;
+                const bool shouldDensify = totalIterations > S.densifyFromIter && totalIterations < S.densifyUntilIter &&
+                                           totalIterations % S.densityControlInterval == 0;                   // :1112-1114
+                if (shouldDensify) {
+                    const auto d0 = std::chrono::high_resolution_clock::now();
+                    const TrainingView& v = trainingImages[imgIdx];
+                    const size_t oldCount = gaussianCount;
+                    MTL::Buffer* positionBuffer = nullptr;
+                    const DensityStats ds = densityController->apply(commandQueue, gaussianBuffer, positionBuffer, nullptr, gaussianCount,
+                                                                     totalIterations, 0.0002f, 0.005f, 0.1f * sceneExtent, v.fx,
+                                                                     (float)v.texture->width(), 2.0f * sceneExtent);   // :1142-1149
+                    optimizer->resizeIfNeeded(gaussianCount);                                                  // :1160
+                    if (gaussianCount > oldCount) optimizer->resetStateForNewGaussians(oldCount);              // :1164-1166 (note D)
+                    st.densifyEvents++; st.pruned += ds.numPruned; st.cloned += ds.numCloned; st.split += ds.numSplit;
+                    st.densifySeconds += std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - d0).count();
+                }
+                if (totalIterations % S.opacityResetInterval == 0 && totalIterations > 0 && totalIterations < S.densifyUntilIter) {
+                    MTL::gs_check(device->ctx(), gs_gaussians_clamp_opacity(gaussianBuffer->gaussians(), S.opacityResetValue), "opacity reset");   // :1179-1185
+                    optimizer->resetOpacityMomentum();                                                         // :1188
+                    optimizer->resetScaleMomentum();
+                    densityController->resetAccumulator(gaussianCount);                                        // :1191
+                    st.opacityResets++;
+                }
+            }
+        }
+        device->waitUntilCompleted();
+        st.seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t0).count();
+        st.iterations = totalIterations;
+        st.finalCount = gaussianCount;
+        return st;
+    }
+
+    std::vector<Gaussian> getGaussians() const {                                 // mtl_engine.hpp:51-53 (contents()) -> explicit download
+        std::vector<Gaussian> out(gaussianCount);
+        if (gaussianCount) gaussianBuffer->download(out.data(), gaussianCount * sizeof(Gaussian));
+        return out;
+    }
+
+    MTL::Device* device = nullptr;
+    MTL::CommandQueue* commandQueue = nullptr;
+    MTL::Library* library = nullptr;
+    MTL::Buffer* gaussianBuffer = nullptr;
+    MTL::Buffer* gaussianGradients = nullptr;
+    MTL::Texture* renderTarget = nullptr;
+    TiledRasterizer* tiledRasterizer = nullptr;
+    AdamOptimizer* optimizer = nullptr;
+    DensityController* densityController = nullptr;
+    std::vector<TrainingView> trainingImages;
+    size_t gaussianCount = 0;
+    float sceneExtent = 1.0f;
+};

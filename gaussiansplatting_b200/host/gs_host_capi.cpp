@@ -1,0 +1,111 @@
+// gs_host_capi.cpp — C entry points of libgs_host.so: the C++ host layer (gs_host.hpp / engine.hpp, the reference's class
+// interfaces over libgs_b200.so) driven from bench.py and the tests through ctypes.
+#include "engine.hpp"
+#include <cstdio>
+
+extern "C" {
+
+typedef struct {
+    uint32_t width, height, num_views, epochs;
+    float fx, fy, cx, cy, scene_extent;
+    uint32_t densify_from, densify_until, densify_interval, opacity_reset_interval;   // 0 = the reference's constants
+    uint32_t seed;
+    int quantize_rgba8;       // 1 = backward reads the 8-bit-quantised render (what the reference's RGBA8 target does)
+} gs_host_train_config;
+
+typedef struct {
+    double seconds, densify_seconds;
+    uint64_t iterations, densify_events, opacity_resets, pruned, cloned, split;
+    uint32_t final_count, adam_timestep;
+    uint64_t last_pairs;
+} gs_host_train_result;
+
+static char g_err[512];
+const char* gs_host_last_error(void) { return g_err; }
+
+// Trains `gaussians` on num_views views (poses: quats[4*v] wxyz + trans[3*v]); the ground truth of view v is the render
+// of `gt_gaussians` from the same pose, produced on the device at load time (all datasets are synthetic).  The trained
+// Gaussians are written to out (capacity out_cap) when out != NULL.
+int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs_gaussian* gt_gaussians, uint32_t n_gt,
+                  const float* quats, const float* trans, const gs_host_train_config* cfg, gs_host_train_result* res,
+                  gs_gaussian* out, uint32_t out_cap) {
+    try {
+        Engine eng(device);
+        std::vector<Gaussian> init(n);
+        std::memcpy(init.data(), gaussians, (size_t)n * sizeof(Gaussian));
+        // ground truth: loadTrainingData (mtl_engine.mm:630-634) replaced by device renders of a second scene
+        {
+            std::vector<Gaussian> gtv(n_gt);
+            std::memcpy(gtv.data(), gt_gaussians, (size_t)n_gt * sizeof(Gaussian));
+            Engine* e = &eng;
+            e->loadGaussians(gtv, cfg->scene_extent);
+            for (uint32_t v = 0; v < cfg->num_views; v++) {
+                TrainingView tv{quats[4 * v], quats[4 * v + 1], quats[4 * v + 2], quats[4 * v + 3], trans[3 * v], trans[3 * v + 1],
+                                trans[3 * v + 2], cfg->fx, cfg->fy, cfg->cx, cfg->cy, e->device->newTexture(cfg->width, cfg->height)};
+                const TiledUniforms u = e->uniformsFor(tv);
+                e->tiledRasterizer->forward(e->commandQueue, e->gaussianBuffer, e->gaussianCount, u, tv.texture);
+                e->trainingImages.push_back(tv);
+            }
+            e->device->waitUntilCompleted();
+            // swap in the model to train (fresh operator objects, as loadGaussians constructs them)
+            delete e->tiledRasterizer; delete e->optimizer; delete e->densityController;
+            e->gaussianBuffer->release(); e->gaussianGradients->release();
+            e->gaussianBuffer = nullptr; e->gaussianGradients = nullptr;
+            e->tiledRasterizer = nullptr; e->optimizer = nullptr; e->densityController = nullptr;
+            e->loadGaussians(init, cfg->scene_extent);
+        }
+        eng.tiledRasterizer->setQuantizeRenderedRGBA8(cfg->quantize_rgba8 != 0);
+        eng.densityController->setSeed(cfg->seed);
+        TrainSchedule S;
+        if (cfg->densify_from) S.densifyFromIter = cfg->densify_from;
+        if (cfg->densify_until) S.densifyUntilIter = cfg->densify_until;
+        if (cfg->densify_interval) S.densityControlInterval = cfg->densify_interval;
+        if (cfg->opacity_reset_interval) S.opacityResetInterval = cfg->opacity_reset_interval;
+        const TrainStats st = eng.train(cfg->epochs, S);
+        if (res) {
+            res->seconds = st.seconds; res->densify_seconds = st.densifySeconds; res->iterations = st.iterations;
+            res->densify_events = st.densifyEvents; res->opacity_resets = st.opacityResets;
+            res->pruned = st.pruned; res->cloned = st.cloned; res->split = st.split;
+            res->final_count = (uint32_t)st.finalCount; res->adam_timestep = eng.optimizer->getTimestep();
+            res->last_pairs = eng.tiledRasterizer->pairCount();
+        }
+        if (out) {
+            const std::vector<Gaussian> g = eng.getGaussians();
+            std::memcpy(out, g.data(), std::min<size_t>(g.size(), out_cap) * sizeof(Gaussian));
+        }
+        for (auto& tv : eng.trainingImages) tv.texture->release();
+        return 0;
+    } catch (const std::exception& e) {
+        std::snprintf(g_err, sizeof(g_err), "%s", e.what());
+        return -1;
+    }
+}
+
+// GPURadixSort64 through the C++ class (host arrays in, host arrays out) — used by the tests of the host layer
+int gs_host_sort64(int device, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint64_t* keys_out, uint32_t* vals_out) {
+    try {
+        MTL::Device* dev = MTL::Device::CreateSystemDefaultDevice(device);
+        if (!dev) throw std::runtime_error("no CUDA device");
+        {
+            MTL::CommandQueue* q = dev->newCommandQueue();
+            MTL::Library lib;
+            MTL::Buffer* k = dev->newBuffer(n * 8 + 8); MTL::Buffer* v = dev->newBuffer(n * 4 + 4);
+            if (n) { k->upload(keys, n * 8); v->upload(vals, n * 4); }
+            GPURadixSort64 sorter(dev, &lib, n ? n : 1);
+            sorter.sort(q, k, v, n);
+            dev->waitUntilCompleted();
+            if (n) {
+                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), keys_out, sorter.getSortedKeys(), n * 8), "download");
+                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), vals_out, sorter.getSortedValues(), n * 4), "download");
+            }
+            k->release(); v->release(); q->release();
+        }
+        dev->release();
+        return 0;
+    } catch (const std::exception& e) {
+        std::snprintf(g_err, sizeof(g_err), "%s", e.what());
+        return -1;
+    }
+}
+
+}  // extern "C"

@@ -85,3 +85,16 @@ def test_product_package_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "from oracle" not in text and "import oracle" not in text and "liboracle" not in text, f
+
+
+def test_host_layer_builds_and_exports(gs):
+    """libgs_host.so (the reference's C++ class interfaces over the C ABI + the headless train loop) is built in-tree,
+    loads, and its headers compile on their own"""
+    from gaussiansplatting_b200 import host, build
+    build.build_host()
+    L = host.lib()
+    for name in ("gs_host_train", "gs_host_sort64", "gs_host_last_error"):
+        assert hasattr(L, name), name
+    hdr = os.path.join(ROOT, "gaussiansplatting_b200", "host", "engine.hpp")
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-fsyntax-only", "-x", "c++", "-"],
+                   input=f'#include "{hdr}"\nint main() {{ return 0; }}\n', text=True, check=True)
