@@ -270,7 +270,7 @@ int gs_grads_destroy(gs_grads* g) {
 int gs_grads_zero(gs_grads* g, uint32_t n) {
     gs_ctx* c = g->c; GS_SETDEV(c);
     GS_TRY(grads_reserve(g, n));
-    GS_CUDA(c, cudaMemsetAsync(g->g, 0, (size_t)g->stride * 16 * sizeof(float), c->stream));
+    if (n) GS_CUDA(c, cudaMemset2DAsync(g->g, (size_t)g->stride * sizeof(float), 0, (size_t)n * sizeof(float), 16, c->stream));   // the live rows only
     return GS_OK;
 }
 int gs_grads_upload(gs_grads* g, const gs_gradients* host, uint32_t n) {
@@ -1015,7 +1015,7 @@ int gs_dens_create(gs_ctx* c, uint32_t max_gaussians, gs_dens** out) {
     if (!d) return GS_ERR_OOM;
     d->c = c; d->max_gaussians = max_gaussians;
     int r = dalloc(c, &d->small, 8);
-    if (r == GS_OK) r = dens_reserve(d, 1024);
+    if (r == GS_OK) r = dens_reserve(d, std::min<uint32_t>(max_gaussians, 4u << 20));
     if (r != GS_OK) { gs_dens_destroy(d); return r; }
     *out = d;
     return GS_OK;
@@ -1062,7 +1062,8 @@ int gs_dens_apply(gs_dens* d, gs_gaussians* g, uint32_t iteration, float focal, 
     if (bound > d->spare_cap) {
         GS_CUDA(c, cudaStreamSynchronize(st));
         cudaFree(d->spare); d->spare = nullptr;
-        d->spare_cap = ((uint32_t)std::min<uint64_t>(bound * 5 / 4, 0xFFFFFF00ull) + 63u) & ~63u;
+        // room for the cap from the start (the model can never exceed max(n, max_gaussians)): no reallocation at later events
+        d->spare_cap = ((uint32_t)std::min<uint64_t>(std::max<uint64_t>(bound, d->max_gaussians), 0xFFFFFF00ull) + 63u) & ~63u;
         GS_TRY(dalloc(c, &d->spare, (size_t)d->spare_cap * 23));
     }
     gs_launch_densify_mark(g->view(), d->accum, d->count, a, d->markers, d->small, st);

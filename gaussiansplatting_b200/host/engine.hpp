@@ -35,6 +35,7 @@ struct TrainStats {
 
 class Engine {
 public:
+    static constexpr size_t kOperatorCapacity = 2000000;
     explicit Engine(int deviceOrdinal = 0) {                                    // initHeadless, mtl_engine.mm:79-86
         device = MTL::Device::CreateSystemDefaultDevice(deviceOrdinal);
         if (!device) throw std::runtime_error("no CUDA device");
@@ -52,7 +53,9 @@ public:
     void loadGaussians(const std::vector<Gaussian>& gaussians, float extent) {   // mtl_engine.mm:278-330
         sceneExtent = extent;
         gaussianCount = gaussians.size();
-        const size_t capacity = std::max<size_t>(gaussianCount, 1);
+        // the reference constructs every operator with capacity 2,000,000 (mtl_engine.mm:317-327) so that densify never
+        // reallocates them; same here (the density controller caps the model at 1,500,000)
+        const size_t capacity = std::max<size_t>(gaussianCount, kOperatorCapacity);
         gaussianBuffer = device->newGaussianBuffer(reinterpret_cast<const gs_gaussian*>(gaussians.data()), gaussianCount, capacity);
         gaussianGradients = device->newGradientBuffer(capacity);
         optimizer = new AdamOptimizer(device, library, capacity);
