@@ -194,6 +194,18 @@ class Image:
     def download_rgba8_ptr(self, host_ptr):
         self.ctx.check(lib().gs_image_download_rgba8(self.h, C.c_void_p(host_ptr)))
 
+    def upload_rgba8_async(self, host_ptr):
+        """H2D of RGBA8 pixels from PINNED host memory on the context's copy-in stream; compute calls that use the image
+        wait for it on the device"""
+        self.ctx.check(lib().gs_image_upload_rgba8_async(self.h, C.c_void_p(host_ptr)))
+
+    def download_rgba8_async(self, host_ptr):
+        """D2H of the image as RGBA8 into PINNED host memory on the copy-out stream; wait() before reading the buffer"""
+        self.ctx.check(lib().gs_image_download_rgba8_async(self.h, C.c_void_p(host_ptr)))
+
+    def wait(self):
+        self.ctx.check(lib().gs_image_wait(self.h))
+
     @property
     def devptr(self):
         return lib().gs_image_devptr(self.h)

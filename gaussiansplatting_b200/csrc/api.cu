@@ -17,6 +17,7 @@ struct gs_ctx {
     bool own_stream = false;
     std::string err;
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
+    cudaStream_t xfer_in = nullptr, xfer_out = nullptr;   // copy streams of the *_async image transfers (created on first use)
 };
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
@@ -90,12 +91,20 @@ int gs_ctx_destroy(gs_ctx* c) {
     if (!c) return GS_OK;
     GS_SETDEV(c);
     cudaStreamSynchronize(c->stream);
+    if (c->xfer_in) { cudaStreamSynchronize(c->xfer_in); cudaStreamDestroy(c->xfer_in); }
+    if (c->xfer_out) { cudaStreamSynchronize(c->xfer_out); cudaStreamDestroy(c->xfer_out); }
     if (c->own_stream) cudaStreamDestroy(c->stream);
     cudaFreeHost(c->h_pinned);
     delete c;
     return GS_OK;
 }
-int gs_ctx_sync(gs_ctx* c) { GS_SETDEV(c); GS_CUDA(c, cudaStreamSynchronize(c->stream)); return GS_OK; }
+int gs_ctx_sync(gs_ctx* c) {
+    GS_SETDEV(c);
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->xfer_in) GS_CUDA(c, cudaStreamSynchronize(c->xfer_in));
+    if (c->xfer_out) GS_CUDA(c, cudaStreamSynchronize(c->xfer_out));
+    return GS_OK;
+}
 const char* gs_last_error(gs_ctx* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
 void* gs_ctx_stream(gs_ctx* c) { return (void*)c->stream; }
 
@@ -226,7 +235,36 @@ struct gs_image {
     uint32_t w = 0, h = 0;
     float4* px = nullptr;
     uint32_t* rgba8 = nullptr;  // staging for 8-bit transfers
+    // *_async transfers run on the ctx's copy streams: ev_use = last compute-stream use of the image, ev_xfer = end of the
+    // transfer in flight; pending: 0 none, 1 upload (readers and writers on the compute stream wait), 2 download (writers wait)
+    cudaEvent_t ev_use = nullptr, ev_xfer = nullptr;
+    int pending = 0;
 };
+static int image_before_read(gs_image* im, cudaStream_t st) {
+    if (im->pending == 1) { GS_CUDA(im->c, cudaStreamWaitEvent(st, im->ev_xfer, 0)); im->pending = 0; }
+    return GS_OK;
+}
+static int image_before_write(gs_image* im, cudaStream_t st) {
+    if (im->pending) { GS_CUDA(im->c, cudaStreamWaitEvent(st, im->ev_xfer, 0)); im->pending = 0; }
+    return GS_OK;
+}
+static int image_after_use(gs_image* im, cudaStream_t st) {
+    if (im->ev_use) GS_CUDA(im->c, cudaEventRecord(im->ev_use, st));
+    return GS_OK;
+}
+// first async call on an image: create its events; everything enqueued on the compute stream so far counts as a use
+static int image_async_begin(gs_image* im, cudaStream_t* xfer) {
+    gs_ctx* c = im->c;
+    if (!*xfer) GS_CUDA(c, cudaStreamCreateWithFlags(xfer, cudaStreamNonBlocking));
+    if (!im->ev_use) {
+        GS_CUDA(c, cudaEventCreateWithFlags(&im->ev_use, cudaEventDisableTiming));
+        GS_CUDA(c, cudaEventCreateWithFlags(&im->ev_xfer, cudaEventDisableTiming));
+        GS_CUDA(c, cudaEventRecord(im->ev_use, c->stream));
+    }
+    GS_CUDA(c, cudaStreamWaitEvent(*xfer, im->ev_use, 0));
+    if (im->pending) GS_CUDA(c, cudaStreamWaitEvent(*xfer, im->ev_xfer, 0));   // one staging buffer per image
+    return GS_OK;
+}
 
 static int grads_reserve(gs_grads* g, uint32_t n) {   // contents are NOT preserved on growth
     if (n <= g->cap) return GS_OK;
@@ -317,17 +355,21 @@ int gs_image_destroy(gs_image* im) {
     if (!im) return GS_OK;
     cudaSetDevice(im->c->device);
     cudaStreamSynchronize(im->c->stream);
+    if (im->pending) cudaEventSynchronize(im->ev_xfer);
+    if (im->ev_use) { cudaEventDestroy(im->ev_use); cudaEventDestroy(im->ev_xfer); }
     cudaFree(im->px); cudaFree(im->rgba8);
     delete im;
     return GS_OK;
 }
 int gs_image_upload_rgba32f(gs_image* im, const float* host) {
     gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_TRY(image_before_write(im, c->stream));
     GS_CUDA(c, cudaMemcpyAsync(im->px, host, (size_t)im->w * im->h * 16, cudaMemcpyHostToDevice, c->stream));
     return GS_OK;
 }
 int gs_image_upload_rgba8(gs_image* im, const uint8_t* host) {
     gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_TRY(image_before_write(im, c->stream));
     GS_CUDA(c, cudaMemcpyAsync(im->rgba8, host, (size_t)im->w * im->h * 4, cudaMemcpyHostToDevice, c->stream));
     gs_launch_rgba8_to_rgba32f(im->rgba8, im->w * im->h, im->px, c->stream);
     GS_LAUNCH_CHECK(c);
@@ -335,16 +377,50 @@ int gs_image_upload_rgba8(gs_image* im, const uint8_t* host) {
 }
 int gs_image_download_rgba32f(gs_image* im, float* host) {
     gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_TRY(image_before_read(im, c->stream));
     GS_CUDA(c, cudaMemcpyAsync(host, im->px, (size_t)im->w * im->h * 16, cudaMemcpyDeviceToHost, c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     return GS_OK;
 }
 int gs_image_download_rgba8(gs_image* im, uint8_t* host) {
     gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_TRY(image_before_write(im, c->stream));      // the 8-bit staging buffer is shared with a transfer in flight
     gs_launch_rgba32f_to_rgba8(im->px, im->w * im->h, im->rgba8, c->stream);
     GS_LAUNCH_CHECK(c);
     GS_CUDA(c, cudaMemcpyAsync(host, im->rgba8, (size_t)im->w * im->h * 4, cudaMemcpyDeviceToHost, c->stream));
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return GS_OK;
+}
+// Asynchronous RGBA8 transfers on the context's copy streams, ordered against the compute stream by events, so that the
+// next view's ground truth and the last render cross PCIe while the blend kernels run.  `host` must be pinned and stay
+// valid until gs_image_wait().  A compute call that touches the image waits (on the device) for a pending upload; a
+// compute call that overwrites it also waits for a pending download.
+int gs_image_upload_rgba8_async(gs_image* im, const uint8_t* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_ARG(c, host, "null host buffer");
+    GS_TRY(image_async_begin(im, &c->xfer_in));
+    GS_CUDA(c, cudaMemcpyAsync(im->rgba8, host, (size_t)im->w * im->h * 4, cudaMemcpyHostToDevice, c->xfer_in));
+    gs_launch_rgba8_to_rgba32f(im->rgba8, im->w * im->h, im->px, c->xfer_in);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaEventRecord(im->ev_xfer, c->xfer_in));
+    im->pending = 1;
+    return GS_OK;
+}
+int gs_image_download_rgba8_async(gs_image* im, uint8_t* host) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    GS_ARG(c, host, "null host buffer");
+    GS_TRY(image_async_begin(im, &c->xfer_out));
+    gs_launch_rgba32f_to_rgba8(im->px, im->w * im->h, im->rgba8, c->xfer_out);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaMemcpyAsync(host, im->rgba8, (size_t)im->w * im->h * 4, cudaMemcpyDeviceToHost, c->xfer_out));
+    GS_CUDA(c, cudaEventRecord(im->ev_xfer, c->xfer_out));
+    im->pending = 2;
+    return GS_OK;
+}
+// block the host until the image's transfer in flight (if any) has completed
+int gs_image_wait(gs_image* im) {
+    gs_ctx* c = im->c; GS_SETDEV(c);
+    if (im->pending) { GS_CUDA(c, cudaEventSynchronize(im->ev_xfer)); im->pending = 0; }
     return GS_OK;
 }
 void* gs_image_devptr(gs_image* im) { return im->px; }
@@ -595,6 +671,7 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     GS_ARG(c, g && u && out, "null handle");
     cudaStream_t st = c->stream;
     const uint32_t n = g->n, W = out->w, H = out->h;
+    GS_TRY(image_before_write(out, st));
     GS_TRY(rast_reserve_gaussians(r, n));
     GS_TRY(rast_reserve_image(r, W, H));
     r->n = n; r->pairs = 0; r->passes = 0; r->mode = g_sort_mode;
@@ -606,7 +683,8 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
                          u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
     r->mark(1);
-    return r->mode == 1 ? forward_pairs64(r, g, u, out) : forward_hoisted(r, g, u, out);
+    GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : forward_hoisted(r, g, u, out));
+    return image_after_use(out, st);
 }
 
 int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniforms* u, gs_image* rendered, gs_image* gt, int flags) {
@@ -616,6 +694,8 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     GS_ARG(c, g->n == r->n, "gaussian count differs from the last forward");
     cudaStream_t st = c->stream;
     const uint32_t n = r->n;
+    GS_TRY(image_before_read(rendered, st));
+    GS_TRY(image_before_read(gt, st));
     r->mark(8);
     if (!(flags & GS_BWD_ACCUMULATE)) GS_TRY(gs_grads_zero(gr, n));   // :687
     else GS_ARG(c, n <= gr->cap, "gradient buffer too small to accumulate into");
@@ -628,6 +708,8 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
                                   gr->view(), gr->stat_mode, st);
     r->mark(10);
     GS_LAUNCH_CHECK(c);
+    GS_TRY(image_after_use(rendered, st));
+    GS_TRY(image_after_use(gt, st));
     return GS_OK;
 }
 

@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
     __shared__ float s_acc[NW][BB * 9];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
+    __shared__ uint32_t s_mask[NW][BB / 32];           // per warp region: which staged entries can reach it at all
     const uint32_t tile = blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
@@ -149,6 +150,21 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
         }
         for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
         __syncthreads();
+        // ---- per-region footprint masks: lane tests one staged entry against every warp's pixel rectangle
+        for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
+            const uint32_t sl = s0 + lane;
+            const bool valid = sl < total;
+            const gs::CullRec cr = gs::cull_rec(s_r0[valid ? sl : 0u], s_r1[valid ? sl : 0u]);
+#pragma unroll
+            for (int w = 0; w < NW; w++) {
+                uint32_t rx, ry; float ex, ey;
+                gs::warp_region<PPT>((uint32_t)w, rx, ry, ex, ey);
+                const bool keep = valid && !gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey);
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+                if (lane == 0) s_mask[w][s0 >> 5] = m;
+            }
+        }
+        __syncthreads();
         if (wmax > lo) {
             // staged list indices ascend: entries at or beyond this warp's extent are of no interest to it
             uint32_t kend = total;
@@ -157,7 +173,13 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
                 while (a < b) { const uint32_t m = (a + b) >> 1; if (__float_as_uint(s_r2[m].y) < wmax) a = m + 1; else b = m; }
                 kend = a;
             }
-            for (int k = (int)kend - 1; k >= 0; k--) {                // :473 back to front
+            for (int wd = ((int)kend - 1) >> 5; wd >= 0; wd--) {      // :473 back to front, reachable entries only
+              uint32_t mk = s_mask[warp][wd];
+              if ((uint32_t)wd == (kend >> 5)) mk &= (1u << (kend & 31u)) - 1u;
+              while (mk) {
+                const int kb = 31 - __clz(mk);
+                mk &= ~(1u << kb);
+                const int k = wd * 32 + kb;
                 const float4 a = s_r0[k];
                 const float4 b = s_r1[k];
                 const float4 c2 = s_r2[k];
@@ -200,6 +222,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
                 for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
                 if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
                 if (lane == 1u) my_acc[k * 9 + 8] = v9;
+              }
             }
         }
         __syncthreads();

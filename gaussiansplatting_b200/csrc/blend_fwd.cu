@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
     __shared__ float s_b[FB];
     __shared__ uint32_t s_idx[FB];
     __shared__ uint32_t s_w[NW];
+    __shared__ uint32_t s_mask[NW][FB / 32];          // per warp region: which staged entries can reach it at all
     __shared__ uint32_t s_degen;
     const uint32_t tile = blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
@@ -130,28 +131,49 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
             slot++;
         }
         __syncthreads();
-        if (ndone < PPT) {
-            for (uint32_t k = 0; k < total; k++) {                   // :334
-                const float4 a = s_r0[k];
-                const float4 b = s_r1[k];
+        // ---- per-region footprint masks: lane tests one staged entry against every warp's pixel rectangle
+        for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
+            const uint32_t sl = s0 + lane;
+            const bool valid = sl < total;
+            const gs::CullRec cr = gs::cull_rec(s_r0[valid ? sl : 0u], s_r1[valid ? sl : 0u]);
 #pragma unroll
-                for (int j = 0; j < PPT; j++) {
-                    if (done[j]) continue;
-                    const float dx = gs::fsub(pxf[j], a.x), dy = gs::fsub(pyf[j], a.y);   // :347
-                    const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
-                    if (!(power <= 0.0f) || power < -4.5f) continue;  // :359
-                    const float G = gs::exp_blend(power);             // :362
-                    const float alpha = fminf(gs::fmul(b.y, G), GS_ALPHA_MAX);   // :363
-                    if (alpha < GS_ALPHA_MIN) continue;               // :366
-                    const float w = gs::fmul(alpha, T[j]);            // :369
-                    Cr[j] = gs::ffma(b.z, w, Cr[j]); Cg[j] = gs::ffma(b.w, w, Cg[j]); Cb[j] = gs::ffma(s_b[k], w, Cb[j]);
-                    Tp[j] = T[j];
-                    if (COUNT) nC++;
-                    T[j] = gs::fmul(T[j], gs::fsub(1.0f, alpha));     // :370
-                    last[j] = range.x + s_idx[k];                     // :372
-                    if (!(T[j] > GS_T_EPS)) { done[j] = true; ndone++; }   // :334 loop condition
+            for (int w = 0; w < NW; w++) {
+                uint32_t rx, ry; float ex, ey;
+                gs::warp_region<PPT>((uint32_t)w, rx, ry, ex, ey);
+                const bool keep = valid && !gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey);
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+                if (lane == 0) s_mask[w][s0 >> 5] = m;
+            }
+        }
+        __syncthreads();
+        if (ndone < PPT) {
+            const uint32_t nwords = (total + 31u) >> 5;
+            for (uint32_t wd = 0; wd < nwords; wd++) {               // :334, entries that can reach this warp's pixels only
+                uint32_t m = s_mask[warp][wd];
+                while (m) {
+                    const uint32_t k = wd * 32u + (uint32_t)__ffs(m) - 1u;
+                    m &= m - 1u;
+                    const float4 a = s_r0[k];
+                    const float4 b = s_r1[k];
+#pragma unroll
+                    for (int j = 0; j < PPT; j++) {
+                        if (done[j]) continue;
+                        const float dx = gs::fsub(pxf[j], a.x), dy = gs::fsub(pyf[j], a.y);   // :347
+                        const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
+                        if (!(power <= 0.0f) || power < -4.5f) continue;  // :359
+                        const float G = gs::exp_blend(power);             // :362
+                        const float alpha = fminf(gs::fmul(b.y, G), GS_ALPHA_MAX);   // :363
+                        if (alpha < GS_ALPHA_MIN) continue;               // :366
+                        const float w = gs::fmul(alpha, T[j]);            // :369
+                        Cr[j] = gs::ffma(b.z, w, Cr[j]); Cg[j] = gs::ffma(b.w, w, Cg[j]); Cb[j] = gs::ffma(s_b[k], w, Cb[j]);
+                        Tp[j] = T[j];
+                        if (COUNT) nC++;
+                        T[j] = gs::fmul(T[j], gs::fsub(1.0f, alpha));     // :370
+                        last[j] = range.x + s_idx[k];                     // :372
+                        if (!(T[j] > GS_T_EPS)) { done[j] = true; ndone++; }   // :334 loop condition
+                    }
+                    if (ndone == PPT) { wd = nwords; break; }
                 }
-                if (ndone == PPT) break;
             }
         }
     }

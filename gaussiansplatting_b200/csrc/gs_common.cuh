@@ -79,6 +79,44 @@ __device__ __forceinline__ void tile_pixel(uint32_t warp, uint32_t lane, int j, 
     else { x = (lane & 7u) * 2u + ((uint32_t)j & 1u); y = warp * 8u + (lane >> 3) * 2u + ((uint32_t)j >> 1); }
 }
 
+// ---- conservative footprint test (pairs.cu explains it): can a splat contribute to ANY pixel centre of the box whose first
+// pixel centre is (px0,py0) and which extends ex, ey further?  Used per (tile, Gaussian) at emit and per (warp region,
+// staged entry) inside the blend kernels.
+struct CullRec { float sx, sy, A, B, C, qthr, iA, iC; };
+__device__ __forceinline__ CullRec cull_rec(const float4 r0, const float4 r1) {
+    CullRec c;
+    c.sx = r0.x; c.sy = r0.y; c.A = -2.0f * r0.z; c.B = -r0.w; c.C = -2.0f * r1.x;
+    c.qthr = fminf(9.0f, 2.0f * __logf(255.0f * r1.y)) + 2e-3f;
+    if (!(c.qthr == c.qthr)) c.qthr = 9.002f;
+    c.iA = 1.0f / c.A; c.iC = 1.0f / c.C;       // only steer where on an edge q is sampled; the margin absorbs their rounding
+    return c;
+}
+__device__ __forceinline__ float edge_min_q(float A, float B, float C, float iC, float cx, float ylo, float yhi) {
+    // min over dy in [ylo,yhi] of A cx^2 + 2 B cx dy + C dy^2
+    const float dy = fminf(fmaxf(-B * cx * iC, ylo), yhi);
+    return A * cx * cx + 2.0f * B * cx * dy + C * dy * dy;
+}
+__device__ __forceinline__ bool box_cannot_contribute(const CullRec& c, float px0, float py0, float ex, float ey) {
+    const float x0 = px0 - c.sx, x1 = x0 + ex;                                 // dx range of the pixel centres
+    const float y0 = py0 - c.sy, y1 = y0 + ey;
+    const bool inx = x0 <= 0.f && x1 >= 0.f, iny = y0 <= 0.f && y1 >= 0.f;
+    if (inx && iny) return false;                                              // centre inside the box: q_min = 0
+    if (!(c.A > 0.f) || !(c.C > 0.f)) return false;                            // degenerate / non-finite conic: keep
+    float q = 3.0e38f;
+    if (!inx) q = fminf(q, edge_min_q(c.A, c.B, c.C, c.iC, x0 > 0.f ? x0 : x1, y0, y1));
+    if (!iny) q = fminf(q, edge_min_q(c.C, c.B, c.A, c.iA, y0 > 0.f ? y0 : y1, x0, x1));
+    const float Dx = fmaxf(fabsf(x0), fabsf(x1)), Dy = fmaxf(fabsf(y0), fabsf(y1));
+    const float noise = 4e-6f * (c.A * Dx * Dx + 2.0f * fabsf(c.B) * Dx * Dy + c.C * Dy * Dy);   // ~32 ulp of the largest term
+    return q > c.qthr + noise;                                                 // NaN compares false: keep
+}
+// the pixel rectangle (within the tile) that warp `warp` owns under tile_pixel<PPT>: first pixel and extent
+template <int PPT>
+__device__ __forceinline__ void warp_region(uint32_t warp, uint32_t& rx, uint32_t& ry, float& ex, float& ey) {
+    if (PPT == 1) { rx = (warp & 1u) * 8u; ry = (warp >> 1) * 4u; ex = 7.f; ey = 3.f; }
+    else if (PPT == 2) { rx = (warp & 1u) * 8u; ry = (warp >> 1) * 8u; ex = 7.f; ey = 7.f; }
+    else { rx = 0u; ry = warp * 8u; ex = 15.f; ey = 7.f; }
+}
+
 // exclusive scan of one small count per thread over a CTA of NW warps; returns the exclusive prefix, *total = CTA sum.
 // s_w: NW words of shared scratch; contains one __syncthreads().
 template <int NW>

@@ -87,32 +87,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, 
 // exceeds qthr by more than the rounding noise of the pinned power arithmetic can never contribute: it stays in the
 // list (so lists, ranges and lastContribIdx remain those of the reference) but is emitted with bit 31 of its value
 // set, and the blend kernels drop it while staging.
-struct CullRec { float sx, sy, A, B, C, qthr, iA, iC; };
-__device__ __forceinline__ CullRec cull_rec(const float4 r0, const float4 r1) {
-    CullRec c;
-    c.sx = r0.x; c.sy = r0.y; c.A = -2.0f * r0.z; c.B = -r0.w; c.C = -2.0f * r1.x;
-    c.qthr = fminf(9.0f, 2.0f * __logf(255.0f * r1.y)) + 2e-3f;
-    if (!(c.qthr == c.qthr)) c.qthr = 9.002f;
-    c.iA = 1.0f / c.A; c.iC = 1.0f / c.C;       // only steer where on an edge q is sampled; the margin absorbs their rounding
-    return c;
-}
-__device__ __forceinline__ float edge_min_q(float A, float B, float C, float iC, float cx, float ylo, float yhi) {
-    // min over dy in [ylo,yhi] of A cx^2 + 2 B cx dy + C dy^2
-    const float dy = fminf(fmaxf(-B * cx * iC, ylo), yhi);
-    return A * cx * cx + 2.0f * B * cx * dy + C * dy * dy;
-}
-__device__ __forceinline__ bool tile_cannot_contribute(const CullRec& c, uint32_t tx, uint32_t ty) {
-    const float x0 = (float)(tx * GS_TILE) + 0.5f - c.sx, x1 = x0 + 15.0f;      // dx range of the pixel centres
-    const float y0 = (float)(ty * GS_TILE) + 0.5f - c.sy, y1 = y0 + 15.0f;
-    const bool inx = x0 <= 0.f && x1 >= 0.f, iny = y0 <= 0.f && y1 >= 0.f;
-    if (inx && iny) return false;                                              // centre inside the box: q_min = 0
-    if (!(c.A > 0.f) || !(c.C > 0.f)) return false;                            // degenerate / non-finite conic: keep
-    float q = 3.0e38f;
-    if (!inx) q = fminf(q, edge_min_q(c.A, c.B, c.C, c.iC, x0 > 0.f ? x0 : x1, y0, y1));
-    if (!iny) q = fminf(q, edge_min_q(c.C, c.B, c.A, c.iA, y0 > 0.f ? y0 : y1, x0, x1));
-    const float Dx = fmaxf(fabsf(x0), fabsf(x1)), Dy = fmaxf(fabsf(y0), fabsf(y1));
-    const float noise = 4e-6f * (c.A * Dx * Dx + 2.0f * fabsf(c.B) * Dx * Dy + c.C * Dy * Dy);   // ~32 ulp of the largest term
-    return q > c.qthr + noise;                                                 // NaN compares false: keep
+// (CullRec / cull_rec / box_cannot_contribute live in gs_common.cuh: the blend kernels reuse the test per warp region)
+__device__ __forceinline__ bool tile_cannot_contribute(const gs::CullRec& c, uint32_t tx, uint32_t ty) {
+    return gs::box_cannot_contribute(c, (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
 }
 
 // K3.  One block = 256 consecutive list positions (Gaussian order, or depth order through `perm`); the block's pairs
@@ -125,7 +102,7 @@ __global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, const ui
                                                          KeyT* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap_pairs) {
     __shared__ uint32_t s_off[257];
     __shared__ uint32_t s_minx[256], s_miny[256], s_tx[256], s_dkey[256], s_gid[256];
-    __shared__ CullRec s_cull[256];
+    __shared__ gs::CullRec s_cull[256];
     const uint32_t g0 = blockIdx.x * 256u;
     const uint32_t i = g0 + threadIdx.x;
     if (i < n) {
@@ -137,7 +114,7 @@ __global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, const ui
         const float4 r0 = O.rec[3 * (size_t)g], r1 = O.rec[3 * (size_t)g + 1];
         const uint32_t k = __float_as_uint(O.rec[3 * (size_t)g + 2].y);        // depth
         s_dkey[threadIdx.x] = (k & 0x80000000u) ? ~k : (k | 0x80000000u);       // tiled_shaders.metal:773-774
-        s_cull[threadIdx.x] = cull_rec(r0, r1);
+        s_cull[threadIdx.x] = gs::cull_rec(r0, r1);
     }
     const uint32_t last = min(g0 + 256u, n);
     const uint32_t cnt = last - g0;

@@ -128,6 +128,14 @@ int gs_image_upload_rgba32f(gs_image*, const float* host);                /* enq
 int gs_image_upload_rgba8(gs_image*, const uint8_t* host);
 int gs_image_download_rgba32f(gs_image*, float* host);                    /* synchronises */
 int gs_image_download_rgba8(gs_image*, uint8_t* host);                    /* synchronises; RGBA8Unorm rounding */
+/* Asynchronous RGBA8 transfers on the context's copy streams (the reference's textures are device-visible shared
+ * memory, mtl_engine.mm:715-727 / image_loader.mm:24; a discrete GPU has to copy, and these let the copy of the NEXT
+ * view's ground truth and of the LAST render overlap the blend kernels).  `host` must be pinned and stay valid until
+ * gs_image_wait().  Compute calls that touch the image are ordered after a pending upload on the device; a compute
+ * call that overwrites it is also ordered after a pending download.  One transfer in flight per image. */
+int gs_image_upload_rgba8_async(gs_image*, const uint8_t* host);
+int gs_image_download_rgba8_async(gs_image*, uint8_t* host);
+int gs_image_wait(gs_image*);                                             /* host blocks until the transfer in flight is done */
 void* gs_image_devptr(gs_image*);                                          /* float4[width*height] */
 
 /* ---- TiledRasterizer (tiled_rasterizer.hpp:56-124) ------------------------------------------------------ */
