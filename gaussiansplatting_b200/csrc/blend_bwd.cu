@@ -45,10 +45,15 @@ __device__ __forceinline__ uint32_t reduce8_index(uint32_t lane) {
     return ((lane >> 4) & 1u) * 4u + ((lane >> 3) & 1u) * 2u + ((lane >> 2) & 1u);
 }
 
-// PPT pixels per thread, NT = 256/PPT threads (NW warps) per tile.  Each round stages BB raw list entries (those flagged
-// GS_CULL_BIT by pairs.cu are dropped, order kept).  A warp reduces the nine moments of an entry over its lanes and
-// stores them in ITS OWN row of shared memory (a warp meets an entry once per round, so no atomics and no conflicts);
-// the rows are summed and flushed with one global float atomic per (tile, Gaussian, moment).
+// PPT (2 or 4) pixels per thread, NT = 256/PPT threads (NW warps) per tile.  Each round stages BB raw list entries (those
+// flagged GS_CULL_BIT by pairs.cu are dropped, order kept) and marks per warp the survivors that can reach the warp's
+// own pixel rectangle.  A warp reduces the nine moments of an entry over its lanes and stores them in ITS OWN row of
+// shared memory (a warp meets an entry once per round, so no atomics and no conflicts); the rows are summed and
+// flushed with one global float atomic per (tile, Gaussian, moment).
+// The walk is branch-free and keeps the thread's pixels two to a packed fp32 pair (FFMA2, gs_common.cuh): a pixel that
+// does not take an entry runs the same instructions with alpha and G forced to 0, which leaves its T and accumulated
+// colour unchanged (T * rcp(1), 0*c + 1*acc) and adds exact zeros to the moments.
+struct BwdEnt { float4 r0, r1; float b; uint32_t idx, gid, pad; };   // 48 B: one base address, three LDS.128
 template <int PPT>
 __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                              const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
@@ -56,8 +61,8 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
                                                              int quantize, const uint32_t* __restrict__ last_idx,
                                                              const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
                                                              float* __restrict__ acc) {
-    constexpr int NT = 256 / PPT, NW = NT / 32, K = (BB + NT - 1) / NT;
-    __shared__ float4 s_r0[BB], s_r1[BB], s_r2[BB];     // r2 = {blue, list index (bits), gaussian id (bits), -}
+    constexpr int NT = 256 / PPT, NW = NT / 32, K = (BB + NT - 1) / NT, NP = PPT / 2;
+    __shared__ BwdEnt s_e[BB];
     __shared__ float s_acc[NW][BB * 9];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
@@ -67,56 +72,64 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint2 range = ranges[tile];                                // :410-413
     const bool redo = tile_flags[tile] != 0u;
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e);
 
-    float pxf[PPT], pyf[PPT], T[PPT], dr[PPT], dg[PPT], db[PPT], ar[PPT], ag[PPT], ab[PPT];
+    gs::f32x2 X2[NP], Y2[NP], T2[NP], dr2[NP], dg2[NP], db2[NP], ar2[NP], ag2[NP], ab2[NP];
     uint32_t e[PPT];                                                 // entries [0, e) of the tile list concern pixel j
     uint32_t emax = 0;
 #pragma unroll
-    for (int j = 0; j < PPT; j++) {
-        uint32_t x, y;
-        gs::tile_pixel<PPT>(warp, lane, j, x, y);
-        const uint32_t px = tX * 16u + x, py = tY * 16u + y;
-        pxf[j] = (float)px + 0.5f; pyf[j] = (float)py + 0.5f;        // :416
-        e[j] = 0; T[j] = 1.0f; dr[j] = 0.f; dg[j] = 0.f; db[j] = 0.f;
-        ar[j] = 1.0f; ag[j] = 1.0f; ab[j] = 1.0f;                    // accum_rec starts at the white background :468-470
-        if (px < W && py < H) {
-            const size_t pix = (size_t)py * W + px;
-            const uint32_t li = last_idx[pix];                       // :404-407
-            if (li != 0xFFFFFFFFu) {
-                e[j] = min(li + 1u, range.x + range.y) - range.x;    // :427
-                const float4 r = rendered[pix], t = gt[pix];         // :418-423
-                float rr[3] = {r.x, r.y, r.z};
-                const float tt[3] = {t.x, t.y, t.z};
-                float s[3];
+    for (int p = 0; p < NP; p++) {
+        float pxf[2], pyf[2], T[2], dr[2], dg[2], db[2];
 #pragma unroll
-                for (int c = 0; c < 3; c++) {
-                    if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
-                    const float diff = rr[c] - tt[c];
-                    s[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
-                }
-                dr[j] = s[0]; dg[j] = s[1]; db[j] = s[2];
-                T[j] = tfinal[pix];
-                if (redo) {
-                    // Rare path (a conic-degenerate entry was walked): redo the reference's first pass (:430-460), which,
-                    // unlike the forward, does not skip such entries.
-                    float Tf = 1.0f;
-                    for (uint32_t k = 0; k < e[j]; k++) {
-                        const uint32_t g = svals[range.x + k] & GS_ID_MASK;
-                        const float4 a = rec[3 * (size_t)g], b = rec[3 * (size_t)g + 1];
-                        const float dx = gs::fsub(pxf[j], a.x), dy = gs::fsub(pyf[j], a.y);
-                        const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
-                        if (!(power <= 0.0f) || power < -4.5f) continue;
-                        const float alpha = fminf(gs::fmul(b.y, gs::exp_blend(power)), GS_ALPHA_MAX);
-                        if (alpha < GS_ALPHA_MIN) continue;
-                        const float test_T = gs::fmul(Tf, gs::fsub(1.0f, alpha));
-                        if (test_T < GS_T_EPS) break;                // :458
-                        Tf = test_T;
+        for (int h = 0; h < 2; h++) {
+            const int j = 2 * p + h;
+            uint32_t x, y;
+            gs::tile_pixel<PPT>(warp, lane, j, x, y);
+            const uint32_t px = tX * 16u + x, py = tY * 16u + y;
+            pxf[h] = (float)px + 0.5f; pyf[h] = (float)py + 0.5f;        // :416
+            e[j] = 0; T[h] = 1.0f; dr[h] = 0.f; dg[h] = 0.f; db[h] = 0.f;
+            if (px < W && py < H) {
+                const size_t pix = (size_t)py * W + px;
+                const uint32_t li = last_idx[pix];                       // :404-407
+                if (li != 0xFFFFFFFFu) {
+                    e[j] = min(li + 1u, range.x + range.y) - range.x;    // :427
+                    const float4 r = rendered[pix], t = gt[pix];         // :418-423
+                    float rr[3] = {r.x, r.y, r.z};
+                    const float tt[3] = {t.x, t.y, t.z};
+                    float s[3];
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
+                        const float diff = rr[c] - tt[c];
+                        s[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
                     }
-                    T[j] = Tf;
+                    dr[h] = s[0]; dg[h] = s[1]; db[h] = s[2];
+                    T[h] = tfinal[pix];
+                    if (redo) {
+                        // Rare path (a conic-degenerate entry was walked): redo the reference's first pass (:430-460), which,
+                        // unlike the forward, does not skip such entries.
+                        float Tf = 1.0f;
+                        for (uint32_t k = 0; k < e[j]; k++) {
+                            const uint32_t g = svals[range.x + k] & GS_ID_MASK;
+                            const float4 a = rec[3 * (size_t)g], b = rec[3 * (size_t)g + 1];
+                            const float dx = gs::fsub(pxf[h], a.x), dy = gs::fsub(pyf[h], a.y);
+                            const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
+                            if (!(power <= 0.0f) || power < -4.5f) continue;
+                            const float alpha = fminf(gs::fmul(b.y, gs::exp_blend(power)), GS_ALPHA_MAX);
+                            if (alpha < GS_ALPHA_MIN) continue;
+                            const float test_T = gs::fmul(Tf, gs::fsub(1.0f, alpha));
+                            if (test_T < GS_T_EPS) break;                // :458
+                            Tf = test_T;
+                        }
+                        T[h] = Tf;
+                    }
                 }
             }
+            emax = max(emax, e[j]);
         }
-        emax = max(emax, e[j]);
+        X2[p] = gs::pk2(pxf[0], pxf[1]); Y2[p] = gs::pk2(pyf[0], pyf[1]); T2[p] = gs::pk2(T[0], T[1]);
+        dr2[p] = gs::pk2(dr[0], dr[1]); dg2[p] = gs::pk2(dg[0], dg[1]); db2[p] = gs::pk2(db[0], db[1]);
+        ar2[p] = gs::bc2(1.0f); ag2[p] = gs::bc2(1.0f); ab2[p] = gs::bc2(1.0f);   // accum_rec starts at the white background :468-470
     }
     // CTA-wide and warp-wide extent of the walk
     const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, emax);
@@ -127,6 +140,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
     for (int w = 0; w < NW; w++) bmax = max(bmax, s_wmax[w]);
 
     float* my_acc = s_acc[warp];
+    const gs::f32x2 one2 = gs::bc2(1.0f);
     for (uint32_t hi = bmax; hi > 0;) {
         const uint32_t lo = hi > (uint32_t)BB ? hi - BB : 0u;
         const uint32_t cntraw = hi - lo;
@@ -144,8 +158,8 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
         for (int q = 0; q < K; q++) {
             if (v[q] >> 31) continue;
             const uint32_t g = v[q];
-            s_r0[slot] = rec[3 * (size_t)g]; s_r1[slot] = rec[3 * (size_t)g + 1];
-            s_r2[slot] = make_float4(rec[3 * (size_t)g + 2].x, __uint_as_float(lo + threadIdx.x * K + q), __uint_as_float(g), 0.f);
+            s_e[slot].r0 = rec[3 * (size_t)g]; s_e[slot].r1 = rec[3 * (size_t)g + 1];
+            s_e[slot].b = rec[3 * (size_t)g + 2].x; s_e[slot].idx = lo + threadIdx.x * K + q; s_e[slot].gid = g;
             slot++;
         }
         for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
@@ -154,7 +168,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
         for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
             const uint32_t sl = s0 + lane;
             const bool valid = sl < total;
-            const gs::CullRec cr = gs::cull_rec(s_r0[valid ? sl : 0u], s_r1[valid ? sl : 0u]);
+            const gs::CullRec cr = gs::cull_rec(s_e[valid ? sl : 0u].r0, s_e[valid ? sl : 0u].r1);
 #pragma unroll
             for (int w = 0; w < NW; w++) {
                 uint32_t rx, ry; float ex, ey;
@@ -170,59 +184,81 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
             uint32_t kend = total;
             if (wmax < hi) {
                 uint32_t a = 0, b = total;
-                while (a < b) { const uint32_t m = (a + b) >> 1; if (__float_as_uint(s_r2[m].y) < wmax) a = m + 1; else b = m; }
+                while (a < b) { const uint32_t m = (a + b) >> 1; if (s_e[m].idx < wmax) a = m + 1; else b = m; }
                 kend = a;
             }
             for (int wd = ((int)kend - 1) >> 5; wd >= 0; wd--) {      // :473 back to front, reachable entries only
-              uint32_t mk = s_mask[warp][wd];
-              if ((uint32_t)wd == (kend >> 5)) mk &= (1u << (kend & 31u)) - 1u;
-              while (mk) {
-                const int kb = 31 - __clz(mk);
-                mk &= ~(1u << kb);
-                const int k = wd * 32 + kb;
-                const float4 a = s_r0[k];
-                const float4 b = s_r1[k];
-                const float4 c2 = s_r2[k];
-                const uint32_t idx = __float_as_uint(c2.y);
-                bool c[PPT], anyc = false;
-                float G[PPT], alpha[PPT], dx[PPT], dy[PPT];
+                uint32_t mk = s_mask[warp][wd];
+                if ((uint32_t)wd == (kend >> 5)) mk &= (1u << (kend & 31u)) - 1u;
+                const uint32_t wbase = ebase + (uint32_t)wd * 32u * (uint32_t)sizeof(BwdEnt);
+                while (mk) {
+                    const int kb = 31 - __clz(mk);
+                    mk &= ~(1u << kb);
+                    const uint32_t addr = wbase + (uint32_t)kb * (uint32_t)sizeof(BwdEnt);
+                    const float4 a = gs::lds128(addr);
+                    const float4 b = gs::lds128(addr + 16u);
+                    const float2 c = gs::lds64(addr + 32u);
+                    const uint32_t idx = __float_as_uint(c.y);
+                    const gs::f32x2 sx = gs::bc2(a.x), sy = gs::bc2(a.y), Ah = gs::bc2(a.z), Bn = gs::bc2(a.w), Ch = gs::bc2(b.x),
+                                    op = gs::bc2(b.y), cr = gs::bc2(b.z), cg = gs::bc2(b.w), cb = gs::bc2(c.x);
+                    gs::f32x2 m2[9];
+                    bool anyc = false;
 #pragma unroll
-                for (int j = 0; j < PPT; j++) {
-                    dx[j] = gs::fsub(pxf[j], a.x); dy[j] = gs::fsub(pyf[j], a.y);   // :483
-                    const float power = gs::blend_power(a.z, a.w, b.x, dx[j], dy[j]);
-                    c[j] = (idx < e[j]) && (power <= 0.0f) && !(power < -4.5f);     // :489
-                    G[j] = 0.f; alpha[j] = 0.f;
-                    if (c[j]) {
-                        G[j] = gs::exp_blend(power);                  // :492
-                        alpha[j] = fminf(gs::fmul(b.y, G[j]), GS_ALPHA_MAX);
-                        c[j] = !(alpha[j] < GS_ALPHA_MIN);            // :495
+                    for (int p = 0; p < NP; p++) {
+                        const gs::f32x2 dx = gs::fsub2(X2[p], sx), dy = gs::fsub2(Y2[p], sy);   // :483
+                        const gs::f32x2 pw2 = gs::blend_power2(Ah, Bn, Ch, dx, dy);
+                        const gs::f32x2 G2 = gs::exp_blend2(pw2);                             // :492
+                        const gs::f32x2 a2 = gs::fmul2(op, G2);
+                        float pw[2], al[2], G[2];
+                        gs::up2(pw2, pw[0], pw[1]); gs::up2(a2, al[0], al[1]); gs::up2(G2, G[0], G[1]);
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            al[h] = fminf(al[h], GS_ALPHA_MAX);
+                            const bool ch = (idx < e[2 * p + h]) && (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);   // :489, :495
+                            al[h] = ch ? al[h] : 0.0f;
+                            G[h] = ch ? G[h] : 0.0f;
+                            anyc |= ch;
+                        }
+                        const gs::f32x2 alpha = gs::pk2(al[0], al[1]), Gq = gs::pk2(G[0], G[1]);
+                        const gs::f32x2 om = gs::fsub2(one2, alpha);
+                        float om0, om1;
+                        gs::up2(om, om0, om1);
+                        const gs::f32x2 Tn = gs::fmul2(T2[p], gs::pk2(gs::rcp_approx(fmaxf(om0, 0.0001f)), gs::rcp_approx(fmaxf(om1, 0.0001f))));   // :498
+                        T2[p] = Tn;
+                        const gs::f32x2 w2 = gs::fmul2(alpha, Tn);                             // :500
+                        gs::f32x2 s2 = gs::fmul2(dr2[p], gs::fsub2(cr, ar2[p]));
+                        s2 = gs::ffma2(dg2[p], gs::fsub2(cg, ag2[p]), s2);
+                        s2 = gs::ffma2(db2[p], gs::fsub2(cb, ab2[p]), s2);
+                        const gs::f32x2 dLdA = gs::fmul2(Tn, s2);                              // :510
+                        ar2[p] = gs::ffma2(alpha, cr, gs::fmul2(om, ar2[p]));                  // :514
+                        ag2[p] = gs::ffma2(alpha, cg, gs::fmul2(om, ag2[p]));
+                        ab2[p] = gs::ffma2(alpha, cb, gs::fmul2(om, ab2[p]));
+                        const gs::f32x2 q = gs::fmul2(dLdA, Gq);
+                        const gs::f32x2 qx = gs::fmul2(q, dx), qy = gs::fmul2(q, dy);
+                        if (p == 0) {
+                            m2[0] = gs::fmul2(dr2[p], w2); m2[1] = gs::fmul2(dg2[p], w2); m2[2] = gs::fmul2(db2[p], w2); m2[3] = q;
+                            m2[4] = qx; m2[5] = qy; m2[6] = gs::fmul2(qx, dx); m2[7] = gs::fmul2(qx, dy); m2[8] = gs::fmul2(qy, dy);
+                        } else {
+                            m2[0] = gs::ffma2(dr2[p], w2, m2[0]); m2[1] = gs::ffma2(dg2[p], w2, m2[1]); m2[2] = gs::ffma2(db2[p], w2, m2[2]);
+                            m2[3] = gs::fadd2(m2[3], q); m2[4] = gs::fadd2(m2[4], qx); m2[5] = gs::fadd2(m2[5], qy);
+                            m2[6] = gs::ffma2(qx, dx, m2[6]); m2[7] = gs::ffma2(qx, dy, m2[7]); m2[8] = gs::ffma2(qy, dy, m2[8]);
+                        }
                     }
-                    anyc |= c[j];
-                }
-                if (!__any_sync(0xFFFFFFFFu, anyc)) continue;
-                float v8[8], v9 = 0.f;
+                    if (!__any_sync(0xFFFFFFFFu, anyc)) continue;
+                    float v8[8], v9;
 #pragma unroll
-                for (int i = 0; i < 8; i++) v8[i] = 0.f;
-#pragma unroll
-                for (int j = 0; j < PPT; j++) {
-                    if (c[j]) {
-                        const float om = 1.0f - alpha[j];
-                        T[j] = __fdividef(T[j], fmaxf(om, 0.0001f));  // :498
-                        const float w = alpha[j] * T[j];              // :500
-                        const float dLdA = T[j] * ((dr[j] * (b.z - ar[j]) + dg[j] * (b.w - ag[j])) + db[j] * (c2.x - ab[j]));   // :510
-                        ar[j] = alpha[j] * b.z + om * ar[j]; ag[j] = alpha[j] * b.w + om * ag[j]; ab[j] = alpha[j] * c2.x + om * ab[j];   // :514
-                        const float q = dLdA * G[j];
-                        const float qx = q * dx[j], qy = q * dy[j];
-                        v8[0] += dr[j] * w; v8[1] += dg[j] * w; v8[2] += db[j] * w; v8[3] += q;
-                        v8[4] += qx; v8[5] += qy; v8[6] += qx * dx[j]; v8[7] += qx * dy[j]; v9 += qy * dy[j];
+                    for (int i = 0; i < 9; i++) {
+                        float l, h;
+                        gs::up2(m2[i], l, h);
+                        if (i < 8) v8[i] = l + h; else v9 = l + h;
                     }
-                }
-                const float tot = warp_reduce8_transposed(v8, lane);
+                    const float tot = warp_reduce8_transposed(v8, lane);
 #pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
-                if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
-                if (lane == 1u) my_acc[k * 9 + 8] = v9;
-              }
+                    for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
+                    const int k = wd * 32 + kb;
+                    if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
+                    if (lane == 1u) my_acc[k * 9 + 8] = v9;
+                }
             }
         }
         __syncthreads();
@@ -230,7 +266,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
             float x = 0.f;
 #pragma unroll
             for (int w = 0; w < NW; w++) x += s_acc[w][i];
-            if (x != 0.f) atomicAdd(&acc[(size_t)__float_as_uint(s_r2[i / 9u].z) * 12u + (i % 9u)], x);
+            if (x != 0.f) atomicAdd(&acc[(size_t)s_e[i / 9u].gid * 12u + (i % 9u)], x);
         }
         __syncthreads();
         hi = lo;
@@ -344,7 +380,7 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, Gs
 }  // namespace
 
 static int g_bwd_ppt = GS_BWD_PPT;
-void gs_tune_bwd_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_bwd_ppt = v; }
+void gs_tune_bwd_ppt(int v) { if (v == 2 || v == 4) g_bwd_ppt = v; }
 
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
@@ -354,8 +390,7 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
     blend_backward_kernel<PPT><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
                                                                  last_idx, tfinal, O.tile_flags, acc)
     if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4);
-    else if (g_bwd_ppt == 2) GS_BWD_LAUNCH(2);
-    else GS_BWD_LAUNCH(1);
+    else GS_BWD_LAUNCH(2);
 }
 
 void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,

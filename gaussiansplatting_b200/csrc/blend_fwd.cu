@@ -68,19 +68,22 @@ __global__ void rebuild_keys64_kernel(const uint32_t* __restrict__ tiles, const 
 #endif
 constexpr int FB = 256;   // raw list entries staged per round
 
-// K6.  PPT pixels per thread, NT = 256/PPT threads per tile.  Each round a CTA reads FB consecutive entries of the
-// tile's sorted list, drops those flagged GS_CULL_BIT (pairs.cu: the splat cannot reach any pixel of this tile),
-// compacts the survivors in list order into shared memory (one 48-B record gather each) and every thread walks them.
+// K6.  PPT (2 or 4) pixels per thread, NT = 256/PPT threads per tile.  Each round a CTA reads FB consecutive entries of
+// the tile's sorted list, drops those flagged GS_CULL_BIT (pairs.cu: the splat cannot reach any pixel of this tile),
+// compacts the survivors in list order into shared memory (one 48-B record gather each), marks per warp the survivors
+// that can reach the warp's own pixel rectangle, and every warp walks its marked entries.
+// The walk is branch-free and keeps the thread's pixels two to a packed fp32 pair (FFMA2): a pixel that does not take an
+// entry runs the same instructions with alpha forced to 0, which leaves C and T bit-unchanged (x*0 + C, T*(1-0)); a
+// finished pixel has NaN coordinates, so every test on it fails.  Per half the operation sequence is the pinned one.
+struct FwdEnt { float4 r0, r1; float b; uint32_t idx; uint32_t pad0, pad1; };   // 48 B: one base address, three LDS
 template <int PPT, bool COUNT>
 __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                             float4* __restrict__ image, uint32_t* __restrict__ last_idx,
                                                             float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags,
                                                             unsigned long long* __restrict__ counters) {
-    constexpr int NT = 256 / PPT, NW = NT / 32, K = FB / NT;
-    __shared__ float4 s_r0[FB], s_r1[FB];
-    __shared__ float s_b[FB];
-    __shared__ uint32_t s_idx[FB];
+    constexpr int NT = 256 / PPT, NW = NT / 32, K = FB / NT, NP = PPT / 2;
+    __shared__ FwdEnt s_e[FB];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_mask[NW][FB / 32];          // per warp region: which staged entries can reach it at all
     __shared__ uint32_t s_degen;
@@ -89,26 +92,34 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint2 range = ranges[tile];                                // :320-323
     if (threadIdx.x == 0) s_degen = 0;
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e);
 
-    uint32_t px[PPT], py[PPT];
-    float pxf[PPT], pyf[PPT], Cr[PPT], Cg[PPT], Cb[PPT], T[PPT], Tp[PPT];
-    uint32_t last[PPT];
-    bool done[PPT];
-    int ndone = 0;
+    uint32_t px[PPT], py[PPT], last[PPT];
+    float Tp[PPT];
+    gs::f32x2 X2[NP], Y2[NP], T2[NP], Cr2[NP], Cg2[NP], Cb2[NP];
     uint32_t nC = 0;   // COUNT only: contributing evaluations (roofline accounting)
+    bool live = false;
+    const float qnan = __uint_as_float(0x7FC00000u);
 #pragma unroll
-    for (int j = 0; j < PPT; j++) {
-        uint32_t x, y;
-        gs::tile_pixel<PPT>(warp, lane, j, x, y);
-        px[j] = tX * 16u + x; py[j] = tY * 16u + y;
-        pxf[j] = (float)px[j] + 0.5f; pyf[j] = (float)py[j] + 0.5f;   // :328
-        Cr[j] = 0.f; Cg[j] = 0.f; Cb[j] = 0.f; T[j] = 1.0f; Tp[j] = 1.0f;
-        last[j] = 0xFFFFFFFFu;
-        done[j] = !(px[j] < W && py[j] < H);
-        ndone += done[j] ? 1 : 0;
+    for (int p = 0; p < NP; p++) {
+        float xf[2], yf[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int j = 2 * p + h;
+            uint32_t x, y;
+            gs::tile_pixel<PPT>(warp, lane, j, x, y);
+            px[j] = tX * 16u + x; py[j] = tY * 16u + y;
+            const bool in = px[j] < W && py[j] < H;
+            xf[h] = in ? (float)px[j] + 0.5f : qnan; yf[h] = (float)py[j] + 0.5f;   // :328
+            Tp[j] = 1.0f; last[j] = 0xFFFFFFFFu;
+            live |= in;
+        }
+        X2[p] = gs::pk2(xf[0], xf[1]); Y2[p] = gs::pk2(yf[0], yf[1]);
+        T2[p] = gs::bc2(1.0f); Cr2[p] = gs::bc2(0.f); Cg2[p] = gs::bc2(0.f); Cb2[p] = gs::bc2(0.f);
     }
+    bool wlive = __any_sync(0xFFFFFFFFu, live);      // warp-uniform: some pixel of this warp still walks
     for (uint32_t base = 0; base < range.y; base += FB) {
-        if (__syncthreads_and(ndone == PPT)) break;
+        if (__syncthreads_and(!wlive)) break;
         // ---- stage: drop culled pairs, keep list order
         const uint32_t cntraw = min((uint32_t)FB, range.y - base);
         uint32_t v[K], nl = 0;
@@ -127,7 +138,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
             const float4 r0 = rec[3 * (size_t)g], r2 = rec[3 * (size_t)g + 2];
             float4 r1 = rec[3 * (size_t)g + 1];
             if (__float_as_uint(r2.w) & 1u) { r1.y = 0.f; s_degen = 1u; }   // :350-351 conic-magnitude skip (forward only)
-            s_r0[slot] = r0; s_r1[slot] = r1; s_b[slot] = r2.x; s_idx[slot] = base + threadIdx.x * K + q;
+            s_e[slot].r0 = r0; s_e[slot].r1 = r1; s_e[slot].b = r2.x; s_e[slot].idx = range.x + base + threadIdx.x * K + q;
             slot++;
         }
         __syncthreads();
@@ -135,7 +146,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
         for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
             const uint32_t sl = s0 + lane;
             const bool valid = sl < total;
-            const gs::CullRec cr = gs::cull_rec(s_r0[valid ? sl : 0u], s_r1[valid ? sl : 0u]);
+            const gs::CullRec cr = gs::cull_rec(s_e[valid ? sl : 0u].r0, s_e[valid ? sl : 0u].r1);
 #pragma unroll
             for (int w = 0; w < NW; w++) {
                 uint32_t rx, ry; float ex, ey;
@@ -146,43 +157,73 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
             }
         }
         __syncthreads();
-        if (ndone < PPT) {
+        if (wlive) {
             const uint32_t nwords = (total + 31u) >> 5;
-            for (uint32_t wd = 0; wd < nwords; wd++) {               // :334, entries that can reach this warp's pixels only
+            for (uint32_t wd = 0; wd < nwords && wlive; wd++) {      // :334, entries that can reach this warp's pixels only
                 uint32_t m = s_mask[warp][wd];
+                const uint32_t wbase = ebase + wd * 32u * (uint32_t)sizeof(FwdEnt);
                 while (m) {
-                    const uint32_t k = wd * 32u + (uint32_t)__ffs(m) - 1u;
+                    const uint32_t kb = (uint32_t)__ffs(m) - 1u;
                     m &= m - 1u;
-                    const float4 a = s_r0[k];
-                    const float4 b = s_r1[k];
+                    const uint32_t addr = wbase + kb * (uint32_t)sizeof(FwdEnt);
+                    const float4 a = gs::lds128(addr);
+                    const float4 b = gs::lds128(addr + 16u);
+                    const float2 c = gs::lds64(addr + 32u);
+                    const uint32_t idx = __float_as_uint(c.y);
+                    const gs::f32x2 sx = gs::bc2(a.x), sy = gs::bc2(a.y), Ah = gs::bc2(a.z), Bn = gs::bc2(a.w), Ch = gs::bc2(b.x),
+                                    op = gs::bc2(b.y), cr = gs::bc2(b.z), cg = gs::bc2(b.w), cb = gs::bc2(c.x);
+                    bool alive = false;
 #pragma unroll
-                    for (int j = 0; j < PPT; j++) {
-                        if (done[j]) continue;
-                        const float dx = gs::fsub(pxf[j], a.x), dy = gs::fsub(pyf[j], a.y);   // :347
-                        const float power = gs::blend_power(a.z, a.w, b.x, dx, dy);
-                        if (!(power <= 0.0f) || power < -4.5f) continue;  // :359
-                        const float G = gs::exp_blend(power);             // :362
-                        const float alpha = fminf(gs::fmul(b.y, G), GS_ALPHA_MAX);   // :363
-                        if (alpha < GS_ALPHA_MIN) continue;               // :366
-                        const float w = gs::fmul(alpha, T[j]);            // :369
-                        Cr[j] = gs::ffma(b.z, w, Cr[j]); Cg[j] = gs::ffma(b.w, w, Cg[j]); Cb[j] = gs::ffma(s_b[k], w, Cb[j]);
-                        Tp[j] = T[j];
-                        if (COUNT) nC++;
-                        T[j] = gs::fmul(T[j], gs::fsub(1.0f, alpha));     // :370
-                        last[j] = range.x + s_idx[k];                     // :372
-                        if (!(T[j] > GS_T_EPS)) { done[j] = true; ndone++; }   // :334 loop condition
+                    for (int p = 0; p < NP; p++) {
+                        const gs::f32x2 dx = gs::fsub2(X2[p], sx), dy = gs::fsub2(Y2[p], sy);   // :347
+                        const gs::f32x2 pw2 = gs::blend_power2(Ah, Bn, Ch, dx, dy);
+                        const gs::f32x2 G2 = gs::exp_blend2(pw2);                             // :362
+                        const gs::f32x2 a2 = gs::fmul2(op, G2);                               // :363
+                        float pw[2], al[2], Tn[2], To[2];
+                        gs::up2(pw2, pw[0], pw[1]); gs::up2(a2, al[0], al[1]); gs::up2(T2[p], To[0], To[1]);
+                        bool c2[2];
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            al[h] = fminf(al[h], GS_ALPHA_MAX);
+                            c2[h] = (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);   // :359, :366 (NaN: all false)
+                            al[h] = c2[h] ? al[h] : 0.0f;
+                        }
+                        const gs::f32x2 alpha = gs::pk2(al[0], al[1]);
+                        const gs::f32x2 w2 = gs::fmul2(alpha, T2[p]);                          // :369
+                        Cr2[p] = gs::ffma2(cr, w2, Cr2[p]); Cg2[p] = gs::ffma2(cg, w2, Cg2[p]); Cb2[p] = gs::ffma2(cb, w2, Cb2[p]);
+                        T2[p] = gs::fmul2(T2[p], gs::fsub2(gs::bc2(1.0f), alpha));            // :370
+                        gs::up2(T2[p], Tn[0], Tn[1]);
+                        float xf[2];
+                        gs::up2(X2[p], xf[0], xf[1]);
+#pragma unroll
+                        for (int h = 0; h < 2; h++) {
+                            const int j = 2 * p + h;
+                            Tp[j] = c2[h] ? To[h] : Tp[j];
+                            last[j] = c2[h] ? idx : last[j];                                  // :372
+                            if (COUNT) nC += c2[h] ? 1u : 0u;
+                            const bool go = Tn[h] > GS_T_EPS;                                 // :334 loop condition
+                            xf[h] = go ? xf[h] : qnan;
+                            alive |= (xf[h] == xf[h]);
+                        }
+                        X2[p] = gs::pk2(xf[0], xf[1]);
                     }
-                    if (ndone == PPT) { wd = nwords; break; }
+                    if (!__any_sync(0xFFFFFFFFu, alive)) { wlive = false; break; }
                 }
             }
         }
+    }
+    float Tf[PPT], Cr[PPT], Cg[PPT], Cb[PPT];
+#pragma unroll
+    for (int p = 0; p < NP; p++) {
+        gs::up2(T2[p], Tf[2 * p], Tf[2 * p + 1]); gs::up2(Cr2[p], Cr[2 * p], Cr[2 * p + 1]);
+        gs::up2(Cg2[p], Cg[2 * p], Cg[2 * p + 1]); gs::up2(Cb2[p], Cb[2 * p], Cb[2 * p + 1]);
     }
     if (COUNT) {
         // E = list entries the reference's loop visits: up to and including the entry that ended the walk, else all
         unsigned long long e = 0, c = nC;
 #pragma unroll
         for (int j = 0; j < PPT; j++)
-            if (px[j] < W && py[j] < H) e += (!(T[j] > GS_T_EPS)) ? (last[j] - range.x + 1u) : range.y;
+            if (px[j] < W && py[j] < H) e += (!(Tf[j] > GS_T_EPS)) ? (last[j] - range.x + 1u) : range.y;
         for (int d = 16; d >= 1; d >>= 1) { e += __shfl_xor_sync(0xFFFFFFFFu, e, d); c += __shfl_xor_sync(0xFFFFFFFFu, c, d); }
         if (lane == 0) { atomicAdd(&counters[0], e); atomicAdd(&counters[1], c); }
         return;
@@ -191,11 +232,11 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
     for (int j = 0; j < PPT; j++) {
         if (px[j] < W && py[j] < H) {
             const size_t pix = (size_t)py[j] * W + px[j];
-            image[pix] = make_float4(gs::fadd(Cr[j], T[j]), gs::fadd(Cg[j], T[j]), gs::fadd(Cb[j], T[j]), 1.0f);   // :377-384 white background
+            image[pix] = make_float4(gs::fadd(Cr[j], Tf[j]), gs::fadd(Cg[j], Tf[j]), gs::fadd(Cb[j], Tf[j]), 1.0f);   // :377-384 white background
             last_idx[pix] = last[j];                                  // :382
             // T_final as tiledBackward's first pass (:430-460) would recompute it: the entry that drives T below
             // 1e-4 is NOT applied there (break before apply), every earlier one is.
-            tfinal[pix] = (T[j] < GS_T_EPS) ? Tp[j] : T[j];
+            tfinal[pix] = (Tf[j] < GS_T_EPS) ? Tp[j] : Tf[j];
         }
     }
     __syncthreads();
@@ -205,7 +246,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
 }  // namespace
 
 static int g_fwd_ppt = GS_FWD_PPT;
-void gs_tune_fwd_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_fwd_ppt = v; }
+void gs_tune_fwd_ppt(int v) { if (v == 2 || v == 4) g_fwd_ppt = v; }
 
 void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* /*lb*/,
                            uint2* ranges, cudaStream_t st) {
@@ -232,14 +273,13 @@ void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, 
     blend_forward_kernel<PPT, false><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
                                                                        tfinal, O.tile_flags, nullptr)
     if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4);
-    else if (g_fwd_ppt == 2) GS_FWD_LAUNCH(2);
-    else GS_FWD_LAUNCH(1);
+    else GS_FWD_LAUNCH(2);
 }
 
 // counts E (entries visited) and C (contributing evaluations) of the forward walk; counters[2] zeroed by the caller
 void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                            uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st) {
     if (ntx * nty == 0) return;
-    blend_forward_kernel<1, true><<<ntx * nty, 256, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
+    blend_forward_kernel<2, true><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
                                                              O.tile_flags, counters);
 }

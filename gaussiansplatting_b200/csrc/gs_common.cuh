@@ -67,6 +67,50 @@ __device__ __forceinline__ float blend_power(float Ah, float Bn, float Ch, float
     return ffma(dx, u, v);
 }
 
+// ---- packed fp32 pairs (sm_100 FFMA2): two IEEE round-to-nearest fp32 operations per issued instruction.  The blend
+// kernels keep TWO pixels of a thread in one pair, which halves the FP32 issue slots of the walk.  Only fma.rn.f32x2 is
+// used: ptxas contracts mul.rn.f32x2 followed by add.rn.f32x2 into one FFMA2 (measured: tools/ubench/f32x2.cu), which
+// would break the pinned rounding sequence, so mul/add/sub are spelled as exact FMAs (a*b + -0, a*1 + b, b*-1 + a).
+// fma.rn.f32x2 is bit-identical to __fmaf_rn per half (same micro-check).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ f32x2 bc2(float x) { return pk2(x, x); }
+__device__ __forceinline__ void up2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b) { return ffma2(a, b, pk2(-0.0f, -0.0f)); }
+__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b) { return ffma2(a, pk2(1.0f, 1.0f), b); }
+__device__ __forceinline__ f32x2 fsub2(f32x2 a, f32x2 b) { return ffma2(b, pk2(-1.0f, -1.0f), a); }
+// exp_blend() on a pair (same operation sequence per half)
+__device__ __forceinline__ f32x2 exp_blend2(f32x2 x) {
+    const f32x2 t = fmul2(x, bc2(GS_LOG2E));
+    const f32x2 r = fadd2(t, bc2(GS_EXP2_MAGIC));
+    const f32x2 nf = fadd2(r, bc2(-GS_EXP2_MAGIC));
+    const f32x2 f = fsub2(t, nf);
+    f32x2 p = bc2(GS_EXP2_C5);
+    p = ffma2(p, f, bc2(GS_EXP2_C4));
+    p = ffma2(p, f, bc2(GS_EXP2_C3));
+    p = ffma2(p, f, bc2(GS_EXP2_C2));
+    p = ffma2(p, f, bc2(GS_EXP2_C1));
+    p = ffma2(p, f, bc2(1.0f));
+    float p0, p1, r0, r1;
+    up2(p, p0, p1); up2(r, r0, r1);
+    return pk2(__uint_as_float(__float_as_uint(p0) + (__float_as_uint(r0) << 23)),
+               __uint_as_float(__float_as_uint(p1) + (__float_as_uint(r1) << 23)));
+}
+// pinned blend exponent on a pair (blend_power per half); the per-entry coefficients are broadcast
+__device__ __forceinline__ f32x2 blend_power2(f32x2 Ah, f32x2 Bn, f32x2 Ch, f32x2 dx, f32x2 dy) {
+    const f32x2 u = ffma2(Ah, dx, fmul2(Bn, dy));
+    const f32x2 v = fmul2(fmul2(Ch, dy), dy);
+    return ffma2(dx, u, v);
+}
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v; asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr)); return v;
+}
+__device__ __forceinline__ float2 lds64(uint32_t addr) {
+    float2 v; asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr)); return v;
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
 // Pixel (within the 16x16 tile) of slot j of a thread, for PPT pixels per thread (256/PPT threads per tile):
