@@ -461,6 +461,7 @@ struct gs_rast {
     cudaEvent_t ev_pairs = nullptr;     // recorded after the pair count landed in pinned memory
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
+    bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
     void mark(int i) { if (prof) cudaEventRecord(ev[i], c->stream); }
@@ -494,6 +495,7 @@ static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     GS_TRY(dalloc(c, &r->proj.cnt, cap));
     GS_TRY(dalloc(c, &r->proj.dkey, cap));
     GS_TRY(dalloc(c, &r->acc, (size_t)cap * 12));
+    r->acc_clean = false;
     GS_TRY(dalloc(c, &r->iota, cap));
     for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->dk_buf[i], cap)); GS_TRY(dalloc(c, &r->perm_buf[i], cap)); }
     GS_CUDA(c, cudaMalloc(&r->dsort_scratch, gs_sort_scratch_bytes(cap, 4)));
@@ -697,15 +699,18 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     GS_TRY(image_before_read(rendered, st));
     GS_TRY(image_before_read(gt, st));
     r->mark(8);
-    if (!(flags & GS_BWD_ACCUMULATE)) GS_TRY(gs_grads_zero(gr, n));   // :687
+    const int accumulate = (flags & GS_BWD_ACCUMULATE) ? 1 : 0;
+    if (!accumulate) GS_TRY(grads_reserve(gr, n));                    // the CPU memset of :687 is folded into K8's store
     else GS_ARG(c, n <= gr->cap, "gradient buffer too small to accumulate into");
-    GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)n * 12 * sizeof(float), st));
+    if (!r->acc_clean) GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)r->cap_g * 12 * sizeof(float), st));
+    r->acc_clean = false;
     const uint32_t* svals = r->sorted_vals;
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
                              (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, st);
     r->mark(9);
     gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,
-                                  gr->view(), gr->stat_mode, st);
+                                  gr->view(), gr->stat_mode, accumulate, st);
+    r->acc_clean = true;                                              // K8 cleared every row K7 touched
     r->mark(10);
     GS_LAUNCH_CHECK(c);
     GS_TRY(image_after_use(rendered, st));

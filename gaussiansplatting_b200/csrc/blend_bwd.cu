@@ -279,7 +279,11 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4*
 // ---------------------------------------------------------------------------------------------------
 struct V9 { float V[9]; };   // upper 3x3 of the view matrix, V[c*3+r] = viewMatrix[c][r]
 
-__global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, GsProjected O, const float* __restrict__ acc,
+// The moment rows are consumed here: a row that held anything is cleared again, so the buffer is all-zero between
+// frames and K7 needs no memset.  ACCUMULATE = false writes the gradient planes (zeros for a Gaussian no pixel touched)
+// instead of adding to them, which saves the caller's zeroing pass and the read of the planes.
+template <bool ACCUMULATE>
+__global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, GsProjected O, float* __restrict__ acc,
                                                                   const __grid_constant__ V9 vm, float fx, float fy, uint32_t n,
                                                                   GsGradPack Gp, int stat_mode) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -289,7 +293,17 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, Gs
     const float m8 = acc[(size_t)i * 12 + 8];
     const bool any = (m0.x != 0.f) | (m0.y != 0.f) | (m0.z != 0.f) | (m0.w != 0.f) | (m1.x != 0.f) | (m1.y != 0.f) |
                      (m1.z != 0.f) | (m1.w != 0.f) | (m8 != 0.f);
-    if (!any) return;                                   // no pixel contributed: every gradient term is +0
+    const uint32_t st = Gp.stride;
+    if (!any) {                                         // no pixel contributed: every gradient term is +0
+        if (!ACCUMULATE) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) Gp.g[(size_t)k * st + i] = 0.f;
+        }
+        return;
+    }
+    *reinterpret_cast<float4*>(acc + (size_t)i * 12) = make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(acc + (size_t)i * 12 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    acc[(size_t)i * 12 + 8] = 0.f;
     const float4 r0 = O.rec[3 * (size_t)i], r1 = O.rec[3 * (size_t)i + 1], r2 = O.rec[3 * (size_t)i + 2];
     const float4 ax = O.aux[i];
     const float A = -2.0f * r0.z, B = -r0.w, C = -2.0f * r1.x;       // conic
@@ -372,9 +386,11 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, Gs
         const bool ok = !isnan(mag) && !isinf(mag) && mag > 0.f;
         g[14] = ok ? mag : 0.f; g[15] = ok ? 1.0f : 0.f;
     } else { g[14] = sx; g[15] = sy; }
-    const uint32_t st = Gp.stride;
 #pragma unroll
-    for (int k = 0; k < 16; k++) Gp.g[(size_t)k * st + i] += g[k];
+    for (int k = 0; k < 16; k++) {
+        if (ACCUMULATE) Gp.g[(size_t)k * st + i] += g[k];
+        else Gp.g[(size_t)k * st + i] = g[k];
+    }
 }
 
 }  // namespace
@@ -393,10 +409,11 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
     else GS_BWD_LAUNCH(2);
 }
 
-void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,
-                                   float fy, uint32_t n, GsGradPack G, int stat_mode, cudaStream_t st) {
+void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, float* acc, const float* V, float fx,
+                                   float fy, uint32_t n, GsGradPack G, int stat_mode, int accumulate, cudaStream_t st) {
     if (n == 0) return;
     V9 vm;
     for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) vm.V[c * 3 + r] = V[c * 4 + r];
-    preprocess_backward_kernel<<<(n + 255) / 256, 256, 0, st>>>(P, O, acc, vm, fx, fy, n, G, stat_mode);
+    if (accumulate) preprocess_backward_kernel<true><<<(n + 255) / 256, 256, 0, st>>>(P, O, acc, vm, fx, fy, n, G, stat_mode);
+    else preprocess_backward_kernel<false><<<(n + 255) / 256, 256, 0, st>>>(P, O, acc, vm, fx, fy, n, G, stat_mode);
 }

@@ -34,20 +34,25 @@ __global__ void tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n
 __global__ void __launch_bounds__(256) tile_starts_kernel(const uint32_t* __restrict__ tiles, uint32_t max_pairs,
                                                           const uint32_t* __restrict__ d_n, uint32_t num_tiles,
                                                           uint2* __restrict__ ranges) {
-    const uint32_t n = min(*d_n, max_pairs);
-    const uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n == 0) { if (t0 < num_tiles) ranges[t0] = make_uint2(0u, 0u); return; }
-    const uint32_t j0 = t0 * 4u;                              // four consecutive entries per thread
-    if (j0 >= n) return;
-    int64_t tp = j0 ? (int64_t)min(tiles[j0 - 1], num_tiles - 1u) : -1;
+    const uint32_t n = min(*d_n, max_pairs);                  // device-side pair count: the grid is fixed, threads stride
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n == 0) { for (; t0 < num_tiles; t0 += stride) ranges[t0] = make_uint2(0u, 0u); return; }
+    for (; (uint64_t)t0 * 4u < n; t0 += stride) {
+        const uint32_t j0 = t0 * 4u;                          // four consecutive entries per thread
+        int64_t tp = j0 ? (int64_t)min(tiles[j0 - 1], num_tiles - 1u) : -1;
+        uint32_t tt4[4] = {0u, 0u, 0u, 0u};
+        if (j0 + 4u <= n) { const uint4 q = *reinterpret_cast<const uint4*>(tiles + j0); tt4[0] = q.x; tt4[1] = q.y; tt4[2] = q.z; tt4[3] = q.w; }
+        else for (uint32_t q = 0; q < 4u && j0 + q < n; q++) tt4[q] = tiles[j0 + q];
 #pragma unroll
-    for (uint32_t q = 0; q < 4u; q++) {
-        const uint32_t j = j0 + q;
-        if (j >= n) break;
-        const uint32_t t = min(tiles[j], num_tiles - 1u);
-        for (int64_t tt = tp + 1; tt <= (int64_t)t; tt++) ranges[tt].x = j;
-        if (j == n - 1u) for (uint32_t tt = t + 1u; tt < num_tiles; tt++) ranges[tt].x = n;
-        tp = t;
+        for (uint32_t q = 0; q < 4u; q++) {
+            const uint32_t j = j0 + q;
+            if (j >= n) break;
+            const uint32_t t = min(tt4[q], num_tiles - 1u);
+            for (int64_t tt = tp + 1; tt <= (int64_t)t; tt++) ranges[tt].x = j;
+            if (j == n - 1u) for (uint32_t tt = t + 1u; tt < num_tiles; tt++) ranges[tt].x = n;
+            tp = t;
+        }
     }
 }
 __global__ void tile_counts_kernel(uint32_t max_pairs, const uint32_t* __restrict__ d_n, uint32_t num_tiles, uint2* __restrict__ ranges) {
@@ -99,10 +104,9 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
     gs::f32x2 X2[NP], Y2[NP], T2[NP], Cr2[NP], Cg2[NP], Cb2[NP];
     uint32_t nC = 0;   // COUNT only: contributing evaluations (roofline accounting)
     bool live = false;
-    const float qnan = __uint_as_float(0x7FC00000u);
 #pragma unroll
     for (int p = 0; p < NP; p++) {
-        float xf[2], yf[2];
+        float xf[2], yf[2], t0[2];
 #pragma unroll
         for (int h = 0; h < 2; h++) {
             const int j = 2 * p + h;
@@ -110,12 +114,13 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
             gs::tile_pixel<PPT>(warp, lane, j, x, y);
             px[j] = tX * 16u + x; py[j] = tY * 16u + y;
             const bool in = px[j] < W && py[j] < H;
-            xf[h] = in ? (float)px[j] + 0.5f : qnan; yf[h] = (float)py[j] + 0.5f;   // :328
+            xf[h] = (float)px[j] + 0.5f; yf[h] = (float)py[j] + 0.5f;   // :328
+            t0[h] = in ? 1.0f : 0.0f;                                   // a pixel outside the image never walks (T = 0 <= eps)
             Tp[j] = 1.0f; last[j] = 0xFFFFFFFFu;
             live |= in;
         }
         X2[p] = gs::pk2(xf[0], xf[1]); Y2[p] = gs::pk2(yf[0], yf[1]);
-        T2[p] = gs::bc2(1.0f); Cr2[p] = gs::bc2(0.f); Cg2[p] = gs::bc2(0.f); Cb2[p] = gs::bc2(0.f);
+        T2[p] = gs::pk2(t0[0], t0[1]); Cr2[p] = gs::bc2(0.f); Cg2[p] = gs::bc2(0.f); Cb2[p] = gs::bc2(0.f);
     }
     bool wlive = __any_sync(0xFFFFFFFFu, live);      // warp-uniform: some pixel of this warp still walks
     for (uint32_t base = 0; base < range.y; base += FB) {
@@ -185,7 +190,8 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
 #pragma unroll
                         for (int h = 0; h < 2; h++) {
                             al[h] = fminf(al[h], GS_ALPHA_MAX);
-                            c2[h] = (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);   // :359, :366 (NaN: all false)
+                            // :334 (the pixel still walks: T > 1e-4), :359, :366
+                            c2[h] = (To[h] > GS_T_EPS) && (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);
                             al[h] = c2[h] ? al[h] : 0.0f;
                         }
                         const gs::f32x2 alpha = gs::pk2(al[0], al[1]);
@@ -193,19 +199,14 @@ __global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* 
                         Cr2[p] = gs::ffma2(cr, w2, Cr2[p]); Cg2[p] = gs::ffma2(cg, w2, Cg2[p]); Cb2[p] = gs::ffma2(cb, w2, Cb2[p]);
                         T2[p] = gs::fmul2(T2[p], gs::fsub2(gs::bc2(1.0f), alpha));            // :370
                         gs::up2(T2[p], Tn[0], Tn[1]);
-                        float xf[2];
-                        gs::up2(X2[p], xf[0], xf[1]);
 #pragma unroll
                         for (int h = 0; h < 2; h++) {
                             const int j = 2 * p + h;
                             Tp[j] = c2[h] ? To[h] : Tp[j];
                             last[j] = c2[h] ? idx : last[j];                                  // :372
                             if (COUNT) nC += c2[h] ? 1u : 0u;
-                            const bool go = Tn[h] > GS_T_EPS;                                 // :334 loop condition
-                            xf[h] = go ? xf[h] : qnan;
-                            alive |= (xf[h] == xf[h]);
+                            alive |= Tn[h] > GS_T_EPS;                                        // :334 loop condition
                         }
-                        X2[p] = gs::pk2(xf[0], xf[1]);
                     }
                     if (!__any_sync(0xFFFFFFFFu, alive)) { wlive = false; break; }
                 }
@@ -257,8 +258,7 @@ void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint
 void gs_launch_tile_ranges32(const uint32_t* sorted_tiles, uint32_t max_pairs, const uint32_t* d_n, uint32_t num_tiles,
                              uint2* ranges, cudaStream_t st) {
     if (num_tiles == 0) return;
-    const uint32_t work = (max_pairs + 3u) / 4u > num_tiles ? (max_pairs + 3u) / 4u : num_tiles;
-    tile_starts_kernel<<<(work + 255) / 256, 256, 0, st>>>(sorted_tiles, max_pairs, d_n, num_tiles, ranges);
+    tile_starts_kernel<<<148 * 8, 256, 0, st>>>(sorted_tiles, max_pairs, d_n, num_tiles, ranges);
     tile_counts_kernel<<<(num_tiles + 255) / 256, 256, 0, st>>>(max_pairs, d_n, num_tiles, ranges);
 }
 void gs_launch_rebuild_keys64(const uint32_t* sorted_tiles, const uint32_t* sorted_vals, const uint32_t* dkey, uint32_t n,

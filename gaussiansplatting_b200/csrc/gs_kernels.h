@@ -78,9 +78,10 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
                               const uint32_t* last_idx, const float* tfinal, float* acc, cudaStream_t st);
 
-// K8: per-Gaussian chain: moments -> parameter gradients, accumulated (+=) into the packed gradient planes
-void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, const float* acc, const float* V, float fx,
-                                   float fy, uint32_t n, GsGradPack G, int stat_mode, cudaStream_t st);
+// K8: per-Gaussian chain: moments -> parameter gradients, written to (accumulate = 0) or added into the packed gradient
+// planes; clears the moment rows it consumed
+void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, float* acc, const float* V, float fx,
+                                   float fy, uint32_t n, GsGradPack G, int stat_mode, int accumulate, cudaStream_t st);
 
 // layout conversion between the reference's AoS wire structs and the device SoA
 void gs_launch_params_from_aos(const void* aos112, uint32_t n, GsParams P, cudaStream_t st);

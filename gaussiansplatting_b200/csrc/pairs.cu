@@ -100,34 +100,43 @@ template <typename KeyT>
 __global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, const uint32_t* __restrict__ perm,
                                                          const uint32_t* __restrict__ offs, uint32_t n, uint32_t ntx,
                                                          KeyT* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap_pairs) {
-    __shared__ uint32_t s_off[257];
+    __shared__ uint32_t s_off[512];                           // [cnt+1 .. 511] = 0xFFFFFFFF: the search needs no bound test
     __shared__ uint32_t s_minx[256], s_miny[256], s_tx[256], s_dkey[256], s_gid[256];
+    __shared__ float s_rtx[256];
+    __shared__ uint32_t s_end;
     __shared__ gs::CullRec s_cull[256];
     const uint32_t g0 = blockIdx.x * 256u;
     const uint32_t i = g0 + threadIdx.x;
+    const uint32_t last = min(g0 + 256u, n);
+    const uint32_t cnt = last - g0;
+    s_off[256 + threadIdx.x] = 0xFFFFFFFFu;
     if (i < n) {
         const uint32_t g = perm ? perm[i] : i;
         s_gid[threadIdx.x] = g;
         s_off[threadIdx.x] = offs[i];
         const uint4 bb = O.bbox[g];
-        s_minx[threadIdx.x] = bb.x; s_miny[threadIdx.x] = bb.y; s_tx[threadIdx.x] = bb.z - bb.x + 1u;
+        const uint32_t tw = bb.z - bb.x + 1u;
+        s_minx[threadIdx.x] = bb.x; s_miny[threadIdx.x] = bb.y; s_tx[threadIdx.x] = tw;
+        s_rtx[threadIdx.x] = 1.0f / (float)tw;
         const float4 r0 = O.rec[3 * (size_t)g], r1 = O.rec[3 * (size_t)g + 1];
         const uint32_t k = __float_as_uint(O.rec[3 * (size_t)g + 2].y);        // depth
         s_dkey[threadIdx.x] = (k & 0x80000000u) ? ~k : (k | 0x80000000u);       // tiled_shaders.metal:773-774
         s_cull[threadIdx.x] = gs::cull_rec(r0, r1);
-    }
-    const uint32_t last = min(g0 + 256u, n);
-    const uint32_t cnt = last - g0;
-    if (threadIdx.x == 0) s_off[cnt] = offs[last];            // offs[n] holds the total
+    } else s_off[threadIdx.x] = 0xFFFFFFFFu;
+    if (threadIdx.x == 0) s_end = offs[last];                 // offs[n] holds the total
     __syncthreads();
-    const uint32_t begin = s_off[0], stop = min(s_off[cnt], cap_pairs);
+    const uint32_t begin = s_off[0], stop = min(s_end, cap_pairs);
+#pragma unroll 2
     for (uint32_t j = begin + threadIdx.x; j < stop; j += 256u) {
         // largest g in [0,cnt) with s_off[g] <= j   (offsets are non-decreasing; empty Gaussians are skipped)
-        uint32_t lo = 0, hi = cnt;
-        while (hi - lo > 1u) { uint32_t mid = (lo + hi) >> 1; if (s_off[mid] <= j) lo = mid; else hi = mid; }
-        const uint32_t k = j - s_off[lo];
+        uint32_t lo = 0;
+#pragma unroll
+        for (uint32_t sft = 128u; sft >= 1u; sft >>= 1) { if (s_off[lo + sft] <= j) lo += sft; }
+        const uint32_t k = j - s_off[lo];                     // < GS_MAX_TILES_PER_GAUSSIAN (256)
         const uint32_t tw = s_tx[lo];
-        const uint32_t ty = s_miny[lo] + k / tw, tx = s_minx[lo] + k % tw;        // :784-786
+        // k / tw for k, tw <= 256: (k + 0.5) / tw is at least 1/512 away from an integer, so the float product truncates exactly
+        const uint32_t row = (uint32_t)(((float)k + 0.5f) * s_rtx[lo]);
+        const uint32_t ty = s_miny[lo] + row, tx = s_minx[lo] + (k - row * tw);   // :784-786
         if (sizeof(KeyT) == 8) keys[j] = (KeyT)(((uint64_t)(ty * ntx + tx) << 32) | (uint64_t)s_dkey[lo]);   // :787
         else keys[j] = (KeyT)(ty * ntx + tx);
         vals[j] = s_gid[lo] | (tile_cannot_contribute(s_cull[lo], tx, ty) ? GS_CULL_BIT : 0u);
