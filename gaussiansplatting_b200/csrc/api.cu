@@ -18,6 +18,7 @@ struct gs_ctx {
     std::string err;
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
     cudaStream_t xfer_in = nullptr, xfer_out = nullptr;   // copy streams of the *_async image transfers (created on first use)
+    cudaStream_t xfer_meta = nullptr;                     // small read-backs (pair count) that must not queue behind an image
 };
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
@@ -93,6 +94,7 @@ int gs_ctx_destroy(gs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     if (c->xfer_in) { cudaStreamSynchronize(c->xfer_in); cudaStreamDestroy(c->xfer_in); }
     if (c->xfer_out) { cudaStreamSynchronize(c->xfer_out); cudaStreamDestroy(c->xfer_out); }
+    if (c->xfer_meta) { cudaStreamSynchronize(c->xfer_meta); cudaStreamDestroy(c->xfer_meta); }
     if (c->own_stream) cudaStreamDestroy(c->stream);
     cudaFreeHost(c->h_pinned);
     delete c;
@@ -103,6 +105,7 @@ int gs_ctx_sync(gs_ctx* c) {
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->xfer_in) GS_CUDA(c, cudaStreamSynchronize(c->xfer_in));
     if (c->xfer_out) GS_CUDA(c, cudaStreamSynchronize(c->xfer_out));
+    if (c->xfer_meta) GS_CUDA(c, cudaStreamSynchronize(c->xfer_meta));
     return GS_OK;
 }
 const char* gs_last_error(gs_ctx* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
@@ -459,6 +462,7 @@ struct gs_rast {
     const uint32_t* sorted_tiles = nullptr;  // hoisted mode: sorted u32 tile ids
     const uint64_t* sorted_keys = nullptr;   // 64-bit mode: sorted keys
     cudaEvent_t ev_pairs = nullptr;     // recorded after the pair count landed in pinned memory
+    cudaEvent_t ev_scan = nullptr;      // recorded on the compute stream after the scan (the copy-out stream waits on it)
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
@@ -553,6 +557,7 @@ int gs_rast_create(gs_ctx* c, uint32_t max_gaussians, gs_rast** out) {
     if (rc == GS_OK) rc = rast_reserve_gaussians(r, std::max(max_gaussians, 64u));
     if (rc == GS_OK) rc = rast_reserve_pairs(r, (uint64_t)std::max(max_gaussians, 64u) * 8);   // AVG_TILES_PER_GAUSSIAN, tiled_rasterizer.hpp:80
     if (rc == GS_OK && cudaEventCreateWithFlags(&r->ev_pairs, cudaEventDisableTiming) != cudaSuccess) rc = GS_ERR_CUDA;
+    if (rc == GS_OK && cudaEventCreateWithFlags(&r->ev_scan, cudaEventDisableTiming) != cudaSuccess) rc = GS_ERR_CUDA;
     if (rc != GS_OK) { gs_rast_destroy(r); return rc; }
     *out = r;
     return GS_OK;
@@ -567,6 +572,7 @@ int gs_rast_destroy(gs_rast* r) {
     cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
     cudaFree(r->counters);
     if (r->ev_pairs) cudaEventDestroy(r->ev_pairs);
+    if (r->ev_scan) cudaEventDestroy(r->ev_scan);
     for (int i = 0; i < GS_PROF_EVENTS; i++) if (r->ev[i]) cudaEventDestroy(r->ev[i]);
     delete r;
     return GS_OK;
@@ -631,8 +637,12 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     const uint32_t* perm = r->perm_buf[dres];
     r->mark(2);
     gs_launch_exclusive_scan(r->proj.cnt, perm, r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
-    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    GS_CUDA(c, cudaEventRecord(r->ev_pairs, st));
+    // the pair count travels to the host on the copy-out stream, so the compute stream never waits for a D2H copy
+    if (!c->xfer_meta) GS_CUDA(c, cudaStreamCreateWithFlags(&c->xfer_meta, cudaStreamNonBlocking));
+    GS_CUDA(c, cudaEventRecord(r->ev_scan, st));
+    GS_CUDA(c, cudaStreamWaitEvent(c->xfer_meta, r->ev_scan, 0));
+    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->xfer_meta));
+    GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
     r->mark(3);
     const GsSortPlan tplan = gs_sort_plan_even(0, tile_bits);
     r->passes = dplan.num_passes + tplan.num_passes;
