@@ -362,8 +362,12 @@ def run_ours(args):
             roofs[k] = {"bound": "fp32", "ms": stage[k], "achieved": a, "peak": fp32_peak, "unit": "TFLOP/s",
                         "frac": a / fp32_peak}
         dom = max((k for k in roofs), key=lambda k: stage[k])
-        out["roofline"] = dict(roofs[dom], kernel=dom, traffic=None, peak_kind=peak_kind,
-                               note="algorithmic bytes/flops per SURVEY 8(d); fp32 peak = 2*128*148*sm_max_mhz")
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this workload
+        # (profiles/r1i_blend_counters.txt); None for a workload or kernel that was not captured
+        ncu_traffic = {"blend_bwd": 119.0e6, "blend_fwd": 42.4e6} if args.workload == "C2" else {}
+        out["roofline"] = dict(roofs[dom], kernel=dom, traffic=ncu_traffic.get(dom), peak_kind=peak_kind,
+                               note="algorithmic bytes/flops per SURVEY 8(d); fp32 peak = 2*128*148*sm_max_mhz; traffic = DRAM "
+                                    "bytes per launch from profiles/r1i_blend_counters.txt (ncu), an FP32-issue-bound kernel")
         out["rooflines"] = roofs
         out["stage_ms"] = stage
         out["evals"] = {"E": E, "C": C, "pairs": P, "sort_passes": passes}
