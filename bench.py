@@ -461,10 +461,17 @@ def main():
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 training loop")
     ap.add_argument("--c3-epochs", type=int, default=100, help="epochs of 16 views for the config-3 loop")
     args = ap.parse_args()
+    # the contract is ONE JSON line on stdout: library chatter on fd 1 (e.g. "NCCL version ...") is sent to stderr, and
+    # print() keeps writing to the real stdout
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
