@@ -25,6 +25,7 @@ static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: 
 static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
 static void gs_set_sort_mode(int v);
 #define GS_PROF_EVENTS 11
+#define GS_MAX_BINS 4096u                            // binned mode up to 512x512 tiles (8192x8192 pixels); larger frames use the hoisted radix sort
 
 #define GS_SETDEV(c) cudaSetDevice((c)->device)
 #define GS_CUDA(c, expr)                                                                          \
@@ -449,6 +450,8 @@ struct gs_rast {
     uint32_t *iota = nullptr, *dk_buf[2] = {nullptr, nullptr}, *perm_buf[2] = {nullptr, nullptr};
     void* dsort_scratch = nullptr;
     uint2* ranges = nullptr;
+    // binned mode (binning.cu): per-tile totals, the bins' runs in the coarse-sorted list, chunk prefix per bin, per-chunk tile counts
+    uint32_t* tile_count = nullptr; uint2* bin_ranges = nullptr; uint32_t* cstart = nullptr; uint32_t* chunk_counts = nullptr;
     uint32_t* last_idx = nullptr;
     float* tfinal = nullptr;
     float* acc = nullptr;
@@ -456,7 +459,8 @@ struct gs_rast {
     // state left behind by forward for backward / inspection (tiled_rasterizer.hpp:94-106)
     uint32_t W = 0, H = 0, ntx = 0, nty = 0, n = 0;
     uint64_t pairs = 0;
-    int mode = 0;                       // sort mode of the last forward: 0 hoisted, 1 full 64-bit pair sort
+    uint64_t coarse_hint = 0;           // coarse pair count of the previous frame (sizes the chunk grids)
+    int mode = 0;                       // pair pipeline of the last forward: 0 binned, 1 full 64-bit pair sort, 2 hoisted radix
     int result = 0, passes = 0;
     const uint32_t* sorted_vals = nullptr;   // per-tile lists (bit 31 = GS_CULL_BIT)
     const uint32_t* sorted_tiles = nullptr;  // hoisted mode: sorted u32 tile ids
@@ -478,11 +482,11 @@ __global__ void iota_kernel(uint32_t* v, uint32_t n) {
 
 static void rast_free_gaussian_arrays(gs_rast* r) {
     cudaFree(r->proj.rec); cudaFree(r->proj.bbox); cudaFree(r->proj.aux); cudaFree(r->proj.covc); cudaFree(r->proj.offs);
-    cudaFree(r->proj.cnt); cudaFree(r->proj.dkey);
+    cudaFree(r->proj.cnt); cudaFree(r->proj.dkey); cudaFree(r->proj.ccnt);
     cudaFree(r->acc); cudaFree(r->scan_scratch); cudaFree(r->iota); cudaFree(r->dsort_scratch);
     for (int i = 0; i < 2; i++) { cudaFree(r->dk_buf[i]); cudaFree(r->perm_buf[i]); r->dk_buf[i] = nullptr; r->perm_buf[i] = nullptr; }
     r->proj.rec = nullptr; r->proj.bbox = nullptr; r->proj.aux = nullptr; r->proj.covc = nullptr; r->proj.offs = nullptr;
-    r->proj.cnt = nullptr; r->proj.dkey = nullptr;
+    r->proj.cnt = nullptr; r->proj.dkey = nullptr; r->proj.ccnt = nullptr;
     r->acc = nullptr; r->scan_scratch = nullptr; r->iota = nullptr; r->dsort_scratch = nullptr;
 }
 static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
@@ -498,6 +502,7 @@ static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     GS_TRY(dalloc(c, &r->proj.offs, (size_t)cap + 1));
     GS_TRY(dalloc(c, &r->proj.cnt, cap));
     GS_TRY(dalloc(c, &r->proj.dkey, cap));
+    GS_TRY(dalloc(c, &r->proj.ccnt, cap));
     GS_TRY(dalloc(c, &r->acc, (size_t)cap * 12));
     r->acc_clean = false;
     GS_TRY(dalloc(c, &r->iota, cap));
@@ -514,10 +519,13 @@ static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureB
     const uint32_t ntx = (W + GS_TILE - 1) / GS_TILE, nty = (H + GS_TILE - 1) / GS_TILE;
     if (ntx * nty > r->cap_tiles) {
         GS_CUDA(c, cudaStreamSynchronize(c->stream));
-        cudaFree(r->ranges); cudaFree(r->proj.tile_flags);
+        cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->tile_count); cudaFree(r->bin_ranges); cudaFree(r->cstart);
         r->cap_tiles = ntx * nty;
         GS_TRY(dalloc(c, &r->ranges, r->cap_tiles));
         GS_TRY(dalloc(c, &r->proj.tile_flags, r->cap_tiles));
+        GS_TRY(dalloc(c, &r->tile_count, r->cap_tiles));
+        GS_TRY(dalloc(c, &r->bin_ranges, (size_t)r->cap_tiles + 2));      // bins <= tiles
+        GS_TRY(dalloc(c, &r->cstart, (size_t)r->cap_tiles + 2));
     }
     if (W * H > r->cap_pix) {
         GS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -533,14 +541,15 @@ static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapac
     if (need <= r->cap_pairs) return GS_OK;
     gs_ctx* c = r->c;
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
-    cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch);
+    cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch); cudaFree(r->chunk_counts);
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); r->kbuf[i] = nullptr; r->vbuf[i] = nullptr; }
-    r->keys_in = nullptr; r->vals_in = nullptr; r->sort_scratch = nullptr;
+    r->keys_in = nullptr; r->vals_in = nullptr; r->sort_scratch = nullptr; r->chunk_counts = nullptr;
     const uint64_t cap = std::max<uint64_t>(need, (uint64_t)(r->cap_pairs * 1.5));
     GS_TRY(dalloc(c, &r->keys_in, cap));
     GS_TRY(dalloc(c, &r->vals_in, cap));
     for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->kbuf[i], cap)); GS_TRY(dalloc(c, &r->vbuf[i], cap)); }
     GS_CUDA(c, cudaMalloc(&r->sort_scratch, gs_sort_scratch_bytes(cap, 8)));
+    GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * 64));
     r->cap_pairs = cap;
     return GS_OK;
 }
@@ -570,6 +579,7 @@ int gs_rast_destroy(gs_rast* r) {
     cudaFree(r->meta); cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch);
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); }
     cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
+    cudaFree(r->tile_count); cudaFree(r->bin_ranges); cudaFree(r->cstart); cudaFree(r->chunk_counts);
     cudaFree(r->counters);
     if (r->ev_pairs) cudaEventDestroy(r->ev_pairs);
     if (r->ev_scan) cudaEventDestroy(r->ev_scan);
@@ -673,9 +683,69 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     return GS_OK;
 }
 
+
+// Binned mode (default): depth order on the N Gaussians, coarse (bin, Gaussian) pairs in that order, ONE stable sort of
+// the coarse pairs by bin id, then per-bin expansion straight into the per-tile lists and ranges (binning.cu).  Same
+// lists and ranges as the other two modes; no sort over the P pairs.
+static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
+    gs_ctx* c = r->c;
+    cudaStream_t st = c->stream;
+    const uint32_t n = r->n, W = r->W, H = r->H;
+    const uint32_t tiles = r->ntx * r->nty, nbins = gs_bin_count(r->ntx, r->nty);
+    int bin_bits = 0;
+    while ((1u << bin_bits) < nbins) bin_bits++;
+    const GsSortPlan dplan = gs_sort_plan(0, 31, ~0ull);
+    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, GS_SORT_HINT_DISTINCT, r->dsort_scratch, st);
+    const uint32_t* perm = r->perm_buf[dres];
+    r->mark(2);
+    uint32_t* d_coarse = r->meta + GS_META_COARSE_PAIRS;
+    uint32_t* d_total = r->meta + GS_META_TOTAL_PAIRS;
+    gs_launch_exclusive_scan(r->proj.ccnt, perm, r->proj.offs, n, d_coarse, r->scan_scratch, st);
+    r->mark(3);
+    const GsSortPlan bplan = gs_sort_plan_even(0, bin_bits);
+    r->passes = dplan.num_passes + bplan.num_passes;
+    if (!c->xfer_meta) GS_CUDA(c, cudaStreamCreateWithFlags(&c->xfer_meta, cudaStreamNonBlocking));
+    for (int attempt = 0; attempt < 4; attempt++) {
+        uint32_t* bk_in = reinterpret_cast<uint32_t*>(r->keys_in);
+        uint32_t* bk[2] = {reinterpret_cast<uint32_t*>(r->kbuf[0]), reinterpret_cast<uint32_t*>(r->kbuf[1])};
+        const uint32_t cap = (uint32_t)std::min<uint64_t>(r->cap_pairs, 0x3FFFFFFFull);
+        gs_launch_emit_coarse(r->proj, perm, r->proj.offs, n, r->ntx, bk_in, r->vals_in, cap, st);
+        r->mark(4);
+        const int res = gs_launch_sort32(bk_in, r->vals_in, bk, r->vbuf, cap, d_coarse, bplan, g_tile_sort_hint, r->sort_scratch, st);
+        const uint32_t* sorted_bins = bplan.num_passes ? bk[res] : bk_in;
+        const uint32_t* cvals = bplan.num_passes ? r->vbuf[res] : r->vals_in;
+        uint32_t* lists = r->vbuf[bplan.num_passes ? (res ^ 1) : 0];
+        r->mark(5);
+        gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
+        gs_launch_bin_expand(r->proj, cvals, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
+                             d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u, st);
+        r->result = 0;
+        r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;
+        // the pair counts travel to the host on their own copy stream; the compute stream carries on with the blend
+        GS_CUDA(c, cudaEventRecord(r->ev_scan, st));
+        GS_CUDA(c, cudaStreamWaitEvent(c->xfer_meta, r->ev_scan, 0));
+        GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->xfer_meta));
+        GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
+        r->mark(6);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+        r->mark(7);
+        GS_LAUNCH_CHECK(c);
+        GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));                   // the GPU is still busy with the kernels above
+        const uint64_t Pc = c->h_pinned[GS_META_COARSE_PAIRS], P = c->h_pinned[GS_META_TOTAL_PAIRS];
+        if (Pc >= (1ull << 30) || P >= (1ull << 30)) { c->err = "pair count exceeds 2^30"; return GS_ERR_CAPACITY; }
+        r->pairs = P;
+        r->coarse_hint = Pc;
+        if (Pc <= r->cap_pairs && P <= r->cap_pairs) break;
+        // rare: grow (synchronises) and redo the pair stages; a clipped coarse list under-counts P, so grow generously then
+        GS_TRY(rast_reserve_pairs(r, Pc > r->cap_pairs ? std::max<uint64_t>(Pc * 4, r->cap_pairs * 2) : P));
+    }
+    (void)u; (void)g; (void)tiles;
+    return GS_OK;
+}
+
 static int g_sort_mode = 0;
 }  // extern "C"
-static void gs_set_sort_mode(int v) { g_sort_mode = v ? 1 : 0; }
+static void gs_set_sort_mode(int v) { g_sort_mode = (v == 1 || v == 2) ? v : 0; }
 extern "C" {
 
 int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
@@ -687,6 +757,7 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     GS_TRY(rast_reserve_gaussians(r, n));
     GS_TRY(rast_reserve_image(r, W, H));
     r->n = n; r->pairs = 0; r->passes = 0; r->mode = g_sort_mode;
+    if (r->mode == 0 && gs_bin_count(r->ntx, r->nty) > GS_MAX_BINS) r->mode = 2;
     // meta: total = 0, key OR = 0, key AND = ~0
     GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
     GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
@@ -695,7 +766,7 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
                          u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
     r->mark(1);
-    GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : forward_hoisted(r, g, u, out));
+    GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : r->mode == 2 ? forward_hoisted(r, g, u, out) : forward_binned(r, g, u, out));
     return image_after_use(out, st);
 }
 
@@ -794,7 +865,8 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
             if (r->mode == 1) src = r->sorted_keys;
             else if (r->pairs) {
                 GS_CUDA(c, cudaMalloc(&tmp[0], r->pairs * 8));
-                gs_launch_rebuild_keys64(r->sorted_tiles, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
+                if (r->mode == 0) gs_launch_rebuild_keys64_ranges(r->ranges, r->ntx * r->nty, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
+                else gs_launch_rebuild_keys64(r->sorted_tiles, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
                 src = tmp[0];
             }
             need = r->pairs * 8; break;

@@ -1,0 +1,314 @@
+// binning.cu — per-tile lists by two-level binning (default pair pipeline, `sort_mode` 0).
+//
+// What it replaces: generateTilePairs + the 64-bit (tile|depth) sort + buildTileRanges (tiled_shaders.metal:745-794,
+// tiled_rasterizer.mm:27-102 / gpu_sort.mm:456-676, sort.metal:553-589).  The result is the same, element for element:
+// for every tile the Gaussians that overlap it in (depth key, Gaussian index) order, and the tile ranges.
+//
+// The Gaussians are already in depth order (K4a, on N keys).  Instead of duplicating every Gaussian into its ~7 tiles and
+// radix-sorting P pairs by tile id, each Gaussian is duplicated into the COARSE bins (8x8 tiles) its bounding box
+// touches (~1.8 per Gaussian at 1080p), the coarse pairs are stably sorted by bin id (ONE onesweep pass over P/4
+// pairs when there are <= 256 bins), and each bin is then expanded locally:
+//   chunk map   a bin's sorted run is cut into chunks of 256 coarse entries; chunk -> (bin, offset) through a prefix table
+//   count       per chunk, per tile of the bin (64 of them): how many of the chunk's entries cover the tile (warp ballots)
+//   bin scan    per bin, per tile: exclusive prefix of those counts over the bin's chunks, and the tile's total
+//   tile scan   exclusive prefix of the tile totals = TileRange.start; the grand total is the pair count P
+//   fill        per chunk again: every (entry, covered tile) gets slot start[tile] + chunk prefix + rank inside the chunk
+//               (ballot word + popc), evaluates the footprint test of pairs.cu for the cull bit, and stores the id
+// Every step is order preserving, so a tile's list comes out in depth order without a sort over the P pairs.
+#include "gs_common.cuh"
+#include "gs_kernels.h"
+
+namespace {
+
+constexpr uint32_t BT = 8;            // tiles per bin side: a bin's tiles fit one 64-bit mask
+constexpr uint32_t CH = 256;          // coarse entries per chunk = threads per CTA
+constexpr uint32_t NWARP = CH / 32;
+
+// K3c: coarse key duplication.  One block = 256 consecutive Gaussians of the depth order; the block's coarse pairs form one
+// contiguous output run (offsets from the scan of ccnt), owner of an output slot by fixed-step search in smem.
+__global__ void __launch_bounds__(256) emit_coarse_kernel(GsProjected O, const uint32_t* __restrict__ perm,
+                                                          const uint32_t* __restrict__ offs, uint32_t n, uint32_t nbx,
+                                                          uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap) {
+    __shared__ uint32_t s_off[512];
+    __shared__ uint32_t s_bx[256], s_by[256], s_bw[256], s_gid[256];
+    __shared__ float s_rbw[256];
+    __shared__ uint32_t s_end;
+    const uint32_t g0 = blockIdx.x * 256u;
+    const uint32_t i = g0 + threadIdx.x;
+    const uint32_t last = min(g0 + 256u, n);
+    s_off[256 + threadIdx.x] = 0xFFFFFFFFu;
+    if (i < n) {
+        const uint32_t g = perm[i];
+        s_gid[threadIdx.x] = g;
+        s_off[threadIdx.x] = offs[i];
+        const uint4 bb = O.bbox[g];
+        const uint32_t bw = (bb.z / BT) - (bb.x / BT) + 1u;
+        s_bx[threadIdx.x] = bb.x / BT; s_by[threadIdx.x] = bb.y / BT; s_bw[threadIdx.x] = bw;
+        s_rbw[threadIdx.x] = 1.0f / (float)bw;
+    } else s_off[threadIdx.x] = 0xFFFFFFFFu;
+    if (threadIdx.x == 0) s_end = offs[last];
+    __syncthreads();
+    const uint32_t begin = s_off[0], stop = min(s_end, cap);
+    for (uint32_t j = begin + threadIdx.x; j < stop; j += 256u) {
+        uint32_t lo = 0;
+#pragma unroll
+        for (uint32_t sft = 128u; sft >= 1u; sft >>= 1) { if (s_off[lo + sft] <= j) lo += sft; }
+        const uint32_t k = j - s_off[lo];                     // < 290 coarse bins per Gaussian (256 tiles in a strip)
+        const uint32_t bw = s_bw[lo];
+        const uint32_t row = (uint32_t)(((float)k + 0.5f) * s_rbw[lo]);
+        keys[j] = (s_by[lo] + row) * nbx + s_bx[lo] + (k - row * bw);
+        vals[j] = s_gid[lo];
+    }
+}
+
+// chunk map: cstart[b] = number of chunks of the bins before b; cstart[nbins] = total.  One CTA.
+__global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict__ bin_ranges, uint32_t nbins, uint32_t* __restrict__ cstart) {
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nbins; base += 1024u) {
+        const uint32_t b = base + threadIdx.x;
+        const uint32_t c = b < nbins ? (bin_ranges[b].y + CH - 1u) / CH : 0u;
+        uint32_t total;
+        const uint32_t ex = gs::cta_excl_scan<32>(c, s_w, &total);
+        const uint32_t carry = s_carry;
+        if (b < nbins) cstart[b] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry = carry + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) cstart[nbins] = s_carry;
+}
+
+struct ChunkCtx { uint32_t bin, first, count; };   // the chunk's bin, first coarse entry, entries in the chunk
+__device__ __forceinline__ ChunkCtx locate_chunk(uint32_t chunk, const uint32_t* s_cstart, uint32_t nbins, const uint2* __restrict__ bin_ranges) {
+    uint32_t lo = 0, hi = nbins;                               // largest b with cstart[b] <= chunk (empty bins share a value: take the last)
+    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (s_cstart[mid] <= chunk) lo = mid; else hi = mid; }
+    const uint2 br = bin_ranges[lo];
+    const uint32_t off = (chunk - s_cstart[lo]) * CH;
+    ChunkCtx c; c.bin = lo; c.first = br.x + off; c.count = min(CH, br.y - off);
+    return c;
+}
+
+// rectangle of local tiles (within bin bx,by) that bbox bb covers
+struct BinRect { uint32_t x0, y0, w, h; };
+__device__ __forceinline__ BinRect bin_rect(const uint4 bb, uint32_t bx, uint32_t by) {
+    const uint32_t ox = bx * BT, oy = by * BT;
+    BinRect r;
+    r.x0 = max(bb.x, ox) - ox; r.y0 = max(bb.y, oy) - oy;
+    r.w = min(bb.z, ox + BT - 1u) - ox - r.x0 + 1u; r.h = min(bb.w, oy + BT - 1u) - oy - r.y0 + 1u;
+    return r;
+}
+
+// count: chunk_counts[chunk][t] = entries of the chunk covering local tile t.  Every entry covers a RECTANGLE of the
+// bin's 8x8 tiles, so it adds +1/-1 at the four corners of a 9x9 difference grid (shared-memory atomics, four per entry
+// whatever its size) and 64 threads take the 2-D prefix sum.  Grid-stride over the chunks.
+__global__ void __launch_bounds__(CH) bin_count_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
+                                                       const uint32_t* __restrict__ cstart, uint32_t nbins, uint32_t nbx,
+                                                       uint32_t* __restrict__ chunk_counts) {
+    extern __shared__ uint32_t s_dyn[];
+    uint32_t* s_cstart = s_dyn;                                // nbins + 1
+    __shared__ int s_diff[9][9];
+    for (uint32_t i = threadIdx.x; i <= nbins; i += CH) s_cstart[i] = cstart[i];
+    __syncthreads();
+    const uint32_t total = s_cstart[nbins];
+    for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
+        const ChunkCtx cc = locate_chunk(chunk, s_cstart, nbins, bin_ranges);
+        if (threadIdx.x < 81u) (&s_diff[0][0])[threadIdx.x] = 0;
+        __syncthreads();
+        if (threadIdx.x < cc.count) {
+            const uint32_t g = cvals[cc.first + threadIdx.x];
+            const BinRect r = bin_rect(O.bbox[g], cc.bin % nbx, cc.bin / nbx);
+            atomicAdd(&s_diff[r.y0][r.x0], 1); atomicAdd(&s_diff[r.y0][r.x0 + r.w], -1);
+            atomicAdd(&s_diff[r.y0 + r.h][r.x0], -1); atomicAdd(&s_diff[r.y0 + r.h][r.x0 + r.w], 1);
+        }
+        __syncthreads();
+        if (threadIdx.x < 64u) {
+            const uint32_t tx = threadIdx.x & 7u, ty = threadIdx.x >> 3;
+            int sum = 0;
+            for (uint32_t y = 0; y <= ty; y++)
+                for (uint32_t x = 0; x <= tx; x++) sum += s_diff[y][x];
+            chunk_counts[(size_t)chunk * 64u + threadIdx.x] = (uint32_t)sum;
+        }
+        __syncthreads();
+    }
+}
+
+// bin scan: one CTA per bin, 16 groups x 64 tiles.  chunk_counts[c][t] becomes the exclusive prefix over the bin's chunks;
+// tile_count[global tile] = the tile's total (0 for a bin without entries; tiles outside the image are skipped).
+__global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restrict__ cstart, uint32_t nbx, uint32_t ntx, uint32_t nty,
+                                                        uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count) {
+    __shared__ uint32_t s_part[16][64];
+    const uint32_t b = blockIdx.x;
+    const uint32_t t = threadIdx.x & 63u, grp = threadIdx.x >> 6;
+    const uint32_t c0 = cstart[b], c1 = cstart[b + 1];
+    const uint32_t nch = c1 - c0, per = (nch + 15u) / 16u;
+    const uint32_t a = min(c0 + grp * per, c1), e = min(a + per, c1);
+    uint32_t s = 0;
+    for (uint32_t c = a; c < e; c++) s += chunk_counts[(size_t)c * 64u + t];
+    s_part[grp][t] = s;
+    __syncthreads();
+    uint32_t run = 0, tot = 0;
+#pragma unroll
+    for (uint32_t g = 0; g < 16u; g++) { const uint32_t v = s_part[g][t]; if (g < grp) run += v; tot += v; }
+    for (uint32_t c = a; c < e; c++) {
+        const uint32_t v = chunk_counts[(size_t)c * 64u + t];
+        chunk_counts[(size_t)c * 64u + t] = run;
+        run += v;
+    }
+    if (grp == 0) {
+        const uint32_t tx = (b % nbx) * BT + (t & 7u), ty = (b / nbx) * BT + (t >> 3);
+        if (tx < ntx && ty < nty) tile_count[ty * ntx + tx] = tot;
+    }
+}
+
+// tile scan: ranges[t] = (exclusive prefix, count); *total = pair count.  One CTA.
+// Ranges are clipped to the list capacity: when the pair buffers turn out too small the frame is redone by the host, and
+// the kernels of the clipped attempt must stay inside the buffers.
+__global__ void __launch_bounds__(1024) tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t ntiles, uint2* __restrict__ ranges,
+                                                         uint32_t* __restrict__ total, uint32_t cap_pairs) {
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < ntiles; base += 8192u) {
+        const uint32_t t0 = base + threadIdx.x * 8u;
+        uint32_t c[8], sum = 0;
+#pragma unroll
+        for (uint32_t q = 0; q < 8u; q++) { c[q] = (t0 + q < ntiles) ? tile_count[t0 + q] : 0u; sum += c[q]; }
+        uint32_t tot;
+        uint32_t ex = gs::cta_excl_scan<32>(sum, s_w, &tot) + s_carry;
+#pragma unroll
+        for (uint32_t q = 0; q < 8u; q++) {
+            if (t0 + q < ntiles) { const uint32_t a = min(ex, cap_pairs); ranges[t0 + q] = make_uint2(a, min(c[q], cap_pairs - a)); }
+            ex += c[q];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = s_carry;
+}
+
+// fill: every (entry, covered tile) of the chunk is stored at start[tile] + prefix over earlier chunks + rank in the chunk.
+// Phase A (one thread per entry): rectangle, footprint record and pair count into shared memory; per warp the ballot
+// word of every tile (which lanes cover it) and from those the slot of each warp's first covering entry.
+// Phase B (one thread per PAIR, so large splats do not unbalance a warp): owner entry by fixed-step search over the
+// scanned pair counts, tile from the rectangle, rank = popc of the ballot word below the owner's lane.
+__global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
+                                                      const uint32_t* __restrict__ cstart, uint32_t nbins, uint32_t nbx, uint32_t ntx,
+                                                      uint32_t nty, const uint32_t* __restrict__ chunk_prefix,
+                                                      const uint2* __restrict__ ranges, uint32_t* __restrict__ out_vals, uint32_t cap_pairs) {
+    extern __shared__ uint32_t s_dyn[];
+    uint32_t* s_cstart = s_dyn;
+    __shared__ uint32_t s_ball[NWARP][64];                     // ballot word per (warp, tile)
+    __shared__ uint32_t s_base[NWARP][64];                     // slot of the warp's first covering entry per tile
+    __shared__ uint32_t s_off[2 * CH];                         // exclusive scan of the entries' pair counts; [CH..] = sentinel
+    __shared__ uint32_t s_rect[CH], s_gid[CH];
+    __shared__ gs::CullRec s_cull[CH];
+    __shared__ uint32_t s_w[NWARP];
+    for (uint32_t i = threadIdx.x; i <= nbins; i += CH) s_cstart[i] = cstart[i];
+    s_off[CH + threadIdx.x] = 0xFFFFFFFFu;
+    __syncthreads();
+    const uint32_t total = s_cstart[nbins];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
+        const ChunkCtx cc = locate_chunk(chunk, s_cstart, nbins, bin_ranges);
+        const uint32_t bx = cc.bin % nbx, by = cc.bin / nbx;
+        unsigned long long mask = 0ull;
+        uint32_t np = 0;
+        if (threadIdx.x < cc.count) {
+            const uint32_t g = cvals[cc.first + threadIdx.x];
+            const BinRect r = bin_rect(O.bbox[g], bx, by);
+            const unsigned long long row = (unsigned long long)(((1u << r.w) - 1u) << r.x0);
+            for (uint32_t y = r.y0; y < r.y0 + r.h; y++) mask |= row << (8u * y);
+            np = r.w * r.h;
+            s_rect[threadIdx.x] = r.x0 | (r.y0 << 4) | (r.w << 8) | ((0x10000u / r.w + 1u) << 12);   // x0, y0 < 8, w <= 8, 17-bit reciprocal
+            s_gid[threadIdx.x] = g;
+            s_cull[threadIdx.x] = gs::cull_rec(O.rec[3 * (size_t)g], O.rec[3 * (size_t)g + 1]);
+        }
+        uint32_t npairs;
+        const uint32_t ex = gs::cta_excl_scan<NWARP>(np, s_w, &npairs);
+        s_off[threadIdx.x] = threadIdx.x < cc.count ? ex : 0xFFFFFFFFu;
+        const uint32_t mlo = (uint32_t)mask, mhi = (uint32_t)(mask >> 32);
+#pragma unroll
+        for (uint32_t t = 0; t < 32u; t++) {
+            const uint32_t a = __ballot_sync(0xFFFFFFFFu, (mlo >> t) & 1u);
+            const uint32_t b = __ballot_sync(0xFFFFFFFFu, (mhi >> t) & 1u);
+            if (lane == t) { s_ball[warp][t] = a; s_ball[warp][t + 32u] = b; }
+        }
+        __syncthreads();
+        if (threadIdx.x < 64u) {
+            const uint32_t t = threadIdx.x;
+            const uint32_t tx = bx * BT + (t & 7u), ty = by * BT + (t >> 3);
+            uint32_t run = (tx < ntx && ty < nty) ? ranges[ty * ntx + tx].x + chunk_prefix[(size_t)chunk * 64u + t] : 0u;
+#pragma unroll
+            for (uint32_t w = 0; w < NWARP; w++) { s_base[w][t] = run; run += __popc(s_ball[w][t]); }
+        }
+        __syncthreads();
+        for (uint32_t j = threadIdx.x; j < npairs; j += CH) {
+            uint32_t e = 0;
+#pragma unroll
+            for (uint32_t sft = CH / 2; sft >= 1u; sft >>= 1) { if (s_off[e + sft] <= j) e += sft; }
+            const uint32_t k = j - s_off[e];                   // < 64
+            const uint32_t rc = s_rect[e];
+            const uint32_t w = (rc >> 8) & 0xFu;
+            const uint32_t row = (k * (rc >> 12)) >> 16;       // k / w for k < 64, w <= 8 (reciprocal 65536/w + 1, exact in that range)
+            const uint32_t lx = (rc & 0xFu) + (k - row * w), ly = ((rc >> 4) & 0xFu) + row;
+            const uint32_t t = ly * 8u + lx;
+            const uint32_t ew = e >> 5, el = e & 31u;
+            const uint32_t slot = s_base[ew][t] + __popc(s_ball[ew][t] & ((1u << el) - 1u));
+            const uint32_t tx = bx * BT + lx, ty = by * BT + ly;
+            const bool cull = gs::box_cannot_contribute(s_cull[e], (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
+            if (slot < cap_pairs) out_vals[slot] = s_gid[e] | (cull ? GS_CULL_BIT : 0u);
+        }
+        __syncthreads();
+    }
+}
+
+// sorted 64-bit keys of the reference for inspection: slot j belongs to the last tile whose start is <= j
+__global__ void __launch_bounds__(256) rebuild_keys64_ranges_kernel(const uint2* __restrict__ ranges, uint32_t ntiles,
+                                                                    const uint32_t* __restrict__ vals, const uint32_t* __restrict__ dkey,
+                                                                    uint32_t n, uint64_t* __restrict__ keys) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    uint32_t lo = 0, hi = ntiles;
+    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (ranges[mid].x <= j) lo = mid; else hi = mid; }
+    keys[j] = ((uint64_t)lo << 32) | (uint64_t)dkey[vals[j] & GS_ID_MASK];
+}
+
+}  // namespace
+
+uint32_t gs_bin_count(uint32_t ntx, uint32_t nty) { return ((ntx + BT - 1u) / BT) * ((nty + BT - 1u) / BT); }
+uint32_t gs_bin_nbx(uint32_t ntx) { return (ntx + BT - 1u) / BT; }
+// chunks needed for `coarse_cap` coarse entries spread over `nbins` bins (every bin may end with a partial chunk)
+size_t gs_bin_max_chunks(uint64_t coarse_cap, uint32_t nbins) { return (size_t)(coarse_cap / CH) + nbins + 1; }
+
+void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
+                           uint32_t* bin_keys, uint32_t* vals, uint32_t cap, cudaStream_t st) {
+    if (n == 0) return;
+    emit_coarse_kernel<<<(n + 255) / 256, 256, 0, st>>>(O, perm, offs, n, gs_bin_nbx(ntx), bin_keys, vals, cap);
+}
+
+void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint2* bin_ranges, uint32_t ntx, uint32_t nty,
+                          uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st) {
+    const uint32_t nbx = gs_bin_nbx(ntx), nbins = gs_bin_count(ntx, nty);
+    if (nbins == 0) return;
+    const size_t dyn = ((size_t)nbins + 1) * sizeof(uint32_t);
+    // The number of chunks lives on the device; the chunk kernels stride over it, so any grid is correct.  The caller
+    // sizes the grid from the previous frame's coarse count (one chunk per CTA: the chunk's dependent gathers of many
+    // CTAs overlap), falling back to a persistent grid.
+    const uint32_t grid = grid_chunks > 148u * 4u ? grid_chunks : 148u * 4u;
+    chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart);
+    bin_count_kernel<<<grid, CH, dyn, st>>>(O, cvals, bin_ranges, cstart, nbins, nbx, chunk_counts);
+    bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count);
+    tile_scan_kernel<<<1, 1024, 0, st>>>(tile_count, ntx * nty, ranges, total_pairs, cap_pairs);
+    bin_fill_kernel<<<grid, CH, dyn, st>>>(O, cvals, bin_ranges, cstart, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+}
+
+void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
+                                     uint32_t n, uint64_t* keys, cudaStream_t st) {
+    if (n) rebuild_keys64_ranges_kernel<<<(n + 255) / 256, 256, 0, st>>>(ranges, ntiles, sorted_vals, dkey, n, keys);
+}

@@ -212,6 +212,7 @@ struct GsProjected {
     float4* aux;     // viewPos.x, viewPos.y, cov2D.a, cov2D.b
     float* covc;     // cov2D.c
     uint32_t* cnt;   // tiles this Gaussian emits (0 = culled / fails generateTilePairs' admission tests)
+    uint32_t* ccnt;  // coarse bins (8x8 tiles) its bounding box touches, 0 when cnt == 0 (binning.cu)
     uint32_t* dkey;  // sortable depth bits (tiled_shaders.metal:773-774); 0xFFFFFFFF when cnt == 0
     uint32_t* offs;  // exclusive scan of cnt in emission order (Gaussian order, or depth order in hoisted mode); [n] = total
     uint32_t* tile_flags;  // per TILE: 1 if the forward walked a conic-degenerate entry (backward then redoes pass 1)

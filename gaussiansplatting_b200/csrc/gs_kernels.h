@@ -6,7 +6,7 @@
 #include "gs_common.cuh"
 
 // meta words written by preprocess / scan (one small device array per rasterizer)
-enum { GS_META_TOTAL_PAIRS = 0, GS_META_KEY_OR = 1, GS_META_KEY_AND = 2, GS_META_COUNT = 4 };
+enum { GS_META_TOTAL_PAIRS = 0, GS_META_KEY_OR = 1, GS_META_KEY_AND = 2, GS_META_COARSE_PAIRS = 3, GS_META_COUNT = 5 };
 
 // K1 ------------------------------------------------------------------------------------------------
 void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* V, const float* VP, float sw, float sh,
@@ -82,6 +82,18 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
 // planes; clears the moment rows it consumed
 void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, float* acc, const float* V, float fx,
                                    float fy, uint32_t n, GsGradPack G, int stat_mode, int accumulate, cudaStream_t st);
+
+// two-level binning (binning.cu): coarse (8x8-tile bin, Gaussian) pairs in depth order, then per-bin expansion into the
+// per-tile lists and tile ranges
+uint32_t gs_bin_count(uint32_t ntx, uint32_t nty);
+size_t gs_bin_max_chunks(uint64_t coarse_cap, uint32_t nbins);
+void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
+                           uint32_t* bin_keys, uint32_t* vals, uint32_t cap, cudaStream_t st);
+void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint2* bin_ranges, uint32_t ntx, uint32_t nty,
+                          uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st);
+void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
+                                     uint32_t n, uint64_t* keys, cudaStream_t st);
 
 // layout conversion between the reference's AoS wire structs and the device SoA
 void gs_launch_params_from_aos(const void* aos112, uint32_t n, GsParams P, cudaStream_t st);

@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
         O.rec[3 * (size_t)i + 0] = r0; O.rec[3 * (size_t)i + 1] = r1; O.rec[3 * (size_t)i + 2] = r2;
         O.bbox[i] = bb; O.aux[i] = ax; O.covc[i] = cc;
         O.cnt[i] = count;
+        O.ccnt[i] = count ? ((bb.z >> 3) - (bb.x >> 3) + 1u) * ((bb.w >> 3) - (bb.y >> 3) + 1u) : 0u;
         O.dkey[i] = count ? dkey : 0xFFFFFFFFu;
     }
     // depth-key OR / AND over Gaussians that emit pairs: digits whose bits never vary need no sort pass

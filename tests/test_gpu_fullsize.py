@@ -1,6 +1,7 @@
 """Full-size (BASELINE config 2: 1 M Gaussians, 1920x1080) checks through size-independent properties — the oracle needs
 seconds per frame at this size, so it is not run here:
-  * the hoisted sort (depth passes on N Gaussians, tile passes on P pairs) and the full 64-bit pair sort must give the SAME
+  * the binned pipeline (default), the hoisted sort (depth passes on N Gaussians, tile passes on P pairs) and the full
+    64-bit pair sort must give the SAME
     sorted keys, per-tile lists, tile ranges, lastContribIdx and image, bit for bit;
   * sortedness, permutation, range contiguity / coverage (the reference's own run-time checks, tiled_rasterizer.mm:577-636);
   * idempotence of forward; linearity of the backward accumulation over views; culled-pair marking never changes results.
@@ -12,9 +13,10 @@ from gaussiansplatting_b200 import synth
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(scope="module")
-def c2(gs, ctx):
-    wl = "C2"
+@pytest.fixture(scope="module", params=["C2", "C4"])
+def c2(request, gs, ctx):
+    """BASELINE config 2 (1 M Gaussians, 1920x1080) and config 4 (3 M Gaussians, 3840x2160)"""
+    wl = request.param
     n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
     G = gs.Gaussians(ctx, n); G.upload(synth.make_scene(n, synth.CONFIG_SEED[wl], synth.CONFIG_S0[wl]))
     R = gs.Rasterizer(ctx, n)
@@ -35,12 +37,15 @@ def snapshot(gs, c2, mode):
                 keys=R.get(gs.RAST_KEYS), vals=R.get(gs.RAST_VALUES))
 
 
-def test_hoisted_sort_equals_pair_sort_at_full_size(gs, c2):
+def test_all_three_pair_pipelines_agree_at_full_size(gs, c2):
+    """sort_mode 0 (two-level binning, default), 1 (the reference's literal 64-bit pair sort), 2 (hoisted radix sort)"""
     a, b = snapshot(gs, c2, 0), snapshot(gs, c2, 1)
-    assert a["pairs"] == b["pairs"] and a["pairs"] > 5_000_000
-    for k in ("keys", "vals", "skeys", "svals", "last", "image"):
-        assert np.array_equal(a[k], b[k]), k
-    assert np.array_equal(a["ranges"]["start"], b["ranges"]["start"]) and np.array_equal(a["ranges"]["count"], b["ranges"]["count"])
+    assert a["pairs"] == b["pairs"] and a["pairs"] > 5_000_000 and a["pairs"] <= c2["R"].pair_count
+    for other in (b, snapshot(gs, c2, 2)):
+        assert other["pairs"] == a["pairs"]
+        for k in ("keys", "vals", "skeys", "svals", "last", "image"):
+            assert np.array_equal(a[k], other[k]), k
+        assert np.array_equal(a["ranges"]["start"], other["ranges"]["start"]) and np.array_equal(a["ranges"]["count"], other["ranges"]["count"])
     P = a["pairs"]
     sk = a["skeys"]
     assert np.all(sk[1:] >= sk[:-1])                                            # sorted

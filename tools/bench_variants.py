@@ -19,7 +19,7 @@ cams = [synth.make_camera(v, 64, W, H, n, synth.CONFIG_ORBIT[wl]) for v in range
 R.forward(Gt, cams[0], gti)
 R.set_profiling(True)
 ref = None
-for mode, fp, bp in ((0, 2, 2), (0, 4, 4), (0, 2, 4), (0, 4, 2)):
+for mode, fp, bp in ((0, 2, 2), (2, 2, 2), (1, 2, 2)):
     gs.tune("sort_mode", mode); gs.tune("fwd_ppt", fp); gs.tune("bwd_ppt", bp)
     acc = None
     for i in range(3 + reps):
