@@ -716,8 +716,9 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         const uint32_t* cvals = bplan.num_passes ? r->vbuf[res] : r->vals_in;
         uint32_t* lists = r->vbuf[bplan.num_passes ? (res ^ 1) : 0];
         r->mark(5);
-        gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
-        gs_launch_bin_expand(r->proj, cvals, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
+        const uint32_t* bin_hist = bplan.num_passes == 1 ? gs_sort_pass_histogram(r->sort_scratch, 0) : nullptr;
+        if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
+        gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
                              d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u, st);
         r->result = 0;
         r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;

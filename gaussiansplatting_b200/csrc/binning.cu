@@ -81,6 +81,21 @@ __global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict
     if (threadIdx.x == 0) cstart[nbins] = s_carry;
 }
 
+// single-pass coarse sort: the sort's digit histogram IS the bin histogram, so the bins' runs and the chunk map come from
+// one scan of it (replaces the run-boundary kernels on the sorted bin ids).  One CTA, nbins <= 256.
+__global__ void __launch_bounds__(256) bins_from_hist_kernel(const uint32_t* __restrict__ hist, uint32_t nbins, uint2* __restrict__ bin_ranges,
+                                                             uint32_t* __restrict__ cstart) {
+    __shared__ uint32_t s_w[8];
+    const uint32_t b = threadIdx.x;
+    const uint32_t cnt = b < nbins ? hist[b] : 0u;
+    uint32_t tot;
+    const uint32_t start = gs::cta_excl_scan<8>(cnt, s_w, &tot);
+    __syncthreads();
+    const uint32_t cs = gs::cta_excl_scan<8>((cnt + CH - 1u) / CH, s_w, &tot);
+    if (b < nbins) { bin_ranges[b] = make_uint2(start, cnt); cstart[b] = cs; }
+    if (b == 0) cstart[nbins] = tot;
+}
+
 struct ChunkCtx { uint32_t bin, first, count; };   // the chunk's bin, first coarse entry, entries in the chunk
 __device__ __forceinline__ ChunkCtx locate_chunk(uint32_t chunk, const uint32_t* s_cstart, uint32_t nbins, const uint2* __restrict__ bin_ranges) {
     uint32_t lo = 0, hi = nbins;                               // largest b with cstart[b] <= chunk (empty bins share a value: take the last)
@@ -291,7 +306,7 @@ void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uin
     emit_coarse_kernel<<<(n + 255) / 256, 256, 0, st>>>(O, perm, offs, n, gs_bin_nbx(ntx), bin_keys, vals, cap);
 }
 
-void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint2* bin_ranges, uint32_t ntx, uint32_t nty,
+void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
                           uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st) {
     const uint32_t nbx = gs_bin_nbx(ntx), nbins = gs_bin_count(ntx, nty);
@@ -301,7 +316,8 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     // sizes the grid from the previous frame's coarse count (one chunk per CTA: the chunk's dependent gathers of many
     // CTAs overlap), falling back to a persistent grid.
     const uint32_t grid = grid_chunks > 148u * 4u ? grid_chunks : 148u * 4u;
-    chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart);
+    if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart);
+    else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart);
     bin_count_kernel<<<grid, CH, dyn, st>>>(O, cvals, bin_ranges, cstart, nbins, nbx, chunk_counts);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count);
     tile_scan_kernel<<<1, 1024, 0, st>>>(tile_count, ntx * nty, ranges, total_pairs, cap_pairs);

@@ -89,7 +89,10 @@ uint32_t gs_bin_count(uint32_t ntx, uint32_t nty);
 size_t gs_bin_max_chunks(uint64_t coarse_cap, uint32_t nbins);
 void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
                            uint32_t* bin_keys, uint32_t* vals, uint32_t cap, cudaStream_t st);
-void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint2* bin_ranges, uint32_t ntx, uint32_t nty,
+// bin_hist: per-bin entry counts when the coarse sort was a single pass (its digit histogram, gs_sort_pass_histogram), else
+// nullptr and bin_ranges must already hold the bins' runs
+const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass);
+void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
                           uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st);
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,

@@ -360,6 +360,8 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
 
 }  // namespace
 
+const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass) { return (const uint32_t*)scratch + (size_t)pass * 256; }
+
 GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
     GsSortPlan pl;
     pl.num_passes = 0;
