@@ -64,6 +64,24 @@ def test_forward_parity(gs, ctx, orc, n, W, H, s0, seed):
     assert len(ref["keys"]) > 0
 
 
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("n,W,H,s0,seed", [
+    (3000, 200, 136, 0.05, 31),        # several coarse bins, ragged edges, splats spanning bins
+    (1500, 16, 1100, 0.03, 32),        # one tile wide, 69 tiles tall (a column of 9 coarse bins)
+    (1500, 1100, 16, 0.03, 33),        # one tile tall
+    (40, 16, 16, 0.2, 34),             # a single tile, a single coarse bin
+])
+def test_forward_parity_in_every_pair_pipeline(gs, ctx, orc, mode, n, W, H, s0, seed):
+    """sort_mode 0 two-level binning (default), 1 the literal 64-bit pair sort, 2 hoisted radix sort: same oracle parity"""
+    gs.tune("sort_mode", mode)
+    try:
+        g = synth.make_scene(n, seed, s0)
+        u = synth.make_camera(1, 8, W, H, n)
+        check_forward(gs, ctx, orc, g, u, W, H)
+    finally:
+        gs.tune("sort_mode", 0)
+
+
 def test_forward_empty_and_culled(gs, ctx, orc):
     """nothing visible (all behind the camera): white image, empty ranges (SURVEY note B)"""
     n, W, H = 500, 64, 48
