@@ -325,9 +325,10 @@ def run_ours(args):
         o.close()
     Dn.set_scene_extent(synth.scene_extent(orbit))
     D.set_stat_mode(False)
-    # kernels per fwd+bwd frame (hoisted mode): preprocess, depth hist + passes, scan, emit, tile hist + passes,
-    # tile starts + counts, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
-    launches_fb = 10 + passes
+    # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan, coarse emit, bin histogram
+    # + passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk counts, bin scan,
+    # tile scan, fill, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
+    launches_fb = 13 + passes + (2 if passes > 5 else 0)
     out["gpu_launches"] = K * launches_fb
 
     if rank == 0:
@@ -349,8 +350,11 @@ def run_ours(args):
         fp32_peak = 2 * 128 * 148 * sm_max_mhz * 1e6 / 1e12          # TFLOP/s at max clock
         # hoisted mode: depth passes on N (u32 key + u32 index), tile passes on P (u32 tile + u32 value)
         dpasses, tpasses = 4, passes - 4
+        # binned pipeline: Pc coarse (bin, Gaussian) pairs; "emit"/"sort" work on those, "ranges" is the per-bin expansion
+        # (two reads of the coarse list, bbox + record gathers per coarse entry, one 4-B store per pair, the ranges)
+        Pc = R.coarse_pair_count
         bytes_alg = {"preprocess": 136.0 * n, "depth_sort": n * (4.0 + 16.0 * dpasses), "scan": 12.0 * n,
-                     "emit": 8.0 * P + 56.0 * n, "sort": P * (4.0 + 16.0 * tpasses), "ranges": 4.0 * P + 8.0 * tiles,
+                     "emit": 8.0 * Pc + 24.0 * n, "sort": Pc * (4.0 + 16.0 * tpasses), "ranges": 4.0 * P + 8.0 * tiles + 72.0 * Pc,
                      "preprocess_bwd": 196.0 * n}
         flops_alg = {"blend_fwd": 25.0 * C + 14.0 * (E - C), "blend_bwd": 70.0 * C + 14.0 * (E - C)}
         roofs = {}
@@ -389,24 +393,30 @@ def run_ours(args):
             sort_res[f"random_u64_2^{logn}"] = {"gkeys_per_s": gk, "ms": ms, "passes": 8, "GB/s": bts / (ms * 1e-3) / 1e9,
                                                 "frac_of_hbm": bts / (ms * 1e-3) / 1e9 / hbm_peak}
             S.close(); ctx.free(dk); ctx.free(dv)
-        sort_ms = stage["depth_sort"] + stage["sort"]
-        sort_res["tile_depth_keys_C2_hoisted"] = {
-            "gkeys_per_s": P / (sort_ms * 1e-3) / 1e9, "ms": sort_ms, "passes": passes, "n": P,
-            "what": "the frame's (tile|depth) order of P pairs: 4 depth passes on the N Gaussians + tile passes on the P pairs"}
+        order_ms = stage["depth_sort"] + stage["scan"] + stage["emit"] + stage["sort"] + stage["ranges"]
+        sort_res["tile_depth_order_C2_binned"] = {
+            "gkeys_per_s": P / (order_ms * 1e-3) / 1e9, "ms": order_ms, "passes": passes, "n": P, "coarse_pairs": Pc,
+            "what": "everything between the projection and the blend (per-tile lists in depth order + ranges) for the frame's P "
+                    "pairs: 4 depth passes on the N Gaussians, coarse pairs, one pass by bin id, per-bin expansion"}
         # the reference's structure for comparison: full 64-bit pair sort of the same keys
         gs.tune("sort_mode", 1)
         R.set_profiling(True)
-        acc1 = 0.0
+        acc1 = accall = 0.0
         for i in range(3 + 5):
             R.forward(G, view(i), img)
             if i >= 3:
-                acc1 += R.timings(False)["sort"]
+                t1 = R.timings(False)
+                acc1 += t1["sort"]
+                accall += t1["depth_sort"] + t1["scan"] + t1["emit"] + t1["sort"] + t1["ranges"]
         R.set_profiling(False)
         p64 = R.sort_passes
         gs.tune("sort_mode", 0)
         R.forward(G, view(0), img)
         sort_res["tile_depth_keys_C2_pairs64"] = {"gkeys_per_s": P / (acc1 / 5 * 1e-3) / 1e9, "ms": acc1 / 5, "passes": p64, "n": P,
-                                                  "GB/s": P * (8.0 + 24.0 * p64) / (acc1 / 5 * 1e-3) / 1e9}
+                                                  "GB/s": P * (8.0 + 24.0 * p64) / (acc1 / 5 * 1e-3) / 1e9,
+                                                  "order_ms": accall / 5,
+                                                  "what": "the reference's structure: 64-bit (tile|depth) keys of the P pairs, radix sort over the "
+                                                          "varying digits; order_ms = scan + emit + sort + ranges, to compare with the binned line"}
         out["sort"] = sort_res
         out["sort_gkeys_per_s"] = sort_res["random_u64_2^24"]["gkeys_per_s"]
 

@@ -35,6 +35,7 @@ def lib():
         L.gs_ctx_stream.restype = C.c_void_p
         L.gs_image_devptr.restype = C.c_void_p
         L.gs_rast_pair_count.restype = C.c_uint64
+        L.gs_rast_coarse_pair_count.restype = C.c_uint64
         for name in ("gs_sort64_sorted_keys", "gs_sort64_sorted_values", "gs_sort32_sorted_keys",
                      "gs_sort32_sorted_indices"):
             getattr(L, name).restype = C.c_void_p
@@ -248,6 +249,10 @@ class Rasterizer:
     @property
     def pair_count(self):
         return int(lib().gs_rast_pair_count(self.h))
+
+    @property
+    def coarse_pair_count(self):
+        return int(lib().gs_rast_coarse_pair_count(self.h))
 
     @property
     def sort_passes(self):

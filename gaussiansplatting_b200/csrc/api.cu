@@ -888,6 +888,7 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
     return rc;
 }
 uint64_t gs_rast_pair_count(const gs_rast* r) { return r->pairs; }
+uint64_t gs_rast_coarse_pair_count(const gs_rast* r) { return r->mode == 0 ? r->coarse_hint : 0; }
 int gs_rast_sort_passes(const gs_rast* r) { return r->passes; }
 
 }  // extern "C"

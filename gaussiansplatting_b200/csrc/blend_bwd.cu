@@ -12,6 +12,12 @@
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
+#ifdef GS_BWD_MINB         // optional: minimum resident CTAs per SM asked of ptxas (register budget knob; measured: no gain)
+#define GS_BWD_BOUNDS(nt) __launch_bounds__(nt, GS_BWD_MINB)
+#else
+#define GS_BWD_BOUNDS(nt) __launch_bounds__(nt)
+#endif
+
 namespace {
 
 #ifndef GS_BWD_PPT
@@ -55,7 +61,7 @@ __device__ __forceinline__ uint32_t reduce8_index(uint32_t lane) {
 // colour unchanged (T * rcp(1), 0*c + 1*acc) and adds exact zeros to the moments.
 struct BwdEnt { float4 r0, r1; float b; uint32_t idx, gid, pad; };   // 48 B: one base address, three LDS.128
 template <int PPT>
-__global__ void __launch_bounds__(256 / PPT) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+__global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                              const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                              const float4* __restrict__ rendered, const float4* __restrict__ gt,
                                                              int quantize, const uint32_t* __restrict__ last_idx,

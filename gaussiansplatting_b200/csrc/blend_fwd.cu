@@ -8,6 +8,10 @@
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
+#ifndef GS_FWD_MINB
+#define GS_FWD_MINB 10     // minimum resident CTAs per SM asked of ptxas (48 registers; measured 243 -> 235 us at C2)
+#endif
+
 namespace {
 
 // lb(t) = first index whose key's tile is >= t  (the reference's binary search, sort.metal:568-577)
@@ -82,7 +86,7 @@ constexpr int FB = 256;   // raw list entries staged per round
 // finished pixel has NaN coordinates, so every test on it fails.  Per half the operation sequence is the pinned one.
 struct FwdEnt { float4 r0, r1; float b; uint32_t idx; uint32_t pad0, pad1; };   // 48 B: one base address, three LDS
 template <int PPT, bool COUNT>
-__global__ void __launch_bounds__(256 / PPT) blend_forward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+__global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                             float4* __restrict__ image, uint32_t* __restrict__ last_idx,
                                                             float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags,

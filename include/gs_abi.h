@@ -167,6 +167,7 @@ int gs_rast_get_timings(gs_rast*, float* ms9, int include_backward);
 /* E = list entries the forward walk visits, C = contributing (pixel, Gaussian) evaluations of the last forward */
 int gs_rast_count_evals(gs_rast*, uint64_t* E, uint64_t* C);
 uint64_t gs_rast_pair_count(const gs_rast*);
+uint64_t gs_rast_coarse_pair_count(const gs_rast*);                      /* (8x8-tile bin, Gaussian) pairs of the last forward in the default binned pipeline; 0 in the sort pipelines */
 int gs_rast_sort_passes(const gs_rast*);                /* digit passes the last forward ran */
 
 /* ---- GPURadixSort64 / GPURadixSort32 (gpu_sort.hpp:14-107) ---------------------------------------------- */
