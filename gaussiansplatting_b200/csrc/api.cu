@@ -58,6 +58,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "fwd_ppt")) { gs_tune_fwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "bwd_ppt")) { gs_tune_bwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
+    if (!strcmp(name, "sort_tiny_tiles")) { gs_tune_sort_tiny(value); return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     return GS_ERR_ARG;
@@ -759,13 +760,14 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     GS_TRY(rast_reserve_image(r, W, H));
     r->n = n; r->pairs = 0; r->passes = 0; r->mode = g_sort_mode;
     if (r->mode == 0 && gs_bin_count(r->ntx, r->nty) > GS_MAX_BINS) r->mode = 2;
-    // meta: total = 0, key OR = 0, key AND = ~0
-    GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
-    GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
+    if (r->mode == 1) {   // meta: key OR = 0, key AND = ~0 (the totals are plain stores of the scans)
+        GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
+        GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
+    }
     r->mark(0);
     // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
     gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
-                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->meta, st);
+                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->mode == 1 ? r->meta : nullptr, st);
     r->mark(1);
     GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : r->mode == 2 ? forward_hoisted(r, g, u, out) : forward_binned(r, g, u, out));
     return image_after_use(out, st);

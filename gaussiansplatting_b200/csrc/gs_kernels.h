@@ -92,6 +92,7 @@ void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uin
 // bin_hist: per-bin entry counts when the coarse sort was a single pass (its digit histogram, gs_sort_pass_histogram), else
 // nullptr and bin_ranges must already hold the bins' runs
 const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass);
+void gs_tune_sort_tiny(int v);
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
                           uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st);

@@ -143,12 +143,20 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
         O.ccnt[i] = count ? ((bb.z >> 3) - (bb.x >> 3) + 1u) * ((bb.w >> 3) - (bb.y >> 3) + 1u) : 0u;
         O.dkey[i] = count ? dkey : 0xFFFFFFFFu;
     }
-    // depth-key OR / AND over Gaussians that emit pairs: digits whose bits never vary need no sort pass
+    // depth-key OR / AND over Gaussians that emit pairs: digits whose bits never vary need no sort pass (only the literal
+    // 64-bit pipeline reads them; two same-address atomics per warp are not free, so the other pipelines skip them)
+    if (meta == nullptr) return;
+    __shared__ uint32_t s_or[8], s_and[8];
     const uint32_t kor = __reduce_or_sync(0xFFFFFFFFu, count ? dkey : 0u);
     const uint32_t kand = __reduce_and_sync(0xFFFFFFFFu, count ? dkey : 0xFFFFFFFFu);
-    if (gs::lane_id() == 0) {
-        if (kor) atomicOr(&meta[GS_META_KEY_OR], kor);
-        if (kand != 0xFFFFFFFFu) atomicAnd(&meta[GS_META_KEY_AND], kand);
+    if (gs::lane_id() == 0) { s_or[threadIdx.x >> 5] = kor; s_and[threadIdx.x >> 5] = kand; }
+    __syncthreads();
+    if (threadIdx.x == 0) {                                  // one pair of atomics per CTA (same-address atomics serialise)
+        uint32_t o = 0u, a = 0xFFFFFFFFu;
+#pragma unroll
+        for (int w = 0; w < 8; w++) { o |= s_or[w]; a &= s_and[w]; }
+        if (o) atomicOr(&meta[GS_META_KEY_OR], o);
+        if (a != 0xFFFFFFFFu) atomicAnd(&meta[GS_META_KEY_AND], a);
     }
 }
 

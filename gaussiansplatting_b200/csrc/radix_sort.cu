@@ -297,7 +297,7 @@ __global__ void depth_keys32_kernel(const float4* __restrict__ pos, float cx, fl
     keys[i] = key;
 }
 
-constexpr uint32_t RS_BIG_TILE = RS_THREADS * 16, RS_SMALL_TILE = RS_THREADS * 8;
+constexpr uint32_t RS_BIG_TILE = RS_THREADS * 16, RS_SMALL_TILE = RS_THREADS * 8, RS_TINY_TILE = RS_THREADS * 4;
 constexpr size_t RS_HIST_BYTES = 8 * 256 * 4;
 constexpr size_t RS_CTR_BYTES = 64;
 
@@ -324,6 +324,8 @@ void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], 
     }
 }
 
+static int g_rs_tiny = 0;   // experiment knob: 1024-pair tiles for inputs around 1 M
+
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
               const uint32_t* d_n, const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st) {
@@ -335,7 +337,8 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     }
     // small inputs: 2048-pair tiles so that every tile is resident at once (one wave) instead of 1.x waves of 4096
     const bool small = n <= (uint64_t)RS_SMALL_TILE * 148 * GS_RS_CTAS;
-    const uint32_t tile_elems = small ? RS_SMALL_TILE : RS_BIG_TILE;
+    const bool tiny = g_rs_tiny && n <= (uint64_t)RS_TINY_TILE * 148 * GS_RS_CTAS * 2;
+    const uint32_t tile_elems = tiny ? RS_TINY_TILE : small ? RS_SMALL_TILE : RS_BIG_TILE;
     const uint32_t tiles = (uint32_t)((n + tile_elems - 1) / tile_elems);
     const size_t status_bytes = (size_t)tiles * 256 * 4;
     uint32_t* ghist = (uint32_t*)scratch;
@@ -352,7 +355,8 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pl, ghist);
     const bool ballot = (hints & GS_SORT_HINT_DISTINCT) != 0;
 #define GS_RS_GO(IPT, B) launch_passes<KeyT, IPT, B>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, pl, tiles, ghist, counters, status, agg2, groups, st)
-    if (small) { if (ballot) GS_RS_GO(8, true); else GS_RS_GO(8, false); }
+    if (tiny) { if (ballot) GS_RS_GO(4, true); else GS_RS_GO(4, false); }
+    else if (small) { if (ballot) GS_RS_GO(8, true); else GS_RS_GO(8, false); }
     else { if (ballot) GS_RS_GO(16, true); else GS_RS_GO(16, false); }
 #undef GS_RS_GO
     return (plan.num_passes & 1) ? 0 : 1;
@@ -360,6 +364,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
 
 }  // namespace
 
+void gs_tune_sort_tiny(int v) { g_rs_tiny = v ? 1 : 0; }
 const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass) { return (const uint32_t*)scratch + (size_t)pass * 256; }
 
 GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
@@ -375,7 +380,7 @@ GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
 }
 
 size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
-    size_t tiles = (size_t)((n + RS_SMALL_TILE - 1) / RS_SMALL_TILE) + 1;
+    size_t tiles = (size_t)((n + RS_TINY_TILE - 1) / RS_TINY_TILE) + 1;
     return RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + (tiles / RS_GROUP + 1) * 256 * 8) * 8;
 }
 
