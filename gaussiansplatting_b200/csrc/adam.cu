@@ -1,6 +1,5 @@
 // adam.cu — K9: fused Adam over the five parameter groups (replaces adamStep, shaders.metal:536-713; host side
-// AdamOptimizer::step, optimizer.mm:228-296).  Pure streaming, HBM-bound: SoA planes, one thread per Gaussian,
-// every load/store a coalesced 4-B (or 16-B for the quaternion) lane.  Arithmetic is pinned (no contraction,
+// AdamOptimizer::step, optimizer.mm:228-296).  Pure streaming, HBM-bound: SoA planes read and written in 16-B lanes.  Arithmetic is pinned (no contraction,
 // IEEE div/sqrt) so parameters and moments match the oracle bit for bit.
 #include "gs_common.cuh"
 #include "gs_kernels.h"
@@ -9,80 +8,142 @@ namespace {
 
 struct AdamK { float lr[5]; float b1, b2, omb1, omb2, eps, bc1, bc2; };
 
+// A parameter whose gradient and both moments are zero (nine of the twelve SH planes always, every parameter of a Gaussian
+// no pixel touched until it first receives a gradient) keeps m = v = +0 and gets the update +0: exactly what the
+// arithmetic below yields (b1*0 + omb1*(+-0) = +0, (lr * 0/bc1) / (sqrt(0/bc2) + eps) = +0), without sending zeros
+// through the IEEE division's slow path.
+__device__ __forceinline__ bool adam_idle(float gr, float m, float v) {
+    return gr == 0.0f && __float_as_uint(m) == 0u && __float_as_uint(v) == 0u;
+}
 __device__ __forceinline__ float adam_update(float gr, float& m, float& v, const AdamK& k, float lr) {
+    if (adam_idle(gr, m, v)) return 0.0f;
     m = gs::fadd(gs::fmul(k.b1, m), gs::fmul(k.omb1, gr));
     v = gs::fadd(gs::fmul(k.b2, v), gs::fmul(gs::fmul(k.omb2, gr), gr));
     const float m_hat = gs::fdiv(m, k.bc1), v_hat = gs::fdiv(v, k.bc2);
     return gs::fdiv(gs::fmul(lr, m_hat), gs::fadd(gs::fsqrt(v_hat), k.eps));
 }
 
-// All 83 inputs of a Gaussian are loaded before anything is stored: the planes are not declared restrict (parameters,
-// moments and gradients are separate allocations but the compiler cannot know), so a load issued after a store would
-// have to wait for it; front-loading keeps ~80 independent 4-B loads in flight per thread.
-__global__ void __launch_bounds__(256) adam_kernel(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const __grid_constant__ AdamK k) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+// Plane-streaming layout of the step.  Apart from three couplings the update of every scalar parameter is independent,
+// so the kernel runs as 18 JOBS (blockIdx.y) that each stream a handful of planes with 16-B vector lanes, four
+// consecutive Gaussians per thread: job 0 = position (3 planes together: the joint 0.1 magnitude clip), job 1 = rotation
+// (float4 planes + renormalisation), jobs 2-4 scale, 5 opacity, 6-17 the SH planes.  A CTA then touches 7-13 streams of
+// 4 KB each instead of 152 streams of 1 KB (one-thread-per-Gaussian version: 2.0 TB/s), which is what DRAM pages want.
+// The third coupling is the reference's early return (a Gaussian with a non-finite gradient or position is skipped as a
+// whole, shaders.metal:567-576): every job re-evaluates that predicate from the four planes involved (16 B / Gaussian,
+// L2 hits after the first job).
+struct Skip4 { bool s[4]; };
+__device__ __forceinline__ Skip4 adam_skip4(const GsParams& P, const GsGradPack& G, size_t i4) {
+    const float4 g0 = *reinterpret_cast<const float4*>(G.g + i4), g3 = *reinterpret_cast<const float4*>(G.g + 3 * (size_t)G.stride + i4),
+                 g11 = *reinterpret_cast<const float4*>(G.g + 11 * (size_t)G.stride + i4), p0 = *reinterpret_cast<const float4*>(P.pos + i4);
+    const float a[4] = {g0.x, g0.y, g0.z, g0.w}, b[4] = {g3.x, g3.y, g3.z, g3.w}, c[4] = {g11.x, g11.y, g11.z, g11.w},
+                d[4] = {p0.x, p0.y, p0.z, p0.w};
+    Skip4 r;
+#pragma unroll
+    for (int e = 0; e < 4; e++)
+        r.s[e] = isnan(a[e]) || isnan(b[e]) || isnan(c[e]) || isinf(a[e]) || isinf(b[e]) ||      // :567-570
+                 isnan(d[e]) || isinf(d[e]) || fabsf(d[e]) > 1e6f;                                // :573-576
+    return r;
+}
+__device__ __forceinline__ void ld4(const float* p, float (&v)[4]) { const float4 t = *reinterpret_cast<const float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+__device__ __forceinline__ void st4(float* p, const float (&v)[4]) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+
+// clean[0] (read): 1 = every non-DC SH value of [0,n) is inside the clamp and its moments are zero, so those nine jobs are the
+// identity and return at once.  clean[1] (preset to 1 by the host, read by the NEXT step): cleared by a job that had to
+// leave an out-of-range value behind because its Gaussian is skipped.
+__global__ void __launch_bounds__(256, 4) adam_kernel(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const __grid_constant__ AdamK k,
+                                                      const uint32_t* __restrict__ clean_in, uint32_t* __restrict__ clean_out) {
+    const size_t i4 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i4 >= n) return;
+    const uint32_t job = blockIdx.y;
+    const bool sh_rest = job >= 6 && ((job - 6) % 4) != 0;           // SH planes other than the three DC ones: no gradient plane
+    if (sh_rest && *clean_in) return;
     const size_t gs_ = G.stride, cap = P.cap, sc = S.cap;
     const float clip = 0.5f;                                          // shaders.metal:582
-    float g[14];
+    const Skip4 sk = adam_skip4(P, G, i4);
+    const bool full = i4 + 4 <= n;                                    // a partial last vector is handled element-wise on store
+    bool live[4];
 #pragma unroll
-    for (int c = 0; c < 14; c++) g[c] = G.g[(size_t)c * gs_ + i];    // pos 0-2, opacity 3, scale 4-6, rot 7-10, SH-DC 11-13
-    float p_pos[3], p_sc[3], p_sh[12], m_pos[3], v_pos[3], m_sc[3], v_sc[3], m_sh[12], v_sh[12];
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-        p_pos[c] = P.pos[c * cap + i]; p_sc[c] = P.scale[c * cap + i];
-        m_pos[c] = S.m_pos[c * sc + i]; v_pos[c] = S.v_pos[c * sc + i];
-        m_sc[c] = S.m_scale[c * sc + i]; v_sc[c] = S.v_scale[c * sc + i];
-    }
-#pragma unroll
-    for (int c = 0; c < 12; c++) { p_sh[c] = P.sh[c * cap + i]; m_sh[c] = S.m_sh[c * sc + i]; v_sh[c] = S.v_sh[c * sc + i]; }
-    const float4 q = P.rot[i];
-    float4 m4 = S.m_rot[i], v4 = S.v_rot[i];
-    float p_op = P.opacity[i], m_op = S.m_op[i], v_op = S.v_op[i];
+    for (int e = 0; e < 4; e++) live[e] = !sk.s[e] && (i4 + e < n);
 
-    if (isnan(g[0]) || isnan(g[3]) || isnan(g[11]) || isinf(g[0]) || isinf(g[3])) return;   // :567-570
-    if (isnan(p_pos[0]) || isinf(p_pos[0]) || fabsf(p_pos[0]) > 1e6f) return;                // :573-576
-    {   // position :586-625
-        float up[3];
+    if (job == 0) {   // position :586-625
+        float g[3][4], p[3][4], m[3][4], v[3][4];
 #pragma unroll
-        for (int c = 0; c < 3; c++) up[c] = adam_update(gs::clampf(g[c], -clip, clip), m_pos[c], v_pos[c], k, k.lr[0]);
-        const float mag = gs::fsqrt(gs::fadd(gs::fadd(gs::fmul(up[0], up[0]), gs::fmul(up[1], up[1])), gs::fmul(up[2], up[2])));
-        if (mag > 0.1f) { const float s = gs::fdiv(0.1f, mag); up[0] = gs::fmul(up[0], s); up[1] = gs::fmul(up[1], s); up[2] = gs::fmul(up[2], s); }
-        const float n0 = gs::fsub(p_pos[0], up[0]), n1 = gs::fsub(p_pos[1], up[1]), n2 = gs::fsub(p_pos[2], up[2]);
-        if (!isnan(n0) && !isnan(n1) && !isnan(n2) && fabsf(n0) < 1e6f && fabsf(n1) < 1e6f && fabsf(n2) < 1e6f) {
-            P.pos[i] = n0; P.pos[cap + i] = n1; P.pos[2 * cap + i] = n2;
+        for (int c = 0; c < 3; c++) {
+            ld4(G.g + c * gs_ + i4, g[c]); ld4(P.pos + c * cap + i4, p[c]);
+            ld4(S.m_pos + c * sc + i4, m[c]); ld4(S.v_pos + c * sc + i4, v[c]);
         }
 #pragma unroll
-        for (int c = 0; c < 3; c++) { S.m_pos[c * sc + i] = m_pos[c]; S.v_pos[c * sc + i] = v_pos[c]; }
-    }
+        for (int e = 0; e < 4; e++) {
+            if (!live[e]) continue;
+            float up[3];
 #pragma unroll
-    for (int c = 0; c < 3; c++) {   // scale :630-656
-        const float u = adam_update(gs::clampf(g[4 + c], -clip, clip), m_sc[c], v_sc[c], k, k.lr[1]);
-        S.m_scale[c * sc + i] = m_sc[c]; S.v_scale[c * sc + i] = v_sc[c];
-        P.scale[c * cap + i] = gs::clampf(gs::fsub(p_sc[c], u), -GS_MAX_SCALE_TRAIN, GS_MAX_SCALE_TRAIN);
-    }
-    {   // rotation :659-675
-        float m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
-        const float qo[4] = {q.x, q.y, q.z, q.w};
-        float nr[4];
+            for (int c = 0; c < 3; c++) up[c] = adam_update(gs::clampf(g[c][e], -clip, clip), m[c][e], v[c][e], k, k.lr[0]);
+            const float mag = gs::fsqrt(gs::fadd(gs::fadd(gs::fmul(up[0], up[0]), gs::fmul(up[1], up[1])), gs::fmul(up[2], up[2])));
+            if (mag > 0.1f) { const float s = gs::fdiv(0.1f, mag); up[0] = gs::fmul(up[0], s); up[1] = gs::fmul(up[1], s); up[2] = gs::fmul(up[2], s); }
+            const float n0 = gs::fsub(p[0][e], up[0]), n1 = gs::fsub(p[1][e], up[1]), n2 = gs::fsub(p[2][e], up[2]);
+            if (!isnan(n0) && !isnan(n1) && !isnan(n2) && fabsf(n0) < 1e6f && fabsf(n1) < 1e6f && fabsf(n2) < 1e6f) {
+                p[0][e] = n0; p[1][e] = n1; p[2][e] = n2;
+            }
+        }
 #pragma unroll
-        for (int c = 0; c < 4; c++) nr[c] = gs::fsub(qo[c], adam_update(gs::clampf(g[7 + c], -clip, clip), m[c], v[c], k, k.lr[2]));
-        S.m_rot[i] = make_float4(m[0], m[1], m[2], m[3]); S.v_rot[i] = make_float4(v[0], v[1], v[2], v[3]);
-        const float len = gs::fsqrt(gs::fadd(gs::fadd(gs::fadd(gs::fmul(nr[0], nr[0]), gs::fmul(nr[1], nr[1])), gs::fmul(nr[2], nr[2])), gs::fmul(nr[3], nr[3])));
-        P.rot[i] = (len > 0.001f) ? make_float4(gs::fdiv(nr[0], len), gs::fdiv(nr[1], len), gs::fdiv(nr[2], len), gs::fdiv(nr[3], len))
-                                  : make_float4(1.f, 0.f, 0.f, 0.f);
+        for (int c = 0; c < 3; c++) {
+            if (full) { st4(P.pos + c * cap + i4, p[c]); st4(S.m_pos + c * sc + i4, m[c]); st4(S.v_pos + c * sc + i4, v[c]); }
+            else for (int e = 0; e < 4; e++) if (i4 + e < n) { P.pos[c * cap + i4 + e] = p[c][e]; S.m_pos[c * sc + i4 + e] = m[c][e]; S.v_pos[c * sc + i4 + e] = v[c][e]; }
+        }
+        return;
     }
-    {   // opacity :678-692
-        const float u = adam_update(gs::clampf(g[3], -clip, clip), m_op, v_op, k, k.lr[3]);
-        S.m_op[i] = m_op; S.v_op[i] = v_op;
-        P.opacity[i] = gs::clampf(gs::fsub(p_op, u), -8.0f, 8.0f);
-    }
+    if (job == 1) {   // rotation :659-675
+        float g[4][4];
 #pragma unroll
-    for (int c = 0; c < 12; c++) {   // SH :695-712 (gradients of the non-DC coefficients are identically zero)
-        const float graw = (c % 4 == 0) ? g[11 + c / 4] : 0.f;
-        const float u = adam_update(gs::clampf(graw, -clip, clip), m_sh[c], v_sh[c], k, k.lr[4]);
-        S.m_sh[c * sc + i] = m_sh[c]; S.v_sh[c * sc + i] = v_sh[c];
-        P.sh[c * cap + i] = gs::clampf(gs::fsub(p_sh[c], u), -2.0f, 2.0f);
+        for (int c = 0; c < 4; c++) ld4(G.g + (7 + c) * gs_ + i4, g[c]);
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            if (!live[e]) continue;
+            const float4 q = P.rot[i4 + e], m4 = S.m_rot[i4 + e], v4 = S.v_rot[i4 + e];
+            float m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+            const float qo[4] = {q.x, q.y, q.z, q.w};
+            float nr[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) nr[c] = gs::fsub(qo[c], adam_update(gs::clampf(g[c][e], -clip, clip), m[c], v[c], k, k.lr[2]));
+            S.m_rot[i4 + e] = make_float4(m[0], m[1], m[2], m[3]); S.v_rot[i4 + e] = make_float4(v[0], v[1], v[2], v[3]);
+            const float len = gs::fsqrt(gs::fadd(gs::fadd(gs::fadd(gs::fmul(nr[0], nr[0]), gs::fmul(nr[1], nr[1])), gs::fmul(nr[2], nr[2])), gs::fmul(nr[3], nr[3])));
+            P.rot[i4 + e] = (len > 0.001f) ? make_float4(gs::fdiv(nr[0], len), gs::fdiv(nr[1], len), gs::fdiv(nr[2], len), gs::fdiv(nr[3], len))
+                                           : make_float4(1.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+    // scalar planes: scale (jobs 2-4) :630-656, opacity (5) :678-692, SH (6-17) :695-712
+    float *pp, *pm, *pv;
+    const float* pg = nullptr;
+    float lr, lo, hi;
+    if (job < 5) { const uint32_t c = job - 2; pp = P.scale + c * cap; pm = S.m_scale + c * sc; pv = S.v_scale + c * sc; pg = G.g + (4 + c) * gs_; lr = k.lr[1]; lo = -GS_MAX_SCALE_TRAIN; hi = GS_MAX_SCALE_TRAIN; }
+    else if (job == 5) { pp = P.opacity; pm = S.m_op; pv = S.v_op; pg = G.g + 3 * gs_; lr = k.lr[3]; lo = -8.0f; hi = 8.0f; }
+    else {   // gradients of the non-DC coefficients are identically zero
+        const uint32_t c = job - 6; pp = P.sh + c * cap; pm = S.m_sh + c * sc; pv = S.v_sh + c * sc;
+        if (c % 4 == 0) pg = G.g + (11 + c / 4) * gs_;
+        lr = k.lr[4]; lo = -2.0f; hi = 2.0f;
+    }
+    float g[4] = {0.f, 0.f, 0.f, 0.f}, p[4], m[4], v[4];
+    if (pg) ld4(pg + i4, g);
+    ld4(pp + i4, p); ld4(pm + i4, m); ld4(pv + i4, v);
+    bool moved = false, pchanged = false, dirty = false;             // moments / parameter different from what was loaded
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+        if (!live[e]) { dirty |= (i4 + e < n) && !(p[e] >= lo && p[e] <= hi); continue; }
+        const float gc = gs::clampf(g[e], -clip, clip);
+        moved |= !adam_idle(gc, m[e], v[e]);
+        const float u = adam_update(gc, m[e], v[e], k, lr);
+        const float pn = gs::clampf(gs::fsub(p[e], u), lo, hi);
+        pchanged |= __float_as_uint(pn) != __float_as_uint(p[e]);
+        p[e] = pn;
+    }
+    if (sh_rest && (dirty || moved)) *clean_out = 0u;                // an unclamped value of a skipped Gaussian, or live moments
+    // an idle vector (all four parameters idle and inside the clamp) writes nothing: 3 of its 6-7 streams disappear
+    if (full) {
+        if (pchanged) st4(pp + i4, p);
+        if (moved) { st4(pm + i4, m); st4(pv + i4, v); }
+    } else if (pchanged || moved) {
+        for (int e = 0; e < 4; e++) if (i4 + e < n) { pp[i4 + e] = p[e]; pm[i4 + e] = m[e]; pv[i4 + e] = v[e]; }
     }
 }
 
@@ -104,12 +165,12 @@ __global__ void accumulate_stats_kernel(GsGradPack G, int stat_mode, uint32_t n,
 }  // namespace
 
 void gs_launch_adam(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const float lrs[5], float beta1, float beta2,
-                    float eps, float bc1, float bc2, cudaStream_t st) {
+                    float eps, float bc1, float bc2, const uint32_t* clean_in, uint32_t* clean_out, cudaStream_t st) {
     if (n == 0) return;
     AdamK k;
     for (int i = 0; i < 5; i++) k.lr[i] = lrs[i];
     k.b1 = beta1; k.b2 = beta2; k.omb1 = 1.0f - beta1; k.omb2 = 1.0f - beta2; k.eps = eps; k.bc1 = bc1; k.bc2 = bc2;
-    adam_kernel<<<(n + 255) / 256, 256, 0, st>>>(P, G, S, n, k);
+    adam_kernel<<<dim3((n + 1023) / 1024, 18), 256, 0, st>>>(P, G, S, n, k, clean_in, clean_out);
 }
 
 void gs_launch_accumulate_stats(GsGradPack G, int stat_mode, uint32_t n, float* accum, uint32_t* count, cudaStream_t st) {

@@ -140,6 +140,7 @@ struct gs_gaussians {
     uint32_t cap = 0, n = 0;
     void* staging = nullptr;    // AoS staging for upload/download
     size_t staging_bytes = 0;
+    bool sh_rest_dirty = true;  // the nine non-DC SH planes may hold values outside Adam's [-2,2] clamp (set by every writer)
     GsParams view() const {
         GsParams P;
         P.cap = cap;
@@ -197,6 +198,7 @@ int gs_gaussians_upload(gs_gaussians* g, const gs_gaussian* host, uint32_t n) {
     GS_TRY(staging_reserve(c, &g->staging, &g->staging_bytes, (size_t)n * sizeof(gs_gaussian)));
     GS_CUDA(c, cudaMemcpyAsync(g->staging, host, (size_t)n * sizeof(gs_gaussian), cudaMemcpyHostToDevice, c->stream));
     gs_launch_params_from_aos(g->staging, n, g->view(), c->stream);
+    g->sh_rest_dirty = true;
     GS_LAUNCH_CHECK(c);
     g->n = n;
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1012,6 +1014,9 @@ struct gs_adam {
     uint32_t cap = 0;           // allocation stride
     uint32_t num = 0;           // the reference's numGaussians (state covers [0, num))
     uint32_t timestep = 0;
+    uint32_t* clean_flags = nullptr;   // device: two words, see gs_adam_step
+    uint32_t sh_clamped_n = 0;  // leading Gaussians whose non-DC SH planes went through the clamp since they were last written
+    bool sh_rest_zero = true;   // moments of the nine non-DC SH planes are all +0 (they never receive a gradient; only an upload can change that)
     GsAdamState view() const {
         GsAdamState S;
         const size_t s = cap;
@@ -1061,13 +1066,15 @@ int gs_adam_create(gs_ctx* c, uint32_t num, gs_adam** out) {
 int gs_adam_destroy(gs_adam* a) {
     if (!a) return GS_OK;
     cudaSetDevice(a->c->device); cudaStreamSynchronize(a->c->stream);
-    cudaFree(a->base); delete a;
+    cudaFree(a->base); cudaFree(a->clean_flags); delete a;
     return GS_OK;
 }
 int gs_adam_reset(gs_adam* a) {                                        // optimizer.mm:80-93
     gs_ctx* c = a->c; GS_SETDEV(c);
     a->timestep = 0;
     GS_CUDA(c, cudaMemsetAsync(a->base, 0, (size_t)a->cap * 46 * sizeof(float), c->stream));
+    a->sh_rest_zero = true;
+    a->sh_clamped_n = 0;                                               // the next step runs every job again
     return GS_OK;
 }
 int gs_adam_resize_if_needed(gs_adam* a, uint32_t n) {                 // optimizer.mm:95-134: grow only, zero-filled tail
@@ -1110,8 +1117,21 @@ int gs_adam_step(gs_adam* a, gs_gaussians* g, gs_grads* gr, const float lrs[5]) 
     const float beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f;             // optimizer.mm:272-274
     const float bc1 = 1.0f - powf(beta1, (float)a->timestep);          // shaders.metal:579-580
     const float bc2 = 1.0f - powf(beta2, (float)a->timestep);
-    gs_launch_adam(g->view(), gr->view(), a->view(), n, lrs, beta1, beta2, eps, bc1, bc2, c->stream);
+    // The non-DC SH planes have no gradient plane at all (gradients.hpp: sh[12] with only the DC terms ever written), so
+    // with zero moments their step is "clamp to [-2,2]": once that has run on the current parameter values it is the
+    // identity, and those nine jobs return at once (108 B / Gaussian not streamed) until someone writes the planes.  The
+    // "clean" word lives on the device (a skipped Gaussian may have to keep an out-of-range value, which only the kernel
+    // sees): flags[t & 1] is read by step t, flags[(t + 1) & 1] is preset to 1 and cleared by step t if it found work left.
+    if (!a->clean_flags) { GS_TRY(dalloc(c, &a->clean_flags, 2)); GS_CUDA(c, cudaMemsetAsync(a->clean_flags, 0, 8, c->stream)); }
+    uint32_t* cin = a->clean_flags + (a->timestep & 1u);
+    uint32_t* cout = a->clean_flags + ((a->timestep + 1u) & 1u);
+    const bool known = a->sh_rest_zero && !g->sh_rest_dirty && n <= a->sh_clamped_n;
+    if (!known) GS_CUDA(c, cudaMemsetAsync(cin, 0, 4, c->stream));      // host-visible writers: force the nine jobs to run
+    GS_CUDA(c, cudaMemsetAsync(cout, 1, 4, c->stream));                   // any non-zero word means clean
+    gs_launch_adam(g->view(), gr->view(), a->view(), n, lrs, beta1, beta2, eps, bc1, bc2, cin, cout, c->stream);
     GS_LAUNCH_CHECK(c);
+    a->sh_clamped_n = std::max(a->sh_clamped_n, n);
+    g->sh_rest_dirty = false;
     return GS_OK;
 }
 
@@ -1133,6 +1153,7 @@ static int adam_xfer(gs_adam* a, int group, int mv, float* host, const float* sr
         GS_CUDA(c, cudaStreamSynchronize(c->stream));
         for (uint32_t i = 0; i < n; i++) for (int k = 0; k < w; k++) host[(size_t)i * w + k] = tmp[(size_t)k * n + i];
     } else {
+        if (group == 4) a->sh_rest_zero = false;   // caller-supplied SH moments: no longer known to be zero
         for (uint32_t i = 0; i < n; i++) for (int k = 0; k < w; k++) tmp[(size_t)k * n + i] = src_host[(size_t)i * w + k];
         GS_CUDA(c, cudaMemcpy2DAsync(d, (size_t)a->cap * 4, tmp.data(), (size_t)n * 4, (size_t)n * 4, w, cudaMemcpyHostToDevice, c->stream));
         GS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1250,6 +1271,7 @@ int gs_dens_apply(gs_dens* d, gs_gaussians* g, uint32_t iteration, float focal, 
     s.numPruned = c->h_pinned[0]; s.numCloned = c->h_pinned[1]; s.numSplit = c->h_pinned[2];
     const uint32_t newCount = c->h_pinned[3];
     std::swap(g->base, d->spare); std::swap(g->cap, d->spare_cap);      // :486-490
+    g->sh_rest_dirty = true;
     g->n = newCount;
     if (stats) *stats = s;
     return gs_dens_reset_accumulator(d, newCount);                      // :493

@@ -7,7 +7,10 @@
 namespace {
 
 constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_IPT = 8;
+#ifndef GS_SCAN_IPT
+#define GS_SCAN_IPT 8
+#endif
+constexpr int SCAN_IPT = GS_SCAN_IPT;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_IPT;
 constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_INC = 2ull << 32;
 

@@ -129,6 +129,55 @@ def test_adam_parity_three_steps(gs, ctx, orc):
         D.close(); A.close(); G.close()
 
 
+def test_adam_idle_plane_skipping_stays_exact(gs, ctx, orc):
+    """The library stops streaming the nine non-DC SH planes once they are known to sit inside Adam's clamp with zero
+    moments, and writes nothing for a parameter whose gradient and moments are zero.  Every path that can invalidate
+    that (parameter upload with out-of-range values, growth of the covered count, caller-supplied SH moments, zero
+    gradients turning non-zero) must still reproduce the oracle bit for bit."""
+    n = 3000
+    lrs = [1.6e-4, 5e-3, 1e-3, 2.5e-2, 2.5e-3]
+    g = synth.make_scene(n, 71, 0.02)
+    g["sh"][::7, 1] = 3.5; g["sh"][::5, 6] = -9.0            # non-DC coefficients outside [-2, 2]: clamped by the first step
+    ref = g.copy()
+    st = orc.AdamState(n)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    A = gs.Adam(ctx, n)
+    D = gs.Grads(ctx, n)
+
+    def step(seed, zero_from=None):
+        gr = make_grads(orc, n, seed)
+        if zero_from is not None:                              # Gaussians no pixel touched: all-zero gradient rows
+            for f in ("position", "opacity", "scale", "rotation", "sh", "viewspace"):
+                gr[f][zero_from:] = 0
+        orc.adam_step(ref, gr, st, lrs)
+        D.upload(gr); A.step(G, D, lrs)
+
+    def check(tag):
+        got = G.download()
+        for f in ("position", "scale", "rotation", "opacity", "sh"):
+            assert np.array_equal(got[f], ref[f], equal_nan=True), (tag, f)
+        for grp in range(5):
+            assert np.array_equal(A.download(grp, 0, n), st.m[grp], equal_nan=True), (tag, grp)
+            assert np.array_equal(A.download(grp, 1, n), st.v[grp], equal_nan=True), (tag, grp)
+    try:
+        step(1, zero_from=n // 2); check("first step clamps")
+        assert np.abs(ref["sh"][20:]).max() <= 2.0 and ref["sh"][5, 6] == -9.0   # Gaussian 5 is skipped (inf gradient): not clamped
+        step(2, zero_from=n // 2); step(3, zero_from=n // 3); check("idle planes skipped")
+        step(4); check("idle rows wake up")
+        # a skipped Gaussian keeps an out-of-range coefficient until its gradient is finite again, then it is clamped
+        gr = make_grads(orc, n, 40); gr["opacity"][5] = 0.25
+        orc.adam_step(ref, gr, st, lrs); D.upload(gr); A.step(G, D, lrs)
+        check("skipped Gaussian comes back"); assert ref["sh"][5, 6] == -2.0
+        g2 = G.download(); g2["sh"][::3, 9] = 7.0; ref["sh"][::3, 9] = 7.0
+        G.upload(g2)
+        step(5); check("re-upload outside the clamp")
+        m = st.m[4].copy(); m[5::12] = 1e-3; st.m[4][:] = m      # caller-supplied moments on a non-DC plane
+        A.upload(4, 0, m, n)
+        step(6); step(7); check("uploaded SH moments")
+    finally:
+        D.close(); A.close(); G.close()
+
+
 # ---- DensityController ------------------------------------------------------------------------------------
 def test_accumulate_gradients_parity(gs, ctx, orc):
     n = 4000
