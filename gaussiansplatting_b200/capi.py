@@ -160,6 +160,13 @@ class Grads:
         lib().gs_grads_destroy(self.h)
 
 
+def loss(ctx, rendered, ground_truth, lambda_dssim=0.2, quantize=False):
+    """MTLEngine::computeLoss: (1 - lambda) * L1 + lambda * D-SSIM, mean over pixels (synchronises)"""
+    out = C.c_float(0.0)
+    ctx.check(lib().gs_loss_compute(ctx.h, rendered.h, ground_truth.h, C.c_float(lambda_dssim), C.c_int(1 if quantize else 0), C.byref(out)))
+    return float(out.value)
+
+
 class Image:
     def __init__(self, ctx, width, height):
         self.ctx, self.w, self.hgt = ctx, width, height

@@ -18,6 +18,7 @@ struct gs_ctx {
     std::string err;
     uint32_t* h_pinned = nullptr;   // small pinned read-back area
     cudaStream_t xfer_in = nullptr, xfer_out = nullptr;   // copy streams of the *_async image transfers (created on first use)
+    double* d_loss = nullptr;                              // accumulator of gs_loss_compute
     cudaStream_t xfer_meta = nullptr;                     // small read-backs (pair count) that must not queue behind an image
 };
 static std::string g_create_err;
@@ -99,6 +100,7 @@ int gs_ctx_destroy(gs_ctx* c) {
     if (c->xfer_meta) { cudaStreamSynchronize(c->xfer_meta); cudaStreamDestroy(c->xfer_meta); }
     if (c->own_stream) cudaStreamDestroy(c->stream);
     cudaFreeHost(c->h_pinned);
+    cudaFree(c->d_loss);
     delete c;
     return GS_OK;
 }
@@ -273,12 +275,14 @@ static int image_async_begin(gs_image* im, cudaStream_t* xfer) {
     return GS_OK;
 }
 
-static int grads_reserve(gs_grads* g, uint32_t n) {   // contents are NOT preserved on growth
+// contents are NOT preserved on growth.  The caller's capacity is honoured exactly at creation (the 16 planes of `stride`
+// floats are the all-reduce payload of view-parallel training: slack there is NVLink traffic); later growth adds 25 %.
+static int grads_reserve(gs_grads* g, uint32_t n, bool exact = false) {
     if (n <= g->cap) return GS_OK;
     gs_ctx* c = g->c;
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     cudaFree(g->g); g->g = nullptr;
-    g->cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    g->cap = ((exact ? n : (uint32_t)(n * 1.25)) + 63u) & ~63u;
     g->stride = g->cap;
     return dalloc(c, &g->g, (size_t)g->cap * 16);
 }
@@ -299,7 +303,7 @@ int gs_grads_create(gs_ctx* c, uint32_t capacity, gs_grads** out) {
     gs_grads* g = new (std::nothrow) gs_grads();
     if (!g) return GS_ERR_OOM;
     g->c = c;
-    int r = grads_reserve(g, std::max(capacity, 64u));
+    int r = grads_reserve(g, std::max(capacity, 64u), true);
     if (r != GS_OK) { delete g; return r; }
     *out = g;
     return GS_OK;
@@ -431,6 +435,27 @@ int gs_image_wait(gs_image* im) {
     return GS_OK;
 }
 void* gs_image_devptr(gs_image* im) { return im->px; }
+
+// MTLEngine::computeLoss (mtl_engine.mm:769-853): (1 - lambda) * L1 + lambda * D-SSIM, mean over the pixels.  Synchronises,
+// as the reference does (waitUntilCompleted + read of the shared buffer).
+int gs_loss_compute(gs_ctx* c, gs_image* rendered, gs_image* gt, float lambda_dssim, int flags, float* loss) {
+    GS_SETDEV(c);
+    GS_ARG(c, rendered && gt && loss, "null argument");
+    GS_ARG(c, rendered->w == gt->w && rendered->h == gt->h, "image sizes differ");
+    GS_TRY(image_before_read(rendered, c->stream));
+    GS_TRY(image_before_read(gt, c->stream));
+    if (!c->d_loss) GS_TRY(dalloc(c, &c->d_loss, 1));
+    GS_CUDA(c, cudaMemsetAsync(c->d_loss, 0, sizeof(double), c->stream));
+    gs_launch_loss(rendered->px, gt->px, rendered->w, rendered->h, lambda_dssim, (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, c->d_loss, c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_TRY(image_after_use(rendered, c->stream));
+    GS_TRY(image_after_use(gt, c->stream));
+    double total = 0.0;
+    GS_CUDA(c, cudaMemcpyAsync(&total, c->d_loss, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    *loss = (float)(total / ((double)rendered->w * rendered->h));
+    return GS_OK;
+}
 
 }  // extern "C"
 

@@ -99,6 +99,10 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
                                      uint32_t n, uint64_t* keys, cudaStream_t st);
 
+// logging loss (0.8 L1 + 0.2 D-SSIM, mean over pixels): adds the sum over pixels to *total (zeroed by the caller)
+void gs_launch_loss(const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize, double* total,
+                    cudaStream_t st);
+
 // layout conversion between the reference's AoS wire structs and the device SoA
 void gs_launch_params_from_aos(const void* aos112, uint32_t n, GsParams P, cudaStream_t st);
 void gs_launch_params_to_aos(GsParams P, uint32_t n, void* aos112, cudaStream_t st);

@@ -16,14 +16,15 @@ class TrainConfig(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("num_views", C.c_uint32), ("epochs", C.c_uint32),
                 ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("scene_extent", C.c_float),
                 ("densify_from", C.c_uint32), ("densify_until", C.c_uint32), ("densify_interval", C.c_uint32),
-                ("opacity_reset_interval", C.c_uint32), ("seed", C.c_uint32), ("quantize_rgba8", C.c_int)]
+                ("opacity_reset_interval", C.c_uint32), ("seed", C.c_uint32), ("quantize_rgba8", C.c_int),
+                ("log_loss_every_step", C.c_int), ("export_dir", C.c_char_p)]
 
 
 class TrainResult(C.Structure):
     _fields_ = [("seconds", C.c_double), ("densify_seconds", C.c_double), ("iterations", C.c_uint64),
                 ("densify_events", C.c_uint64), ("opacity_resets", C.c_uint64), ("pruned", C.c_uint64),
                 ("cloned", C.c_uint64), ("split", C.c_uint64), ("final_count", C.c_uint32), ("adam_timestep", C.c_uint32),
-                ("last_pairs", C.c_uint64)]
+                ("last_pairs", C.c_uint64), ("first_loss", C.c_float), ("last_loss", C.c_float), ("views_exported", C.c_uint32)]
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

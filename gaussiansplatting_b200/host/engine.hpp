@@ -9,6 +9,8 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <fstream>
+#include <string>
 #include <vector>
 #include "gs_host.hpp"
 
@@ -108,7 +110,42 @@ public:
         return u;
     }
 
-    // one training iteration on view imgIdx (the reference returns the logging loss; that kernel is off the gradient path)
+    // computeLoss, mtl_engine.mm:769-853: (1 - lambdaDSSIM) * L1 + lambdaDSSIM * D-SSIM, mean over pixels (synchronises)
+    float computeLoss(MTL::Texture* rendered, MTL::Texture* groundTruth) {
+        float loss = 0.0f;
+        MTL::gs_check(device->ctx(), gs_loss_compute(device->ctx(), rendered->image(), groundTruth->image(), lambdaDSSIM,
+                                                     GS_BWD_QUANTIZE_RGBA8 /* RGBA8Unorm render target */, &loss), "computeLoss");
+        return loss;
+    }
+    // saveTextureToPPM, mtl_engine.mm:19-63 (binary P6 from the RGBA8 contents of a headless device image)
+    static bool saveTextureToPPM(MTL::Texture* texture, const std::string& path) {
+        const uint32_t w = texture->width(), h = texture->height();
+        std::vector<uint8_t> rgba((size_t)w * h * 4), rgb((size_t)w * h * 3);
+        texture->getBytesRGBA8(rgba.data());
+        for (size_t i = 0; i < (size_t)w * h; i++) { rgb[3 * i] = rgba[4 * i]; rgb[3 * i + 1] = rgba[4 * i + 1]; rgb[3 * i + 2] = rgba[4 * i + 2]; }
+        std::ofstream f(path, std::ios::binary);
+        if (!f) return false;
+        f << "P6\n" << w << " " << h << "\n255\n";
+        f.write(reinterpret_cast<const char*>(rgb.data()), (std::streamsize)rgb.size());
+        return (bool)f;
+    }
+    // exportTrainingViews, mtl_engine.mm:1223-1306: forward of every training view at its own resolution -> <dir>/view_NNN.ppm
+    size_t exportTrainingViews(const std::string& dir) {
+        size_t written = 0;
+        for (size_t i = 0; i < trainingImages.size(); i++) {
+            const TrainingView& v = trainingImages[i];
+            MTL::Texture* t = device->newTexture(v.texture->width(), v.texture->height());
+            tiledRasterizer->forward(commandQueue, gaussianBuffer, gaussianCount, uniformsFor(v), t);
+            char name[64];
+            std::snprintf(name, sizeof name, "/view_%03zu.ppm", i);
+            written += saveTextureToPPM(t, dir + name) ? 1 : 0;
+            t->release();
+        }
+        return written;
+    }
+
+    // one training iteration on view imgIdx.  The reference computes the logging loss in every step with a full device
+    // sync (:991); here that is opt-in (logLossEveryStep) because the loss is off the gradient path; lastLoss keeps it.
     float trainStep(size_t imgIdx, float lrPos, float lrScale, float lrRot, float lrOpacity, float lrSH) {
         const TrainingView& v = trainingImages[imgIdx];
         if (!renderTarget || renderTarget->width() != v.texture->width() || renderTarget->height() != v.texture->height()) {
@@ -117,10 +154,11 @@ public:
         }
         const TiledUniforms u = uniformsFor(v);
         tiledRasterizer->forward(commandQueue, gaussianBuffer, gaussianCount, u, renderTarget);                       // :973
+        if (logLossEveryStep) lastLoss = computeLoss(renderTarget, v.texture);                                        // :991
         tiledRasterizer->backward(commandQueue, gaussianBuffer, gaussianGradients, gaussianCount, u, renderTarget, v.texture);   // :994
         densityController->accumulateGradients(commandQueue, gaussianGradients, gaussianCount);                       // :998
         optimizer->step(commandQueue, gaussianBuffer, gaussianGradients, lrPos, lrScale, lrRot, lrOpacity, lrSH);     // :1001
-        return 0.0f;
+        return lastLoss;
     }
 
     TrainStats train(size_t numEpochs, const TrainSchedule& S = TrainSchedule()) {   // mtl_engine.mm:1047-1221
@@ -183,4 +221,7 @@ public:
     std::vector<TrainingView> trainingImages;
     size_t gaussianCount = 0;
     float sceneExtent = 1.0f;
+    float lambdaDSSIM = 0.2f;          // mtl_engine.hpp:147
+    bool logLossEveryStep = false;
+    float lastLoss = 0.0f;
 };

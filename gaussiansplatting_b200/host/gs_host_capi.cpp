@@ -11,6 +11,8 @@ typedef struct {
     uint32_t densify_from, densify_until, densify_interval, opacity_reset_interval;   // 0 = the reference's constants
     uint32_t seed;
     int quantize_rgba8;       // 1 = backward reads the 8-bit-quantised render (what the reference's RGBA8 target does)
+    int log_loss_every_step;  // 1 = computeLoss in every trainStep with a device sync, as the reference does (mtl_engine.mm:991)
+    const char* export_dir;   // non-NULL: exportTrainingViews(dir) after training (view_NNN.ppm)
 } gs_host_train_config;
 
 typedef struct {
@@ -18,6 +20,8 @@ typedef struct {
     uint64_t iterations, densify_events, opacity_resets, pruned, cloned, split;
     uint32_t final_count, adam_timestep;
     uint64_t last_pairs;
+    float first_loss, last_loss;   // logging loss of the first / last iteration (0 unless log_loss_every_step)
+    uint32_t views_exported;
 } gs_host_train_result;
 
 static char g_err[512];
@@ -61,6 +65,15 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
         if (cfg->densify_until) S.densifyUntilIter = cfg->densify_until;
         if (cfg->densify_interval) S.densityControlInterval = cfg->densify_interval;
         if (cfg->opacity_reset_interval) S.opacityResetInterval = cfg->opacity_reset_interval;
+        eng.logLossEveryStep = cfg->log_loss_every_step != 0;
+        float first_loss = 0.0f;
+        if (eng.logLossEveryStep && cfg->epochs) {     // the loss of iteration 1, before any update
+            TiledUniforms u0 = eng.uniformsFor(eng.trainingImages[0]);
+            MTL::Texture* t0 = eng.device->newTexture(cfg->width, cfg->height);
+            eng.tiledRasterizer->forward(eng.commandQueue, eng.gaussianBuffer, eng.gaussianCount, u0, t0);
+            first_loss = eng.computeLoss(t0, eng.trainingImages[0].texture);
+            t0->release();
+        }
         const TrainStats st = eng.train(cfg->epochs, S);
         if (res) {
             res->seconds = st.seconds; res->densify_seconds = st.densifySeconds; res->iterations = st.iterations;
@@ -68,6 +81,11 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
             res->pruned = st.pruned; res->cloned = st.cloned; res->split = st.split;
             res->final_count = (uint32_t)st.finalCount; res->adam_timestep = eng.optimizer->getTimestep();
             res->last_pairs = eng.tiledRasterizer->pairCount();
+            res->first_loss = first_loss; res->last_loss = eng.lastLoss; res->views_exported = 0;
+        }
+        if (cfg->export_dir) {
+            const size_t w = eng.exportTrainingViews(cfg->export_dir);
+            if (res) res->views_exported = (uint32_t)w;
         }
         if (out) {
             const std::vector<Gaussian> g = eng.getGaussians();

@@ -138,6 +138,12 @@ int gs_image_download_rgba8_async(gs_image*, uint8_t* host);
 int gs_image_wait(gs_image*);                                             /* host blocks until the transfer in flight is done */
 void* gs_image_devptr(gs_image*);                                          /* float4[width*height] */
 
+/* ---- logging loss: MTLEngine::computeLoss (mtl_engine.mm:769-853; computeL1Loss / computeSSIM / computeCombinedLoss /
+ * reduceLoss, shaders.metal:319-511).  (1 - lambda_dssim) * L1 + lambda_dssim * D-SSIM (11x11 Gaussian window, sigma 1.5,
+ * mean RGB, clamp to edge), mean over pixels.  Off the gradient path.  flags: GS_BWD_QUANTIZE_RGBA8 reads the rendered
+ * image as the reference's RGBA8Unorm texture would hold it.  Synchronises. */
+int gs_loss_compute(gs_ctx*, gs_image* rendered, gs_image* ground_truth, float lambda_dssim, int flags, float* loss);
+
 /* ---- TiledRasterizer (tiled_rasterizer.hpp:56-124) ------------------------------------------------------ */
 int gs_rast_create(gs_ctx*, uint32_t max_gaussians, gs_rast** out);
 int gs_rast_destroy(gs_rast*);

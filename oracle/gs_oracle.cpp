@@ -863,4 +863,54 @@ float orc_lr_decay(float lr_init, float lr_final, uint64_t iter, uint64_t maxIte
     return lr_init * powf(lr_final / lr_init, t);
 }
 
+/* MTLEngine::computeLoss (mtl_engine.mm:769-853): computeL1Loss (shaders.metal:320-340), computeSSIM (:377-466),
+ * computeCombinedLoss (:470-498), reduceLoss (:343-358).  rendered / gt: RGBA float, row-major.  quantize: read the rendered
+ * image through an RGBA8Unorm texture as the reference does (note G).  Returns sum / pixelCount. */
+float orc_loss(const float* rendered, const float* gt, uint32_t width, uint32_t height, float lambda_dssim, int quantize) {
+    const int W = (int)width, H = (int)height;
+    auto rd = [&](const float* img, int x, int y, int c, bool q) {
+        float v = img[((size_t)y * W + x) * 4 + c];
+        if (q) v = floorf(fminf(fmaxf(v, 0.0f), 1.0f) * 255.0f + 0.5f) / 255.0f;
+        return v;
+    };
+    const float two_sigma_sq = 2.0f * 1.5f * 1.5f;
+    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+    double total = 0.0;                                       /* the reference adds 1024 float partial sums atomically */
+#pragma omp parallel for reduction(+ : total) schedule(static)
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            float mu_x = 0.f, mu_y = 0.f, wsum = 0.f;
+            for (int dy = -5; dy <= 5; dy++)
+                for (int dx = -5; dx <= 5; dx++) {
+                    const int px = std::min(std::max(x + dx, 0), W - 1), py = std::min(std::max(y + dy, 0), H - 1);
+                    const float w = expf(-(float)(dx * dx + dy * dy) / two_sigma_sq);
+                    wsum += w;
+                    const float xv = (rd(rendered, px, py, 0, quantize) + rd(rendered, px, py, 1, quantize) + rd(rendered, px, py, 2, quantize)) / 3.0f;
+                    const float yv = (rd(gt, px, py, 0, false) + rd(gt, px, py, 1, false) + rd(gt, px, py, 2, false)) / 3.0f;
+                    mu_x += w * xv; mu_y += w * yv;
+                }
+            mu_x /= wsum; mu_y /= wsum;
+            float sxx = 0.f, syy = 0.f, sxy = 0.f;
+            wsum = 0.f;
+            for (int dy = -5; dy <= 5; dy++)
+                for (int dx = -5; dx <= 5; dx++) {
+                    const int px = std::min(std::max(x + dx, 0), W - 1), py = std::min(std::max(y + dy, 0), H - 1);
+                    const float w = expf(-(float)(dx * dx + dy * dy) / two_sigma_sq);
+                    wsum += w;
+                    const float xv = (rd(rendered, px, py, 0, quantize) + rd(rendered, px, py, 1, quantize) + rd(rendered, px, py, 2, quantize)) / 3.0f;
+                    const float yv = (rd(gt, px, py, 0, false) + rd(gt, px, py, 1, false) + rd(gt, px, py, 2, false)) / 3.0f;
+                    const float a = xv - mu_x, b = yv - mu_y;
+                    sxx += w * a * a; syy += w * b * b; sxy += w * a * b;
+                }
+            sxx /= wsum; syy /= wsum; sxy /= wsum;
+            const float num = (2.0f * mu_x * mu_y + C1) * (2.0f * sxy + C2);
+            const float den = (mu_x * mu_x + mu_y * mu_y + C1) * (sxx + syy + C2);
+            const float dssim = fminf(fmaxf((1.0f - num / den) / 2.0f, 0.0f), 1.0f);
+            const float l1 = (fabsf(rd(rendered, x, y, 0, quantize) - rd(gt, x, y, 0, false)) + fabsf(rd(rendered, x, y, 1, quantize) - rd(gt, x, y, 1, false)) +
+                              fabsf(rd(rendered, x, y, 2, quantize) - rd(gt, x, y, 2, false))) / 3.0f;
+            total += (double)((1.0f - lambda_dssim) * l1 + lambda_dssim * dssim);
+        }
+    return (float)(total / ((double)W * H));
+}
+
 } /* extern "C" */

@@ -189,3 +189,12 @@ def render(g, u, threads=1):
     img, last, stats = forward(proj, svals, ranges, u, threads)
     return dict(proj=proj, keys=keys, vals=vals, skeys=skeys, svals=svals, ranges=ranges,
                 image=img, last=last, E=stats[0], C=stats[1])
+
+
+def loss(rendered, gt, lambda_dssim=0.2, quantize=False):
+    """MTLEngine::computeLoss (mtl_engine.mm:769-853): (1-lambda) L1 + lambda D-SSIM, mean over pixels"""
+    r = np.ascontiguousarray(rendered, np.float32); g = np.ascontiguousarray(gt, np.float32)
+    assert r.shape == g.shape and r.ndim == 3 and r.shape[2] == 4
+    f = lib().orc_loss
+    f.restype = C.c_float
+    return float(f(_p(r), _p(g), C.c_uint32(r.shape[1]), C.c_uint32(r.shape[0]), C.c_float(lambda_dssim), C.c_int(1 if quantize else 0)))

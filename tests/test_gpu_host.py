@@ -73,3 +73,29 @@ def test_cxx_engine_train_matches_python_driver(gs, ctx):
     for fld in ("position", "scale", "rotation", "opacity", "sh"):
         a, b = out[fld].astype(np.float64), ref[fld].astype(np.float64)
         assert np.quantile(np.abs(a - b), 0.999) <= 1e-3, fld
+
+
+def test_cxx_engine_logging_loss_and_ppm_export(gs, tmp_path):
+    """Engine::computeLoss in every trainStep (the reference's behaviour, mtl_engine.mm:991), exportTrainingViews /
+    saveTextureToPPM from a headless device image (mtl_engine.mm:19-63, 1224-1306)"""
+    from gaussiansplatting_b200 import host
+    n, W, H, V, orbit = 4000, 128, 96, 3, 3.0
+    g = synth.make_scene(n, 81, 0.05)
+    gt = synth.make_scene(n, 81 ^ 0xA5A5, 0.05)
+    poses = [synth.orbit_pose(v, V, orbit) for v in range(V)]
+    quats = np.array([p[0] for p in poses], np.float32)
+    trans = np.array([p[1] for p in poses], np.float32)
+    f = 0.9 * W
+    cfg = host.TrainConfig(width=W, height=H, num_views=V, epochs=20, fx=f, fy=f, cx=W / 2, cy=H / 2,
+                           scene_extent=synth.scene_extent(orbit), densify_from=10 ** 6, densify_until=10 ** 6 + 1, densify_interval=5,
+                           opacity_reset_interval=10 ** 6, seed=7, quantize_rgba8=1, log_loss_every_step=1,
+                           export_dir=str(tmp_path).encode())
+    res, _ = host.train(g, gt, quats, trans, cfg)
+    assert 0.0 < res["last_loss"] < res["first_loss"] < 1.0          # 60 Adam steps reduce the logging loss
+    assert res["views_exported"] == V
+    for v in range(V):
+        raw = (tmp_path / f"view_{v:03d}.ppm").read_bytes()
+        head = f"P6\n{W} {H}\n255\n".encode()
+        assert raw.startswith(head) and len(raw) == len(head) + W * H * 3
+    px = np.frombuffer(raw[len(head):], np.uint8)
+    assert px.min() < 250 and px.max() == 255                       # splats over the white background

@@ -349,3 +349,30 @@ def test_backward_finite_differences(orc):
             assert abs(fd - ana) <= 0.05 * max(abs(fd), abs(ana)) + 0.05, (i, field, idx, fd, ana)
             checked += 1
     assert checked >= 20
+
+
+def test_logging_loss_against_an_independent_float64_statement(orc):
+    """orc.loss (MTLEngine::computeLoss, mtl_engine.mm:769-853) against numpy float64: 11x11 Gaussian window sigma 1.5 on
+    mean RGB with clamp-to-edge, two-pass variances, D-SSIM clamped to [0,1], 0.8 L1 + 0.2 D-SSIM, mean over pixels"""
+    rng = np.random.default_rng(3)
+    H, W = 37, 45
+    a = rng.random((H, W, 4)).astype(np.float32)
+    b = np.clip(a + 0.2 * rng.standard_normal((H, W, 4)), 0, 1).astype(np.float32)
+    xs, ys = a[..., :3].astype(np.float64).mean(-1), b[..., :3].astype(np.float64).mean(-1)
+    d = np.arange(-5, 6)
+    w = np.exp(-(d[:, None] ** 2 + d[None, :] ** 2) / 4.5)
+    w /= w.sum()
+    xp, yp = np.pad(xs, 5, mode="edge"), np.pad(ys, 5, mode="edge")
+    win = lambda p: np.lib.stride_tricks.sliding_window_view(p, (11, 11))          # [H, W, 11, 11]
+    mx, my = (win(xp) * w).sum((-1, -2)), (win(yp) * w).sum((-1, -2))
+    dx, dy = win(xp) - mx[..., None, None], win(yp) - my[..., None, None]
+    sxx, syy, sxy = (w * dx * dx).sum((-1, -2)), (w * dy * dy).sum((-1, -2)), (w * dx * dy).sum((-1, -2))
+    ssim = (2 * mx * my + 1e-4) * (2 * sxy + 9e-4) / ((mx * mx + my * my + 1e-4) * (sxx + syy + 9e-4))
+    dssim = np.clip((1 - ssim) / 2, 0, 1)
+    l1 = np.abs(a[..., :3].astype(np.float64) - b[..., :3]).mean(-1)
+    want = (0.8 * l1 + 0.2 * dssim).mean()
+    assert abs(orc.loss(a, b) - want) <= 2e-6
+    assert orc.loss(a, a) == 0.0
+    assert abs(orc.loss(a, b, lambda_dssim=0.0) - l1.mean()) <= 1e-6
+    aq = np.floor(np.clip(a, 0, 1) * 255 + 0.5).astype(np.float32) / 255
+    assert abs(orc.loss(a, b, quantize=True) - orc.loss(aq, b)) <= 1e-7
