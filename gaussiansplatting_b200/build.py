@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libgs_b200.so")
-SOURCES = ["preprocess.cu", "pairs.cu", "binning.cu", "radix_sort.cu", "blend_fwd.cu", "blend_bwd.cu", "layout.cu", "loss.cu", "adam.cu",
+SOURCES = ["preprocess.cu", "pairs.cu", "binning.cu", "radix_sort.cu", "blend_fwd.cu", "blend_bwd.cu", "layout.cu", "loss.cu", "viewer.cu", "adam.cu",
            "densify.cu", "api.cu"]
 HEADERS = ["gs_common.cuh", "gs_kernels.h", os.path.join("..", "..", "include", "gs_abi.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -7,7 +7,7 @@ GsError is raised.
 import ctypes as C
 import os
 import numpy as np
-from .layouts import GAUSSIAN, GRADIENTS, PROJECTED, TILERANGE, UNIFORMS
+from .layouts import GAUSSIAN, GRADIENTS, PROJECTED, TILERANGE, UNIFORMS, VIEW_UNIFORMS, VIEW_SPLAT
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GS_LIB", os.path.join(_HERE, "libgs_b200.so"))
@@ -15,6 +15,9 @@ _lib = None
 
 GS_BWD_QUANTIZE_RGBA8 = 1
 GS_BWD_ACCUMULATE = 2
+GS_VIEW_QUANTIZE_RGBA8 = 1
+GS_VIEW_COUNT_FRAGMENTS = 2
+(VIEW_SPLATS, VIEW_SORTED_TILES, VIEW_SORTED_VALUES, VIEW_TILE_RANGES) = range(4)
 (RAST_PROJECTED, RAST_KEYS, RAST_VALUES, RAST_SORTED_KEYS, RAST_SORTED_VALUES, RAST_TILE_RANGES, RAST_LAST_IDX,
  RAST_TFINAL) = range(8)
 
@@ -36,6 +39,7 @@ def lib():
         L.gs_image_devptr.restype = C.c_void_p
         L.gs_rast_pair_count.restype = C.c_uint64
         L.gs_rast_coarse_pair_count.restype = C.c_uint64
+        L.gs_viewer_pair_count.restype = C.c_uint64
         for name in ("gs_sort64_sorted_keys", "gs_sort64_sorted_values", "gs_sort32_sorted_keys",
                      "gs_sort32_sorted_indices"):
             getattr(L, name).restype = C.c_void_p
@@ -343,6 +347,41 @@ class Sort32:
 
     def close(self):
         lib().gs_sort32_destroy(self.h)
+
+
+class Viewer:
+    """The draw of MTLEngine::render (mtl_engine.mm:401-609; vertexShader / fragmentShader, shaders.metal:160-317) as CUDA
+    compute into a headless Image."""
+    def __init__(self, ctx, max_gaussians):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        ctx.check(lib().gs_viewer_create(ctx.h, C.c_uint32(max_gaussians), C.byref(self.h)))
+
+    def render(self, gaussians, d_sorted_indices, view_uniforms, out_image, flags=0):
+        u = np.ascontiguousarray(view_uniforms, VIEW_UNIFORMS)
+        self.ctx.check(lib().gs_viewer_render(self.h, gaussians.h, C.c_void_p(d_sorted_indices), _p(u), out_image.h, C.c_int(flags)))
+
+    @property
+    def pair_count(self):
+        return int(lib().gs_viewer_pair_count(self.h))
+
+    def fragments(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self.ctx.check(lib().gs_viewer_fragments(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def get(self, which, n=None, tiles=None):
+        if which == VIEW_SPLATS:
+            out = np.zeros(n, VIEW_SPLAT)
+        elif which == VIEW_TILE_RANGES:
+            out = np.zeros(tiles, TILERANGE)
+        else:
+            out = np.zeros(self.pair_count, np.uint32)
+        self.ctx.check(lib().gs_viewer_get(self.h, C.c_int(which), _p(out), C.c_size_t(out.nbytes)))
+        return out
+
+    def close(self):
+        lib().gs_viewer_destroy(self.h)
 
 
 class Adam:

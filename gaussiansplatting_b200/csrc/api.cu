@@ -1031,6 +1031,165 @@ const uint32_t* gs_sort32_sorted_indices(gs_sort32* s) { return s->vbuf[s->resul
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------------
+// Viewer draw (MTLEngine::render, mtl_engine.mm:401-609, without the window): viewer.cu
+// ------------------------------------------------------------------------------------------------------
+struct gs_viewer {
+    gs_ctx* c;
+    uint32_t cap_g = 0, cap_tiles = 0;
+    uint64_t cap_pairs = 0;
+    float4* rec = nullptr; uint4* bbox = nullptr; uint32_t* cnt = nullptr; uint32_t* offs = nullptr;
+    uint32_t* meta = nullptr;                       // [0] = pair count of the frame
+    void* scan_scratch = nullptr;
+    uint32_t *tiles_in = nullptr, *vals_in = nullptr, *tbuf[2] = {nullptr, nullptr}, *vbuf[2] = {nullptr, nullptr};
+    void* sort_scratch = nullptr;
+    uint2* ranges = nullptr;
+    unsigned long long* counters = nullptr;
+    void* staging = nullptr; size_t staging_bytes = 0;
+    uint32_t W = 0, H = 0, ntx = 0, nty = 0, n = 0;
+    uint64_t pairs = 0;
+    const uint32_t* sorted_tiles = nullptr; const uint32_t* sorted_vals = nullptr;
+};
+static void viewer_free_pairs(gs_viewer* v) {
+    cudaFree(v->tiles_in); cudaFree(v->vals_in); cudaFree(v->sort_scratch);
+    for (int i = 0; i < 2; i++) { cudaFree(v->tbuf[i]); cudaFree(v->vbuf[i]); v->tbuf[i] = nullptr; v->vbuf[i] = nullptr; }
+    v->tiles_in = nullptr; v->vals_in = nullptr; v->sort_scratch = nullptr;
+}
+static int viewer_reserve_pairs(gs_viewer* v, uint64_t need) {
+    if (need <= v->cap_pairs) return GS_OK;
+    gs_ctx* c = v->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    viewer_free_pairs(v);
+    const uint64_t cap = std::max<uint64_t>(need, (uint64_t)(v->cap_pairs * 1.5));
+    v->cap_pairs = 0;
+    GS_TRY(dalloc(c, &v->tiles_in, cap)); GS_TRY(dalloc(c, &v->vals_in, cap));
+    for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &v->tbuf[i], cap)); GS_TRY(dalloc(c, &v->vbuf[i], cap)); }
+    GS_CUDA(c, cudaMalloc(&v->sort_scratch, gs_sort_scratch_bytes(cap, 4)));
+    v->cap_pairs = cap;
+    return GS_OK;
+}
+static void viewer_free_gaussians(gs_viewer* v) {
+    cudaFree(v->rec); cudaFree(v->bbox); cudaFree(v->cnt); cudaFree(v->offs); cudaFree(v->scan_scratch);
+    v->rec = nullptr; v->bbox = nullptr; v->cnt = nullptr; v->offs = nullptr; v->scan_scratch = nullptr;
+}
+static int viewer_reserve_gaussians(gs_viewer* v, uint32_t n) {
+    if (n <= v->cap_g) return GS_OK;
+    gs_ctx* c = v->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    viewer_free_gaussians(v);
+    v->cap_g = 0;
+    const uint32_t cap = ((uint32_t)(n * 1.25) + 63u) & ~63u;
+    GS_TRY(dalloc(c, &v->rec, (size_t)cap * 3)); GS_TRY(dalloc(c, &v->bbox, cap)); GS_TRY(dalloc(c, &v->cnt, cap));
+    GS_TRY(dalloc(c, &v->offs, (size_t)cap + 1));
+    GS_CUDA(c, cudaMalloc(&v->scan_scratch, gs_scan_scratch_bytes(cap)));
+    v->cap_g = cap;
+    return GS_OK;
+}
+
+extern "C" {
+
+int gs_viewer_create(gs_ctx* c, uint32_t max_gaussians, gs_viewer** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out, "out");
+    gs_viewer* v = new (std::nothrow) gs_viewer();
+    if (!v) return GS_ERR_OOM;
+    v->c = c;
+    int rc = dalloc(c, &v->meta, 4);
+    if (rc == GS_OK) rc = dalloc(c, &v->counters, 2);
+    if (rc == GS_OK) rc = viewer_reserve_gaussians(v, std::max(max_gaussians, 64u));
+    if (rc == GS_OK) rc = viewer_reserve_pairs(v, (uint64_t)std::max(max_gaussians, 64u) * 8);
+    if (rc != GS_OK) { gs_viewer_destroy(v); return rc; }
+    *out = v;
+    return GS_OK;
+}
+int gs_viewer_destroy(gs_viewer* v) {
+    if (!v) return GS_OK;
+    cudaSetDevice(v->c->device);
+    cudaStreamSynchronize(v->c->stream);
+    viewer_free_gaussians(v); viewer_free_pairs(v);
+    cudaFree(v->meta); cudaFree(v->counters); cudaFree(v->ranges); cudaFree(v->staging);
+    delete v;
+    return GS_OK;
+}
+int gs_viewer_render(gs_viewer* v, gs_gaussians* g, const uint32_t* d_order, const gs_view_uniforms* u, gs_image* out, int flags) {
+    gs_ctx* c = v->c; GS_SETDEV(c);
+    cudaStream_t st = c->stream;
+    GS_ARG(c, g && u && out, "null argument");
+    GS_ARG(c, d_order || g->n == 0, "sorted indices (GPURadixSort32::sort) are required");
+    const uint32_t W = out->w, H = out->h, n = g->n;
+    GS_ARG(c, (float)W == u->screenSize[0] && (float)H == u->screenSize[1], "uniforms.screenSize must equal the render target size");
+    const uint32_t ntx = (W + GS_TILE - 1) / GS_TILE, nty = (H + GS_TILE - 1) / GS_TILE, tiles = ntx * nty;
+    GS_TRY(viewer_reserve_gaussians(v, n));
+    if (tiles > v->cap_tiles) {
+        GS_CUDA(c, cudaStreamSynchronize(st));
+        cudaFree(v->ranges); v->ranges = nullptr; v->cap_tiles = 0;
+        GS_TRY(dalloc(c, &v->ranges, tiles));
+        v->cap_tiles = tiles;
+    }
+    v->W = W; v->H = H; v->ntx = ntx; v->nty = nty; v->n = n;
+    GS_TRY(image_before_write(out, st));
+    gs_launch_view_splats(g->view(), u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1], u->focalLength[0],
+                          u->focalLength[1], n, v->rec, v->bbox, v->cnt, st);
+    GS_CUDA(c, cudaMemsetAsync(v->meta, 0, 4 * sizeof(uint32_t), st));
+    if (n) gs_launch_exclusive_scan(v->cnt, d_order, v->offs, n, v->meta, v->scan_scratch, st);
+    GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, v->meta, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaStreamSynchronize(st));                              // pair count (sizes the pair buffers), as the tiled forward does
+    const uint64_t P = c->h_pinned[0];
+    if (P >= (1ull << 30)) { c->err = "pair count exceeds 2^30"; return GS_ERR_CAPACITY; }
+    GS_TRY(viewer_reserve_pairs(v, P));
+    v->pairs = P;
+    int tile_bits = 0;
+    while ((1u << tile_bits) < tiles) tile_bits++;
+    const GsSortPlan plan = gs_sort_plan_even(0, tile_bits);
+    const uint32_t cap = (uint32_t)std::min<uint64_t>(v->cap_pairs, 0x3FFFFFFFull);
+    gs_launch_view_emit(v->bbox, v->cnt, d_order, v->offs, n, ntx, v->tiles_in, v->vals_in, cap, st);
+    // instances of one tile arrive in draw order; match.any ranking suits the long runs of equal tile ids of large quads
+    const int res = gs_launch_sort32(v->tiles_in, v->vals_in, v->tbuf, v->vbuf, cap, v->meta, plan, g_tile_sort_hint, v->sort_scratch, st);
+    v->sorted_tiles = plan.num_passes ? v->tbuf[res] : v->tiles_in;
+    v->sorted_vals = plan.num_passes ? v->vbuf[res] : v->vals_in;
+    gs_launch_tile_ranges32(v->sorted_tiles, cap, v->meta, tiles, v->ranges, st);
+    const bool count = (flags & GS_VIEW_COUNT_FRAGMENTS) != 0;
+    if (count) GS_CUDA(c, cudaMemsetAsync(v->counters, 0, 2 * sizeof(unsigned long long), st));
+    gs_launch_view_blend(v->rec, v->sorted_vals, v->ranges, W, H, ntx, nty, (flags & GS_VIEW_QUANTIZE_RGBA8) ? 1 : 0, out->px,
+                         count ? v->counters : nullptr, st);
+    GS_LAUNCH_CHECK(c);
+    GS_TRY(image_after_use(out, st));
+    return GS_OK;
+}
+int gs_viewer_get(gs_viewer* v, int which, void* host, size_t bytes) {
+    gs_ctx* c = v->c; GS_SETDEV(c);
+    cudaStream_t st = c->stream;
+    GS_ARG(c, host || bytes == 0, "host");
+    const void* src = nullptr; size_t need = 0;
+    switch (which) {
+    case GS_VIEW_SPLATS:
+        need = (size_t)v->n * sizeof(gs_view_splat);
+        GS_TRY(staging_reserve(c, &v->staging, &v->staging_bytes, need));
+        gs_launch_view_splats_to_wire(v->rec, v->bbox, v->n, v->staging, st);
+        src = v->staging; break;
+    case GS_VIEW_SORTED_TILES: need = v->pairs * 4; src = v->sorted_tiles; break;
+    case GS_VIEW_SORTED_VALUES: need = v->pairs * 4; src = v->sorted_vals; break;
+    case GS_VIEW_TILE_RANGES: need = (size_t)v->ntx * v->nty * sizeof(gs_tile_range); src = v->ranges; break;
+    default: GS_ARG(c, false, "which");
+    }
+    GS_ARG(c, bytes >= need, "host buffer too small");
+    if (need) GS_CUDA(c, cudaMemcpyAsync(host, src, need, cudaMemcpyDeviceToHost, st));
+    GS_CUDA(c, cudaStreamSynchronize(st));
+    return GS_OK;
+}
+uint64_t gs_viewer_pair_count(const gs_viewer* v) { return v->pairs; }
+int gs_viewer_fragments(gs_viewer* v, uint64_t* shaded, uint64_t* blended) {
+    gs_ctx* c = v->c; GS_SETDEV(c);
+    unsigned long long h[2] = {0, 0};
+    GS_CUDA(c, cudaMemcpyAsync(h, v->counters, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (shaded) *shaded = h[0];
+    if (blended) *blended = h[1];
+    return GS_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
 // AdamOptimizer (optimizer.hpp:23-95, optimizer.mm)
 // ------------------------------------------------------------------------------------------------------
 struct gs_adam {

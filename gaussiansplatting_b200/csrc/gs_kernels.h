@@ -99,6 +99,18 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
                                      uint32_t n, uint64_t* keys, cudaStream_t st);
 
+// viewer splat path (viewer.cu; vertexShader / fragmentShader + blend state of MTLEngine::render as compute).  rec: 3 float4 per
+// Gaussian {cx, cy, k0, k1}{k2, radius, opacity, r}{g, b, valid, 0}; bbox: tile box of the quad; cnt: its tile count (0 = not drawn)
+void gs_launch_view_splats(const GsParams& P, const float* V, const float* VP, float sw, float sh, float fx, float fy, uint32_t n,
+                           float4* rec, uint4* bbox, uint32_t* cnt, cudaStream_t st);
+// draw position j is Gaussian order[j], its pairs start at offs[j]; writes are bounded by cap_pairs
+void gs_launch_view_emit(const uint4* bbox, const uint32_t* cnt, const uint32_t* order, const uint32_t* offs, uint32_t n,
+                         uint32_t ntx, uint32_t* tiles, uint32_t* vals, uint32_t cap_pairs, cudaStream_t st);
+// counters (may be null): [0] += fragments shaded, [1] += fragments blended
+void gs_launch_view_blend(const float4* rec, const uint32_t* vals, const uint2* ranges, uint32_t W, uint32_t H, uint32_t ntx,
+                          uint32_t nty, int quantize, float4* image, unsigned long long* counters, cudaStream_t st);
+void gs_launch_view_splats_to_wire(const float4* rec, const uint4* bbox, uint32_t n, void* out64, cudaStream_t st);
+
 // logging loss (0.8 L1 + 0.2 D-SSIM, mean over pixels): adds the sum over pixels to *total (zeroed by the caller)
 void gs_launch_loss(const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize, double* total,
                     cudaStream_t st);

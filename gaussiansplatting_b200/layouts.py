@@ -24,3 +24,18 @@ UNIFORMS = np.dtype([("viewMatrix", "<f4", 16), ("projectionMatrix", "<f4", 16),
                      ("numGaussians", "<u4"), ("_pad2", "<u4")])
 assert GAUSSIAN.itemsize == 112 and GRADIENTS.itemsize == 112 and PROJECTED.itemsize == 88
 assert TILERANGE.itemsize == 8 and UNIFORMS.itemsize == 240
+# viewer draw (gs_viewer_*): Uniforms of mtl_engine.hpp:30-38 (host layout, 240 B) and the per-instance inspection record
+VIEW_UNIFORMS = np.dtype([("viewMatrix", "<f4", 16), ("projectionMatrix", "<f4", 16), ("viewProjectionMatrix", "<f4", 16),
+                          ("screenSize", "<f4", 2), ("focalLength", "<f4", 2), ("cameraPos", "<f4", 4), ("_pad", "<f4", 4)])
+VIEW_SPLAT = np.dtype([("center", "<f4", 2), ("conic", "<f4", 3), ("radius", "<f4"), ("opacity", "<f4"), ("color", "<f4", 3),
+                       ("valid", "<u4"), ("tileMinX", "<u4"), ("tileMinY", "<u4"), ("tileMaxX", "<u4"), ("tileMaxY", "<u4"),
+                       ("_pad", "<u4")])
+assert VIEW_UNIFORMS.itemsize == 240 and VIEW_SPLAT.itemsize == 64
+
+
+def view_uniforms(u):
+    """Uniforms of the viewer draw from a TiledUniforms record: same matrices, screen size, focal length and camera"""
+    v = np.zeros(1, VIEW_UNIFORMS)
+    for f in ("viewMatrix", "projectionMatrix", "viewProjectionMatrix", "screenSize", "focalLength", "cameraPos"):
+        v[f] = u[f]
+    return v

@@ -60,11 +60,26 @@ typedef struct {               /* TiledUniforms — tiled_rasterizer.hpp:42-53 (
     uint32_t numTilesX, numTilesY, numGaussians, _pad2;
 } gs_uniforms;
 
+typedef struct {               /* Uniforms — mtl_engine.hpp:30-38 (host layout: simd_float3 occupies 16 B, struct rounded to 240 B) */
+    float viewMatrix[16], projectionMatrix[16], viewProjectionMatrix[16];
+    float screenSize[2], focalLength[2];
+    float cameraPos[4];
+    float _pad[4];
+} gs_view_uniforms;
+
+typedef struct {               /* what the restated vertex stage hands to the rasteriser, per instance (inspection only) */
+    float center[2];           /* quad centre in framebuffer pixels */
+    float conic[3]; float radius; float opacity; float color[3];
+    uint32_t valid;            /* 0: the instance draws nothing (invalid, behind the camera, depth-clipped, off screen) */
+    uint32_t tileMinX, tileMinY, tileMaxX, tileMaxY; uint32_t _pad;
+} gs_view_splat;
+
 typedef struct { uint32_t numPruned, numCloned, numSplit; } gs_density_stats;   /* DensityStats — density_control.hpp:13-17 */
 
 #if defined(__cplusplus)
 static_assert(sizeof(gs_gaussian) == 112 && sizeof(gs_gradients) == 112 && sizeof(gs_projected) == 88, "wire layout");
 static_assert(sizeof(gs_tile_range) == 8 && sizeof(gs_uniforms) == 240, "wire layout");
+static_assert(sizeof(gs_view_uniforms) == 240 && sizeof(gs_view_splat) == 64, "wire layout");
 #endif
 
 typedef struct gs_ctx gs_ctx;
@@ -76,6 +91,7 @@ typedef struct gs_sort64 gs_sort64;         /* GPURadixSort64 */
 typedef struct gs_sort32 gs_sort32;         /* GPURadixSort32 */
 typedef struct gs_adam gs_adam;             /* AdamOptimizer */
 typedef struct gs_dens gs_dens;             /* DensityController */
+typedef struct gs_viewer gs_viewer;         /* the draw of MTLEngine::render as CUDA compute */
 
 /* ---- context (replaces MTL::Device + MTL::CommandQueue, mtl_engine.mm:79-86) ----------------------------- */
 int gs_ctx_create(int device, gs_ctx** out);
@@ -190,6 +206,26 @@ int gs_sort32_sort_depth(gs_sort32*, const void* d_positions_float4, const float
 int gs_sort32_sort(gs_sort32*, const uint32_t* d_keys, const uint32_t* d_vals, uint64_t n);
 const uint32_t* gs_sort32_sorted_keys(gs_sort32*);
 const uint32_t* gs_sort32_sorted_indices(gs_sort32*);
+
+/* ---- viewer draw: MTLEngine::render (mtl_engine.mm:401-609) without the window ---------------------------
+ * vertexShader / fragmentShader (shaders.metal:160-317) and the render pipeline's blend state (mtl_engine.mm:354-362:
+ * source ONE, destination ONE_MINUS_SRC_ALPHA, clear colour white :583) as CUDA compute into a headless gs_image: one
+ * quad per Gaussian, drawn in the order of d_sorted_indices (the buffer GPURadixSort32::sort returns, far first), each
+ * pixel centre inside the quad shaded and blended in that order.  uniforms->screenSize must equal the image size.
+ * GS_VIEW_QUANTIZE_RGBA8 rounds the target to RGBA8Unorm after every blend, as the reference's attachment stores it
+ * (mtl_engine.mm:351); default is fp32 accumulation.  Synchronises once (pair count), like gs_rast_forward. */
+int gs_viewer_create(gs_ctx*, uint32_t max_gaussians, gs_viewer** out);
+int gs_viewer_destroy(gs_viewer*);
+enum { GS_VIEW_QUANTIZE_RGBA8 = 1, GS_VIEW_COUNT_FRAGMENTS = 2 };
+int gs_viewer_render(gs_viewer*, gs_gaussians*, const uint32_t* d_sorted_indices, const gs_view_uniforms* u, gs_image* out, int flags);
+enum { GS_VIEW_SPLATS = 0,        /* gs_view_splat[n] */
+       GS_VIEW_SORTED_TILES = 1,  /* uint32[pairs] tile id of every (tile, instance) pair, tile-major, draw order inside a tile */
+       GS_VIEW_SORTED_VALUES = 2, /* uint32[pairs] Gaussian index of the pair */
+       GS_VIEW_TILE_RANGES = 3 }; /* gs_tile_range[tiles] */
+int gs_viewer_get(gs_viewer*, int which, void* host, size_t bytes);      /* synchronises */
+uint64_t gs_viewer_pair_count(const gs_viewer*);
+/* fragments shaded / blended by the last render that had GS_VIEW_COUNT_FRAGMENTS set; synchronises */
+int gs_viewer_fragments(gs_viewer*, uint64_t* shaded, uint64_t* blended);
 
 /* ---- AdamOptimizer (optimizer.hpp:23-95) ---------------------------------------------------------------- */
 int gs_adam_create(gs_ctx*, uint32_t num_gaussians, gs_adam** out);

@@ -28,11 +28,18 @@ UNIFORMS = np.dtype([("viewMatrix", "<f4", 16), ("projectionMatrix", "<f4", 16),
                      ("numGaussians", "<u4"), ("_pad2", "<u4")])
 assert GAUSSIAN.itemsize == 112 and GRADIENTS.itemsize == 112 and PROJECTED.itemsize == 88
 assert TILERANGE.itemsize == 8 and UNIFORMS.itemsize == 240
+# viewer path (viewer_oracle.cpp): Uniforms of mtl_engine.hpp:30-38 and the per-instance record of the restated vertex stage
+VIEW_UNIFORMS = np.dtype([("viewMatrix", "<f4", 16), ("projectionMatrix", "<f4", 16), ("viewProjectionMatrix", "<f4", 16),
+                          ("screenSize", "<f4", 2), ("focalLength", "<f4", 2), ("cameraPos", "<f4", 4), ("_pad", "<f4", 4)])
+VIEW_SPLAT = np.dtype([("center", "<f4", 2), ("conic", "<f4", 3), ("radius", "<f4"), ("opacity", "<f4"), ("color", "<f4", 3),
+                       ("valid", "<u4"), ("tileMinX", "<u4"), ("tileMinY", "<u4"), ("tileMaxX", "<u4"), ("tileMaxY", "<u4"),
+                       ("_pad", "<u4")])
+assert VIEW_UNIFORMS.itemsize == 240 and VIEW_SPLAT.itemsize == 64
 
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("gs_oracle.cpp", "orc_types.h", "orc_math.h")]
+    srcs = [os.path.join(_HERE, f) for f in ("gs_oracle.cpp", "viewer_oracle.cpp", "orc_types.h", "orc_math.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return so
@@ -198,3 +205,36 @@ def loss(rendered, gt, lambda_dssim=0.2, quantize=False):
     f = lib().orc_loss
     f.restype = C.c_float
     return float(f(_p(r), _p(g), C.c_uint32(r.shape[1]), C.c_uint32(r.shape[0]), C.c_float(lambda_dssim), C.c_int(1 if quantize else 0)))
+
+
+def view_uniforms(u):
+    """Uniforms (mtl_engine.hpp:30-38) of the viewer from a TiledUniforms record: same matrices, sizes and camera"""
+    v = np.zeros(1, VIEW_UNIFORMS)
+    for f in ("viewMatrix", "projectionMatrix", "viewProjectionMatrix", "screenSize", "focalLength", "cameraPos"):
+        v[f] = u[f]
+    return v
+
+
+def viewer_order(g, cam):
+    """GPURadixSort32::sort (gpu_sort.mm:196-338): back-to-front instance order of the viewer"""
+    pos4 = np.zeros((len(g), 4), np.float32)
+    pos4[:, :3] = g["position"]
+    k, v = depth_keys32(pos4, cam)
+    return sort_pairs32(k, v)[1]
+
+
+def viewer_splats(g, vu, threads=1):
+    out = np.zeros(len(g), VIEW_SPLAT)
+    lib().orc_viewer_splats(_p(g), C.c_uint32(len(g)), _p(vu), _p(out), C.c_int(threads))
+    return out
+
+
+def viewer_render(g, order, vu, quantize=False, threads=1):
+    """MTLEngine::render's draw (mtl_engine.mm:575-605) -> (image HxWx4 float32, fragments shaded, fragments blended)"""
+    W, H = int(vu["screenSize"][0][0]), int(vu["screenSize"][0][1])
+    img = np.zeros((H, W, 4), np.float32)
+    stats = np.zeros(2, np.uint64)
+    o = np.ascontiguousarray(order, np.uint32)
+    lib().orc_viewer_render(_p(g), C.c_uint32(len(g)), _p(o), _p(vu), C.c_uint32(W), C.c_uint32(H),
+                            C.c_int(1 if quantize else 0), _p(img), _p(stats), C.c_int(threads))
+    return img, int(stats[0]), int(stats[1])
