@@ -420,6 +420,39 @@ def run_ours(args):
         out["sort"] = sort_res
         out["sort_gkeys_per_s"] = sort_res["random_u64_2^24"]["gkeys_per_s"]
 
+        # ---- the viewer frame (GPURadixSort32 draw order + the instanced-quad draw of MTLEngine::render as CUDA
+        # compute into a headless image) on the same scene; CPU restatement of the same frame beside it
+        if not args.no_viewer:
+            from gaussiansplatting_b200.layouts import view_uniforms
+            S32, Vw = gs.Sort32(ctx, n), gs.Viewer(ctx, n)
+            dpos = ctx.alloc(n * 16)
+            G.positions(dpos)
+
+            def viewer_frame(i):
+                u = view(i)
+                S32.sort_depth(dpos, u["cameraPos"][0][:3], n)
+                Vw.render(G, S32.sorted_indices, view_uniforms(u), img)
+            for i in range(3):
+                viewer_frame(i)
+            reps = 10
+            vms = timed(viewer_frame, reps, collective=False) / reps
+            Vw.render(G, S32.sorted_indices, view_uniforms(view(0)), img, gs.GS_VIEW_COUNT_FRAGMENTS)
+            shaded, blended = Vw.fragments()
+            out["viewer"] = {"ms_per_frame": vms, "frames_per_s": 1e3 / vms, "pairs": Vw.pair_count, "fragments_shaded": shaded,
+                             "fragments_blended": blended, "gfragments_per_s": shaded / (vms * 1e-3) / 1e9,
+                             "what": f"{args.workload} scene through gs_sort32_sort_depth + gs_viewer_render (back-to-front, no early "
+                                     "exit: every quad fragment is shaded), device time incl. the pair-count read-back"}
+            if world == 1 and not args.no_cpu:
+                from oracle import orc
+                orc.build()
+                u0 = view(0)
+                t0 = time.time()
+                order = orc.viewer_order(g_host, u0["cameraPos"][0][:3])
+                orc.viewer_render(g_host, order, orc.view_uniforms(u0), threads=0)
+                out["viewer"]["cpu_oracle_ms_per_frame"] = (time.time() - t0) * 1e3
+                out["viewer"]["cpu_cores"] = orc.max_threads()
+            ctx.free(dpos); Vw.close(); S32.close()
+
         # ---- BASELINE config 3: training loop with Adam + densify/prune through the C++ host layer (Engine::train,
         # the reference's mtl_engine.mm:1047-1221 schedule time-compressed so that densify / opacity-reset events occur)
         if world == 1 and not args.no_c3:
@@ -469,6 +502,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=list(synth.CONFIG_N))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 training loop")
+    ap.add_argument("--no-viewer", action="store_true", help="skip the viewer-frame line (SURVEY 8f-3)")
     ap.add_argument("--c3-epochs", type=int, default=100, help="epochs of 16 views for the config-3 loop")
     args = ap.parse_args()
     # the contract is ONE JSON line on stdout: library chatter on fd 1 (e.g. "NCCL version ...") is sent to stderr, and

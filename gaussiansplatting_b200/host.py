@@ -69,3 +69,19 @@ def sort64(keys, vals, device=0):
     if rc != 0:
         raise GsError("gs_host_sort64: " + lib().gs_host_last_error().decode())
     return ko, vo
+
+
+def render_view(gaussians, quat, trans, fx, fy, cx, cy, width, height, rgba8_target=False, device=0):
+    """One viewer frame through the C++ Engine::render (MTLEngine::render, mtl_engine.mm:401-609, headless): returns
+    (image HxWx4 float32, (tile, instance) pair count)"""
+    g = np.ascontiguousarray(gaussians, GAUSSIAN)
+    q = np.ascontiguousarray(quat, np.float32)
+    t = np.ascontiguousarray(trans, np.float32)
+    out = np.zeros((height, width, 4), np.float32)
+    pairs = C.c_uint64()
+    rc = lib().gs_host_render_view(C.c_int(device), _p(g), C.c_uint32(len(g)), _p(q), _p(t), C.c_float(fx), C.c_float(fy),
+                                   C.c_float(cx), C.c_float(cy), C.c_uint32(width), C.c_uint32(height),
+                                   C.c_int(1 if rgba8_target else 0), _p(out), C.byref(pairs))
+    if rc != 0:
+        raise GsError("gs_host_render_view: " + lib().gs_host_last_error().decode())
+    return out, pairs.value

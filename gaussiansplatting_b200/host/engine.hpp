@@ -4,7 +4,8 @@
 //   trainStep       mtl_engine.mm:856-1025  uniforms from the COLMAP pose -> forward -> backward -> accumulateGradients -> Adam
 //   train           mtl_engine.mm:1047-1221 LR schedule, densify every 100 iterations in (500, 15000), opacity reset every 3000
 //   viewMatrixFromColmap / projectionFromColmap  mtl_engine.mm:637-682;  exponentialLRDecay  :1039-1045
-// Window, GLFW, the instanced-quad viewer and the logging-only loss kernels are not here (DESIGN.md "Out of scope").
+//   render          mtl_engine.mm:401-609   viewer frame: GPURadixSort32 draw order + the instanced-quad draw, into a headless texture
+// Window, GLFW, swapchain and input callbacks are not here (DESIGN.md "Out of scope").
 #pragma once
 #include <chrono>
 #include <cmath>
@@ -45,7 +46,8 @@ public:
         library = device->newDefaultLibrary();
     }
     ~Engine() {
-        delete tiledRasterizer; delete optimizer; delete densityController;
+        delete tiledRasterizer; delete optimizer; delete densityController; delete gpuSort; delete renderPipeline;
+        if (positionBuffer) positionBuffer->release();
         if (gaussianBuffer) gaussianBuffer->release();
         if (gaussianGradients) gaussianGradients->release();
         if (renderTarget) renderTarget->release();
@@ -64,6 +66,54 @@ public:
         DensityController::setSceneExtent(extent);
         densityController = new DensityController(device, library);
         tiledRasterizer = new TiledRasterizer(device, library, (uint32_t)capacity);
+    }
+
+    // updatePositionBuffer, mtl_engine.mm:1028-1036: float4 position per Gaussian for the viewer's depth sort (device-side copy)
+    void updatePositionBuffer() {
+        if (!positionBuffer || positionCapacity < gaussianCount) {
+            if (positionBuffer) positionBuffer->release();
+            positionCapacity = std::max<size_t>(gaussianCount, kOperatorCapacity);
+            positionBuffer = device->newBuffer(positionCapacity * 16);
+        }
+        MTL::gs_check(device->ctx(), gs_gaussians_positions(gaussianBuffer->gaussians(), positionBuffer->devptr()), "updatePositionBuffer");
+    }
+    // the free-camera branch of MTLEngine::render (mtl_engine.mm:537-548): 45 degree vertical field of view, fx = fy
+    static Uniforms viewerUniforms(const simd_float4x4& view, const simd_float4x4& projection, simd_float3 cameraPos, uint32_t width, uint32_t height) {
+        Uniforms u{};
+        u.viewMatrix = view; u.projectionMatrix = projection;
+        for (int c = 0; c < 4; c++) {
+            const float* vc = &view.columns[c].x;
+            float out[4] = {0, 0, 0, 0};
+            for (int k = 0; k < 4; k++) { const float* pk = &projection.columns[k].x; for (int r = 0; r < 4; r++) out[r] += pk[r] * vc[k]; }
+            u.viewProjectionMatrix.columns[c] = {out[0], out[1], out[2], out[3]};
+        }
+        const float fy = (float)height / (2.0f * std::tan(45.0f * 3.14159265358979323846f / 180.0f / 2.0f));
+        u.screenSize = {(float)width, (float)height};
+        u.focalLength = {fy, fy};
+        u.cameraPos = cameraPos;
+        return u;
+    }
+    // the training-view branch (mtl_engine.mm:409-440): the COLMAP pose and intrinsics scaled to the target size
+    Uniforms viewerUniformsFor(const TrainingView& v, uint32_t width, uint32_t height) const {
+        const float sx = (float)width / (float)v.texture->width(), sy = (float)height / (float)v.texture->height();
+        TrainingView s = v;
+        s.fx = v.fx * sx; s.fy = v.fy * sy; s.cx = v.cx * sx; s.cy = v.cy * sy;
+        const simd_float4x4 V = viewMatrixFromColmap(s), P = projectionFromColmap(s, (float)width, (float)height);
+        const simd_float4* R = V.columns;
+        const simd_float3 cam = {-(R[0].x * v.tx + R[0].y * v.ty + R[0].z * v.tz), -(R[1].x * v.tx + R[1].y * v.ty + R[1].z * v.tz),
+                                 -(R[2].x * v.tx + R[2].y * v.ty + R[2].z * v.tz), 0};
+        Uniforms u = viewerUniforms(V, P, cam, width, height);
+        u.focalLength = {s.fx, s.fy};
+        return u;
+    }
+    // MTLEngine::render, mtl_engine.mm:401-609, into a headless texture instead of the CAMetalLayer drawable: back-to-front
+    // order from GPURadixSort32 (:403), then the instanced-quad draw with blending over a white clear (:575-605)
+    void render(const Uniforms& uniforms, MTL::Texture* target) {
+        if (!gpuSort) gpuSort = new GPURadixSort32(device, library, kOperatorCapacity);               // mtl_engine.mm:317
+        if (!renderPipeline) renderPipeline = new SplatRenderPipeline(device, library, (uint32_t)kOperatorCapacity);
+        if (!positionBuffer || positionsStale) { updatePositionBuffer(); positionsStale = false; }
+        const uint32_t* sortedIndices = gpuSort->sort(commandQueue, positionBuffer, uniforms.cameraPos, gaussianCount);
+        renderPipeline->draw(commandQueue, gaussianBuffer, uniforms, sortedIndices, target);
     }
 
     static simd_float4x4 viewMatrixFromColmap(const TrainingView& v) {           // mtl_engine.mm:637-660: V = [R(q) | t]
@@ -158,6 +208,7 @@ public:
         tiledRasterizer->backward(commandQueue, gaussianBuffer, gaussianGradients, gaussianCount, u, renderTarget, v.texture);   // :994
         densityController->accumulateGradients(commandQueue, gaussianGradients, gaussianCount);                       // :998
         optimizer->step(commandQueue, gaussianBuffer, gaussianGradients, lrPos, lrScale, lrRot, lrOpacity, lrSH);     // :1001
+        positionsStale = true;                                       // the reference refreshes positionBuffer once per epoch (:1198)
         return lastLoss;
     }
 
@@ -215,6 +266,11 @@ public:
     MTL::Buffer* gaussianBuffer = nullptr;
     MTL::Buffer* gaussianGradients = nullptr;
     MTL::Texture* renderTarget = nullptr;
+    MTL::Buffer* positionBuffer = nullptr;
+    size_t positionCapacity = 0;
+    bool positionsStale = true;
+    GPURadixSort32* gpuSort = nullptr;
+    SplatRenderPipeline* renderPipeline = nullptr;
     TiledRasterizer* tiledRasterizer = nullptr;
     AdamOptimizer* optimizer = nullptr;
     DensityController* densityController = nullptr;

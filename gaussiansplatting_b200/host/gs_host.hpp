@@ -41,6 +41,13 @@ struct TiledUniforms {            // tiled_rasterizer.hpp:42-53
 static_assert(sizeof(Gaussian) == sizeof(gs_gaussian) && sizeof(GaussianGradients) == sizeof(gs_gradients), "wire layout");
 static_assert(sizeof(ProjectedGaussian) == sizeof(gs_projected) && sizeof(TileRange) == sizeof(gs_tile_range), "wire layout");
 static_assert(sizeof(TiledUniforms) == sizeof(gs_uniforms), "wire layout");
+struct Uniforms {                 // mtl_engine.hpp:30-38 (the viewer's uniform block)
+    simd_float4x4 viewMatrix, projectionMatrix, viewProjectionMatrix;
+    simd_float2 screenSize, focalLength;
+    simd_float3 cameraPos;
+    float _pad;
+};
+static_assert(sizeof(Uniforms) == sizeof(gs_view_uniforms), "wire layout");
 
 // ---- GPURadixSort64 (gpu_sort.hpp:64-107) --------------------------------------------------------------------------
 class GPURadixSort64 {
@@ -79,6 +86,28 @@ public:
 private:
     MTL::Device* device_;
     gs_sort32* s_ = nullptr;
+};
+
+// ---- the viewer's draw call (MTLEngine::createPipeline + the render encoder of MTLEngine::render, mtl_engine.mm:337-375,575-605):
+// vertexShader / fragmentShader + blend state as CUDA compute into a headless texture; no reference class of its own
+class SplatRenderPipeline {
+public:
+    SplatRenderPipeline(MTL::Device* device, MTL::Library*, uint32_t maxGaussians) : device_(device) {
+        MTL::gs_check(device->ctx(), gs_viewer_create(device->ctx(), maxGaussians, &v_), "SplatRenderPipeline");
+    }
+    ~SplatRenderPipeline() { gs_viewer_destroy(v_); }
+    // drawPrimitives(TriangleStrip, 0, 4, gaussianCount) with vertex buffers (gaussians, uniforms, sortedIndices), :592-597
+    void draw(MTL::CommandQueue*, MTL::Buffer* gaussianBuffer, const Uniforms& uniforms, const uint32_t* sortedIndices, MTL::Texture* target) {
+        MTL::gs_check(device_->ctx(), gs_viewer_render(v_, gaussianBuffer->gaussians(), sortedIndices,
+                                                       reinterpret_cast<const gs_view_uniforms*>(&uniforms), target->image(),
+                                                       quantize_ ? GS_VIEW_QUANTIZE_RGBA8 : 0), "SplatRenderPipeline::draw");
+    }
+    void setRGBA8Target(bool on) { quantize_ = on; }                           // colour attachment RGBA8Unorm, :351
+    uint64_t pairCount() const { return gs_viewer_pair_count(v_); }
+private:
+    MTL::Device* device_;
+    gs_viewer* v_ = nullptr;
+    bool quantize_ = false;
 };
 
 // ---- TiledRasterizer (tiled_rasterizer.hpp:56-75) ------------------------------------------------------------------

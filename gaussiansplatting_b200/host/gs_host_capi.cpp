@@ -100,6 +100,30 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
 }
 
 // GPURadixSort64 through the C++ class (host arrays in, host arrays out) — used by the tests of the host layer
+// One viewer frame through the C++ host layer: Engine::loadGaussians + Engine::render (MTLEngine::render, mtl_engine.mm:401-609)
+// with the training-view uniforms of pose (quat wxyz, trans) at width x height; rgba_out: width*height*4 floats.
+int gs_host_render_view(int device, const gs_gaussian* gaussians, uint32_t n, const float quat[4], const float trans[3], float fx, float fy,
+                        float cx, float cy, uint32_t width, uint32_t height, int rgba8_target, float* rgba_out, uint64_t* pairs) {
+    try {
+        Engine eng(device);
+        std::vector<Gaussian> init(n);
+        std::memcpy(init.data(), gaussians, (size_t)n * sizeof(Gaussian));
+        eng.loadGaussians(init, 1.0f);
+        MTL::Texture* target = eng.device->newTexture(width, height);
+        TrainingView tv{quat[0], quat[1], quat[2], quat[3], trans[0], trans[1], trans[2], fx, fy, cx, cy, target};
+        const Uniforms u = eng.viewerUniformsFor(tv, width, height);
+        eng.render(u, target);
+        if (rgba8_target) { eng.renderPipeline->setRGBA8Target(true); eng.render(u, target); }
+        MTL::gs_check(eng.device->ctx(), gs_image_download_rgba32f(target->image(), rgba_out), "download");
+        if (pairs) *pairs = eng.renderPipeline->pairCount();
+        target->release();
+        return 0;
+    } catch (const std::exception& e) {
+        std::snprintf(g_err, sizeof(g_err), "%s", e.what());
+        return -1;
+    }
+}
+
 int gs_host_sort64(int device, const uint64_t* keys, const uint32_t* vals, uint64_t n, uint64_t* keys_out, uint32_t* vals_out) {
     try {
         MTL::Device* dev = MTL::Device::CreateSystemDefaultDevice(device);
