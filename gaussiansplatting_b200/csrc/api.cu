@@ -1291,6 +1291,7 @@ int gs_adam_reset_state_for_new(gs_adam* a, uint32_t start) {          // :150-1
     return adam_zero_range(a, start, a->num, 31);
 }
 uint32_t gs_adam_timestep(const gs_adam* a) { return a->timestep; }
+int gs_adam_set_timestep(gs_adam* a, uint32_t t) { a->timestep = t; return GS_OK; }
 
 int gs_adam_step(gs_adam* a, gs_gaussians* g, gs_grads* gr, const float lrs[5]) {
     gs_ctx* c = a->c; GS_SETDEV(c);

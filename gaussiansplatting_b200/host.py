@@ -17,7 +17,9 @@ class TrainConfig(C.Structure):
                 ("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("scene_extent", C.c_float),
                 ("densify_from", C.c_uint32), ("densify_until", C.c_uint32), ("densify_interval", C.c_uint32),
                 ("opacity_reset_interval", C.c_uint32), ("seed", C.c_uint32), ("quantize_rgba8", C.c_int),
-                ("log_loss_every_step", C.c_int), ("export_dir", C.c_char_p)]
+                ("log_loss_every_step", C.c_int), ("export_dir", C.c_char_p), ("load_checkpoint", C.c_char_p),
+                ("save_checkpoint", C.c_char_p), ("export_ply", C.c_char_p), ("start_iteration", C.c_uint32),
+                ("total_iterations", C.c_uint32)]
 
 
 class TrainResult(C.Structure):
@@ -85,3 +87,50 @@ def render_view(gaussians, quat, trans, fx, fy, cx, cy, width, height, rgba8_tar
     if rc != 0:
         raise GsError("gs_host_render_view: " + lib().gs_host_last_error().decode())
     return out, pairs.value
+
+
+def ply_export(path, gaussians):
+    """PLYExporter::exportPLY (ply_exporter.hpp:17-162)"""
+    g = np.ascontiguousarray(gaussians, GAUSSIAN)
+    if lib().gs_host_ply_export(str(path).encode(), _p(g), C.c_uint64(len(g))) != 0:
+        raise GsError(f"cannot write {path}")
+
+
+def ply_load(path):
+    """load_ply (ply_loader.cpp:54-290) -> (Gaussians, info dict)"""
+    n, info = C.c_uint64(), (C.c_uint64 * 4)()
+    if lib().gs_host_ply_load(str(path).encode(), None, C.c_uint64(0), C.byref(n), info) != 0:
+        raise GsError("load_ply: " + lib().gs_host_last_error().decode())
+    out = np.zeros(n.value, GAUSSIAN)
+    if lib().gs_host_ply_load(str(path).encode(), _p(out), C.c_uint64(len(out)), C.byref(n), info) != 0:
+        raise GsError("load_ply: " + lib().gs_host_last_error().decode())
+    return out, dict(vertices=info[0], skipped=info[1], linear_scales=bool(info[2]), has_sh_rest=bool(info[3]))
+
+
+def checkpoint_resave(in_path, out_path, scene_extent=1.0, device=0):
+    if lib().gs_host_checkpoint_resave(C.c_int(device), str(in_path).encode(), str(out_path).encode(), C.c_float(scene_extent)) != 0:
+        raise GsError("checkpoint: " + lib().gs_host_last_error().decode())
+
+
+def ply_device_roundtrip(in_path, out_path, device=0):
+    if lib().gs_host_ply_device_roundtrip(C.c_int(device), str(in_path).encode(), str(out_path).encode()) != 0:
+        raise GsError("ply roundtrip: " + lib().gs_host_last_error().decode())
+
+
+def read_checkpoint(path):
+    """parse Engine::saveCheckpoint's file (engine.hpp) -> dict"""
+    raw = open(path, "rb").read()
+    assert raw[:4] == b"GSCK"
+    version, = np.frombuffer(raw, "<u4", 1, 4)
+    n = int(np.frombuffer(raw, "<u8", 1, 8)[0])
+    t = int(np.frombuffer(raw, "<u4", 1, 16)[0])
+    off = 24
+    g = np.frombuffer(raw, GAUSSIAN, n, off).copy(); off += n * 112
+    m, v = [], []
+    for w in (3, 3, 4, 1, 12):
+        m.append(np.frombuffer(raw, "<f4", n * w, off).copy()); off += n * w * 4
+        v.append(np.frombuffer(raw, "<f4", n * w, off).copy()); off += n * w * 4
+    accum = np.frombuffer(raw, "<f4", n, off).copy(); off += 4 * n
+    views = np.frombuffer(raw, "<u4", n, off).copy(); off += 4 * n
+    assert off == len(raw)
+    return dict(version=int(version), n=n, timestep=t, gaussians=g, m=m, v=v, accum=accum, views=views)

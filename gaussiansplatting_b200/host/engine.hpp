@@ -14,6 +14,7 @@
 #include <string>
 #include <vector>
 #include "gs_host.hpp"
+#include "ply_io.hpp"
 
 struct TrainingView {              // TrainingImage + ColmapImage/ColmapCamera of the reference, reduced to what trainStep reads
     float qw, qx, qy, qz;          // world -> camera rotation (COLMAP)
@@ -23,6 +24,8 @@ struct TrainingView {              // TrainingImage + ColmapImage/ColmapCamera o
 };
 
 struct TrainSchedule {             // the constants of MTLEngine::train (mtl_engine.mm:1053-1068, mtl_engine.hpp:167)
+    size_t startIteration = 0;     // resuming from a checkpoint: iterations already done (LR decay, densify and reset schedule continue)
+    size_t totalIterations = 0;    // 0 = numEpochs * views (the reference); set when a run is split over several train() calls
     size_t opacityResetInterval = 3000, densifyFromIter = 500, densifyUntilIter = 15000, densityControlInterval = 100;
     float opacityResetValue = -4.6f;
     float positionLRInit = 0.00016f, positionLRFinal = 0.0000016f, scaleLR = 0.005f, rotationLR = 0.001f,
@@ -214,8 +217,8 @@ public:
 
     TrainStats train(size_t numEpochs, const TrainSchedule& S = TrainSchedule()) {   // mtl_engine.mm:1047-1221
         TrainStats st;
-        const size_t totalExpectedIters = numEpochs * trainingImages.size();
-        size_t totalIterations = 0;
+        const size_t totalExpectedIters = S.totalIterations ? S.totalIterations : S.startIteration + numEpochs * trainingImages.size();
+        size_t totalIterations = S.startIteration;
         device->waitUntilCompleted();
         const auto t0 = std::chrono::high_resolution_clock::now();
         for (size_t epoch = 0; epoch < numEpochs; epoch++) {
@@ -249,7 +252,7 @@ public:
         }
         device->waitUntilCompleted();
         st.seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t0).count();
-        st.iterations = totalIterations;
+        st.iterations = totalIterations - S.startIteration;
         st.finalCount = gaussianCount;
         return st;
     }
@@ -258,6 +261,81 @@ public:
         std::vector<Gaussian> out(gaussianCount);
         if (gaussianCount) gaussianBuffer->download(out.data(), gaussianCount * sizeof(Gaussian));
         return out;
+    }
+
+    // ---- on-disk state ---------------------------------------------------------------------------------
+    // main.mm:483-489: PLYExporter::exportPLY(path, engine.getGaussians(), count) — the explicit download replaces contents()
+    bool exportPLY(const std::string& path) const {
+        const std::vector<Gaussian> g = getGaussians();
+        return PLYExporter::exportPLY(path, g.data(), g.size());
+    }
+    // main.mm:383-389 (the --ply path): load_ply + loadGaussians; returns the number of Gaussians loaded (0 = failure)
+    size_t loadPLY(const std::string& path, float extent) {
+        const std::vector<Gaussian> g = load_ply(path);
+        if (g.empty()) return 0;
+        releaseModel();
+        loadGaussians(g, extent);
+        return g.size();
+    }
+    // Raw checkpoint for resumable runs (no reference counterpart: the reference can only restart from a PLY, which loses the
+    // optimizer): parameters, the ten Adam moment buffers in the reference's layout (optimizer.mm:34-60), the timestep and the
+    // density controller's accumulators.  Layout: "GSCK", u32 version, u64 count, u32 timestep, u32 0, Gaussian[count],
+    // for group in (position, scale, rotation, opacity, sh): m then v as float[count*width], float accum[count], u32 views[count].
+    bool saveCheckpoint(const std::string& path) const {
+        std::ofstream f(path, std::ios::binary);
+        if (!f) return false;
+        const uint64_t n = gaussianCount;
+        const uint32_t version = 1, t = optimizer->getTimestep(), zero = 0;
+        f.write("GSCK", 4); f.write((const char*)&version, 4); f.write((const char*)&n, 8); f.write((const char*)&t, 4); f.write((const char*)&zero, 4);
+        const std::vector<Gaussian> g = getGaussians();
+        f.write((const char*)g.data(), (std::streamsize)(n * sizeof(Gaussian)));
+        static const int width[5] = {3, 3, 4, 1, 12};
+        std::vector<float> buf;
+        for (int group = 0; group < 5; group++)
+            for (int mv = 0; mv < 2; mv++) {
+                buf.assign(n * width[group], 0.0f);
+                if (n) MTL::gs_check(device->ctx(), gs_adam_download(optimizer->handle(), group, mv, buf.data(), (uint32_t)n), "checkpoint: moments");
+                f.write((const char*)buf.data(), (std::streamsize)(buf.size() * 4));
+            }
+        std::vector<float> accum(n, 0.0f); std::vector<uint32_t> views(n, 0);
+        if (n) MTL::gs_check(device->ctx(), gs_dens_download(densityController->handle(), accum.data(), views.data(), nullptr, (uint32_t)n), "checkpoint: accumulators");
+        f.write((const char*)accum.data(), (std::streamsize)(n * 4)); f.write((const char*)views.data(), (std::streamsize)(n * 4));
+        return (bool)f;
+    }
+    bool loadCheckpoint(const std::string& path, float extent) {
+        std::ifstream f(path, std::ios::binary);
+        char magic[4]; uint32_t version = 0, t = 0, zero = 0; uint64_t n = 0;
+        if (!f || !f.read(magic, 4) || std::memcmp(magic, "GSCK", 4) != 0) return false;
+        f.read((char*)&version, 4); f.read((char*)&n, 8); f.read((char*)&t, 4); f.read((char*)&zero, 4);
+        if (!f || version != 1 || n > (1ull << 30)) return false;
+        std::vector<Gaussian> g(n);
+        f.read((char*)g.data(), (std::streamsize)(n * sizeof(Gaussian)));
+        if (!f) return false;
+        releaseModel();
+        loadGaussians(g, extent);
+        static const int width[5] = {3, 3, 4, 1, 12};
+        std::vector<float> buf;
+        for (int group = 0; group < 5; group++)
+            for (int mv = 0; mv < 2; mv++) {
+                buf.resize(n * width[group]);
+                f.read((char*)buf.data(), (std::streamsize)(buf.size() * 4));
+                if (!f) return false;
+                if (n) MTL::gs_check(device->ctx(), gs_adam_upload(optimizer->handle(), group, mv, buf.data(), (uint32_t)n), "checkpoint: moments");
+            }
+        MTL::gs_check(device->ctx(), gs_adam_set_timestep(optimizer->handle(), t), "checkpoint: timestep");
+        std::vector<float> accum(n); std::vector<uint32_t> views(n);
+        f.read((char*)accum.data(), (std::streamsize)(n * 4)); f.read((char*)views.data(), (std::streamsize)(n * 4));
+        if (!f) return false;
+        if (n) MTL::gs_check(device->ctx(), gs_dens_upload(densityController->handle(), accum.data(), views.data(), (uint32_t)n), "checkpoint: accumulators");
+        return true;
+    }
+    void releaseModel() {                  // drop the model and its operator objects (loadGaussians constructs fresh ones)
+        delete tiledRasterizer; delete optimizer; delete densityController;
+        tiledRasterizer = nullptr; optimizer = nullptr; densityController = nullptr;
+        if (gaussianBuffer) gaussianBuffer->release();
+        if (gaussianGradients) gaussianGradients->release();
+        gaussianBuffer = nullptr; gaussianGradients = nullptr;
+        gaussianCount = 0; positionsStale = true;
     }
 
     MTL::Device* device = nullptr;

@@ -159,6 +159,7 @@ public:
         MTL::gs_check(device_->ctx(), gs_adam_reset_state_for_new(a_, (uint32_t)startIdx), "resetStateForNewGaussians");
     }
     uint32_t getTimestep() const { return gs_adam_timestep(a_); }
+    gs_adam* handle() const { return a_; }
 private:
     MTL::Device* device_;
     gs_adam* a_ = nullptr;
@@ -195,6 +196,7 @@ public:
         MTL::gs_check(device_->ctx(), gs_dens_reset_accumulator(d_, (uint32_t)gaussianCount), "resetAccumulator");
     }
     static void setSceneExtent(float extent) { sceneExtent() = extent; }          // density_control.mm:79-84 (file-scope static)
+    gs_dens* handle() const { return d_; }
     void setSeed(uint32_t s) { gs_dens_set_seed(d_, s); }                          // counter-based split RNG (SURVEY note L)
 private:
     static float& sceneExtent() { static float e = 1.0f; return e; }

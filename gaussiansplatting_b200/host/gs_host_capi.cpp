@@ -13,6 +13,10 @@ typedef struct {
     int quantize_rgba8;       // 1 = backward reads the 8-bit-quantised render (what the reference's RGBA8 target does)
     int log_loss_every_step;  // 1 = computeLoss in every trainStep with a device sync, as the reference does (mtl_engine.mm:991)
     const char* export_dir;   // non-NULL: exportTrainingViews(dir) after training (view_NNN.ppm)
+    const char* load_checkpoint;   // non-NULL: Engine::loadCheckpoint replaces the model + optimizer state before training
+    const char* save_checkpoint;   // non-NULL: Engine::saveCheckpoint after training
+    const char* export_ply;        // non-NULL: Engine::exportPLY after training (PLYExporter, main.mm:483-489)
+    uint32_t start_iteration, total_iterations;   // TrainSchedule::startIteration / totalIterations (resumed runs)
 } gs_host_train_config;
 
 typedef struct {
@@ -58,9 +62,12 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
             e->tiledRasterizer = nullptr; e->optimizer = nullptr; e->densityController = nullptr;
             e->loadGaussians(init, cfg->scene_extent);
         }
+        if (cfg->load_checkpoint && !eng.loadCheckpoint(cfg->load_checkpoint, cfg->scene_extent))
+            throw std::runtime_error(std::string("cannot load checkpoint ") + cfg->load_checkpoint);
         eng.tiledRasterizer->setQuantizeRenderedRGBA8(cfg->quantize_rgba8 != 0);
         eng.densityController->setSeed(cfg->seed);
         TrainSchedule S;
+        S.startIteration = cfg->start_iteration; S.totalIterations = cfg->total_iterations;
         if (cfg->densify_from) S.densifyFromIter = cfg->densify_from;
         if (cfg->densify_until) S.densifyUntilIter = cfg->densify_until;
         if (cfg->densify_interval) S.densityControlInterval = cfg->densify_interval;
@@ -83,6 +90,8 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
             res->last_pairs = eng.tiledRasterizer->pairCount();
             res->first_loss = first_loss; res->last_loss = eng.lastLoss; res->views_exported = 0;
         }
+        if (cfg->save_checkpoint && !eng.saveCheckpoint(cfg->save_checkpoint)) throw std::runtime_error("cannot write checkpoint");
+        if (cfg->export_ply && !eng.exportPLY(cfg->export_ply)) throw std::runtime_error("cannot write PLY");
         if (cfg->export_dir) {
             const size_t w = eng.exportTrainingViews(cfg->export_dir);
             if (res) res->views_exported = (uint32_t)w;
@@ -117,6 +126,45 @@ int gs_host_render_view(int device, const gs_gaussian* gaussians, uint32_t n, co
         MTL::gs_check(eng.device->ctx(), gs_image_download_rgba32f(target->image(), rgba_out), "download");
         if (pairs) *pairs = eng.renderPipeline->pairCount();
         target->release();
+        return 0;
+    } catch (const std::exception& e) {
+        std::snprintf(g_err, sizeof(g_err), "%s", e.what());
+        return -1;
+    }
+}
+
+// PLYExporter::exportPLY / load_ply (ply_exporter.hpp:17-162, ply_loader.cpp:54-290): host-only, no device needed
+int gs_host_ply_export(const char* path, const gs_gaussian* gaussians, uint64_t n) {
+    return PLYExporter::exportPLY(path, reinterpret_cast<const Gaussian*>(gaussians), n) ? 0 : -1;
+}
+// out may be NULL to query the count; info4 = {vertices in the file, skipped, linear scales detected, has f_rest}
+int gs_host_ply_load(const char* path, gs_gaussian* out, uint64_t cap, uint64_t* n_loaded, uint64_t* info4) {
+    PlyLoadInfo I;
+    const std::vector<Gaussian> g = load_ply(path, &I);
+    if (n_loaded) *n_loaded = g.size();
+    if (info4) { info4[0] = I.vertexCount; info4[1] = I.skipped; info4[2] = I.linearScales; info4[3] = I.hasShRest; }
+    if (!I.error.empty()) { std::snprintf(g_err, sizeof(g_err), "%s", I.error.c_str()); return -1; }
+    if (out) std::memcpy(out, g.data(), std::min<uint64_t>(g.size(), cap) * sizeof(Gaussian));
+    return 0;
+}
+// loads a checkpoint into a fresh Engine (device upload of parameters, moments, accumulators) and writes it back from the device
+int gs_host_checkpoint_resave(int device, const char* in_path, const char* out_path, float scene_extent) {
+    try {
+        Engine eng(device);
+        if (!eng.loadCheckpoint(in_path, scene_extent)) throw std::runtime_error(std::string("cannot load checkpoint ") + in_path);
+        if (!eng.saveCheckpoint(out_path)) throw std::runtime_error(std::string("cannot write checkpoint ") + out_path);
+        return 0;
+    } catch (const std::exception& e) {
+        std::snprintf(g_err, sizeof(g_err), "%s", e.what());
+        return -1;
+    }
+}
+// load_ply -> Engine::loadGaussians -> Engine::exportPLY: a PLY through the device model and back
+int gs_host_ply_device_roundtrip(int device, const char* in_path, const char* out_path) {
+    try {
+        Engine eng(device);
+        if (eng.loadPLY(in_path, 1.0f) == 0) throw std::runtime_error(std::string("cannot load ") + in_path);
+        if (!eng.exportPLY(out_path)) throw std::runtime_error(std::string("cannot write ") + out_path);
         return 0;
     } catch (const std::exception& e) {
         std::snprintf(g_err, sizeof(g_err), "%s", e.what());

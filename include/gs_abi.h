@@ -239,6 +239,7 @@ int gs_adam_reset_opacity_momentum(gs_adam*);
 int gs_adam_reset_scale_momentum(gs_adam*);
 int gs_adam_reset_state_for_new(gs_adam*, uint32_t start_idx);
 uint32_t gs_adam_timestep(const gs_adam*);
+int gs_adam_set_timestep(gs_adam*, uint32_t t);          /* restoring a checkpoint (the reference keeps `timestep` as a plain member, optimizer.hpp:64) */
 /* moments in the reference's layout: group 0 position [n*3], 1 scale [n*3], 2 rotation [n*4], 3 opacity [n], 4 sh [n*12];
  * which_moment 0 = m, 1 = v.  Synchronise. */
 int gs_adam_download(gs_adam*, int group, int which_moment, float* host, uint32_t n);

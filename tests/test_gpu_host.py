@@ -121,3 +121,66 @@ def test_cxx_engine_render_matches_the_viewer_oracle(gs, orc):
     img8, _ = host.render_view(g, q, t, f, f, W / 2.0, H / 2.0, W, H, rgba8_target=True)
     want8 = orc.viewer_render(g, order, vu, quantize=True, threads=0)[0]
     assert np.abs(img8 - want8).max() <= 1e-4
+
+
+def _train_setup(n=5000, W=192, H=128, V=4, seed=91):
+    g = synth.make_scene(n, seed, 0.05)
+    gt = synth.make_scene(n, seed ^ 0xA5A5, 0.05)
+    poses = [synth.orbit_pose(v, V, 3.0) for v in range(V)]
+    return g, gt, np.array([p[0] for p in poses], np.float32), np.array([p[1] for p in poses], np.float32)
+
+
+def test_checkpoint_and_ply_of_a_trained_model(gs, tmp_path):
+    """SURVEY 8f-4: the trained state on disk.  Engine::saveCheckpoint holds exactly the device state (parameters, the ten
+    Adam moment buffers, timestep, density accumulators); loading it into a fresh Engine and saving again is the identity;
+    Engine::exportPLY (PLYExporter, main.mm:483-489) + load_ply bring back the trained Gaussians."""
+    from gaussiansplatting_b200 import host
+    n, W, H, V = 5000, 192, 128, 4
+    g, gt, quats, trans = _train_setup(n, W, H, V)
+    f = 0.9 * W
+    ck, ck2, ply, ply2 = [str(tmp_path / s).encode() for s in ("a.gsck", "b.gsck", "a.ply", "b.ply")]
+    cfg = host.TrainConfig(width=W, height=H, num_views=V, epochs=5, fx=f, fy=f, cx=W / 2, cy=H / 2, scene_extent=synth.scene_extent(3.0),
+                           densify_from=6, densify_until=10 ** 6, densify_interval=7, opacity_reset_interval=10 ** 6, seed=3,
+                           quantize_rgba8=1, save_checkpoint=ck, export_ply=ply)
+    res, out = host.train(g, gt, quats, trans, cfg, want_output=True)
+    c = host.read_checkpoint(ck.decode())
+    assert c["n"] == res["final_count"] == len(out) and c["timestep"] == res["adam_timestep"] == 20
+    assert np.array_equal(c["gaussians"].view(np.uint8), out.view(np.uint8))
+    assert all(np.abs(m).max() > 0 for m in c["m"][:4]) and all(v.min() >= 0 and v.max() > 0 for v in c["v"][:4])
+    assert c["views"].max() >= 1 and c["accum"].max() > 0
+    host.checkpoint_resave(ck.decode(), ck2.decode(), synth.scene_extent(3.0))
+    assert open(ck2, "rb").read() == open(ck, "rb").read(), "checkpoint -> device -> checkpoint must be the identity"
+    # PLY: what the exporter wrote is the trained model; the loader normalises quaternions (Adam keeps them unit already)
+    back, info = host.ply_load(ply.decode())
+    assert info["vertices"] == len(out) and info["skipped"] == 0 and not info["linear_scales"]
+    for fld in ("position", "scale", "opacity", "sh"):
+        assert np.array_equal(back[fld], out[fld]), fld
+    assert np.abs(back["rotation"] - out["rotation"]).max() <= 1e-6
+    host.ply_device_roundtrip(ply.decode(), ply2.decode())      # load_ply -> device model -> exportPLY
+    again, _ = host.ply_load(ply2.decode())
+    assert np.array_equal(again["position"], back["position"]) and np.array_equal(again["sh"], back["sh"])
+    assert np.abs(again["rotation"] - back["rotation"]).max() <= 1e-6
+
+
+def test_training_resumes_from_a_checkpoint(gs, tmp_path):
+    """a run split in two by a checkpoint follows the uninterrupted run: same schedule position (timestep, LR decay, densify
+    events), parameters equal up to the noise of the backward's float atomics"""
+    from gaussiansplatting_b200 import host
+    n, W, H, V = 5000, 192, 128, 4
+    g, gt, quats, trans = _train_setup(n, W, H, V, seed=93)
+    f = 0.9 * W
+    ck = str(tmp_path / "half.gsck").encode()
+    base = dict(width=W, height=H, num_views=V, fx=f, fy=f, cx=W / 2, cy=H / 2, scene_extent=synth.scene_extent(3.0), densify_from=6,
+                densify_until=10 ** 6, densify_interval=7, opacity_reset_interval=16, seed=3, quantize_rgba8=1)
+    full, out_full = host.train(g, gt, quats, trans, host.TrainConfig(epochs=8, **base), want_output=True)
+    first, _ = host.train(g, gt, quats, trans, host.TrainConfig(epochs=4, total_iterations=32, save_checkpoint=ck, **base))
+    second, out_res = host.train(g, gt, quats, trans, host.TrainConfig(epochs=4, start_iteration=16, total_iterations=32,
+                                                                        load_checkpoint=ck, **base), want_output=True)
+    assert first["adam_timestep"] == 16 and second["adam_timestep"] == full["adam_timestep"] == 32
+    assert first["densify_events"] + second["densify_events"] == full["densify_events"]
+    assert first["opacity_resets"] + second["opacity_resets"] == full["opacity_resets"] == 2
+    assert abs(int(second["final_count"]) - int(full["final_count"])) <= 0.01 * full["final_count"]
+    if second["final_count"] == full["final_count"]:
+        for fld in ("position", "scale", "opacity"):
+            d = np.abs(out_res[fld].astype(np.float64) - out_full[fld].astype(np.float64))
+            assert np.quantile(d, 0.99) <= 2e-3, fld
