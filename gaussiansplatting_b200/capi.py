@@ -409,6 +409,10 @@ class Adam:
     def reset_scale_momentum(self):
         self.ctx.check(lib().gs_adam_reset_scale_momentum(self.h))
 
+    def permute_after_densify(self, density, gaussians, old_n):
+        """opt-in correction of SURVEY note D: moments follow the Gaussians through Density.apply"""
+        self.ctx.check(lib().gs_adam_permute_after_densify(self.h, density.h, gaussians.h, C.c_uint32(old_n)))
+
     def reset_state_for_new(self, start):
         self.ctx.check(lib().gs_adam_reset_state_for_new(self.h, C.c_uint32(start)))
 

@@ -1363,6 +1363,7 @@ struct gs_dens {
     uint32_t *count = nullptr, *markers = nullptr, *rank = nullptr, *out_off = nullptr, *small = nullptr;   // small: counts3 + stats4
     void* scan_scratch = nullptr;
     float* spare = nullptr; uint32_t spare_cap = 0;   // ping-pong target for the rebuilt model state
+    uint32_t applied_n = 0;             // count the last apply marked (markers / out_off describe [0, applied_n)); 0 = no plan
 };
 static int dens_reserve(gs_dens* d, uint32_t n) {
     if (n <= d->cap) return GS_OK;
@@ -1432,6 +1433,7 @@ int gs_dens_apply(gs_dens* d, gs_gaussians* g, uint32_t iteration, float focal, 
     if (stats) *stats = s;
     const uint32_t n = g->n;
     GS_TRY(dens_reserve(d, n));
+    d->applied_n = 0;
     if (iteration >= 15000u) return gs_dens_reset_accumulator(d, n);   // :216-220
     cudaStream_t st = c->stream;
     GsDensifyArgs a;
@@ -1458,8 +1460,27 @@ int gs_dens_apply(gs_dens* d, gs_gaussians* g, uint32_t iteration, float focal, 
     std::swap(g->base, d->spare); std::swap(g->cap, d->spare_cap);      // :486-490
     g->sh_rest_dirty = true;
     g->n = newCount;
+    d->applied_n = n;
     if (stats) *stats = s;
     return gs_dens_reset_accumulator(d, newCount);                      // :493
+}
+int gs_adam_permute_after_densify(gs_adam* a, gs_dens* d, gs_gaussians* g, uint32_t old_n) {
+    gs_ctx* c = a->c; GS_SETDEV(c);
+    GS_ARG(c, d && g, "null argument");
+    const uint32_t new_n = g->n;
+    if (d->applied_n == 0) return gs_adam_resize_if_needed(a, new_n);      // the apply changed nothing (past DENSIFY_UNTIL_ITER)
+    GS_ARG(c, d->applied_n == old_n, "old_n does not match the last gs_dens_apply");
+    GS_ARG(c, old_n <= a->num, "optimizer state smaller than the model");
+    const uint32_t ncap = std::max<uint32_t>(a->cap, ((uint32_t)(new_n * 1.25) + 63u) & ~63u);
+    float* nb = nullptr;
+    GS_TRY(dalloc(c, &nb, (size_t)ncap * 46));
+    GS_CUDA(c, cudaMemsetAsync(nb, 0, (size_t)ncap * 46 * sizeof(float), c->stream));
+    gs_launch_permute_moments(a->base, a->cap, nb, ncap, d->markers, d->out_off, old_n, new_n, c->stream);
+    GS_LAUNCH_CHECK(c);
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(a->base);
+    a->base = nb; a->cap = ncap; a->num = std::max(a->num, new_n);
+    return GS_OK;
 }
 int gs_dens_download(gs_dens* d, float* accum, uint32_t* count, uint32_t* markers, uint32_t n) {
     gs_ctx* c = d->c; GS_SETDEV(c);

@@ -150,7 +150,32 @@ __global__ void __launch_bounds__(256) densify_scatter_kernel(GsParams A, GsPara
     }
 }
 
+// corrected optimizer-state mode (SURVEY note D / 8f-4): carry the Adam moments of every surviving Gaussian to its new index.
+// A kept Gaussian and the first copy of a clone keep their moments; the second copy of a clone and both halves of a split start
+// from zero (the destination buffer is zero-filled by the caller).  46 floats per Gaussian: 38 planes + two float4 rows.
+__global__ void __launch_bounds__(256) permute_moments_kernel(const float* __restrict__ src, uint32_t src_cap, float* __restrict__ dst,
+                                                              uint32_t dst_cap, const uint32_t* __restrict__ markers,
+                                                              const uint32_t* __restrict__ out_off, uint32_t n, uint32_t new_n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t m = markers[i];
+    if (m == 1u || m == 3u) return;
+    const uint32_t o = out_off[i];
+    if (o >= new_n) return;
+#pragma unroll 2
+    for (int k = 0; k < 38; k++) dst[(size_t)k * dst_cap + o] = src[(size_t)k * src_cap + i];
+    const float4* sr = reinterpret_cast<const float4*>(src + 38 * (size_t)src_cap);
+    float4* dr = reinterpret_cast<float4*>(dst + 38 * (size_t)dst_cap);
+    dr[o] = sr[i];
+    dr[(size_t)dst_cap + o] = sr[(size_t)src_cap + i];
+}
+
 }  // namespace
+
+void gs_launch_permute_moments(const float* src, uint32_t src_cap, float* dst, uint32_t dst_cap, const uint32_t* markers,
+                               const uint32_t* out_off, uint32_t n, uint32_t new_n, cudaStream_t st) {
+    if (n) permute_moments_kernel<<<(n + 255) / 256, 256, 0, st>>>(src, src_cap, dst, dst_cap, markers, out_off, n, new_n);
+}
 
 void gs_launch_densify_mark(GsParams P, const float* accum, const uint32_t* count, GsDensifyArgs a, uint32_t* markers,
                             uint32_t* counts3, cudaStream_t st) {

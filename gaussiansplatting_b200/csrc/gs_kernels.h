@@ -150,6 +150,10 @@ void gs_launch_densify_plan(uint32_t* markers, uint32_t n, uint32_t max_gaussian
 void gs_launch_densify_scatter(GsParams Pin, GsParams Pout, const uint32_t* markers, const uint32_t* out_off,
                                GsDensifyArgs a, cudaStream_t st);
 
+// corrected optimizer-state mode: moments of survivors move with them (src/dst: 46 floats per Gaussian, dst zero-filled)
+void gs_launch_permute_moments(const float* src, uint32_t src_cap, float* dst, uint32_t dst_cap, const uint32_t* markers,
+                               const uint32_t* out_off, uint32_t n, uint32_t new_n, cudaStream_t st);
+
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
 void gs_tune_fwd_ppt(int v);
 void gs_tune_bwd_ppt(int v);

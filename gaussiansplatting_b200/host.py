@@ -19,7 +19,7 @@ class TrainConfig(C.Structure):
                 ("opacity_reset_interval", C.c_uint32), ("seed", C.c_uint32), ("quantize_rgba8", C.c_int),
                 ("log_loss_every_step", C.c_int), ("export_dir", C.c_char_p), ("load_checkpoint", C.c_char_p),
                 ("save_checkpoint", C.c_char_p), ("export_ply", C.c_char_p), ("start_iteration", C.c_uint32),
-                ("total_iterations", C.c_uint32)]
+                ("total_iterations", C.c_uint32), ("permute_moments", C.c_int)]
 
 
 class TrainResult(C.Structure):

@@ -236,8 +236,12 @@ public:
                     const DensityStats ds = densityController->apply(commandQueue, gaussianBuffer, positionBuffer, nullptr, gaussianCount,
                                                                      totalIterations, 0.0002f, 0.005f, 0.1f * sceneExtent, v.fx,
                                                                      (float)v.texture->width(), 2.0f * sceneExtent);   // :1142-1149
-                    optimizer->resizeIfNeeded(gaussianCount);                                                  // :1160
-                    if (gaussianCount > oldCount) optimizer->resetStateForNewGaussians(oldCount);              // :1164-1166 (note D)
+                    if (permuteMoments) {
+                        optimizer->permuteStateForDensify(*densityController, gaussianBuffer, oldCount);       // corrected mode (note D), opt-in
+                    } else {
+                        optimizer->resizeIfNeeded(gaussianCount);                                              // :1160
+                        if (gaussianCount > oldCount) optimizer->resetStateForNewGaussians(oldCount);          // :1164-1166 (note D)
+                    }
                     st.densifyEvents++; st.pruned += ds.numPruned; st.cloned += ds.numCloned; st.split += ds.numSplit;
                     st.densifySeconds += std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - d0).count();
                 }
@@ -357,5 +361,6 @@ public:
     float sceneExtent = 1.0f;
     float lambdaDSSIM = 0.2f;          // mtl_engine.hpp:147
     bool logLossEveryStep = false;
+    bool permuteMoments = false;       // false = the reference's behaviour (moments stay at their old index through densify, SURVEY note D)
     float lastLoss = 0.0f;
 };

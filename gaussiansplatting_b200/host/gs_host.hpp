@@ -160,6 +160,8 @@ public:
     }
     uint32_t getTimestep() const { return gs_adam_timestep(a_); }
     gs_adam* handle() const { return a_; }
+    // opt-in correction of SURVEY note D: moments follow the Gaussians through DensityController::apply (declared after it)
+    void permuteStateForDensify(class DensityController& dc, MTL::Buffer* gaussians, size_t oldCount);
 private:
     MTL::Device* device_;
     gs_adam* a_ = nullptr;
@@ -203,3 +205,6 @@ private:
     MTL::Device* device_;
     gs_dens* d_ = nullptr;
 };
+inline void AdamOptimizer::permuteStateForDensify(DensityController& dc, MTL::Buffer* gaussians, size_t oldCount) {
+    MTL::gs_check(device_->ctx(), gs_adam_permute_after_densify(a_, dc.handle(), gaussians->gaussians(), (uint32_t)oldCount), "permuteStateForDensify");
+}

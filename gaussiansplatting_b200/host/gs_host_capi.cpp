@@ -17,6 +17,7 @@ typedef struct {
     const char* save_checkpoint;   // non-NULL: Engine::saveCheckpoint after training
     const char* export_ply;        // non-NULL: Engine::exportPLY after training (PLYExporter, main.mm:483-489)
     uint32_t start_iteration, total_iterations;   // TrainSchedule::startIteration / totalIterations (resumed runs)
+    int permute_moments;           // 1 = Engine::permuteMoments (corrected optimizer state through densify, SURVEY note D)
 } gs_host_train_config;
 
 typedef struct {
@@ -73,6 +74,7 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
         if (cfg->densify_interval) S.densityControlInterval = cfg->densify_interval;
         if (cfg->opacity_reset_interval) S.opacityResetInterval = cfg->opacity_reset_interval;
         eng.logLossEveryStep = cfg->log_loss_every_step != 0;
+        eng.permuteMoments = cfg->permute_moments != 0;
         float first_loss = 0.0f;
         if (eng.logLossEveryStep && cfg->epochs) {     // the loss of iteration 1, before any update
             TiledUniforms u0 = eng.uniformsFor(eng.trainingImages[0]);

@@ -255,6 +255,11 @@ int gs_dens_reset_accumulator(gs_dens*, uint32_t n);
 /* apply(...): may replace the device storage inside *g and changes its count; synchronises (new count read-back) */
 int gs_dens_apply(gs_dens*, gs_gaussians* g, uint32_t iteration, float focal_length, float image_width,
                   float avg_depth, gs_density_stats* stats);
+/* Opt-in correction of SURVEY note D (the reference re-orders the Gaussians at densify but leaves the Adam moments where they
+ * were, mtl_engine.mm:1159-1167): call right after gs_dens_apply INSTEAD of resize_if_needed + reset_state_for_new.  Moments of
+ * kept Gaussians and of the first copy of a clone follow them to their new index; the second copy of a clone, both halves of a
+ * split and nothing else start from zero.  old_n = the count before the apply; the new count is read from the model. */
+int gs_adam_permute_after_densify(gs_adam*, gs_dens*, gs_gaussians*, uint32_t old_n);
 int gs_dens_download(gs_dens*, float* accum, uint32_t* count, uint32_t* markers, uint32_t n);   /* any may be NULL */
 int gs_dens_upload(gs_dens*, const float* accum, const uint32_t* count, uint32_t n);
 

@@ -184,3 +184,20 @@ def test_training_resumes_from_a_checkpoint(gs, tmp_path):
         for fld in ("position", "scale", "opacity"):
             d = np.abs(out_res[fld].astype(np.float64) - out_full[fld].astype(np.float64))
             assert np.quantile(d, 0.99) <= 2e-3, fld
+
+
+def test_cxx_engine_corrected_optimizer_state_mode(gs):
+    """Engine::permuteMoments (opt-in, SURVEY note D): the schedule is unchanged and training still reduces the logging loss"""
+    from gaussiansplatting_b200 import host
+    n, W, H, V = 5000, 192, 128, 4
+    g, gt, quats, trans = _train_setup(n, W, H, V, seed=95)
+    g["opacity"][::9] = -6.0                     # nearly transparent: pruned at the first densify, so the model is re-ordered
+    f = 0.9 * W
+    base = dict(width=W, height=H, num_views=V, epochs=10, fx=f, fy=f, cx=W / 2, cy=H / 2, scene_extent=synth.scene_extent(3.0),
+                densify_from=6, densify_until=10 ** 6, densify_interval=7, opacity_reset_interval=10 ** 6, seed=3, quantize_rgba8=1,
+                log_loss_every_step=1)
+    ref, _ = host.train(g, gt, quats, trans, host.TrainConfig(**base))
+    fix, _ = host.train(g, gt, quats, trans, host.TrainConfig(permute_moments=1, **base))
+    assert fix["densify_events"] == ref["densify_events"] == 5 and fix["adam_timestep"] == 40
+    assert fix["pruned"] + fix["cloned"] + fix["split"] > 0 and fix["final_count"] != n      # the model was re-ordered
+    assert 0.0 < fix["last_loss"] < fix["first_loss"]

@@ -231,3 +231,47 @@ def test_densify_apply_parity(gs, ctx, orc, iteration, max_g):
         Dn.close(); G.close()
     if max_g < 3000:
         assert len(ref) <= max_g and rstats[2] < 190 + (max_g > 2000) * 1000
+
+
+def test_adam_moments_follow_the_gaussians_in_the_corrected_mode(gs, ctx, orc):
+    """gs_adam_permute_after_densify (opt-in correction of SURVEY note D): after DensityController::apply re-orders the model,
+    a kept Gaussian and the first copy of a clone keep their moments at the new index; everything new starts from zero.
+    Expected layout stated here in numpy from the post-cap markers (prune 1 -> 0 outputs, keep 0 -> 1, clone 2 / split 3 -> 2)."""
+    n = 3000
+    g = synth.make_scene(n, 72, 0.02)
+    g["scale"][:500] = np.log(0.2)
+    g["opacity"][500:700] = -7.0
+    accum = (synth.uniform01(6, n, 1) * 1e-3).astype(np.float32)
+    count = (synth.uniform01(6, n, 2) * 3).astype(np.uint32)
+    rng = np.random.default_rng(4)
+    widths = (3, 3, 4, 1, 12)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    Dn = gs.Density(ctx, 1500000)
+    A = gs.Adam(ctx, n)
+    try:
+        mom = [[rng.standard_normal(n * w).astype(np.float32) for w in widths] for _ in range(2)]
+        for mv in range(2):
+            for grp, w in enumerate(widths):
+                A.upload(grp, mv, mom[mv][grp], n)
+        Dn.set_scene_extent(3.3); Dn.set_seed(99)
+        Dn.upload(accum, count)
+        stats = Dn.apply(G, 1000, 230.0, 256.0, 6.6)
+        assert min(stats) > 0, "the case must prune, clone and split"
+        _, _, m = Dn.download(n, markers=True)
+        outs = np.array([1, 0, 2, 2], np.int64)[m]
+        off = np.concatenate([[0], np.cumsum(outs)[:-1]])
+        new_n = int(outs.sum())
+        assert new_n == G.count
+        A.permute_after_densify(Dn, G, n)
+        carry = (m == 0) | (m == 2)
+        for mv in range(2):
+            for grp, w in enumerate(widths):
+                want = np.zeros((new_n, w), np.float32)
+                want[off[carry]] = mom[mv][grp].reshape(n, w)[carry]
+                got = A.download(grp, mv, new_n).reshape(new_n, w)
+                assert np.array_equal(got, want), (mv, grp)
+        # the model rows the moments now sit beside are the survivors themselves
+        after = G.download()
+        assert np.array_equal(after["opacity"][off[carry]], g["opacity"][carry])
+    finally:
+        A.close(); Dn.close(); G.close()
