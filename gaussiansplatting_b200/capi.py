@@ -302,6 +302,13 @@ class Sort64:
     def sorted_values(self):
         return lib().gs_sort64_sorted_values(self.h)
 
+    @property
+    def last_plan_hybrid(self):
+        """True if the last sort completed on the prefix-passes + local-pass plan, False on the 8-pass LSD plan"""
+        h = C.c_int()
+        self.ctx.check(lib().gs_sort64_last_plan(self.h, C.byref(h)))
+        return bool(h.value)
+
     def sort_host(self, keys, vals, begin_bit=0, end_bit=64):
         """convenience for tests: upload, sort, download"""
         keys = np.ascontiguousarray(keys, np.uint64)

@@ -60,6 +60,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "bwd_ppt")) { gs_tune_bwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
     if (!strcmp(name, "sort_tiny_tiles")) { gs_tune_sort_tiny(value); return GS_OK; }
+    if (!strcmp(name, "sort_hybrid")) { gs_tune_sort_hybrid(value); return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     return GS_ERR_ARG;
@@ -987,6 +988,14 @@ int gs_sort64_sort(gs_sort64* s, const uint64_t* d_keys, const uint32_t* d_vals,
     const GsSortPlan plan = gs_sort_plan(begin_bit, end_bit, ~0ull);
     s->result = gs_launch_sort64(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, g_sort_api_hint, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+int gs_sort64_last_plan(gs_sort64* s, int* hybrid) {
+    gs_ctx* c = s->c; GS_SETDEV(c);
+    uint32_t f[3] = {0, 0, 0};
+    GS_CUDA(c, cudaMemcpyAsync(f, gs_sort_flags(s->scratch), sizeof(f), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (hybrid) *hybrid = (f[0] != 0u && f[1] == 0u) ? 1 : 0;
     return GS_OK;
 }
 const uint64_t* gs_sort64_sorted_keys(gs_sort64* s) { return s->kbuf[s->result]; }

@@ -14,6 +14,7 @@
 //     global digit offsets by decoupled look-back over the preceding tiles' status words, reorders the tile
 //     through shared memory so global stores are digit-contiguous, and scatters keys then values;
 //   * tile ids are handed out by an atomic ticket so a tile only ever waits on tiles that already started.
+#include <climits>
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
@@ -25,17 +26,22 @@ namespace {
 #ifndef GS_RS_CTAS
 #define GS_RS_CTAS 4
 #endif
+#ifndef GS_RS_BIG_IPT
+#define GS_RS_BIG_IPT 16
+#endif
 constexpr int RS_THREADS = GS_RS_THREADS;   // >= 256: threads 0..255 also own one digit each
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr uint32_t ST_AGG = 0x40000000u, ST_INC = 0x80000000u, ST_VAL = 0x3FFFFFFFu;
 
-struct PassList { int n; int shift[8]; uint32_t mask[8]; };
+constexpr int RS_MAX_PASSES = 11;   // 8 LSD passes + up to 3 prefix passes of the hybrid plan
+struct PassList { int n; int shift[RS_MAX_PASSES]; uint32_t mask[RS_MAX_PASSES]; };
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict__ keys, uint64_t n_max,
-                                                         const uint32_t* __restrict__ d_n, PassList pl,
-                                                         uint32_t* __restrict__ ghist) {
+                                                         const uint32_t* __restrict__ d_n, const __grid_constant__ PassList pl, int p0, int np,
+                                                         uint32_t* __restrict__ ghist, const uint32_t* __restrict__ gate) {
     __shared__ uint32_t sh[8][256];
+    if (gate && *gate == 0u) return;                              // hybrid plan succeeded: the LSD histograms are not needed
     const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;   // element count may live on the device (no host sync)
     for (int i = threadIdx.x; i < 8 * 256; i += blockDim.x) (&sh[0][0])[i] = 0;
     __syncthreads();
@@ -44,12 +50,12 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict_
         const KeyT k = keys[i];
 #pragma unroll
         for (int p = 0; p < 8; p++)
-            if (p < pl.n) atomicAdd(&sh[p][(uint32_t)(k >> pl.shift[p]) & pl.mask[p]], 1u);
+            if (p < np) atomicAdd(&sh[p][(uint32_t)(k >> pl.shift[p]) & pl.mask[p]], 1u);   // pl starts at pass p0 (static indices: no local copy)
     }
     __syncthreads();
-    for (int p = 0; p < pl.n; p++)
+    for (int p = 0; p < np; p++)
         for (int d = threadIdx.x; d < 256; d += blockDim.x)
-            if (sh[p][d]) atomicAdd(&ghist[p * 256 + d], sh[p][d]);
+            if (sh[p][d]) atomicAdd(&ghist[(p0 + p) * 256 + d], sh[p][d]);
 }
 
 // exclusive scan of one value per thread over the CTA (only the first 256 threads carry non-zero values)
@@ -118,8 +124,9 @@ __global__ void __launch_bounds__(RS_THREADS, GS_RS_CTAS) onesweep_kernel(const 
                                                                  const uint32_t* __restrict__ d_n,
                                                                  int shift, uint32_t mask, int nbits, const uint32_t* __restrict__ ghist,
                                                                  uint32_t* counter, uint32_t* status, unsigned long long* agg2,
-                                                                 int aligned16) {
+                                                                 int aligned16, const uint32_t* __restrict__ gate) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    if (gate && *gate == 0u) return;                              // this pass belongs to the plan that is not being run (hybrid sort)
     constexpr int RS_TILE = RS_THREADS * RS_IPT;
     OnesweepSmem<KeyT, RS_IPT>& S = *reinterpret_cast<OnesweepSmem<KeyT, RS_IPT>*>(smem_raw);
     const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;
@@ -297,14 +304,171 @@ __global__ void depth_keys32_kernel(const float4* __restrict__ pos, float cx, fl
     keys[i] = key;
 }
 
-constexpr uint32_t RS_BIG_TILE = RS_THREADS * 16, RS_SMALL_TILE = RS_THREADS * 8, RS_TINY_TILE = RS_THREADS * 4;
-constexpr size_t RS_HIST_BYTES = 8 * 256 * 4;
+
+// ------------------------------------------------------------------------------------------------------------------
+// Hybrid plan for full 64-bit sorts (GPURadixSort64 on caller keys): the onesweep passes above are bound by per-SM work
+// (ranking, shared-memory reorder, look-back), not by HBM, so the way to go faster is FEWER passes over the data.
+//   1. two (n <= 2^25) or three stable onesweep passes over the TOP T bits only -> the data is grouped into 2^T
+//      segments (avg ~256 elements), each holding its elements in input order;
+//   2. ONE local pass: a CTA takes the segments that start in its 2048-element chunk, bins every element by its next B
+//      key bits (avg 1-2 elements per bin, shared-memory counters), and finishes each bin with a tiny insertion sort on
+//      (full key, original position) — stable, in place.
+// That is 3-4 trips through HBM instead of 9.  It only works when the keys spread over the top bits; everything else is
+// caught on the device without a host round trip: a pre-check on the top digit's histogram, and in the local pass a
+// segment that does not fit, a bin index out of range or a bin with more than LS_KMAX elements raise a flag, after
+// which the plain 8-pass LSD plan runs from the untouched input (its launches return at once when the flag is clear).
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int LS_THREADS = 256, LS_IPT = 16, LS_LOAD = LS_THREADS * LS_IPT, LS_CH = 2048, LS_NBINS = 4096, LS_KMAX = 24;
+enum { RS_FLAG_HYBRID = 12, RS_FLAG_FAIL = 13, RS_FLAG_LSD = 14 };   // words of the counter block
+
+__global__ void hybrid_precheck_kernel(const uint32_t* __restrict__ top_hist, int bins, uint64_t n, uint32_t* __restrict__ ctr) {
+    // keys must spread over the most significant prefix digit: no value of it may hold more than 4x its fair share
+    __shared__ uint32_t s_max;
+    if (threadIdx.x == 0) s_max = 0;
+    __syncthreads();
+    uint32_t m = 0;
+    for (int d = threadIdx.x; d < bins; d += blockDim.x) m = max(m, top_hist[d]);
+    atomicMax(&s_max, m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const bool ok = (uint64_t)s_max <= 4ull * (n / (uint64_t)bins) + 1024ull;
+        ctr[RS_FLAG_HYBRID] = ok ? 1u : 0u;
+        ctr[RS_FLAG_LSD] = ok ? 0u : 1u;
+    }
+}
+__global__ void hybrid_decide_kernel(uint32_t* __restrict__ ctr) {
+    if (threadIdx.x == 0) ctr[RS_FLAG_LSD] = (ctr[RS_FLAG_HYBRID] == 0u || ctr[RS_FLAG_FAIL] != 0u) ? 1u : 0u;
+}
+
+__device__ __forceinline__ uint32_t ls_pad(uint32_t bin) { return bin + (bin >> 4); }   // thread-contiguous runs of 16 bins without bank conflicts
+struct LocalSortSmem {
+    uint64_t keys[LS_LOAD];
+    uint32_t vals[LS_LOAD];
+    uint32_t cnt[LS_NBINS + LS_NBINS / 16 + 2];   // per-bin counts, then exclusive starts; index through ls_pad (one pad word per 16 bins)
+    uint16_t pos[LS_LOAD];           // original position inside the region (the stable tie-break)
+    uint32_t scan[LS_THREADS / 32];
+    int first, last_end;
+    uint32_t fail;
+    uint64_t prev_key;
+};
+
+__global__ void __launch_bounds__(LS_THREADS, 3) local_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint64_t n,
+                                                                   int T, int B, uint32_t* __restrict__ ctr) {
+    extern __shared__ __align__(16) unsigned char ls_raw[];
+    LocalSortSmem& S = *reinterpret_cast<LocalSortSmem*>(ls_raw);
+    if (ctr[RS_FLAG_HYBRID] == 0u) return;
+    const uint64_t base = (uint64_t)blockIdx.x * LS_CH;
+    if (base >= n) return;
+    const int avail = (int)min((uint64_t)LS_LOAD, n - base);
+    const int tsh = 64 - T, rsh = 64 - T - B;
+    if (threadIdx.x == 0) { S.first = INT_MAX; S.last_end = INT_MAX; S.fail = 0u; S.prev_key = base ? keys[base - 1] : 0ull; }
+    for (int i = threadIdx.x; i < LS_NBINS + LS_NBINS / 16 + 2; i += LS_THREADS) S.cnt[i] = 0u;
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        const int i = threadIdx.x + k * LS_THREADS;
+        if (i < avail) { S.keys[i] = keys[base + i]; S.vals[i] = vals[base + i]; }
+    }
+    __syncthreads();
+    // segment boundaries: the first one inside the chunk starts the region this CTA owns, the first one at or after the
+    // chunk's end closes it (a segment belongs to the CTA in whose chunk it starts)
+    int my_first = INT_MAX, my_end = INT_MAX;
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        const int i = threadIdx.x + k * LS_THREADS;
+        if (i < avail) {
+            const bool boundary = (i == 0) ? (base == 0 || (S.keys[0] >> tsh) != (S.prev_key >> tsh)) : ((S.keys[i] >> tsh) != (S.keys[i - 1] >> tsh));
+            if (boundary) { if (i < LS_CH) my_first = min(my_first, i); else my_end = min(my_end, i); }
+        }
+    }
+    if (my_first != INT_MAX) atomicMin(&S.first, my_first);
+    if (my_end != INT_MAX) atomicMin(&S.last_end, my_end);
+    __syncthreads();
+    const int first = S.first;
+    if (first == INT_MAX) return;                                   // no segment starts here (it belongs to an earlier CTA)
+    int le = S.last_end;
+    if (le == INT_MAX) {
+        if (base + (uint64_t)avail == n) le = avail;               // the data ends inside the loaded window
+        else { if (threadIdx.x == 0) atomicExch(&ctr[RS_FLAG_FAIL], 1u); return; }   // a segment longer than the window
+    }
+    const uint64_t bin0 = (S.keys[first] >> tsh) << B;
+    // bin every owned element by its top T + B bits (relative to the region's first segment); rank = arrival order
+    uint64_t kk[LS_IPT]; uint32_t vv[LS_IPT]; uint32_t br[LS_IPT];
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        const int i = threadIdx.x + k * LS_THREADS;
+        br[k] = 0xFFFFFFFFu;
+        if (i >= first && i < le) {
+            kk[k] = S.keys[i]; vv[k] = S.vals[i];
+            const uint64_t bin = (kk[k] >> rsh) - bin0;
+            if (bin >= (uint64_t)LS_NBINS) S.fail = 1u;
+            else br[k] = (uint32_t)bin | (atomicAdd(&S.cnt[ls_pad((uint32_t)bin)], 1u) << 12);
+        }
+    }
+    __syncthreads();
+    if (S.fail) { if (threadIdx.x == 0) atomicExch(&ctr[RS_FLAG_FAIL], 1u); return; }
+    // exclusive scan of the bin counts (16 consecutive bins per thread); a crowded bin means the keys do not spread: give up
+    uint32_t c[LS_NBINS / LS_THREADS], tot = 0;
+    bool crowded = false;
+#pragma unroll
+    for (int k = 0; k < LS_NBINS / LS_THREADS; k++) { c[k] = S.cnt[ls_pad(threadIdx.x * (LS_NBINS / LS_THREADS) + k)]; tot += c[k]; crowded |= c[k] > (uint32_t)LS_KMAX; }
+    if (crowded) S.fail = 1u;
+    uint32_t inc = tot;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (gs::lane_id() >= (uint32_t)d) inc += t; }
+    if (gs::lane_id() == 31u) S.scan[threadIdx.x >> 5] = inc;
+    __syncthreads();
+    if (S.fail) { if (threadIdx.x == 0) atomicExch(&ctr[RS_FLAG_FAIL], 1u); return; }
+    uint32_t off = inc - tot;
+#pragma unroll
+    for (int w = 0; w < LS_THREADS / 32; w++) if (w < (int)(threadIdx.x >> 5)) off += S.scan[w];
+#pragma unroll
+    for (int k = 0; k < LS_NBINS / LS_THREADS; k++) { S.cnt[ls_pad(threadIdx.x * (LS_NBINS / LS_THREADS) + k)] = off; off += c[k]; }
+    __syncthreads();
+    // scatter into bin order (every thread holds its elements in registers, the staging area is free to overwrite)
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        if (br[k] != 0xFFFFFFFFu) {
+            const int i = threadIdx.x + k * LS_THREADS;
+            const uint32_t dst = (uint32_t)first + S.cnt[ls_pad(br[k] & 0xFFFu)] + (br[k] >> 12);
+            S.keys[dst] = kk[k]; S.vals[dst] = vv[k]; S.pos[dst] = (uint16_t)i;
+        }
+    }
+    __syncthreads();
+    // finish each bin: insertion sort on (key, original position); bins hold 1-2 elements on average, LS_KMAX at most
+    const uint32_t total = (uint32_t)(le - first);
+#pragma unroll 1
+    for (int k = 0; k < LS_NBINS / LS_THREADS; k++) {
+        const uint32_t b = threadIdx.x + (uint32_t)k * LS_THREADS;     // neighbouring lanes finish neighbouring bins: their elements sit side by side
+        const uint32_t s0 = S.cnt[ls_pad(b)], e0 = (b + 1 < (uint32_t)LS_NBINS) ? S.cnt[ls_pad(b + 1)] : total;
+        for (uint32_t a = s0 + 1; a < e0; a++) {
+            const uint64_t xk = S.keys[first + a]; const uint32_t xv = S.vals[first + a]; const uint16_t xp = S.pos[first + a];
+            uint32_t q = a;
+            while (q > s0) {
+                const uint64_t yk = S.keys[first + q - 1]; const uint16_t yp = S.pos[first + q - 1];
+                if (!(yk > xk || (yk == xk && yp > xp))) break;
+                S.keys[first + q] = yk; S.vals[first + q] = S.vals[first + q - 1]; S.pos[first + q] = yp;
+                q--;
+            }
+            S.keys[first + q] = xk; S.vals[first + q] = xv; S.pos[first + q] = xp;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        const int i = threadIdx.x + k * LS_THREADS;
+        if (i >= first && i < le) { keys[base + i] = S.keys[i]; vals[base + i] = S.vals[i]; }
+    }
+}
+
+constexpr uint32_t RS_BIG_TILE = RS_THREADS * GS_RS_BIG_IPT, RS_SMALL_TILE = RS_THREADS * 8, RS_TINY_TILE = RS_THREADS * 4;
+constexpr size_t RS_HIST_BYTES = RS_MAX_PASSES * 256 * 4;
 constexpr size_t RS_CTR_BYTES = 64;
 
 template <typename KeyT, int IPT, bool BALLOT>
 void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n, const uint32_t* d_n,
                    const GsSortPlan& plan, const PassList& pl, uint32_t tiles, uint32_t* ghist, uint32_t* counters,
-                   uint32_t* status, unsigned long long* agg2, size_t groups, cudaStream_t st) {
+                   uint32_t* status, unsigned long long* agg2, size_t groups, cudaStream_t st, const uint32_t* gate = nullptr,
+                   int slot0 = 0, int dst0 = 0) {
     const size_t smem = sizeof(OnesweepSmem<KeyT, IPT>);
     static bool attr_set = false;
     if (!attr_set) {
@@ -313,18 +477,28 @@ void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], 
     }
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
-    int dst = 0;
+    int dst = dst0;
     for (int p = 0; p < plan.num_passes; p++) {
         const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
+        const int q = slot0 + p;                                   // scratch slot (histogram row, ticket, status block) of this pass
         onesweep_kernel<KeyT, IPT, BALLOT><<<tiles, RS_THREADS, smem, st>>>(
-            kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[p], pl.mask[p], plan.bits[p], ghist + p * 256, counters + p,
-            status + (size_t)p * tiles * 256, agg2 + (size_t)p * groups * 256, aligned16);
+            kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[q], pl.mask[q], plan.bits[p], ghist + q * 256, counters + q,
+            status + (size_t)q * tiles * 256, agg2 + (size_t)q * groups * 256, aligned16, gate);
         kin = kbuf[dst]; vin = vbuf[dst];
         dst ^= 1;
     }
 }
 
 static int g_rs_tiny = 0;   // experiment knob: 1024-pair tiles for inputs around 1 M
+
+static inline PassList pass_window(const PassList& pl, int p0, int np) {
+    PassList w; w.n = np;
+    for (int p = 0; p < RS_MAX_PASSES; p++) { const bool in = p < np; w.shift[p] = in ? pl.shift[p0 + p] : 0; w.mask[p] = in ? pl.mask[p0 + p] : 0u; }
+    return w;
+}
+static int g_rs_hybrid = 1;   // knob: 0 = always the plain LSD plan
+
+static inline int ceil_log2_u64(uint64_t n) { int l = 0; while ((1ull << l) < n) l++; return l; }
 
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
@@ -346,25 +520,66 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     uint32_t* status = (uint32_t*)((char*)scratch + RS_HIST_BYTES + RS_CTR_BYTES);
     const size_t groups = (tiles + RS_GROUP - 1) / RS_GROUP;
     const size_t agg_bytes = groups * 256 * 8;
-    unsigned long long* agg2 = (unsigned long long*)((char*)status + status_bytes * plan.num_passes);
-    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (status_bytes + agg_bytes) * plan.num_passes, st);
+    // hybrid plan: full 64-bit sorts of caller keys (all eight 8-bit digits), element count known on the host, 2^20 .. 2^28
+    bool hybrid = g_rs_hybrid && sizeof(KeyT) == 8 && d_n == nullptr && plan.num_passes == 8 && n >= (1ull << 20) && n <= (1ull << 28);
+    for (int p = 0; hybrid && p < 8; p++) hybrid = plan.shifts[p] == 8 * p && plan.bits[p] == 8;
+    int T = 0, B = 0;
+    GsSortPlan pre; pre.num_passes = 0;
+    if (hybrid) {
+        const int lg = ceil_log2_u64(n);
+        T = lg <= 25 ? (lg - 8 < 12 ? 12 : (lg - 8 > 16 ? 16 : lg - 8)) : lg - 8;      // avg segment 256 .. 512 elements
+        B = lg - T - 1; if (B < 2) B = 2;                                            // avg 1 .. 2 elements per bin
+        pre = gs_sort_plan_even(64 - T, 64);
+    }
+    const int slots = plan.num_passes + pre.num_passes;
+    unsigned long long* agg2 = (unsigned long long*)((char*)status + status_bytes * slots);
+    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (status_bytes + agg_bytes) * slots, st);
     PassList pl;
-    pl.n = plan.num_passes;
-    for (int p = 0; p < 8; p++) { pl.shift[p] = p < pl.n ? plan.shifts[p] : 0; pl.mask[p] = p < pl.n ? ((1u << plan.bits[p]) - 1u) : 0u; }
+    pl.n = slots;
+    for (int p = 0; p < RS_MAX_PASSES; p++) {
+        if (p < plan.num_passes) { pl.shift[p] = plan.shifts[p]; pl.mask[p] = (1u << plan.bits[p]) - 1u; }
+        else if (p < slots) { pl.shift[p] = pre.shifts[p - plan.num_passes]; pl.mask[p] = (1u << pre.bits[p - plan.num_passes]) - 1u; }
+        else { pl.shift[p] = 0; pl.mask[p] = 0u; }
+    }
     uint64_t hb = (n + 2047) / 2048; int hist_blocks = (int)(hb < 148 * 8 ? hb : 148 * 8);
-    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pl, ghist);
     const bool ballot = (hints & GS_SORT_HINT_DISTINCT) != 0;
-#define GS_RS_GO(IPT, B) launch_passes<KeyT, IPT, B>(keys_in, vals_in, kbuf, vbuf, n, d_n, plan, pl, tiles, ghist, counters, status, agg2, groups, st)
-    if (tiny) { if (ballot) GS_RS_GO(4, true); else GS_RS_GO(4, false); }
-    else if (small) { if (ballot) GS_RS_GO(8, true); else GS_RS_GO(8, false); }
-    else { if (ballot) GS_RS_GO(16, true); else GS_RS_GO(16, false); }
+#define GS_RS_GO(IPT, B_, PLAN, GATE, SLOT0, DST0) launch_passes<KeyT, IPT, B_>(keys_in, vals_in, kbuf, vbuf, n, d_n, PLAN, pl, tiles, ghist, counters, status, agg2, groups, st, GATE, SLOT0, DST0)
+#define GS_RS_RUN(PLAN, GATE, SLOT0, DST0)                                                                    \
+    do {                                                                                                      \
+        if (tiny) { if (ballot) GS_RS_GO(4, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(4, false, PLAN, GATE, SLOT0, DST0); }          \
+        else if (small) { if (ballot) GS_RS_GO(8, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(8, false, PLAN, GATE, SLOT0, DST0); }    \
+        else { if (ballot) GS_RS_GO(GS_RS_BIG_IPT, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(GS_RS_BIG_IPT, false, PLAN, GATE, SLOT0, DST0); } \
+    } while (0)
+    if (!hybrid) {
+        radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, 0, plan.num_passes), 0, plan.num_passes, ghist, nullptr);
+        GS_RS_RUN(plan, nullptr, 0, 0);
+        return (plan.num_passes & 1) ? 0 : 1;
+    }
+    // ---- hybrid: prefix passes end in buffer 1 (2 passes: 0 then 1; 3 passes: start at 1 -> 1, 0, 1), the local pass works in
+    // place there, and the 8-pass LSD fallback ends in buffer 1 as well, so the caller's result index does not depend on the flags
+    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, plan.num_passes, pre.num_passes), plan.num_passes, pre.num_passes, ghist, nullptr);
+    const int top = plan.num_passes + pre.num_passes - 1;
+    hybrid_precheck_kernel<<<1, 256, 0, st>>>(ghist + top * 256, 1 << pre.bits[pre.num_passes - 1], n, counters);
+    GS_RS_RUN(pre, counters + RS_FLAG_HYBRID, plan.num_passes, (pre.num_passes & 1) ? 1 : 0);
+    if constexpr (sizeof(KeyT) == 8) {
+        static bool ls_attr = false;
+        if (!ls_attr) { cudaFuncSetAttribute(local_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem)); ls_attr = true; }
+        const uint32_t chunks = (uint32_t)((n + LS_CH - 1) / LS_CH);
+        local_sort_kernel<<<chunks, LS_THREADS, sizeof(LocalSortSmem), st>>>(reinterpret_cast<uint64_t*>(kbuf[1]), vbuf[1], n, T, B, counters);
+    }
+    hybrid_decide_kernel<<<1, 32, 0, st>>>(counters);
+    radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, 0, plan.num_passes), 0, plan.num_passes, ghist, counters + RS_FLAG_LSD);
+    GS_RS_RUN(plan, counters + RS_FLAG_LSD, 0, 0);
+#undef GS_RS_RUN
 #undef GS_RS_GO
-    return (plan.num_passes & 1) ? 0 : 1;
+    return 1;
 }
 
 }  // namespace
 
 void gs_tune_sort_tiny(int v) { g_rs_tiny = v ? 1 : 0; }
+void gs_tune_sort_hybrid(int v) { g_rs_hybrid = v ? 1 : 0; }
+const uint32_t* gs_sort_flags(const void* scratch) { return (const uint32_t*)((const char*)scratch + RS_HIST_BYTES) + RS_FLAG_HYBRID; }
 const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass) { return (const uint32_t*)scratch + (size_t)pass * 256; }
 
 GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
@@ -381,7 +596,7 @@ GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
 
 size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
     size_t tiles = (size_t)((n + RS_TINY_TILE - 1) / RS_TINY_TILE) + 1;
-    return RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + (tiles / RS_GROUP + 1) * 256 * 8) * 8;
+    return RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + (tiles / RS_GROUP + 1) * 256 * 8) * RS_MAX_PASSES;
 }
 
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,

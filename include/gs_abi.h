@@ -199,6 +199,9 @@ int gs_sort64_destroy(gs_sort64*);
 int gs_sort64_sort(gs_sort64*, const uint64_t* d_keys, const uint32_t* d_vals, uint64_t n, int begin_bit, int end_bit);
 const uint64_t* gs_sort64_sorted_keys(gs_sort64*);      /* borrowed, valid until the next sort */
 const uint32_t* gs_sort64_sorted_values(gs_sort64*);
+/* which plan the last sort ran on: 1 = prefix passes + local pass (radix_sort.cu, full 64-bit sorts of spread keys), 0 = the
+ * 8-pass LSD plan (always for sub-ranges and small inputs; the device-side fallback otherwise).  Synchronises. */
+int gs_sort64_last_plan(gs_sort64*, int* hybrid);
 int gs_sort32_create(gs_ctx*, uint64_t max_elements, gs_sort32** out);
 int gs_sort32_destroy(gs_sort32*);
 /* sort(queue, positionBuffer, cameraPos, n): float4 positions -> back-to-front indices (computeDepths, sort.metal:36-72) */

@@ -27,5 +27,5 @@ for ballot, logn in [(b, l) for l in sizes for b in (0, 1)]:
         S.sort(dk, dv, m)
     e1.record(stream); e1.synchronize()
     ms = e0.elapsed_time(e1) / reps
-    print(f"ballot={ballot} u64+u32 n=2^{logn}: {ms:.3f} ms  {m / ms / 1e6:.2f} Gkeys/s  {m * 200 / ms / 1e6:.0f} GB/s algorithmic (8 passes)")
+    print(f"hybrid={S.last_plan_hybrid} ballot={ballot} u64+u32 n=2^{logn}: {ms:.3f} ms  {m / ms / 1e6:.2f} Gkeys/s  {m * 200 / ms / 1e6:.0f} GB/s algorithmic (8 passes)")
     S.close(); ctx.free(dk); ctx.free(dv)
