@@ -318,7 +318,7 @@ __global__ void depth_keys32_kernel(const float4* __restrict__ pos, float cx, fl
 // segment that does not fit, a bin index out of range or a bin with more than LS_KMAX elements raise a flag, after
 // which the plain 8-pass LSD plan runs from the untouched input (its launches return at once when the flag is clear).
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int LS_THREADS = 256, LS_IPT = 16, LS_LOAD = LS_THREADS * LS_IPT, LS_CH = 2048, LS_NBINS = 4096, LS_KMAX = 24;
+constexpr int LS_THREADS = 256, LS_IPT = 12, LS_LOAD = LS_THREADS * LS_IPT, LS_CH = 2048, LS_NBINS = 4096, LS_KMAX = 24;   // window = chunk + 1024: the longest segment that fits
 enum { RS_FLAG_HYBRID = 12, RS_FLAG_FAIL = 13, RS_FLAG_LSD = 14 };   // words of the counter block
 
 __global__ void hybrid_precheck_kernel(const uint32_t* __restrict__ top_hist, int bins, uint64_t n, uint32_t* __restrict__ ctr) {
@@ -434,24 +434,36 @@ __global__ void __launch_bounds__(LS_THREADS, 3) local_sort_kernel(uint64_t* __r
         }
     }
     __syncthreads();
-    // finish each bin: insertion sort on (key, original position); bins hold 1-2 elements on average, LS_KMAX at most
+    // finish each bin by counting: an element's place inside its bin is the number of bin mates that order before it on
+    // (key, original position).  Bins hold 1-2 elements on average (LS_KMAX at most), every lane works on its own element
+    // (no serial per-bin loop), and neighbouring lanes read neighbouring shared-memory words.
     const uint32_t total = (uint32_t)(le - first);
-#pragma unroll 1
-    for (int k = 0; k < LS_NBINS / LS_THREADS; k++) {
-        const uint32_t b = threadIdx.x + (uint32_t)k * LS_THREADS;     // neighbouring lanes finish neighbouring bins: their elements sit side by side
-        const uint32_t s0 = S.cnt[ls_pad(b)], e0 = (b + 1 < (uint32_t)LS_NBINS) ? S.cnt[ls_pad(b + 1)] : total;
-        for (uint32_t a = s0 + 1; a < e0; a++) {
-            const uint64_t xk = S.keys[first + a]; const uint32_t xv = S.vals[first + a]; const uint16_t xp = S.pos[first + a];
-            uint32_t q = a;
-            while (q > s0) {
-                const uint64_t yk = S.keys[first + q - 1]; const uint16_t yp = S.pos[first + q - 1];
-                if (!(yk > xk || (yk == xk && yp > xp))) break;
-                S.keys[first + q] = yk; S.vals[first + q] = S.vals[first + q - 1]; S.pos[first + q] = yp;
-                q--;
+    uint32_t dstp[LS_IPT];
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++) {
+        const uint32_t e = threadIdx.x + (uint32_t)k * LS_THREADS;
+        dstp[k] = 0xFFFFFFFFu;
+        if (e < total) {
+            const uint32_t i = (uint32_t)first + e;
+            const uint64_t xk = S.keys[i];
+            const uint32_t b = (uint32_t)((xk >> rsh) - bin0);
+            const uint32_t s0 = S.cnt[ls_pad(b)], e0 = (b + 1 < (uint32_t)LS_NBINS) ? S.cnt[ls_pad(b + 1)] : total;
+            uint32_t r = e - s0;                                   // alone in its bin: it stays where it is
+            if (e0 - s0 > 1u) {
+                const uint16_t xp = S.pos[i];
+                r = 0;
+                for (uint32_t j = s0; j < e0; j++) {
+                    const uint64_t yk = S.keys[first + j];
+                    r += (yk < xk || (yk == xk && S.pos[first + j] < xp)) ? 1u : 0u;
+                }
             }
-            S.keys[first + q] = xk; S.vals[first + q] = xv; S.pos[first + q] = xp;
+            kk[k] = xk; vv[k] = S.vals[i]; dstp[k] = (uint32_t)first + s0 + r;
         }
     }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < LS_IPT; k++)
+        if (dstp[k] != 0xFFFFFFFFu) { S.keys[dstp[k]] = kk[k]; S.vals[dstp[k]] = vv[k]; }
     __syncthreads();
 #pragma unroll
     for (int k = 0; k < LS_IPT; k++) {
