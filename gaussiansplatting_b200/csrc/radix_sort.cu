@@ -8,8 +8,8 @@
 //
 // Design (HBM-bound; per pass every pair is read once and written once, 12 B + 12 B for u64 keys):
 //   * one up-front kernel builds the digit histograms of ALL passes in a single read of the keys;
-//   * one kernel per pass: a CTA stages a tile of 256 x 16 pairs into shared memory with two TMA bulk copies
-//     (cp.async.bulk + mbarrier: the whole 48 KB is in flight from one instruction, no registers), ranks them with
+//   * one kernel per pass: a CTA stages a tile of 384 x 12 pairs into shared memory with two TMA bulk copies
+//     (cp.async.bulk + mbarrier: the whole 54 KB is in flight from one instruction, no registers), ranks them with
 //     warp-level match_any (stable: warp, row, lane order), publishes its per-digit counts, resolves its
 //     global digit offsets by decoupled look-back over the preceding tiles' status words, reorders the tile
 //     through shared memory so global stores are digit-contiguous, and scatters keys then values;
@@ -20,14 +20,16 @@
 
 namespace {
 
+// CTA shape of the onesweep passes.  Measured on B200 (tools/sort_bench.py, bench.py stage times): 384 threads x 12 items, 3 CTAs / SM
+// (36 warps resident, 4608-pair tiles) beats 256 x 16 x 4 (32 warps) by 3-11 % on 2^20 .. 2^26 pairs: the passes are latency bound.
 #ifndef GS_RS_THREADS
-#define GS_RS_THREADS 256
+#define GS_RS_THREADS 384
 #endif
 #ifndef GS_RS_CTAS
-#define GS_RS_CTAS 4
+#define GS_RS_CTAS 3
 #endif
 #ifndef GS_RS_BIG_IPT
-#define GS_RS_BIG_IPT 16
+#define GS_RS_BIG_IPT 12
 #endif
 constexpr int RS_THREADS = GS_RS_THREADS;   // >= 256: threads 0..255 also own one digit each
 constexpr int RS_WARPS = RS_THREADS / 32;
@@ -116,9 +118,9 @@ struct OnesweepSmem {
     alignas(8) uint64_t bar;
 };
 
-// RS_IPT items per thread (tile = 256 * RS_IPT pairs: 4096 for large inputs, 2048 when the whole input then fits in one
+// RS_IPT items per thread (tile = RS_THREADS * RS_IPT pairs: 4608 for large inputs, 3072 when the whole input then fits in one
 // resident wave); BALLOT selects the peer-finding primitive of the ranking step.
-template <typename KeyT, int RS_IPT, bool BALLOT>
+template <typename KeyT, int RS_IPT, bool BALLOT, bool GATED>
 __global__ void __launch_bounds__(RS_THREADS, GS_RS_CTAS) onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                                  KeyT* __restrict__ kout, uint32_t* __restrict__ vout, uint64_t n_max,
                                                                  const uint32_t* __restrict__ d_n,
@@ -126,12 +128,13 @@ __global__ void __launch_bounds__(RS_THREADS, GS_RS_CTAS) onesweep_kernel(const 
                                                                  uint32_t* counter, uint32_t* status, unsigned long long* agg2,
                                                                  int aligned16, const uint32_t* __restrict__ gate) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    if (gate && *gate == 0u) return;                              // this pass belongs to the plan that is not being run (hybrid sort)
     constexpr int RS_TILE = RS_THREADS * RS_IPT;
     OnesweepSmem<KeyT, RS_IPT>& S = *reinterpret_cast<OnesweepSmem<KeyT, RS_IPT>*>(smem_raw);
     const uint64_t n = d_n ? min((uint64_t)*d_n, n_max) : n_max;
 
-    if (threadIdx.x == 0) { S.tile = atomicAdd(counter, 1u); mbar_init(&S.bar, 1); }
+    // gate (hybrid sort): a pass of the plan that is not being run takes a tile id beyond the input and leaves through the
+    // bounds check below — no extra control flow in the hot path
+    if (threadIdx.x == 0) { S.tile = (GATED && *gate == 0u) ? 0x7FFFFFFFu : atomicAdd(counter, 1u); mbar_init(&S.bar, 1); }
     for (int i = threadIdx.x; i < RS_WARPS * 256 / 2; i += RS_THREADS) reinterpret_cast<uint32_t*>(&S.wh[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = S.tile;
@@ -484,7 +487,8 @@ void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], 
     const size_t smem = sizeof(OnesweepSmem<KeyT, IPT>);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         attr_set = true;
     }
     const KeyT* kin = keys_in;
@@ -493,9 +497,14 @@ void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], 
     for (int p = 0; p < plan.num_passes; p++) {
         const int aligned16 = (((uintptr_t)kin | (uintptr_t)vin) & 15) == 0;
         const int q = slot0 + p;                                   // scratch slot (histogram row, ticket, status block) of this pass
-        onesweep_kernel<KeyT, IPT, BALLOT><<<tiles, RS_THREADS, smem, st>>>(
-            kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[q], pl.mask[q], plan.bits[p], ghist + q * 256, counters + q,
-            status + (size_t)q * tiles * 256, agg2 + (size_t)q * groups * 256, aligned16, gate);
+        if (gate)
+            onesweep_kernel<KeyT, IPT, BALLOT, true><<<tiles, RS_THREADS, smem, st>>>(
+                kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[q], pl.mask[q], plan.bits[p], ghist + q * 256, counters + q,
+                status + (size_t)q * tiles * 256, agg2 + (size_t)q * groups * 256, aligned16, gate);
+        else
+            onesweep_kernel<KeyT, IPT, BALLOT, false><<<tiles, RS_THREADS, smem, st>>>(
+                kin, vin, kbuf[dst], vbuf[dst], n, d_n, pl.shift[q], pl.mask[q], plan.bits[p], ghist + q * 256, counters + q,
+                status + (size_t)q * tiles * 256, agg2 + (size_t)q * groups * 256, aligned16, gate);
         kin = kbuf[dst]; vin = vbuf[dst];
         dst ^= 1;
     }
@@ -572,7 +581,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, plan.num_passes, pre.num_passes), plan.num_passes, pre.num_passes, ghist, nullptr);
     const int top = plan.num_passes + pre.num_passes - 1;
     hybrid_precheck_kernel<<<1, 256, 0, st>>>(ghist + top * 256, 1 << pre.bits[pre.num_passes - 1], n, counters);
-    GS_RS_RUN(pre, counters + RS_FLAG_HYBRID, plan.num_passes, (pre.num_passes & 1) ? 1 : 0);
+    GS_RS_RUN(pre, nullptr, plan.num_passes, (pre.num_passes & 1) ? 1 : 0);   // ungated (a gated CTA pays one more global round trip before its ticket)
     if constexpr (sizeof(KeyT) == 8) {
         static bool ls_attr = false;
         if (!ls_attr) { cudaFuncSetAttribute(local_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem)); ls_attr = true; }
