@@ -275,3 +275,53 @@ def test_adam_moments_follow_the_gaussians_in_the_corrected_mode(gs, ctx, orc):
         assert np.array_equal(after["opacity"][off[carry]], g["opacity"][carry])
     finally:
         A.close(); Dn.close(); G.close()
+
+
+def _sorted_ok(S, keys):
+    vals = np.arange(len(keys), dtype=np.uint32)
+    k, v = S.sort_host(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    return np.array_equal(k, keys[order]) and np.array_equal(v, vals[order])
+
+
+def test_sort64_hybrid_plan_and_its_device_side_fallback(gs, ctx):
+    """GPURadixSort64 on full 64-bit keys: spread keys finish on the prefix-passes + local-pass plan; keys the plan cannot
+    take (one hot value, no entropy in the top bits, crowded bins) are caught ON THE DEVICE and sorted by the 8-pass LSD plan.
+    Either way the result is numpy's stable sort, bit for bit."""
+    n = (1 << 20) + 4321
+    rng = np.random.default_rng(3)
+    S = gs.Sort64(ctx, n)
+    try:
+        cases = [("random", synth.splitmix64(41, n, 1), True),
+                 ("random, every key twice", np.repeat(synth.splitmix64(42, (n + 1) // 2, 1), 2)[:n], True),
+                 ("already sorted", np.sort(synth.splitmix64(43, n, 1)), True),
+                 ("all equal", np.full(n, 0xDEADBEEF12345678, np.uint64), False),
+                 ("only the low 32 bits vary", rng.integers(0, 1 << 32, n, dtype=np.uint64), False),
+                 ("top 16 bits random, rest zero", rng.integers(0, 1 << 16, n, dtype=np.uint64) << np.uint64(48), False),
+                 ("30 % one hot key", np.where(rng.random(n) < 0.3, np.uint64(1) << np.uint64(63), synth.splitmix64(44, n, 1)), False)]
+        for name, keys, want_hybrid in cases:
+            assert _sorted_ok(S, keys), name
+            assert S.last_plan_hybrid == want_hybrid, name
+        gs.tune("sort_hybrid", 0)
+        assert _sorted_ok(S, cases[0][1]) and not S.last_plan_hybrid
+    finally:
+        gs.tune("sort_hybrid", 1)
+        S.close()
+
+
+@pytest.mark.parametrize("logn", [22, 24])
+def test_sort64_hybrid_full_size(gs, ctx, logn):
+    """the bench's standalone sort sizes: sortedness, stability and permutation checked without a host sort of 16 M keys
+    taking minutes: numpy's stable argsort is the checker"""
+    n = 1 << logn
+    S = gs.Sort64(ctx, n)
+    try:
+        assert _sorted_ok(S, synth.splitmix64(1234 + logn, n, 5)) and S.last_plan_hybrid
+        # a sub-range sort never takes the hybrid plan: bits [8, 40) only
+        keys = synth.splitmix64(7, 1 << 20, 2)
+        vals = np.arange(len(keys), dtype=np.uint32)
+        k, v = S.sort_host(keys, vals, 8, 40)
+        order = np.argsort((keys >> np.uint64(8)) & np.uint64((1 << 32) - 1), kind="stable")
+        assert np.array_equal(v, vals[order]) and not S.last_plan_hybrid
+    finally:
+        S.close()
