@@ -130,40 +130,65 @@ __global__ void __launch_bounds__(256) view_splat_kernel(GsParams P, const __gri
     cnt[i] = count;
 }
 
-// draw position j = Gaussian order[j]; its tiles go to offs[j] ... in ty-major, tx-minor order.  One warp per draw position:
-// viewer quads reach 65 x 65 tiles (radius <= 512), a thread per Gaussian would serialise on them.
+// draw position j = Gaussian order[j]; its tiles go to offs[j] ... in ty-major, tx-minor order.  One thread per draw position
+// writes a small quad's pairs itself; quads above 16 tiles (they reach 65 x 65 at radius 512) are handed to the whole warp, one
+// after the other, so that a huge splat does not serialise a lane.
 __global__ void __launch_bounds__(256) view_emit_kernel(const uint4* __restrict__ bbox, const uint32_t* __restrict__ cnt,
                                                         const uint32_t* __restrict__ order, const uint32_t* __restrict__ offs,
                                                         uint32_t n, uint32_t ntx, uint32_t* __restrict__ tiles,
                                                         uint32_t* __restrict__ vals, uint32_t cap_pairs) {
-    const uint32_t j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (j >= n) return;
-    const uint32_t i = order[j];
-    if (i >= n) return;
-    const uint32_t c = cnt[i];
-    if (c == 0) return;
-    const uint4 bb = bbox[i];
-    const uint32_t off = offs[j], wx = bb.z - bb.x + 1u;
-    for (uint32_t k = gs::lane_id(); k < c; k += 32u) {
-        const uint32_t p = off + k;
-        if (p >= cap_pairs) break;
-        tiles[p] = (bb.y + k / wx) * ntx + bb.x + k % wx;
-        vals[p] = i;
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i = 0, c = 0, off = 0;
+    uint4 bb = make_uint4(0u, 0u, 0u, 0u);
+    if (j < n) {
+        i = order[j];
+        if (i < n) { c = cnt[i]; bb = bbox[i]; off = offs[j]; }
+    }
+    const bool big = c > 16u;
+    if (!big && c) {
+        const uint32_t wx = bb.z - bb.x + 1u;
+        for (uint32_t k = 0; k < c; k++) {
+            const uint32_t p = off + k;
+            if (p >= cap_pairs) break;
+            tiles[p] = (bb.y + k / wx) * ntx + bb.x + k % wx;
+            vals[p] = i;
+        }
+    }
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, big);
+    while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const uint32_t bi = __shfl_sync(0xFFFFFFFFu, i, src), bc = __shfl_sync(0xFFFFFFFFu, c, src), bo = __shfl_sync(0xFFFFFFFFu, off, src);
+        const uint32_t bx = __shfl_sync(0xFFFFFFFFu, bb.x, src), by = __shfl_sync(0xFFFFFFFFu, bb.y, src), bz = __shfl_sync(0xFFFFFFFFu, bb.z, src);
+        const uint32_t wx = bz - bx + 1u;
+        for (uint32_t k = gs::lane_id(); k < bc; k += 32u) {
+            const uint32_t p = bo + k;
+            if (p >= cap_pairs) break;
+            tiles[p] = (by + k / wx) * ntx + bx + k % wx;
+            vals[p] = bi;
+        }
     }
 }
 
 __device__ __forceinline__ float quant8(float v) { return gs::fdiv(rintf(gs::fmul(fminf(fmaxf(v, 0.0f), 1.0f), 255.0f)), 255.0f); }
 
-// V4: one CTA per tile, one pixel per thread, entries staged 256 at a time (3 x float4 each) through shared memory
-template <int QUANT>
+// V4: one CTA per tile, one pixel per thread (a warp owns an 8 x 4 pixel patch), entries staged 256 at a time (3 x float4 each)
+// through shared memory.  Before a batch is walked, thread t tests staged entry t against the eight warp patches: the quad
+// must reach the patch (the rasteriser's own interval test on the patch's extreme pixel centres: exact, rounding is monotone)
+// and the splat must be able to pass the two discards somewhere in it (the conservative footprint test of gs_common.cuh:
+// power < -4.5 <=> q > 9, alpha < 1/255 <=> q > 2 ln(255 opacity), with its rounding margin).  A warp then walks only the
+// entries whose bit is set in its mask word, in draw order.  COUNT (fragment statistics for the parity tests) keeps every
+// entry whose quad reaches the patch, so that "shaded" counts what the rasteriser would shade.
+template <int QUANT, int COUNT>
 __global__ void __launch_bounds__(256) view_blend_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ vals,
                                                          const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                          float4* __restrict__ image, unsigned long long* __restrict__ counters) {
     __shared__ float4 s_rec[256 * 3];
+    __shared__ uint32_t s_mask[8][8];
     const uint32_t tile = blockIdx.x;
     const uint32_t tx = tile % ntx, ty = tile / ntx;
-    const uint32_t lx = (threadIdx.x & 7u) + ((threadIdx.x >> 5) & 1u) * 8u;       // a warp owns an 8 x 4 pixel patch
-    const uint32_t ly = ((threadIdx.x >> 3) & 3u) + (threadIdx.x >> 6) * 4u;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint32_t lx = (lane & 7u) + (warp & 1u) * 8u, ly = (lane >> 3) + (warp >> 1) * 4u;
     const uint32_t px = tx * GS_TILE + lx, py = ty * GS_TILE + ly;
     const bool inside = px < W && py < H;
     const float fx = gs::fadd((float)px, 0.5f), fy = gs::fadd((float)py, 0.5f);
@@ -173,40 +198,65 @@ __global__ void __launch_bounds__(256) view_blend_kernel(const float4* __restric
     for (uint32_t base = 0; base < rg.y; base += 256u) {
         const uint32_t m = min(256u, rg.y - base);
         __syncthreads();
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
         if (threadIdx.x < m) {
             const uint32_t id = vals[rg.x + base + threadIdx.x];
-            s_rec[threadIdx.x * 3 + 0] = rec[3 * (size_t)id + 0];
-            s_rec[threadIdx.x * 3 + 1] = rec[3 * (size_t)id + 1];
-            s_rec[threadIdx.x * 3 + 2] = rec[3 * (size_t)id + 2];
+            a0 = rec[3 * (size_t)id + 0]; a1 = rec[3 * (size_t)id + 1];
+            s_rec[threadIdx.x * 3 + 0] = a0; s_rec[threadIdx.x * 3 + 1] = a1; s_rec[threadIdx.x * 3 + 2] = rec[3 * (size_t)id + 2];
+        }
+        {   // patch masks: lane tests its staged entry against every warp's 8 x 4 patch
+            gs::CullRec c;
+            c.sx = a0.x; c.sy = a0.y; c.A = a0.z; c.B = -a0.w; c.C = a1.x;           // pixel y runs down, the conic's y up: B flips
+            c.qthr = fminf(9.0f, 2.0f * __logf(255.0f * a1.z)) + 2e-3f;
+            if (!(c.qthr == c.qthr)) c.qthr = 9.002f;
+            c.iA = 1.0f / c.A; c.iC = 1.0f / c.C;
+            const float r = a1.y;
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                const float x_lo = gs::fadd((float)(tx * GS_TILE + (uint32_t)(w & 1) * 8u), 0.5f), x_hi = gs::fadd(x_lo, 7.0f);
+                const float y_lo = gs::fadd((float)(ty * GS_TILE + (uint32_t)(w >> 1) * 4u), 0.5f), y_hi = gs::fadd(y_lo, 3.0f);
+                // some pixel centre of the patch inside the quad?  (dx >= -r && dx < r && dy > -r && dy <= r with dx = x - cx, dy = cy - y)
+                bool keep = threadIdx.x < m && gs::fsub(x_hi, a0.x) >= -r && gs::fsub(x_lo, a0.x) < r &&
+                            gs::fsub(a0.y, y_lo) > -r && gs::fsub(a0.y, y_hi) <= r;
+                if (!COUNT) keep = keep && !gs::box_cannot_contribute(c, x_lo, y_lo, 7.0f, 3.0f);
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+                if (lane == 0) s_mask[w][warp] = bal;
+            }
         }
         __syncthreads();
         if (!inside) continue;
-        for (uint32_t e = 0; e < m; e++) {
-            const float4 a0 = s_rec[e * 3 + 0], a1 = s_rec[e * 3 + 1];
-            const float dx = gs::fsub(fx, a0.x), dy = gs::fsub(a0.y, fy), r = a1.y;
-            if (!(dx >= -r && dx < r && dy > -r && dy <= r)) continue;              // top-left fill rule on the quad
-            shaded++;
-            const float t1 = gs::fmul(gs::fmul(a0.z, dx), dx), t2 = gs::fmul(gs::fmul(gs::fmul(2.0f, a0.w), dx), dy);
-            const float t3 = gs::fmul(gs::fmul(a1.x, dy), dy);
-            const float power = gs::fmul(-0.5f, gs::fadd(gs::fadd(t1, t2), t3));    // shaders.metal:296-298
-            if (!(power <= 0.0f && power >= -4.5f)) continue;                       // :301
-            const float alpha = gs::fmul(a1.z, gs::exp_blend(power));               // :304-305
-            if (alpha < GS_ALPHA_MIN) continue;                                     // :308
-            blended++;
-            const float4 a2 = s_rec[e * 3 + 2];
-            const float om = gs::fsub(1.0f, alpha);
-            cr = gs::fadd(gs::fmul(a1.w, alpha), gs::fmul(cr, om));                 // ONE, ONE_MINUS_SRC_ALPHA
-            cg = gs::fadd(gs::fmul(a2.x, alpha), gs::fmul(cg, om));
-            cb = gs::fadd(gs::fmul(a2.y, alpha), gs::fmul(cb, om));
-            ca = gs::fadd(alpha, gs::fmul(ca, om));
-            if (QUANT) { cr = quant8(cr); cg = quant8(cg); cb = quant8(cb); ca = quant8(ca); }
+        const uint32_t nwords = (m + 31u) >> 5;
+        for (uint32_t wd = 0; wd < nwords; wd++) {
+            uint32_t mk = s_mask[warp][wd];
+            while (mk) {
+                const uint32_t e = wd * 32u + (uint32_t)__ffs(mk) - 1u;
+                mk &= mk - 1u;
+                const float4 e0 = s_rec[e * 3 + 0], e1 = s_rec[e * 3 + 1];
+                const float dx = gs::fsub(fx, e0.x), dy = gs::fsub(e0.y, fy), r = e1.y;
+                if (!(dx >= -r && dx < r && dy > -r && dy <= r)) continue;          // top-left fill rule on the quad
+                if (COUNT) shaded++;
+                const float t1 = gs::fmul(gs::fmul(e0.z, dx), dx), t2 = gs::fmul(gs::fmul(gs::fmul(2.0f, e0.w), dx), dy);
+                const float t3 = gs::fmul(gs::fmul(e1.x, dy), dy);
+                const float power = gs::fmul(-0.5f, gs::fadd(gs::fadd(t1, t2), t3));    // shaders.metal:296-298
+                if (!(power <= 0.0f && power >= -4.5f)) continue;                       // :301
+                const float alpha = gs::fmul(e1.z, gs::exp_blend(power));               // :304-305
+                if (alpha < GS_ALPHA_MIN) continue;                                     // :308
+                if (COUNT) blended++;
+                const float4 e2 = s_rec[e * 3 + 2];
+                const float om = gs::fsub(1.0f, alpha);
+                cr = gs::fadd(gs::fmul(e1.w, alpha), gs::fmul(cr, om));                 // ONE, ONE_MINUS_SRC_ALPHA
+                cg = gs::fadd(gs::fmul(e2.x, alpha), gs::fmul(cg, om));
+                cb = gs::fadd(gs::fmul(e2.y, alpha), gs::fmul(cb, om));
+                ca = gs::fadd(alpha, gs::fmul(ca, om));
+                if (QUANT) { cr = quant8(cr); cg = quant8(cg); cb = quant8(cb); ca = quant8(ca); }
+            }
         }
     }
     if (inside) image[(size_t)py * W + px] = make_float4(cr, cg, cb, ca);
-    if (counters) {
+    if (COUNT) {
         shaded = __reduce_add_sync(0xFFFFFFFFu, shaded);
         blended = __reduce_add_sync(0xFFFFFFFFu, blended);
-        if (gs::lane_id() == 0) { atomicAdd(&counters[0], (unsigned long long)shaded); atomicAdd(&counters[1], (unsigned long long)blended); }
+        if (lane == 0) { atomicAdd(&counters[0], (unsigned long long)shaded); atomicAdd(&counters[1], (unsigned long long)blended); }
     }
 }
 
@@ -236,13 +286,18 @@ void gs_launch_view_splats(const GsParams& P, const float* V, const float* VP, f
 void gs_launch_view_emit(const uint4* bbox, const uint32_t* cnt, const uint32_t* order, const uint32_t* offs, uint32_t n,
                          uint32_t ntx, uint32_t* tiles, uint32_t* vals, uint32_t cap_pairs, cudaStream_t st) {
     if (n == 0) return;
-    const uint64_t threads = (uint64_t)n * 32u;
-    view_emit_kernel<<<(uint32_t)((threads + 255) / 256), 256, 0, st>>>(bbox, cnt, order, offs, n, ntx, tiles, vals, cap_pairs);
+    view_emit_kernel<<<(n + 255) / 256, 256, 0, st>>>(bbox, cnt, order, offs, n, ntx, tiles, vals, cap_pairs);
 }
 void gs_launch_view_blend(const float4* rec, const uint32_t* vals, const uint2* ranges, uint32_t W, uint32_t H, uint32_t ntx,
                           uint32_t nty, int quantize, float4* image, unsigned long long* counters, cudaStream_t st) {
-    if (quantize) view_blend_kernel<1><<<ntx * nty, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
-    else view_blend_kernel<0><<<ntx * nty, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+    const uint32_t g = ntx * nty;
+    if (counters) {
+        if (quantize) view_blend_kernel<1, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+        else view_blend_kernel<0, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+    } else {
+        if (quantize) view_blend_kernel<1, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+        else view_blend_kernel<0, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+    }
 }
 void gs_launch_view_splats_to_wire(const float4* rec, const uint4* bbox, uint32_t n, void* out64, cudaStream_t st) {
     if (n == 0) return;

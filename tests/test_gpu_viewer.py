@@ -30,9 +30,12 @@ def _draw(gs, ctx, g, u, flags=0, order=None):
             host_order = np.ascontiguousarray(order, np.uint32)
             ctx.upload(pos, host_order)
             d_order = pos
-        V.render(G, d_order, vu, img, flags | gs.GS_VIEW_COUNT_FRAGMENTS)
+        V.render(G, d_order, vu, img, flags)                  # the product path: patches a splat cannot reach are skipped
+        fast = img.download()
+        V.render(G, d_order, vu, img, flags | gs.GS_VIEW_COUNT_FRAGMENTS)   # counting path: every quad fragment is shaded
+        assert np.array_equal(fast.view(np.uint32), img.download().view(np.uint32)), "footprint skipping changed the image"
         ntx, nty = (W + 15) // 16, (H + 15) // 16
-        return dict(image=img.download(), order=host_order, splats=V.get(gs.VIEW_SPLATS, n=n), tiles=V.get(gs.VIEW_SORTED_TILES),
+        return dict(image=fast, order=host_order, splats=V.get(gs.VIEW_SPLATS, n=n), tiles=V.get(gs.VIEW_SORTED_TILES),
                     vals=V.get(gs.VIEW_SORTED_VALUES), ranges=V.get(gs.VIEW_TILE_RANGES, tiles=ntx * nty), frags=V.fragments(),
                     pairs=V.pair_count)
     finally:
