@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libgs_b200.so")
 SOURCES = ["preprocess.cu", "pairs.cu", "binning.cu", "radix_sort.cu", "blend_fwd.cu", "blend_bwd.cu", "layout.cu", "loss.cu", "viewer.cu", "adam.cu",
-           "densify.cu", "api.cu"]
+           "densify.cu", "peer_reduce.cu", "api.cu"]
 HEADERS = ["gs_common.cuh", "gs_kernels.h", os.path.join("..", "..", "include", "gs_abi.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",

@@ -356,6 +356,37 @@ class Sort32:
         lib().gs_sort32_destroy(self.h)
 
 
+class PeerReduce:
+    """gs_dp_*: the per-step gradient sum of view-parallel training over NVLink peer memory (csrc/peer_reduce.cu).
+    usage on every rank: pr = PeerReduce(ctx, rank, world); blob = pr.export(grads); pr.connect(all blobs in rank order);
+    then pr.allreduce(grads, n) after the step's backward calls."""
+    BLOB_BYTES = 192
+
+    def __init__(self, ctx, rank, world):
+        self.ctx = ctx
+        self.h = C.c_void_p()
+        ctx.check(lib().gs_dp_create(ctx.h, C.c_int(rank), C.c_int(world), C.byref(self.h)))
+
+    def export(self, grads):
+        blob = (C.c_ubyte * self.BLOB_BYTES)()
+        self.ctx.check(lib().gs_dp_export(self.h, grads.h, blob))
+        return bytes(blob)
+
+    def connect(self, blobs):
+        raw = b"".join(blobs)
+        buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
+        self.ctx.check(lib().gs_dp_connect(self.h, buf))
+
+    def allreduce(self, grads, n):
+        self.ctx.check(lib().gs_dp_allreduce_grads(self.h, grads.h, C.c_uint32(n)))
+
+    def check(self):
+        self.ctx.check(lib().gs_dp_check(self.h))
+
+    def close(self):
+        lib().gs_dp_destroy(self.h)
+
+
 class Viewer:
     """The draw of MTLEngine::render (mtl_engine.mm:401-609; vertexShader / fragmentShader, shaders.metal:160-317) as CUDA
     compute into a headless Image."""

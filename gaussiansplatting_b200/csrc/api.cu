@@ -1040,6 +1040,106 @@ const uint32_t* gs_sort32_sorted_indices(gs_sort32* s) { return s->vbuf[s->resul
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------------
+// View-parallel gradient sum over NVLink peer memory (peer_reduce.cu)
+// ------------------------------------------------------------------------------------------------------
+struct gs_dp_blob {             // what a rank publishes: IPC handles of its gradient buffer and flag words + the buffer's geometry
+    cudaIpcMemHandle_t buf, flags;
+    uint32_t stride, cap, rank, magic;
+    unsigned char pad[GS_DP_BLOB_BYTES - 2 * sizeof(cudaIpcMemHandle_t) - 16];
+};
+static_assert(sizeof(gs_dp_blob) == GS_DP_BLOB_BYTES && GS_DP_MAX_RANKS == GS_MAX_PEERS, "blob layout");
+struct gs_dp {
+    gs_ctx* c;
+    int rank = 0, world = 1;
+    gs_grads* bound = nullptr;
+    float* bound_ptr = nullptr;
+    uint32_t* my_flags = nullptr;       // 3 barriers x GS_MAX_PEERS words, written by the peers
+    uint32_t* d_err = nullptr;
+    uint32_t epoch = 0;
+    bool connected = false;
+    void* opened[2 * GS_MAX_PEERS] = {};
+    GsPeerSet peers{};
+};
+
+extern "C" {
+
+int gs_dp_create(gs_ctx* c, int rank, int world, gs_dp** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out && world >= 1 && world <= GS_DP_MAX_RANKS && rank >= 0 && rank < world, "rank / world (one node, at most 8 ranks)");
+    gs_dp* d = new (std::nothrow) gs_dp();
+    if (!d) return GS_ERR_OOM;
+    d->c = c; d->rank = rank; d->world = world;
+    int rc = dalloc(c, &d->my_flags, 3 * GS_MAX_PEERS);
+    if (rc == GS_OK) rc = dalloc(c, &d->d_err, 1);
+    if (rc == GS_OK && cudaMemset(d->my_flags, 0, 3 * GS_MAX_PEERS * sizeof(uint32_t)) != cudaSuccess) rc = GS_ERR_CUDA;
+    if (rc == GS_OK && cudaMemset(d->d_err, 0, sizeof(uint32_t)) != cudaSuccess) rc = GS_ERR_CUDA;
+    if (rc != GS_OK) { gs_dp_destroy(d); return rc; }
+    *out = d;
+    return GS_OK;
+}
+int gs_dp_destroy(gs_dp* d) {
+    if (!d) return GS_OK;
+    cudaSetDevice(d->c->device); cudaStreamSynchronize(d->c->stream);
+    for (void* p : d->opened) if (p) cudaIpcCloseMemHandle(p);
+    cudaFree(d->my_flags); cudaFree(d->d_err);
+    delete d;
+    return GS_OK;
+}
+int gs_dp_export(gs_dp* d, gs_grads* g, void* blob_out) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, g && blob_out && g->g, "gradient buffer");
+    gs_dp_blob b;
+    memset(&b, 0, sizeof(b));
+    GS_CUDA(c, cudaIpcGetMemHandle(&b.buf, g->g));
+    GS_CUDA(c, cudaIpcGetMemHandle(&b.flags, d->my_flags));
+    b.stride = g->stride; b.cap = g->cap; b.rank = (uint32_t)d->rank; b.magic = 0x47534450u;
+    memcpy(blob_out, &b, sizeof(b));
+    d->bound = g; d->bound_ptr = g->g;
+    return GS_OK;
+}
+int gs_dp_connect(gs_dp* d, const void* blobs) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, blobs && d->bound, "export first, then connect with every rank's blob");
+    const gs_dp_blob* B = static_cast<const gs_dp_blob*>(blobs);
+    d->peers.rank = d->rank; d->peers.world = d->world;
+    for (int q = 0; q < d->world; q++) {
+        GS_ARG(c, B[q].magic == 0x47534450u && (int)B[q].rank == q, "blob order / contents");
+        GS_ARG(c, B[q].stride == d->bound->stride, "every rank's gradient buffer must have the same capacity");
+        if (q == d->rank) { d->peers.bufs[q] = d->bound_ptr; d->peers.flags[q] = d->my_flags; continue; }
+        void *pb = nullptr, *pf = nullptr;
+        GS_CUDA(c, cudaIpcOpenMemHandle(&pb, B[q].buf, cudaIpcMemLazyEnablePeerAccess));
+        d->opened[2 * q] = pb;
+        GS_CUDA(c, cudaIpcOpenMemHandle(&pf, B[q].flags, cudaIpcMemLazyEnablePeerAccess));
+        d->opened[2 * q + 1] = pf;
+        d->peers.bufs[q] = static_cast<float*>(pb); d->peers.flags[q] = static_cast<uint32_t*>(pf);
+    }
+    d->connected = true;
+    return GS_OK;
+}
+int gs_dp_allreduce_grads(gs_dp* d, gs_grads* g, uint32_t n) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    if (d->world == 1) return GS_OK;
+    GS_ARG(c, d->connected, "gs_dp_connect first");
+    GS_ARG(c, g == d->bound && g->g == d->bound_ptr, "the gradient buffer was reallocated after gs_dp_export");
+    GS_ARG(c, n <= g->cap, "n");
+    if (n == 0) return GS_OK;
+    d->epoch++;
+    gs_launch_peer_allreduce(d->peers, n, g->stride, d->epoch, d->d_err, c->stream);
+    GS_LAUNCH_CHECK(c);
+    return GS_OK;
+}
+int gs_dp_check(gs_dp* d) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    uint32_t e = 0;
+    GS_CUDA(c, cudaMemcpyAsync(&e, d->d_err, sizeof(e), cudaMemcpyDeviceToHost, c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (e) { c->err = "peer all-reduce: a rank did not arrive within 5 s"; return GS_ERR_NCCL; }
+    return GS_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
 // Viewer draw (MTLEngine::render, mtl_engine.mm:401-609, without the window): viewer.cu
 // ------------------------------------------------------------------------------------------------------
 struct gs_viewer {

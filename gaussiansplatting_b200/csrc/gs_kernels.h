@@ -156,6 +156,12 @@ void gs_launch_densify_scatter(GsParams Pin, GsParams Pout, const uint32_t* mark
 void gs_launch_permute_moments(const float* src, uint32_t src_cap, float* dst, uint32_t dst_cap, const uint32_t* markers,
                                const uint32_t* out_off, uint32_t n, uint32_t new_n, cudaStream_t st);
 
+// view-parallel gradient sum over NVLink peer memory (peer_reduce.cu).  bufs[q] / flags[q]: rank q's packed gradient buffer and
+// its 3 x GS_MAX_PEERS flag words, mapped into this process (q == rank: local memory)
+#define GS_MAX_PEERS 8
+struct GsPeerSet { float* bufs[GS_MAX_PEERS]; uint32_t* flags[GS_MAX_PEERS]; int rank, world; };
+void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, cudaStream_t st);
+
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
 void gs_tune_fwd_ppt(int v);
 void gs_tune_bwd_ppt(int v);

@@ -92,6 +92,7 @@ typedef struct gs_sort32 gs_sort32;         /* GPURadixSort32 */
 typedef struct gs_adam gs_adam;             /* AdamOptimizer */
 typedef struct gs_dens gs_dens;             /* DensityController */
 typedef struct gs_viewer gs_viewer;         /* the draw of MTLEngine::render as CUDA compute */
+typedef struct gs_dp gs_dp;                 /* view-parallel gradient sum over NVLink peer memory (one per rank) */
 
 /* ---- context (replaces MTL::Device + MTL::CommandQueue, mtl_engine.mm:79-86) ----------------------------- */
 int gs_ctx_create(int device, gs_ctx** out);
@@ -136,6 +137,25 @@ int gs_grads_download(gs_grads*, gs_gradients* host, uint32_t n);         /* syn
 int gs_grads_set_stat_mode(gs_grads*, int per_view_stats);
 /* the packed fp32 device buffer (16 planes of `stride` floats) — hand this to ncclAllReduce / torch.distributed */
 int gs_grads_packed(gs_grads*, void** dptr, uint64_t* num_floats, uint32_t* stride);
+
+/* ---- view-parallel training: the per-step gradient sum over the ranks of one node ----------------
+ * The reference trains on one device (mtl_engine.mm:1085-1093); this is the only exchange step the multi-GPU path adds.  It runs
+ * as this library's own kernels over NVLink peer memory (csrc/peer_reduce.cu): every rank maps the others' packed gradient
+ * buffers through CUDA IPC, reduces its slice in rank order and gathers the rest, so all ranks end with bit-identical sums.
+ *   1. every rank: gs_dp_create, gs_dp_export(grads, blob)          (blob: GS_DP_BLOB_BYTES)
+ *   2. exchange the blobs by any means (torch.distributed.all_gather_object, MPI, a file) — rank order
+ *   3. every rank: gs_dp_connect(all blobs)
+ *   4. per step, on every rank, after the backward calls: gs_dp_allreduce_grads(grads, n)   (enqueues; planes [0, n) are summed)
+ * The gradient buffer must not be reallocated after export (create it at its final capacity).  gs_dp_check synchronises and
+ * reports GS_ERR_NCCL if a peer did not arrive within 5 s (the kernels give up instead of hanging the device). */
+#define GS_DP_BLOB_BYTES 192
+#define GS_DP_MAX_RANKS 8
+int gs_dp_create(gs_ctx*, int rank, int world, gs_dp** out);
+int gs_dp_destroy(gs_dp*);
+int gs_dp_export(gs_dp*, gs_grads*, void* blob_out);
+int gs_dp_connect(gs_dp*, const void* blobs_in_rank_order);
+int gs_dp_allreduce_grads(gs_dp*, gs_grads*, uint32_t n);
+int gs_dp_check(gs_dp*);
 
 /* ---- images ------------------------------------------------------------------------------------------- */
 int gs_image_create(gs_ctx*, uint32_t width, uint32_t height, gs_image** out);
