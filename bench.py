@@ -289,24 +289,39 @@ def run_ours(args):
     D.set_stat_mode(True)                            # per-view densify statistics ride in columns 14-15 (survive sums)
     vp = dp.ViewParallel(dist)
     gbuf = vp.device_tensor(D) if dist is not None else None
+    # the gradient sum: this library's own kernels over NVLink peer memory (gs_dp_*, csrc/peer_reduce.cu); NCCL's all-reduce on
+    # the same buffer is timed beside it (--allreduce nccl makes it the headline instead)
+    PR = None
+    if dist is not None:
+        PR = gs.PeerReduce(ctx, rank, world)
+        blobs = [None] * world
+        dist.all_gather_object(blobs, PR.export(D))
+        PR.connect(blobs)
 
-    def make_train_step(views_per_step):
+    def make_train_step(views_per_step, use_peer):
         def step(i):
             mine = vp.views(i, views_per_step, NVT)
             for k, v in enumerate(mine):
                 R.forward(G5, cams5[v], img)
                 R.backward(G5, D, cams5[v], img, gts5[v], gs.GS_BWD_ACCUMULATE if k else 0)
             if dist is not None:
-                with torch.cuda.stream(stream):      # NCCL orders itself after / before the ctx stream: no host sync
-                    dist.all_reduce(gbuf)
+                if use_peer:
+                    PR.allreduce(D, n5)              # enqueued on the ctx stream behind the backward kernels
+                else:
+                    with torch.cuda.stream(stream):  # NCCL orders itself after / before the ctx stream: no host sync
+                        dist.all_reduce(gbuf)
             Dn.accumulate(D, n5)
             A5.step(G5, D, LRS)
         return step
 
-    for name, vps in (("train", world), ("c5", 8)):
+    peer_first = args.allreduce == "peer"
+    runs = [("train", world, peer_first), ("c5", 8, peer_first)]
+    if dist is not None:
+        runs += [("train_alt", world, not peer_first), ("c5_alt", 8, not peer_first)]
+    for name, vps, use_peer in runs:
         if vps % world:
             continue
-        stepf = make_train_step(vps)
+        stepf = make_train_step(vps, use_peer)
         G5.upload(g5_host); A5.reset(); Dn.reset_accumulator(n5)
         for i in range(3):
             stepf(i)
@@ -315,13 +330,22 @@ def run_ours(args):
             out["train_iters_per_s"] = 1e3 * K / ms
             out["train_views_per_s"] = 1e3 * K * world / ms
             out["train_config"] = (f"C5 scene: {n5} Gaussians, {W5}x{H5}, 1 view per GPU per step, {R.pair_count} tile pairs, "
-                                   "fwd + bwd + accumulateGradients + Adam" + (", NCCL all-reduce of the 64 B/Gaussian packed gradients" if world > 1 else ""))
-        else:
+                                   "fwd + bwd + accumulateGradients + Adam" + (f", {args.allreduce} all-reduce of the 64 B/Gaussian packed gradients" if world > 1 else ""))
+        elif name == "c5":
             out["c5_steps_per_s"] = 1e3 * K / ms
             out["c5_config"] = f"BASELINE config 5: 8 views per step over {world} GPU(s) (strong scaling), one all-reduce per step"
+        else:
+            alt = "nccl" if peer_first else "peer"
+            out[f"{name.replace('_alt', '')}_{'iters' if name.startswith('train') else 'steps'}_per_s_{alt}_allreduce"] = 1e3 * K / ms
+    if dist is not None:
+        PR.check()
+        out["allreduce"] = {"impl": args.allreduce, "payload_bytes": 64 * n5,
+                            "what": "peer = gs_dp_allreduce_grads (own kernels over NVLink peer memory: barrier, slice reduce in rank "
+                                    "order + store to every rank, barrier); nccl = torch.distributed.all_reduce on the same buffer; the "
+                                    "*_allreduce keys hold the other implementation's numbers"}
     clocks = sampler.stop()                         # sampled over every timed region above (fwd+bwd, e2e, training)
     out["clocks"] = clocks
-    for o in gts5 + [A5, G5]:
+    for o in gts5 + [A5, G5] + ([PR] if PR is not None else []):
         o.close()
     Dn.set_scene_extent(synth.scene_extent(orbit))
     D.set_stat_mode(False)
@@ -515,6 +539,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=list(synth.CONFIG_N))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 training loop")
+    ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"], help="gradient sum of view-parallel training (N > 1)")
     ap.add_argument("--no-viewer", action="store_true", help="skip the viewer-frame line (SURVEY 8f-3)")
     ap.add_argument("--c3-epochs", type=int, default=100, help="epochs of 16 views for the config-3 loop")
     args = ap.parse_args()

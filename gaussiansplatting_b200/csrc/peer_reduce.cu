@@ -3,15 +3,15 @@
 //
 // Every rank maps every other rank's gradient buffer and flag words through CUDA IPC once (gs_dp_connect).  One call then is
 //   barrier A   every rank's gradients are complete (its per-Gaussian chain kernel ran earlier on the same stream)
-//   reduce      rank r sums slice r of the 16 planes over ALL ranks, in rank order, reading the peers' buffers directly
-//               (16-byte system-scope loads that bypass L1) and writes the sum into its own buffer
-//   barrier B   all slices are reduced
-//   gather      every rank copies the other slices from their owners
-//   barrier C   nobody still reads a buffer that the next step is about to overwrite
+//   reduce +    rank r sums slice r of the 16 planes over ALL ranks, in rank order, reading the peers' buffers directly
+//   broadcast   (16-byte system-scope loads that bypass L1), and stores the sum into slice r of EVERY rank's buffer (posted
+//               writes: reads and writes keep both directions of the links busy).  Slice r of any buffer is touched by rank r
+//               only — read, then overwritten by the same thread — so no rank ever sees a half-updated slice
+//   barrier B   all sums have landed everywhere; nobody reads or writes a buffer that the next step is about to overwrite
 // Only the owner of a slice adds, and always in rank order, so every rank ends with bit-identical sums (the replicas of
 // the model must not drift).  A barrier is one small kernel: thread t stores the call's epoch into rank t's flag word
 // (release, system scope) and spins on its own word from rank t (acquire) — bounded: after 5 s it raises an error word and
-// leaves, so a lost peer cannot hang the device.  Traffic per rank: 2 (g-1)/g of the payload over NVLink, both directions busy.
+// leaves, so a lost peer cannot hang the device.  Traffic per rank: (g-1)/g of the payload in each direction of its links.
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
@@ -52,30 +52,31 @@ __global__ void dp_barrier_kernel(const __grid_constant__ GsPeerSet P, int slot,
 // vector v of the flattened payload: plane v / n4, float4 index v % n4 inside the plane
 __device__ __forceinline__ size_t vec_offset(uint32_t v, uint32_t n4, uint32_t stride4) { return (size_t)(v / n4) * stride4 + (v % n4); }
 
+template <int WORLD>
 __global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ GsPeerSet P, uint32_t n4, uint32_t stride4, uint32_t v0, uint32_t v1) {
-    float4* own = reinterpret_cast<float4*>(P.bufs[P.rank]);
-    for (uint32_t v = v0 + blockIdx.x * blockDim.x + threadIdx.x; v < v1; v += gridDim.x * blockDim.x) {
-        const size_t o = vec_offset(v, n4, stride4);
-        float4 x[GS_MAX_PEERS];
+    constexpr int U = WORLD <= 2 ? 4 : 2;                       // vectors per thread per round: U * (WORLD - 1) remote loads in flight
+    const float4* own = reinterpret_cast<const float4*>(P.bufs[P.rank]);
+    const uint32_t T = gridDim.x * blockDim.x;
+    for (uint32_t vb = v0 + blockIdx.x * blockDim.x + threadIdx.x; vb < v1; vb += U * T) {
+        float4 x[U][WORLD];
+        size_t o[U];
 #pragma unroll
-        for (int q = 0; q < GS_MAX_PEERS; q++)
-            if (q < P.world) x[q] = (q == P.rank) ? own[o] : ld_sys_f4(reinterpret_cast<const float4*>(P.bufs[q]) + o);
-        float4 s = x[0];
+        for (int u = 0; u < U; u++) {
+            const uint32_t v = vb + (uint32_t)u * T;
+            o[u] = vec_offset(v < v1 ? v : vb, n4, stride4);
 #pragma unroll
-        for (int q = 1; q < GS_MAX_PEERS; q++)
-            if (q < P.world) { s.x = __fadd_rn(s.x, x[q].x); s.y = __fadd_rn(s.y, x[q].y); s.z = __fadd_rn(s.z, x[q].z); s.w = __fadd_rn(s.w, x[q].w); }
-        own[o] = s;
-    }
-}
-
-__global__ void __launch_bounds__(256) dp_gather_kernel(const __grid_constant__ GsPeerSet P, uint32_t n4, uint32_t stride4, uint32_t V) {
-    float4* own = reinterpret_cast<float4*>(P.bufs[P.rank]);
-    const uint32_t per = (V + (uint32_t)P.world - 1u) / (uint32_t)P.world;
-    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x) {
-        const int owner = (int)(v / per);
-        if (owner == P.rank) continue;
-        const size_t o = vec_offset(v, n4, stride4);
-        own[o] = ld_sys_f4(reinterpret_cast<const float4*>(P.bufs[owner]) + o);
+            for (int q = 0; q < WORLD; q++)
+                x[u][q] = (q == P.rank) ? own[o[u]] : ld_sys_f4(reinterpret_cast<const float4*>(P.bufs[q]) + o[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (vb + (uint32_t)u * T >= v1) break;
+            float4 s = x[u][0];
+#pragma unroll
+            for (int q = 1; q < WORLD; q++) { s.x = __fadd_rn(s.x, x[u][q].x); s.y = __fadd_rn(s.y, x[u][q].y); s.z = __fadd_rn(s.z, x[u][q].z); s.w = __fadd_rn(s.w, x[u][q].w); }
+#pragma unroll
+            for (int q = 0; q < WORLD; q++) reinterpret_cast<float4*>(P.bufs[q])[o[u]] = s;
+        }
     }
 }
 
@@ -88,8 +89,13 @@ void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, u
     const uint32_t v0 = std::min(V, per * (uint32_t)P.rank), v1 = std::min(V, v0 + per);
     const int grid = 148 * 8;
     dp_barrier_kernel<<<1, 32, 0, st>>>(P, 0, epoch, err);
-    if (v1 > v0) dp_reduce_kernel<<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1);
+    if (v1 > v0) {
+        switch (P.world) {
+#define GS_DP_CASE(W) case W: dp_reduce_kernel<W><<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1); break;
+            GS_DP_CASE(2) GS_DP_CASE(3) GS_DP_CASE(4) GS_DP_CASE(5) GS_DP_CASE(6) GS_DP_CASE(7) GS_DP_CASE(8)
+#undef GS_DP_CASE
+        default: break;
+        }
+    }
     dp_barrier_kernel<<<1, 32, 0, st>>>(P, 1, epoch, err);
-    dp_gather_kernel<<<grid, 256, 0, st>>>(P, n4, stride4, V);
-    dp_barrier_kernel<<<1, 32, 0, st>>>(P, 2, epoch, err);
 }

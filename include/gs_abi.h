@@ -141,7 +141,8 @@ int gs_grads_packed(gs_grads*, void** dptr, uint64_t* num_floats, uint32_t* stri
 /* ---- view-parallel training: the per-step gradient sum over the ranks of one node ----------------
  * The reference trains on one device (mtl_engine.mm:1085-1093); this is the only exchange step the multi-GPU path adds.  It runs
  * as this library's own kernels over NVLink peer memory (csrc/peer_reduce.cu): every rank maps the others' packed gradient
- * buffers through CUDA IPC, reduces its slice in rank order and gathers the rest, so all ranks end with bit-identical sums.
+ * buffers through CUDA IPC, reduces its slice in rank order and stores the sum into every rank's buffer, so all ranks end with
+ * bit-identical sums.
  *   1. every rank: gs_dp_create, gs_dp_export(grads, blob)          (blob: GS_DP_BLOB_BYTES)
  *   2. exchange the blobs by any means (torch.distributed.all_gather_object, MPI, a file) — rank order
  *   3. every rank: gs_dp_connect(all blobs)
