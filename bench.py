@@ -349,10 +349,10 @@ def run_ours(args):
         o.close()
     Dn.set_scene_extent(synth.scene_extent(orbit))
     D.set_stat_mode(False)
-    # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan, coarse emit, bin histogram
-    # + passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk counts, bin scan,
+    # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan + coarse emit + bin histogram
+    # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk counts, bin scan,
     # tile scan, fill, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
-    launches_fb = 13 + passes + (2 if passes > 5 else 0)
+    launches_fb = 11 + passes + (2 if passes > 5 else 0)     # the scan and the bin histogram run inside the coarse-emit kernel
     out["gpu_launches"] = K * launches_fb
 
     if rank == 0:
@@ -380,6 +380,8 @@ def run_ours(args):
         bytes_alg = {"preprocess": 136.0 * n, "depth_sort": n * (4.0 + 16.0 * dpasses), "scan": 12.0 * n,
                      "emit": 8.0 * Pc + 24.0 * n, "sort": Pc * (4.0 + 16.0 * tpasses), "ranges": 4.0 * P + 8.0 * tiles + 72.0 * Pc,
                      "preprocess_bwd": 196.0 * n}
+        if stage["scan"] < 0.004:       # fused: the scan runs inside the coarse-emit kernel (look-back over its blocks), no kernel of its own
+            bytes_alg.pop("scan")
         flops_alg = {"blend_fwd": 25.0 * C + 14.0 * (E - C), "blend_bwd": 70.0 * C + 14.0 * (E - C)}
         roofs = {}
         for k, b in bytes_alg.items():

@@ -23,6 +23,7 @@ struct gs_ctx {
 };
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
+static int g_emit_fused = 1;                        // binned pipeline: scan + coarse emit + bin histogram as one kernel
 static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
 static void gs_set_sort_mode(int v);
 #define GS_PROF_EVENTS 11
@@ -61,6 +62,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
     if (!strcmp(name, "sort_tiny_tiles")) { gs_tune_sort_tiny(value); return GS_OK; }
     if (!strcmp(name, "sort_hybrid")) { gs_tune_sort_hybrid(value); return GS_OK; }
+    if (!strcmp(name, "emit_fused")) { g_emit_fused = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     return GS_ERR_ARG;
@@ -470,6 +472,7 @@ struct gs_rast {
     GsProjected proj{};
     uint32_t* meta = nullptr;
     void* scan_scratch = nullptr; size_t scan_scratch_bytes = 0;
+    void* emit_scratch = nullptr;       // ticket + look-back status words of the fused scan / coarse emit
     // pair buffers.  64-bit mode: keys_in/kbuf hold u64 (tile|depth) keys.  Hoisted mode: the same allocations hold
     // u32 tile ids (first half used).
     uint64_t *keys_in = nullptr, *kbuf[2] = {nullptr, nullptr};
@@ -512,11 +515,11 @@ __global__ void iota_kernel(uint32_t* v, uint32_t n) {
 static void rast_free_gaussian_arrays(gs_rast* r) {
     cudaFree(r->proj.rec); cudaFree(r->proj.bbox); cudaFree(r->proj.aux); cudaFree(r->proj.covc); cudaFree(r->proj.offs);
     cudaFree(r->proj.cnt); cudaFree(r->proj.dkey); cudaFree(r->proj.ccnt);
-    cudaFree(r->acc); cudaFree(r->scan_scratch); cudaFree(r->iota); cudaFree(r->dsort_scratch);
+    cudaFree(r->acc); cudaFree(r->scan_scratch); cudaFree(r->emit_scratch); cudaFree(r->iota); cudaFree(r->dsort_scratch);
     for (int i = 0; i < 2; i++) { cudaFree(r->dk_buf[i]); cudaFree(r->perm_buf[i]); r->dk_buf[i] = nullptr; r->perm_buf[i] = nullptr; }
     r->proj.rec = nullptr; r->proj.bbox = nullptr; r->proj.aux = nullptr; r->proj.covc = nullptr; r->proj.offs = nullptr;
     r->proj.cnt = nullptr; r->proj.dkey = nullptr; r->proj.ccnt = nullptr;
-    r->acc = nullptr; r->scan_scratch = nullptr; r->iota = nullptr; r->dsort_scratch = nullptr;
+    r->acc = nullptr; r->scan_scratch = nullptr; r->emit_scratch = nullptr; r->iota = nullptr; r->dsort_scratch = nullptr;
 }
 static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     if (n <= r->cap_g) return GS_OK;
@@ -540,6 +543,7 @@ static int rast_reserve_gaussians(gs_rast* r, uint32_t n) {
     iota_kernel<<<(cap + 255) / 256, 256, 0, c->stream>>>(r->iota, cap);
     r->scan_scratch_bytes = gs_scan_scratch_bytes(cap);
     GS_CUDA(c, cudaMalloc(&r->scan_scratch, r->scan_scratch_bytes));
+    GS_CUDA(c, cudaMalloc(&r->emit_scratch, gs_emit_coarse_scratch_bytes(cap)));
     r->cap_g = cap;
     return GS_OK;
 }
@@ -578,7 +582,7 @@ static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapac
     GS_TRY(dalloc(c, &r->vals_in, cap));
     for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->kbuf[i], cap)); GS_TRY(dalloc(c, &r->vbuf[i], cap)); }
     GS_CUDA(c, cudaMalloc(&r->sort_scratch, gs_sort_scratch_bytes(cap, 8)));
-    GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * 64));
+    GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * 65));    // 64 counts per chunk, then the chunk -> bin table
     r->cap_pairs = cap;
     return GS_OK;
 }
@@ -729,18 +733,24 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
     r->mark(2);
     uint32_t* d_coarse = r->meta + GS_META_COARSE_PAIRS;
     uint32_t* d_total = r->meta + GS_META_TOTAL_PAIRS;
-    gs_launch_exclusive_scan(r->proj.ccnt, perm, r->proj.offs, n, d_coarse, r->scan_scratch, st);
-    r->mark(3);
     const GsSortPlan bplan = gs_sort_plan_even(0, bin_bits);
+    // fused: the scan, the coarse emit and the bin sort's digit histograms are one kernel (binning.cu)
+    const bool fused = g_emit_fused && bplan.num_passes >= 1 && bplan.num_passes <= 2;
+    if (!fused) gs_launch_exclusive_scan(r->proj.ccnt, perm, r->proj.offs, n, d_coarse, r->scan_scratch, st);
+    r->mark(3);
     r->passes = dplan.num_passes + bplan.num_passes;
     if (!c->xfer_meta) GS_CUDA(c, cudaStreamCreateWithFlags(&c->xfer_meta, cudaStreamNonBlocking));
     for (int attempt = 0; attempt < 4; attempt++) {
         uint32_t* bk_in = reinterpret_cast<uint32_t*>(r->keys_in);
         uint32_t* bk[2] = {reinterpret_cast<uint32_t*>(r->kbuf[0]), reinterpret_cast<uint32_t*>(r->kbuf[1])};
         const uint32_t cap = (uint32_t)std::min<uint64_t>(r->cap_pairs, 0x3FFFFFFFull);
-        gs_launch_emit_coarse(r->proj, perm, r->proj.offs, n, r->ntx, bk_in, r->vals_in, cap, st);
+        if (fused) {
+            uint32_t* ghist = gs_sort_prepare(cap, bplan, r->sort_scratch, st);
+            gs_launch_emit_coarse_scan(r->proj, perm, n, r->ntx, bk_in, r->vals_in, cap, d_coarse, r->emit_scratch, bplan, ghist, st);
+        } else gs_launch_emit_coarse(r->proj, perm, r->proj.offs, n, r->ntx, bk_in, r->vals_in, cap, st);
         r->mark(4);
-        const int res = gs_launch_sort32(bk_in, r->vals_in, bk, r->vbuf, cap, d_coarse, bplan, g_tile_sort_hint, r->sort_scratch, st);
+        const int res = gs_launch_sort32(bk_in, r->vals_in, bk, r->vbuf, cap, d_coarse, bplan, g_tile_sort_hint | (fused ? GS_SORT_HINT_PREHIST : 0),
+                                         r->sort_scratch, st);
         const uint32_t* sorted_bins = bplan.num_passes ? bk[res] : bk_in;
         const uint32_t* cvals = bplan.num_passes ? r->vbuf[res] : r->vals_in;
         uint32_t* lists = r->vbuf[bplan.num_passes ? (res ^ 1) : 0];
@@ -748,7 +758,8 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         const uint32_t* bin_hist = bplan.num_passes == 1 ? gs_sort_pass_histogram(r->sort_scratch, 0) : nullptr;
         if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
         gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
-                             d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u, st);
+                             d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u,
+                             r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 64, st);
         r->result = 0;
         r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;
         // the pair counts travel to the host on their own copy stream; the compute stream carries on with the blend

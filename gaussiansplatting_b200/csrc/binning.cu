@@ -61,8 +61,124 @@ __global__ void __launch_bounds__(256) emit_coarse_kernel(GsProjected O, const u
     }
 }
 
-// chunk map: cstart[b] = number of chunks of the bins before b; cstart[nbins] = total.  One CTA.
-__global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict__ bin_ranges, uint32_t nbins, uint32_t* __restrict__ cstart) {
+// K2 + K3c + the bin sort's histogram kernel in one: the exclusive scan of the coarse counts in depth order runs as a
+// decoupled look-back over the blocks (ticket order, one 64-bit status word per block: flag << 32 | sum), each block then
+// emits its run as emit_coarse_kernel does and counts the digits of the coming radix passes (plan order, at most two).
+struct EmitDigits { int np; int shift[2]; uint32_t mask[2]; };
+constexpr unsigned long long EC_AGG = 1ull << 32, EC_INC = 2ull << 32;
+__device__ __forceinline__ unsigned long long ec_ld(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ec_st(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+#ifndef GS_EC_SUB
+#define GS_EC_SUB 4
+#endif
+#ifndef GS_EC_MINB
+#define GS_EC_MINB 7
+#endif
+constexpr uint32_t EC_SUB = GS_EC_SUB;                // sub-runs of 256 Gaussians per block: one look-back per 256 * EC_SUB Gaussians
+__global__ void __launch_bounds__(256, GS_EC_MINB) emit_coarse_scan_kernel(GsProjected O, const uint32_t* __restrict__ perm, uint32_t n, uint32_t nbx,
+                                                               uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap,
+                                                               uint32_t* __restrict__ total, uint32_t* counter, unsigned long long* status,
+                                                               uint32_t* __restrict__ ghist, const EmitDigits dg) {
+    __shared__ uint32_t s_off[512];
+    __shared__ uint32_t s_bx[256], s_by[256], s_bw[256], s_gid[256];
+    __shared__ float s_rbw[256];
+    __shared__ uint32_t s_hist[2][256];
+    __shared__ uint32_t s_w[8];
+    __shared__ uint32_t s_tile, s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
+    s_hist[0][threadIdx.x] = 0u; s_hist[1][threadIdx.x] = 0u;
+    s_off[256 + threadIdx.x] = 0xFFFFFFFFu;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t i0 = tile * (256u * EC_SUB) + threadIdx.x;
+    uint32_t g[EC_SUB], c[EC_SUB], ex[EC_SUB], sub[EC_SUB], pk[EC_SUB];   // pk: bin x | bin y << 10 | width in bins << 20
+#pragma unroll
+    for (uint32_t q = 0; q < EC_SUB; q++) {
+        const uint32_t i = i0 + q * 256u;
+        g[q] = (i < n) ? perm[i] : 0u;
+        c[q] = (i < n) ? O.ccnt[g[q]] : 0u;
+        const uint4 bb = c[q] ? O.bbox[g[q]] : make_uint4(0u, 0u, 0u, 0u);
+        pk[q] = (bb.x / BT) | ((bb.y / BT) << 10) | (((bb.z / BT) - (bb.x / BT) + 1u) << 20);
+    }
+    uint32_t block_sum = 0;
+#pragma unroll
+    for (uint32_t q = 0; q < EC_SUB; q++) {
+        ex[q] = gs::cta_excl_scan<8>(c[q], s_w, &sub[q]) + block_sum;
+        block_sum += sub[q];
+        __syncthreads();
+    }
+    if (threadIdx.x < 32u) {
+        // look-back by one warp: 32 predecessors per round, the nearest inclusive prefix ends the walk
+        const uint32_t lane = threadIdx.x;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            if (lane == 0) ec_st(&status[0], EC_INC | block_sum);
+        } else {
+            if (lane == 0) ec_st(&status[tile], EC_AGG | block_sum);
+            int base = (int)tile - 1;
+            while (true) {
+                const int idx = base - (int)lane;
+                unsigned long long s = EC_INC;
+                if (idx >= 0) do { s = ec_ld(&status[idx]); } while ((s >> 32) == 0ull);
+                const uint32_t incmask = __ballot_sync(0xFFFFFFFFu, (s & EC_INC) != 0ull);
+                const int first = incmask ? (__ffs(incmask) - 1) : 31;
+                uint32_t v = ((int)lane <= first) ? (uint32_t)s : 0u;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+                excl += v;
+                if (incmask) break;
+                base -= 32;
+            }
+            if (lane == 0) ec_st(&status[tile], EC_INC | (unsigned long long)(excl + block_sum));
+        }
+        if (lane == 0) {
+            s_prefix = excl;
+            if ((uint64_t)(tile + 1u) * (256u * EC_SUB) >= n) *total = excl + block_sum;
+        }
+    }
+    __syncthreads();
+    uint32_t begin = s_prefix;
+#pragma unroll
+    for (uint32_t q = 0; q < EC_SUB; q++) {
+        if (q) __syncthreads();
+        s_off[threadIdx.x] = (i0 + q * 256u < n) ? s_prefix + ex[q] : 0xFFFFFFFFu;
+        s_gid[threadIdx.x] = g[q];
+        const uint32_t bw = pk[q] >> 20;
+        s_bx[threadIdx.x] = pk[q] & 1023u; s_by[threadIdx.x] = (pk[q] >> 10) & 1023u; s_bw[threadIdx.x] = bw;
+        s_rbw[threadIdx.x] = 1.0f / (float)bw;
+        __syncthreads();
+        const uint32_t stop = min(begin + sub[q], cap);
+        for (uint32_t j = begin + threadIdx.x; j < stop; j += 256u) {
+            uint32_t lo = 0;
+#pragma unroll
+            for (uint32_t sft = 128u; sft >= 1u; sft >>= 1) { if (s_off[lo + sft] <= j) lo += sft; }
+            const uint32_t k = j - s_off[lo];                     // < 290 coarse bins per Gaussian (256 tiles in a strip)
+            const uint32_t bw2 = s_bw[lo];
+            const uint32_t row = (uint32_t)(((float)k + 0.5f) * s_rbw[lo]);
+            const uint32_t key = (s_by[lo] + row) * nbx + s_bx[lo] + (k - row * bw2);
+            keys[j] = key;
+            vals[j] = s_gid[lo];
+            atomicAdd(&s_hist[0][(key >> dg.shift[0]) & dg.mask[0]], 1u);
+            if (dg.np > 1) atomicAdd(&s_hist[1][(key >> dg.shift[1]) & dg.mask[1]], 1u);
+        }
+        begin += sub[q];
+    }
+    __syncthreads();
+    for (int p = 0; p < dg.np; p++) {
+        const uint32_t h = s_hist[p][threadIdx.x];
+        if (h) atomicAdd(&ghist[p * 256 + threadIdx.x], h);
+    }
+}
+
+// chunk map: cstart[b] = number of chunks of the bins before b; cstart[nbins] = total; chunk_bin[c] = the bin of chunk c.  One CTA.
+__global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict__ bin_ranges, uint32_t nbins, uint32_t* __restrict__ cstart,
+                                                         uint32_t* __restrict__ chunk_bin) {
     __shared__ uint32_t s_w[32];
     __shared__ uint32_t s_carry;
     if (threadIdx.x == 0) s_carry = 0;
@@ -73,7 +189,10 @@ __global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict
         uint32_t total;
         const uint32_t ex = gs::cta_excl_scan<32>(c, s_w, &total);
         const uint32_t carry = s_carry;
-        if (b < nbins) cstart[b] = carry + ex;
+        if (b < nbins) {
+            cstart[b] = carry + ex;
+            for (uint32_t k = 0; k < c; k++) chunk_bin[carry + ex + k] = b;
+        }
         __syncthreads();
         if (threadIdx.x == 0) s_carry = carry + total;
         __syncthreads();
@@ -84,8 +203,9 @@ __global__ void __launch_bounds__(1024) chunk_map_kernel(const uint2* __restrict
 // single-pass coarse sort: the sort's digit histogram IS the bin histogram, so the bins' runs and the chunk map come from
 // one scan of it (replaces the run-boundary kernels on the sorted bin ids).  One CTA, nbins <= 256.
 __global__ void __launch_bounds__(256) bins_from_hist_kernel(const uint32_t* __restrict__ hist, uint32_t nbins, uint2* __restrict__ bin_ranges,
-                                                             uint32_t* __restrict__ cstart) {
+                                                             uint32_t* __restrict__ cstart, uint32_t* __restrict__ chunk_bin) {
     __shared__ uint32_t s_w[8];
+    __shared__ uint32_t s_cs[257];
     const uint32_t b = threadIdx.x;
     const uint32_t cnt = b < nbins ? hist[b] : 0u;
     uint32_t tot;
@@ -93,17 +213,39 @@ __global__ void __launch_bounds__(256) bins_from_hist_kernel(const uint32_t* __r
     __syncthreads();
     const uint32_t cs = gs::cta_excl_scan<8>((cnt + CH - 1u) / CH, s_w, &tot);
     if (b < nbins) { bin_ranges[b] = make_uint2(start, cnt); cstart[b] = cs; }
-    if (b == 0) cstart[nbins] = tot;
+    s_cs[b] = b < nbins ? cs : tot;
+    if (b == 0) { cstart[nbins] = tot; s_cs[256] = tot; }
+    __syncthreads();
+    // chunk table, coalesced: chunk c belongs to the last bin whose first chunk is <= c
+    for (uint32_t c = threadIdx.x; c < tot; c += 256u) {
+        uint32_t lo = 0;
+#pragma unroll
+        for (uint32_t sft = 128u; sft >= 1u; sft >>= 1) { if (s_cs[lo + sft] <= c) lo += sft; }
+        chunk_bin[c] = lo;
+    }
 }
 
 struct ChunkCtx { uint32_t bin, first, count; };   // the chunk's bin, first coarse entry, entries in the chunk
-__device__ __forceinline__ ChunkCtx locate_chunk(uint32_t chunk, const uint32_t* s_cstart, uint32_t nbins, const uint2* __restrict__ bin_ranges) {
-    uint32_t lo = 0, hi = nbins;                               // largest b with cstart[b] <= chunk (empty bins share a value: take the last)
-    while (hi - lo > 1u) { const uint32_t mid = (lo + hi) >> 1; if (s_cstart[mid] <= chunk) lo = mid; else hi = mid; }
-    const uint2 br = bin_ranges[lo];
-    const uint32_t off = (chunk - s_cstart[lo]) * CH;
-    ChunkCtx c; c.bin = lo; c.first = br.x + off; c.count = min(CH, br.y - off);
+__device__ __forceinline__ ChunkCtx locate_chunk(uint32_t chunk, const uint32_t* __restrict__ chunk_bin, const uint32_t* __restrict__ cstart,
+                                                 const uint2* __restrict__ bin_ranges) {
+    const uint32_t b = chunk_bin[chunk];
+    const uint2 br = bin_ranges[b];
+    const uint32_t off = (chunk - cstart[b]) * CH;
+    ChunkCtx c; c.bin = b; c.first = br.x + off; c.count = min(CH, br.y - off);
     return c;
+}
+
+// bit-matrix transpose across the warp: bit i of the result in lane t = bit t of x in lane i (five exchange rounds)
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t x, uint32_t lane) {
+    uint32_t m = 0x0000FFFFu;
+#pragma unroll
+    for (uint32_t j = 16u; j >= 1u; j >>= 1) {
+        const uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, x, j);
+        if (lane & j) x ^= (x ^ (o >> j)) & m;
+        else x ^= ((o ^ (x >> j)) & m) << j;
+        m ^= m << (j >> 1);
+    }
+    return x;
 }
 
 // rectangle of local tiles (within bin bx,by) that bbox bb covers
@@ -120,16 +262,12 @@ __device__ __forceinline__ BinRect bin_rect(const uint4 bb, uint32_t bx, uint32_
 // bin's 8x8 tiles, so it adds +1/-1 at the four corners of a 9x9 difference grid (shared-memory atomics, four per entry
 // whatever its size) and 64 threads take the 2-D prefix sum.  Grid-stride over the chunks.
 __global__ void __launch_bounds__(CH) bin_count_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
-                                                       const uint32_t* __restrict__ cstart, uint32_t nbins, uint32_t nbx,
-                                                       uint32_t* __restrict__ chunk_counts) {
-    extern __shared__ uint32_t s_dyn[];
-    uint32_t* s_cstart = s_dyn;                                // nbins + 1
+                                                       const uint32_t* __restrict__ cstart, const uint32_t* __restrict__ chunk_bin,
+                                                       uint32_t nbins, uint32_t nbx, uint32_t* __restrict__ chunk_counts) {
     __shared__ int s_diff[9][9];
-    for (uint32_t i = threadIdx.x; i <= nbins; i += CH) s_cstart[i] = cstart[i];
-    __syncthreads();
-    const uint32_t total = s_cstart[nbins];
+    const uint32_t total = cstart[nbins];
     for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
-        const ChunkCtx cc = locate_chunk(chunk, s_cstart, nbins, bin_ranges);
+        const ChunkCtx cc = locate_chunk(chunk, chunk_bin, cstart, bin_ranges);
         if (threadIdx.x < 81u) (&s_diff[0][0])[threadIdx.x] = 0;
         __syncthreads();
         if (threadIdx.x < cc.count) {
@@ -212,32 +350,30 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(const uint32_t* __restr
 // Phase B (one thread per PAIR, so large splats do not unbalance a warp): owner entry by fixed-step search over the
 // scanned pair counts, tile from the rectangle, rank = popc of the ballot word below the owner's lane.
 __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
-                                                      const uint32_t* __restrict__ cstart, uint32_t nbins, uint32_t nbx, uint32_t ntx,
+                                                      const uint32_t* __restrict__ cstart, const uint32_t* __restrict__ chunk_bin,
+                                                      uint32_t nbins, uint32_t nbx, uint32_t ntx,
                                                       uint32_t nty, const uint32_t* __restrict__ chunk_prefix,
                                                       const uint2* __restrict__ ranges, uint32_t* __restrict__ out_vals, uint32_t cap_pairs) {
-    extern __shared__ uint32_t s_dyn[];
-    uint32_t* s_cstart = s_dyn;
     __shared__ uint32_t s_ball[NWARP][64];                     // ballot word per (warp, tile)
     __shared__ uint32_t s_base[NWARP][64];                     // slot of the warp's first covering entry per tile
     __shared__ uint32_t s_off[2 * CH];                         // exclusive scan of the entries' pair counts; [CH..] = sentinel
     __shared__ uint32_t s_rect[CH], s_gid[CH];
     __shared__ gs::CullRec s_cull[CH];
     __shared__ uint32_t s_w[NWARP];
-    for (uint32_t i = threadIdx.x; i <= nbins; i += CH) s_cstart[i] = cstart[i];
     s_off[CH + threadIdx.x] = 0xFFFFFFFFu;
     __syncthreads();
-    const uint32_t total = s_cstart[nbins];
+    const uint32_t total = cstart[nbins];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
-        const ChunkCtx cc = locate_chunk(chunk, s_cstart, nbins, bin_ranges);
+        const ChunkCtx cc = locate_chunk(chunk, chunk_bin, cstart, bin_ranges);
         const uint32_t bx = cc.bin % nbx, by = cc.bin / nbx;
         unsigned long long mask = 0ull;
         uint32_t np = 0;
         if (threadIdx.x < cc.count) {
             const uint32_t g = cvals[cc.first + threadIdx.x];
             const BinRect r = bin_rect(O.bbox[g], bx, by);
-            const unsigned long long row = (unsigned long long)(((1u << r.w) - 1u) << r.x0);
-            for (uint32_t y = r.y0; y < r.y0 + r.h; y++) mask |= row << (8u * y);
+            const unsigned long long row = (unsigned long long)(((1u << r.w) - 1u) << r.x0);               // < 256: one byte per tile row
+            mask = row * ((0x0101010101010101ull >> (8u * (8u - r.h))) << (8u * r.y0));                     // rows y0 .. y0 + h - 1
             np = r.w * r.h;
             s_rect[threadIdx.x] = r.x0 | (r.y0 << 4) | (r.w << 8) | ((0x10000u / r.w + 1u) << 12);   // x0, y0 < 8, w <= 8, 17-bit reciprocal
             s_gid[threadIdx.x] = g;
@@ -246,13 +382,8 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
         uint32_t npairs;
         const uint32_t ex = gs::cta_excl_scan<NWARP>(np, s_w, &npairs);
         s_off[threadIdx.x] = threadIdx.x < cc.count ? ex : 0xFFFFFFFFu;
-        const uint32_t mlo = (uint32_t)mask, mhi = (uint32_t)(mask >> 32);
-#pragma unroll
-        for (uint32_t t = 0; t < 32u; t++) {
-            const uint32_t a = __ballot_sync(0xFFFFFFFFu, (mlo >> t) & 1u);
-            const uint32_t b = __ballot_sync(0xFFFFFFFFu, (mhi >> t) & 1u);
-            if (lane == t) { s_ball[warp][t] = a; s_ball[warp][t + 32u] = b; }
-        }
+        s_ball[warp][lane] = warp_transpose32((uint32_t)mask, lane);                // lane t: which lanes cover tile t
+        s_ball[warp][lane + 32u] = warp_transpose32((uint32_t)(mask >> 32), lane);
         __syncthreads();
         if (threadIdx.x < 64u) {
             const uint32_t t = threadIdx.x;
@@ -306,22 +437,35 @@ void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uin
     emit_coarse_kernel<<<(n + 255) / 256, 256, 0, st>>>(O, perm, offs, n, gs_bin_nbx(ntx), bin_keys, vals, cap);
 }
 
+size_t gs_emit_coarse_scratch_bytes(uint32_t n) { return 8 + ((size_t)n / (256u * EC_SUB) + 2u) * 8; }
+// fused scan + coarse emit + digit histograms; `plan` is the coming sort's (1 or 2 passes), `ghist` its prepared block
+void gs_launch_emit_coarse_scan(const GsProjected& O, const uint32_t* perm, uint32_t n, uint32_t ntx, uint32_t* bin_keys, uint32_t* vals,
+                                uint32_t cap, uint32_t* total, void* scratch, const GsSortPlan& plan, uint32_t* ghist, cudaStream_t st) {
+    if (n == 0) { cudaMemsetAsync(total, 0, 4, st); return; }
+    const uint32_t blocks = (n + 256u * EC_SUB - 1u) / (256u * EC_SUB);
+    cudaMemsetAsync(scratch, 0, 8 + (size_t)blocks * 8, st);
+    EmitDigits dg;
+    dg.np = plan.num_passes;
+    for (int p = 0; p < 2; p++) { dg.shift[p] = p < plan.num_passes ? plan.shifts[p] : 0; dg.mask[p] = p < plan.num_passes ? (1u << plan.bits[p]) - 1u : 0u; }
+    emit_coarse_scan_kernel<<<blocks, 256, 0, st>>>(O, perm, n, gs_bin_nbx(ntx), bin_keys, vals, cap, total, (uint32_t*)scratch,
+                                                    (unsigned long long*)((char*)scratch + 8), ghist, dg);
+}
+
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
-                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st) {
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, cudaStream_t st) {
     const uint32_t nbx = gs_bin_nbx(ntx), nbins = gs_bin_count(ntx, nty);
     if (nbins == 0) return;
-    const size_t dyn = ((size_t)nbins + 1) * sizeof(uint32_t);
     // The number of chunks lives on the device; the chunk kernels stride over it, so any grid is correct.  The caller
     // sizes the grid from the previous frame's coarse count (one chunk per CTA: the chunk's dependent gathers of many
     // CTAs overlap), falling back to a persistent grid.
     const uint32_t grid = grid_chunks > 148u * 4u ? grid_chunks : 148u * 4u;
-    if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart);
-    else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart);
-    bin_count_kernel<<<grid, CH, dyn, st>>>(O, cvals, bin_ranges, cstart, nbins, nbx, chunk_counts);
+    if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
+    else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
+    bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count);
     tile_scan_kernel<<<1, 1024, 0, st>>>(tile_count, ntx * nty, ranges, total_pairs, cap_pairs);
-    bin_fill_kernel<<<grid, CH, dyn, st>>>(O, cvals, bin_ranges, cstart, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+    bin_fill_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
 }
 
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,

@@ -40,7 +40,10 @@ size_t gs_sort_scratch_bytes(uint64_t n, int key_bytes);
 // Returns the index (0/1) of the buffer holding the result.
 // hints: GS_SORT_HINT_DISTINCT = the digits met in a warp row (32 consecutive elements) are mostly distinct (random keys,
 // tile ids of a Gaussian's neighbouring tiles): rank with ballots; otherwise with match.any (runs of equal digits).
-enum { GS_SORT_HINT_DISTINCT = 1 };
+// GS_SORT_HINT_PREHIST (32-bit keys) = the scratch was cleared by gs_sort_prepare and the producer of the keys has
+// already counted the digits of every pass into the block it returned: no clear and no histogram kernel here.
+enum { GS_SORT_HINT_DISTINCT = 1, GS_SORT_HINT_PREHIST = 2 };
+uint32_t* gs_sort_prepare(uint64_t n, const GsSortPlan& plan, void* scratch, cudaStream_t st);
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,
                      const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st);
 // n is a host-side BOUND (grid, scratch); when d_n is non-null the true count is read from the device (min(*d_n, n)),
@@ -89,6 +92,10 @@ uint32_t gs_bin_count(uint32_t ntx, uint32_t nty);
 size_t gs_bin_max_chunks(uint64_t coarse_cap, uint32_t nbins);
 void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uint32_t* offs, uint32_t n, uint32_t ntx,
                            uint32_t* bin_keys, uint32_t* vals, uint32_t cap, cudaStream_t st);
+// the same pairs from ONE kernel that also scans the coarse counts (no offsets array) and counts the bin sort's digits
+size_t gs_emit_coarse_scratch_bytes(uint32_t n);
+void gs_launch_emit_coarse_scan(const GsProjected& O, const uint32_t* perm, uint32_t n, uint32_t ntx, uint32_t* bin_keys, uint32_t* vals,
+                                uint32_t cap, uint32_t* total, void* scratch, const GsSortPlan& plan, uint32_t* ghist, cudaStream_t st);
 // bin_hist: per-bin entry counts when the coarse sort was a single pass (its digit histogram, gs_sort_pass_histogram), else
 // nullptr and bin_ranges must already hold the bins' runs
 const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass);
@@ -97,7 +104,7 @@ const uint32_t* gs_sort_flags(const void* scratch);   // three words: hybrid pla
 void gs_tune_sort_hybrid(int v);   // 1 (default): full 64-bit sorts may take the prefix-passes + local-pass plan (radix_sort.cu)
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
-                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, cudaStream_t st);
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, cudaStream_t st);
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
                                      uint32_t n, uint64_t* keys, cudaStream_t st);
 

@@ -521,6 +521,10 @@ static int g_rs_hybrid = 1;   // knob: 0 = always the plain LSD plan
 
 static inline int ceil_log2_u64(uint64_t n) { int l = 0; while ((1ull << l) < n) l++; return l; }
 
+static inline bool rs_small(uint64_t n) { return n <= (uint64_t)RS_SMALL_TILE * 148 * GS_RS_CTAS; }
+static inline bool rs_tiny(uint64_t n) { return g_rs_tiny && n <= (uint64_t)RS_TINY_TILE * 148 * GS_RS_CTAS * 2; }
+static inline uint32_t rs_tile_elems(uint64_t n) { return rs_tiny(n) ? RS_TINY_TILE : rs_small(n) ? RS_SMALL_TILE : RS_BIG_TILE; }
+
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
               const uint32_t* d_n, const GsSortPlan& plan, int hints, void* scratch, cudaStream_t st) {
@@ -531,9 +535,8 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
         return 0;
     }
     // small inputs: 2048-pair tiles so that every tile is resident at once (one wave) instead of 1.x waves of 4096
-    const bool small = n <= (uint64_t)RS_SMALL_TILE * 148 * GS_RS_CTAS;
-    const bool tiny = g_rs_tiny && n <= (uint64_t)RS_TINY_TILE * 148 * GS_RS_CTAS * 2;
-    const uint32_t tile_elems = tiny ? RS_TINY_TILE : small ? RS_SMALL_TILE : RS_BIG_TILE;
+    const bool small = rs_small(n), tiny = rs_tiny(n);
+    const uint32_t tile_elems = rs_tile_elems(n);
     const uint32_t tiles = (uint32_t)((n + tile_elems - 1) / tile_elems);
     const size_t status_bytes = (size_t)tiles * 256 * 4;
     uint32_t* ghist = (uint32_t*)scratch;
@@ -554,7 +557,9 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     }
     const int slots = plan.num_passes + pre.num_passes;
     unsigned long long* agg2 = (unsigned long long*)((char*)status + status_bytes * slots);
-    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (status_bytes + agg_bytes) * slots, st);
+    // GS_SORT_HINT_PREHIST: the caller cleared the scratch (gs_sort_prepare) and filled the digit histograms itself
+    const bool prehist = (hints & GS_SORT_HINT_PREHIST) != 0 && !hybrid;
+    if (!prehist) cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (status_bytes + agg_bytes) * slots, st);
     PassList pl;
     pl.n = slots;
     for (int p = 0; p < RS_MAX_PASSES; p++) {
@@ -572,7 +577,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
         else { if (ballot) GS_RS_GO(GS_RS_BIG_IPT, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(GS_RS_BIG_IPT, false, PLAN, GATE, SLOT0, DST0); } \
     } while (0)
     if (!hybrid) {
-        radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, 0, plan.num_passes), 0, plan.num_passes, ghist, nullptr);
+        if (!prehist) radix_hist_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_in, n, d_n, pass_window(pl, 0, plan.num_passes), 0, plan.num_passes, ghist, nullptr);
         GS_RS_RUN(plan, nullptr, 0, 0);
         return (plan.num_passes & 1) ? 0 : 1;
     }
@@ -618,6 +623,16 @@ GsSortPlan gs_sort_plan(int begin_bit, int end_bit, uint64_t varying_mask) {
 size_t gs_sort_scratch_bytes(uint64_t n, int /*key_bytes*/) {
     size_t tiles = (size_t)((n + RS_TINY_TILE - 1) / RS_TINY_TILE) + 1;
     return RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + (tiles / RS_GROUP + 1) * 256 * 8) * RS_MAX_PASSES;
+}
+
+// Clears the scratch of a coming gs_launch_sort32(..., GS_SORT_HINT_PREHIST) over at most n elements and returns the
+// histogram block: the caller's producer kernel adds the count of digit d of pass p (plan order) to hist[p * 256 + d].
+uint32_t* gs_sort_prepare(uint64_t n, const GsSortPlan& plan, void* scratch, cudaStream_t st) {
+    if (n == 0 || plan.num_passes == 0) return (uint32_t*)scratch;
+    const uint32_t tile_elems = rs_tile_elems(n);
+    const size_t tiles = (size_t)((n + tile_elems - 1) / tile_elems), groups = (tiles + RS_GROUP - 1) / RS_GROUP;
+    cudaMemsetAsync(scratch, 0, RS_HIST_BYTES + RS_CTR_BYTES + (tiles * 256 * 4 + groups * 256 * 8) * plan.num_passes, st);   // as sort_impl
+    return (uint32_t*)scratch;
 }
 
 int gs_launch_sort64(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* kbuf[2], uint32_t* vbuf[2], uint64_t n,

@@ -1,0 +1,46 @@
+"""A/B of one gs_tune knob on the fwd+bwd frame (config C2 by default): per-stage device times with the knob at 0 and 1,
+alternating so clock drift shows up in both.  usage: python tools/stage_ab.py KNOB [workload] [frames]"""
+import os
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from gaussiansplatting_b200 import capi as gs, synth
+
+knob = sys.argv[1]
+wl = sys.argv[2] if len(sys.argv) > 2 else "C2"
+frames = int(sys.argv[3]) if len(sys.argv) > 3 else 20
+n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
+ctx = gs.Context(0)
+stream = torch.cuda.ExternalStream(ctx.stream, device=0)
+G = gs.Gaussians(ctx, n); G.upload(synth.make_scene(n, synth.CONFIG_SEED[wl], synth.CONFIG_S0[wl]))
+Gt = gs.Gaussians(ctx, n); Gt.upload(synth.make_scene(n, synth.CONFIG_SEED[wl] ^ 0xA5A5, synth.CONFIG_S0[wl]))
+R = gs.Rasterizer(ctx, n)
+img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
+D = gs.Grads(ctx, n)
+cams = [synth.make_camera(v, 64, W, H, n, synth.CONFIG_ORBIT[wl]) for v in range(64)]
+R.forward(Gt, cams[0], gti)
+
+def frame(i):
+    R.forward(G, cams[i % 64], img)
+    R.backward(G, D, cams[i % 64], img, gti)
+
+for rep in range(3):
+    for v in (0, 1):
+        gs.tune(knob, v)
+        for i in range(3):
+            frame(i)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(frames):
+            frame(i)
+        e1.record(stream); e1.synchronize()
+        ms = e0.elapsed_time(e1) / frames
+        R.set_profiling(True)
+        acc = {}
+        for i in range(frames):
+            frame(i); ctx.sync()
+            for k, t in R.timings().items():
+                acc[k] = acc.get(k, 0.0) + t / frames
+        R.set_profiling(False)
+        print(f"{knob}={v}: {ms:.4f} ms/frame | " + " ".join(f"{k} {t * 1e3:.0f}" for k, t in acc.items()), flush=True)
