@@ -350,9 +350,9 @@ def run_ours(args):
     Dn.set_scene_extent(synth.scene_extent(orbit))
     D.set_stat_mode(False)
     # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan + coarse emit + bin histogram
-    # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk counts, bin scan,
-    # tile scan, fill, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
-    launches_fb = 11 + passes + (2 if passes > 5 else 0)     # the scan and the bin histogram run inside the coarse-emit kernel
+    # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk
+    # counts, bin scan + tile scan (one kernel), fill, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
+    launches_fb = 10 + passes + (2 if passes > 5 else 0)
     out["gpu_launches"] = K * launches_fb
 
     if rank == 0:

@@ -556,7 +556,8 @@ static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureB
         r->cap_tiles = ntx * nty;
         GS_TRY(dalloc(c, &r->ranges, r->cap_tiles));
         GS_TRY(dalloc(c, &r->proj.tile_flags, r->cap_tiles));
-        GS_TRY(dalloc(c, &r->tile_count, r->cap_tiles));
+        GS_TRY(dalloc(c, &r->tile_count, (size_t)r->cap_tiles + 1));     // + the bin-scan CTAs' completion ticket (self-resetting)
+        GS_CUDA(c, cudaMemsetAsync(r->tile_count + r->cap_tiles, 0, sizeof(uint32_t), c->stream));
         GS_TRY(dalloc(c, &r->bin_ranges, (size_t)r->cap_tiles + 2));      // bins <= tiles
         GS_TRY(dalloc(c, &r->cstart, (size_t)r->cap_tiles + 2));
     }
@@ -759,7 +760,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
         gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
                              d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u,
-                             r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 64, st);
+                             r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 64, r->tile_count + r->cap_tiles, st);
         r->result = 0;
         r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;
         // the pair counts travel to the host on their own copy stream; the compute stream carries on with the blend

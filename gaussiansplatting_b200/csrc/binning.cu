@@ -62,112 +62,72 @@ __global__ void __launch_bounds__(256) emit_coarse_kernel(GsProjected O, const u
 }
 
 // K2 + K3c + the bin sort's histogram kernel in one: the exclusive scan of the coarse counts in depth order runs as a
-// decoupled look-back over the blocks (ticket order, one 64-bit status word per block: flag << 32 | sum), each block then
+// look-back over the blocks (ticket order, gs::lookback_excl_warp), each block then
 // emits its run as emit_coarse_kernel does and counts the digits of the coming radix passes (plan order, at most two).
 struct EmitDigits { int np; int shift[2]; uint32_t mask[2]; };
-constexpr unsigned long long EC_AGG = 1ull << 32, EC_INC = 2ull << 32;
-__device__ __forceinline__ unsigned long long ec_ld(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void ec_st(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-#ifndef GS_EC_SUB
-#define GS_EC_SUB 4
-#endif
-#ifndef GS_EC_MINB
-#define GS_EC_MINB 7
-#endif
-constexpr uint32_t EC_SUB = GS_EC_SUB;                // sub-runs of 256 Gaussians per block: one look-back per 256 * EC_SUB Gaussians
-__global__ void __launch_bounds__(256, GS_EC_MINB) emit_coarse_scan_kernel(GsProjected O, const uint32_t* __restrict__ perm, uint32_t n, uint32_t nbx,
+constexpr uint32_t EC_IPT = 4, EC_RUN = 256u * EC_IPT;   // Gaussians per thread / per block: one look-back per 1024 Gaussians
+__global__ void __launch_bounds__(256, 6) emit_coarse_scan_kernel(GsProjected O, const uint32_t* __restrict__ perm, uint32_t n, uint32_t nbx,
                                                                uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t cap,
                                                                uint32_t* __restrict__ total, uint32_t* counter, unsigned long long* status,
-                                                               uint32_t* __restrict__ ghist, const EmitDigits dg) {
-    __shared__ uint32_t s_off[512];
-    __shared__ uint32_t s_bx[256], s_by[256], s_bw[256], s_gid[256];
-    __shared__ float s_rbw[256];
+                                                               unsigned long long* group_sum, uint32_t* __restrict__ ghist, const EmitDigits dg) {
+    __shared__ uint32_t s_off[2 * EC_RUN];                 // first output slot of every Gaussian of the run; [EC_RUN..) = sentinel
+    __shared__ uint32_t s_pk[EC_RUN], s_gid[EC_RUN];       // bin x | bin y << 10 | width in bins << 20 ; Gaussian index
     __shared__ uint32_t s_hist[2][256];
     __shared__ uint32_t s_w[8];
     __shared__ uint32_t s_tile, s_prefix;
     if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
     s_hist[0][threadIdx.x] = 0u; s_hist[1][threadIdx.x] = 0u;
-    s_off[256 + threadIdx.x] = 0xFFFFFFFFu;
+#pragma unroll
+    for (uint32_t q = 0; q < EC_IPT; q++) s_off[EC_RUN + q * 256u + threadIdx.x] = 0xFFFFFFFFu;
     __syncthreads();
     const uint32_t tile = s_tile;
-    const uint32_t i0 = tile * (256u * EC_SUB) + threadIdx.x;
-    uint32_t g[EC_SUB], c[EC_SUB], ex[EC_SUB], sub[EC_SUB], pk[EC_SUB];   // pk: bin x | bin y << 10 | width in bins << 20
+    const uint32_t i0 = tile * EC_RUN + threadIdx.x * EC_IPT;      // a thread owns EC_IPT consecutive Gaussians of the depth order
+    uint32_t g[EC_IPT], c[EC_IPT], pk[EC_IPT];
+    if (i0 + EC_IPT <= n) {
+        const uint4 p4 = *reinterpret_cast<const uint4*>(perm + i0);
+        g[0] = p4.x; g[1] = p4.y; g[2] = p4.z; g[3] = p4.w;
+    } else {
 #pragma unroll
-    for (uint32_t q = 0; q < EC_SUB; q++) {
-        const uint32_t i = i0 + q * 256u;
-        g[q] = (i < n) ? perm[i] : 0u;
-        c[q] = (i < n) ? O.ccnt[g[q]] : 0u;
-        const uint4 bb = c[q] ? O.bbox[g[q]] : make_uint4(0u, 0u, 0u, 0u);
+        for (uint32_t q = 0; q < EC_IPT; q++) g[q] = (i0 + q < n) ? perm[i0 + q] : 0u;
+    }
+    uint32_t sum = 0;
+#pragma unroll
+    for (uint32_t q = 0; q < EC_IPT; q++) {
+        c[q] = (i0 + q < n) ? O.ccnt[g[q]] : 0u;
+        const uint4 bb = O.bbox[g[q]];                       // not made to wait for the count: both gathers fly together
         pk[q] = (bb.x / BT) | ((bb.y / BT) << 10) | (((bb.z / BT) - (bb.x / BT) + 1u) << 20);
+        sum += c[q];
     }
-    uint32_t block_sum = 0;
-#pragma unroll
-    for (uint32_t q = 0; q < EC_SUB; q++) {
-        ex[q] = gs::cta_excl_scan<8>(c[q], s_w, &sub[q]) + block_sum;
-        block_sum += sub[q];
-        __syncthreads();
-    }
+    uint32_t block_sum;
+    uint32_t ex = gs::cta_excl_scan<8>(sum, s_w, &block_sum);
     if (threadIdx.x < 32u) {
-        // look-back by one warp: 32 predecessors per round, the nearest inclusive prefix ends the walk
-        const uint32_t lane = threadIdx.x;
-        uint32_t excl = 0;
-        if (tile == 0) {
-            if (lane == 0) ec_st(&status[0], EC_INC | block_sum);
-        } else {
-            if (lane == 0) ec_st(&status[tile], EC_AGG | block_sum);
-            int base = (int)tile - 1;
-            while (true) {
-                const int idx = base - (int)lane;
-                unsigned long long s = EC_INC;
-                if (idx >= 0) do { s = ec_ld(&status[idx]); } while ((s >> 32) == 0ull);
-                const uint32_t incmask = __ballot_sync(0xFFFFFFFFu, (s & EC_INC) != 0ull);
-                const int first = incmask ? (__ffs(incmask) - 1) : 31;
-                uint32_t v = ((int)lane <= first) ? (uint32_t)s : 0u;
-#pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
-                excl += v;
-                if (incmask) break;
-                base -= 32;
-            }
-            if (lane == 0) ec_st(&status[tile], EC_INC | (unsigned long long)(excl + block_sum));
-        }
-        if (lane == 0) {
+        const uint32_t excl = gs::lookback_excl_warp(tile, block_sum, status, group_sum, threadIdx.x);
+        if (threadIdx.x == 0) {
             s_prefix = excl;
-            if ((uint64_t)(tile + 1u) * (256u * EC_SUB) >= n) *total = excl + block_sum;
+            if ((uint64_t)(tile + 1u) * EC_RUN >= n) *total = excl + block_sum;
         }
+    }
+#pragma unroll
+    for (uint32_t q = 0; q < EC_IPT; q++) {                  // block-relative for now: the prefix is added when a slot is looked up
+        s_off[threadIdx.x * EC_IPT + q] = (i0 + q < n) ? ex : 0xFFFFFFFFu;
+        s_pk[threadIdx.x * EC_IPT + q] = pk[q]; s_gid[threadIdx.x * EC_IPT + q] = g[q];
+        ex += c[q];
     }
     __syncthreads();
-    uint32_t begin = s_prefix;
+    const uint32_t begin = s_prefix;
+    const uint32_t count = begin < cap ? min(block_sum, cap - begin) : 0u;
+    for (uint32_t j = threadIdx.x; j < count; j += 256u) {
+        uint32_t lo = 0;
 #pragma unroll
-    for (uint32_t q = 0; q < EC_SUB; q++) {
-        if (q) __syncthreads();
-        s_off[threadIdx.x] = (i0 + q * 256u < n) ? s_prefix + ex[q] : 0xFFFFFFFFu;
-        s_gid[threadIdx.x] = g[q];
-        const uint32_t bw = pk[q] >> 20;
-        s_bx[threadIdx.x] = pk[q] & 1023u; s_by[threadIdx.x] = (pk[q] >> 10) & 1023u; s_bw[threadIdx.x] = bw;
-        s_rbw[threadIdx.x] = 1.0f / (float)bw;
-        __syncthreads();
-        const uint32_t stop = min(begin + sub[q], cap);
-        for (uint32_t j = begin + threadIdx.x; j < stop; j += 256u) {
-            uint32_t lo = 0;
-#pragma unroll
-            for (uint32_t sft = 128u; sft >= 1u; sft >>= 1) { if (s_off[lo + sft] <= j) lo += sft; }
-            const uint32_t k = j - s_off[lo];                     // < 290 coarse bins per Gaussian (256 tiles in a strip)
-            const uint32_t bw2 = s_bw[lo];
-            const uint32_t row = (uint32_t)(((float)k + 0.5f) * s_rbw[lo]);
-            const uint32_t key = (s_by[lo] + row) * nbx + s_bx[lo] + (k - row * bw2);
-            keys[j] = key;
-            vals[j] = s_gid[lo];
-            atomicAdd(&s_hist[0][(key >> dg.shift[0]) & dg.mask[0]], 1u);
-            if (dg.np > 1) atomicAdd(&s_hist[1][(key >> dg.shift[1]) & dg.mask[1]], 1u);
-        }
-        begin += sub[q];
+        for (uint32_t sft = EC_RUN / 2; sft >= 1u; sft >>= 1) { if (s_off[lo + sft] <= j) lo += sft; }
+        const uint32_t k = j - s_off[lo];                     // < 290 coarse bins per Gaussian (256 tiles in a strip)
+        const uint32_t p = s_pk[lo], bw = p >> 20;
+        const uint32_t row = (uint32_t)(((float)k + 0.5f) * (1.0f / (float)bw));
+        const uint32_t key = (((p >> 10) & 1023u) + row) * nbx + (p & 1023u) + (k - row * bw);
+        keys[begin + j] = key;
+        vals[begin + j] = s_gid[lo];
+        atomicAdd(&s_hist[0][(key >> dg.shift[0]) & dg.mask[0]], 1u);
+        if (dg.np > 1) atomicAdd(&s_hist[1][(key >> dg.shift[1]) & dg.mask[1]], 1u);
     }
     __syncthreads();
     for (int p = 0; p < dg.np; p++) {
@@ -288,11 +248,41 @@ __global__ void __launch_bounds__(CH) bin_count_kernel(GsProjected O, const uint
     }
 }
 
+// tile scan: ranges[t] = (exclusive prefix, count); *total = pair count.  One CTA of 1024 threads (the last bin-scan CTA).
+// Ranges are clipped to the list capacity: when the pair buffers turn out too small the frame is redone by the host, and
+// the kernels of the clipped attempt must stay inside the buffers.
+__device__ __forceinline__ void tile_scan_cta(const uint32_t* __restrict__ tile_count, uint32_t ntiles, uint2* __restrict__ ranges,
+                                              uint32_t* __restrict__ total, uint32_t cap_pairs, uint32_t* s_w, uint32_t* s_carry) {
+    if (threadIdx.x == 0) *s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < ntiles; base += 8192u) {
+        const uint32_t t0 = base + threadIdx.x * 8u;
+        uint32_t c[8], sum = 0;
+#pragma unroll
+        for (uint32_t q = 0; q < 8u; q++) { c[q] = (t0 + q < ntiles) ? __ldcg(tile_count + t0 + q) : 0u; sum += c[q]; }
+        uint32_t tot;
+        uint32_t ex = gs::cta_excl_scan<32>(sum, s_w, &tot) + *s_carry;
+#pragma unroll
+        for (uint32_t q = 0; q < 8u; q++) {
+            if (t0 + q < ntiles) { const uint32_t a = min(ex, cap_pairs); ranges[t0 + q] = make_uint2(a, min(c[q], cap_pairs - a)); }
+            ex += c[q];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) *s_carry += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total = *s_carry;
+}
+
 // bin scan: one CTA per bin, 16 groups x 64 tiles.  chunk_counts[c][t] becomes the exclusive prefix over the bin's chunks;
 // tile_count[global tile] = the tile's total (0 for a bin without entries; tiles outside the image are skipped).
+// The CTA that finishes last (ticket in *done, which it resets) then scans the tile totals into the tile ranges.
 __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restrict__ cstart, uint32_t nbx, uint32_t ntx, uint32_t nty,
-                                                        uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count) {
+                                                        uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count,
+                                                        uint32_t* done, uint2* __restrict__ ranges, uint32_t* __restrict__ total, uint32_t cap_pairs) {
     __shared__ uint32_t s_part[16][64];
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_carry, s_last;
     const uint32_t b = blockIdx.x;
     const uint32_t t = threadIdx.x & 63u, grp = threadIdx.x >> 6;
     const uint32_t c0 = cstart[b], c1 = cstart[b + 1];
@@ -314,34 +304,14 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restri
         const uint32_t tx = (b % nbx) * BT + (t & 7u), ty = (b / nbx) * BT + (t >> 3);
         if (tx < ntx && ty < nty) tile_count[ty * ntx + tx] = tot;
     }
-}
-
-// tile scan: ranges[t] = (exclusive prefix, count); *total = pair count.  One CTA.
-// Ranges are clipped to the list capacity: when the pair buffers turn out too small the frame is redone by the host, and
-// the kernels of the clipped attempt must stay inside the buffers.
-__global__ void __launch_bounds__(1024) tile_scan_kernel(const uint32_t* __restrict__ tile_count, uint32_t ntiles, uint2* __restrict__ ranges,
-                                                         uint32_t* __restrict__ total, uint32_t cap_pairs) {
-    __shared__ uint32_t s_w[32];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
+    __threadfence();
     __syncthreads();
-    for (uint32_t base = 0; base < ntiles; base += 8192u) {
-        const uint32_t t0 = base + threadIdx.x * 8u;
-        uint32_t c[8], sum = 0;
-#pragma unroll
-        for (uint32_t q = 0; q < 8u; q++) { c[q] = (t0 + q < ntiles) ? tile_count[t0 + q] : 0u; sum += c[q]; }
-        uint32_t tot;
-        uint32_t ex = gs::cta_excl_scan<32>(sum, s_w, &tot) + s_carry;
-#pragma unroll
-        for (uint32_t q = 0; q < 8u; q++) {
-            if (t0 + q < ntiles) { const uint32_t a = min(ex, cap_pairs); ranges[t0 + q] = make_uint2(a, min(c[q], cap_pairs - a)); }
-            ex += c[q];
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) s_carry += tot;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) *total = s_carry;
+    if (threadIdx.x == 0) s_last = (atomicAdd(done, 1u) == gridDim.x - 1u) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) *done = 0u;
+    __threadfence();
+    tile_scan_cta(tile_count, ntx * nty, ranges, total, cap_pairs, s_w, &s_carry);
 }
 
 // fill: every (entry, covered tile) of the chunk is stored at start[tile] + prefix over earlier chunks + rank in the chunk.
@@ -437,23 +407,24 @@ void gs_launch_emit_coarse(const GsProjected& O, const uint32_t* perm, const uin
     emit_coarse_kernel<<<(n + 255) / 256, 256, 0, st>>>(O, perm, offs, n, gs_bin_nbx(ntx), bin_keys, vals, cap);
 }
 
-size_t gs_emit_coarse_scratch_bytes(uint32_t n) { return 8 + ((size_t)n / (256u * EC_SUB) + 2u) * 8; }
+size_t gs_emit_coarse_scratch_bytes(uint32_t n) { const size_t b = (size_t)n / EC_RUN + 2u; return 8 + b * 8 + (b / 32 + 1) * 8; }
 // fused scan + coarse emit + digit histograms; `plan` is the coming sort's (1 or 2 passes), `ghist` its prepared block
 void gs_launch_emit_coarse_scan(const GsProjected& O, const uint32_t* perm, uint32_t n, uint32_t ntx, uint32_t* bin_keys, uint32_t* vals,
                                 uint32_t cap, uint32_t* total, void* scratch, const GsSortPlan& plan, uint32_t* ghist, cudaStream_t st) {
     if (n == 0) { cudaMemsetAsync(total, 0, 4, st); return; }
-    const uint32_t blocks = (n + 256u * EC_SUB - 1u) / (256u * EC_SUB);
-    cudaMemsetAsync(scratch, 0, 8 + (size_t)blocks * 8, st);
+    const uint32_t blocks = (n + EC_RUN - 1u) / EC_RUN;
+    cudaMemsetAsync(scratch, 0, 8 + (size_t)blocks * 8 + ((size_t)blocks / 32 + 1) * 8, st);
+    unsigned long long* status = (unsigned long long*)((char*)scratch + 8);
     EmitDigits dg;
     dg.np = plan.num_passes;
     for (int p = 0; p < 2; p++) { dg.shift[p] = p < plan.num_passes ? plan.shifts[p] : 0; dg.mask[p] = p < plan.num_passes ? (1u << plan.bits[p]) - 1u : 0u; }
     emit_coarse_scan_kernel<<<blocks, 256, 0, st>>>(O, perm, n, gs_bin_nbx(ntx), bin_keys, vals, cap, total, (uint32_t*)scratch,
-                                                    (unsigned long long*)((char*)scratch + 8), ghist, dg);
+                                                    status, status + blocks, ghist, dg);
 }
 
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
-                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, cudaStream_t st) {
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* done, cudaStream_t st) {
     const uint32_t nbx = gs_bin_nbx(ntx), nbins = gs_bin_count(ntx, nty);
     if (nbins == 0) return;
     // The number of chunks lives on the device; the chunk kernels stride over it, so any grid is correct.  The caller
@@ -463,8 +434,7 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
     else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
     bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
-    bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count);
-    tile_scan_kernel<<<1, 1024, 0, st>>>(tile_count, ntx * nty, ranges, total_pairs, cap_pairs);
+    bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count, done, ranges, total_pairs, cap_pairs);
     bin_fill_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
 }
 

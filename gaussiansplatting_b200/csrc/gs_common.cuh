@@ -177,6 +177,36 @@ __device__ __forceinline__ uint32_t cta_excl_scan(uint32_t x, uint32_t* s_w, uin
     return off + inc - x;
 }
 
+// ---- block-sum look-back in two dependent round trips, whatever the tile count.  Every tile (ticket order) publishes its
+// sum in status[tile] and adds it to its group's word (32 tiles per group; the contributor count rides in bits 40+).  A
+// tile's exclusive prefix = the earlier tiles of its own group + the completed earlier groups: it never waits for another
+// tile's PREFIX, only for earlier tiles to have published their own sums.  Called by one full warp; all words start at 0.
+__device__ __forceinline__ uint32_t lookback_excl_warp(uint32_t tile, uint32_t block_sum, unsigned long long* status,
+                                                       unsigned long long* group_sum, uint32_t lane) {
+    if (lane == 0) {
+        const unsigned long long mine = (1ull << 40) | (unsigned long long)block_sum;
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(status + tile), "l"(mine) : "memory");
+        atomicAdd(group_sum + (tile >> 5), mine);
+    }
+    const uint32_t grp = tile >> 5, first = grp << 5;
+    uint32_t v = 0;
+    if (first + lane < tile) {
+        unsigned long long s;
+        do { asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(s) : "l"(status + first + lane) : "memory"); } while ((s >> 40) == 0ull);
+        v = (uint32_t)s;
+    }
+    for (uint32_t g0 = 0; g0 < grp; g0 += 32u) {
+        if (g0 + lane < grp) {
+            unsigned long long s;
+            do { asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(s) : "l"(group_sum + g0 + lane) : "memory"); } while ((s >> 40) != 32ull);
+            v += (uint32_t)s;
+        }
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+    return v;
+}
+
 // relaxed gpu-scope load/store for look-back status words
 __device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
     uint32_t v;

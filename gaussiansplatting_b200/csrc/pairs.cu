@@ -12,22 +12,13 @@ constexpr int SCAN_THREADS = 256;
 #endif
 constexpr int SCAN_IPT = GS_SCAN_IPT;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_IPT;
-constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_INC = 2ull << 32;
 
-__device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_relaxed64(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
 
-// scratch layout: [0] dynamic tile counter (u32, + pad to 8 B), then one u64 status word per tile
+// scratch layout: [0] dynamic tile counter (u32, + pad to 8 B), one u64 status word per tile, one u64 word per 32 tiles
 // out[j] = sum_{j'<j} in[perm ? perm[j'] : j'] ; out[n] = *total = the sum.  in == out (perm == nullptr) is allowed.
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, const uint32_t* __restrict__ perm, uint32_t* out,
                                                             uint32_t n, uint32_t* __restrict__ total,
-                                                            uint32_t* counter, unsigned long long* status) {
+                                                            uint32_t* counter, unsigned long long* status, unsigned long long* group_sum) {
     __shared__ uint32_t s_tile, s_warp[SCAN_THREADS / 32], s_prefix;
     if (threadIdx.x == 0) s_tile = atomicAdd(counter, 1u);
     __syncthreads();
@@ -48,30 +39,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const uint32_t* in, 
 #pragma unroll
     for (int w = 0; w < SCAN_THREADS / 32; w++) { if (w < (int)warp) warp_off += s_warp[w]; block_sum += s_warp[w]; }
     if (warp == 0) {
-        // decoupled look-back by one warp: 32 predecessors per round, the nearest inclusive prefix ends the walk
-        uint32_t excl = 0;
-        const uint32_t lane = gs::lane_id();
-        if (tile == 0) {
-            if (lane == 0) st_relaxed64(&status[0], FLAG_INC | block_sum);
-        } else {
-            if (lane == 0) st_relaxed64(&status[tile], FLAG_AGG | block_sum);
-            int base = (int)tile - 1;
-            while (true) {
-                const int idx = base - (int)lane;
-                unsigned long long s = FLAG_INC;                       // before the first tile: inclusive prefix 0
-                if (idx >= 0) do { s = ld_relaxed64(&status[idx]); } while ((s >> 32) == 0ull);
-                const uint32_t incmask = __ballot_sync(0xFFFFFFFFu, (s & FLAG_INC) != 0ull);
-                const int first = incmask ? (__ffs(incmask) - 1) : 31;
-                uint32_t v = ((int)lane <= first) ? (uint32_t)s : 0u;
-#pragma unroll
-                for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
-                excl += v;
-                if (incmask) break;
-                base -= 32;
-            }
-            if (lane == 0) st_relaxed64(&status[tile], FLAG_INC | (unsigned long long)(excl + block_sum));
-        }
-        if (lane == 0) {
+        const uint32_t excl = gs::lookback_excl_warp(tile, block_sum, status, group_sum, gs::lane_id());
+        if (gs::lane_id() == 0) {
             s_prefix = excl;
             if ((uint64_t)(tile + 1) * SCAN_TILE >= n) { out[n] = excl + block_sum; *total = excl + block_sum; }
         }
@@ -150,16 +119,16 @@ __global__ void __launch_bounds__(256) emit_pairs_kernel(GsProjected O, const ui
 
 size_t gs_scan_scratch_bytes(uint32_t n) {
     size_t tiles = ((size_t)n + SCAN_TILE - 1) / SCAN_TILE + 1;
-    return 8 + tiles * 8;
+    return 8 + tiles * 8 + (tiles / 32 + 1) * 8;
 }
 
 void gs_launch_exclusive_scan(const uint32_t* in, const uint32_t* perm, uint32_t* out, uint32_t n, uint32_t* total,
                               void* scratch, cudaStream_t st) {
     if (n == 0) { cudaMemsetAsync(out, 0, 4, st); cudaMemsetAsync(total, 0, 4, st); return; }
     uint32_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-    cudaMemsetAsync(scratch, 0, 8 + (size_t)tiles * 8, st);
-    scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(in, perm, out, n, total, (uint32_t*)scratch,
-                                                (unsigned long long*)((char*)scratch + 8));
+    cudaMemsetAsync(scratch, 0, 8 + (size_t)tiles * 8 + ((size_t)tiles / 32 + 1) * 8, st);
+    unsigned long long* status = (unsigned long long*)((char*)scratch + 8);
+    scan_kernel<<<tiles, SCAN_THREADS, 0, st>>>(in, perm, out, n, total, (uint32_t*)scratch, status, status + tiles);
 }
 
 void gs_launch_emit_pairs(const GsProjected& O, const uint32_t* offs, uint32_t n, uint32_t ntx, uint64_t* keys, uint32_t* vals,
