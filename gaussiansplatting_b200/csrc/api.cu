@@ -23,6 +23,7 @@ struct gs_ctx {
 };
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
+static int g_tile_order = 1;                        // blend CTAs take the tiles longest list first (tile_order_kernel)
 static int g_emit_fused = 1;                        // binned pipeline: scan + coarse emit + bin histogram as one kernel
 static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
 static void gs_set_sort_mode(int v);
@@ -59,6 +60,7 @@ int gs_tune(const char* name, int value) {
     if (!name) return GS_ERR_ARG;
     if (!strcmp(name, "fwd_ppt")) { gs_tune_fwd_ppt(value); return GS_OK; }
     if (!strcmp(name, "bwd_ppt")) { gs_tune_bwd_ppt(value); return GS_OK; }
+    if (!strcmp(name, "tile_order")) { g_tile_order = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
     if (!strcmp(name, "sort_tiny_tiles")) { gs_tune_sort_tiny(value); return GS_OK; }
     if (!strcmp(name, "sort_hybrid")) { gs_tune_sort_hybrid(value); return GS_OK; }
@@ -555,7 +557,8 @@ static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureB
         cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->tile_count); cudaFree(r->bin_ranges); cudaFree(r->cstart);
         r->cap_tiles = ntx * nty;
         GS_TRY(dalloc(c, &r->ranges, r->cap_tiles));
-        GS_TRY(dalloc(c, &r->proj.tile_flags, r->cap_tiles));
+        r->proj.tile_order = nullptr;
+        GS_TRY(dalloc(c, &r->proj.tile_flags, (size_t)r->cap_tiles * 2));   // flags, then the blend CTAs' tile order
         GS_TRY(dalloc(c, &r->tile_count, (size_t)r->cap_tiles + 1));     // + the bin-scan CTAs' completion ticket (self-resetting)
         GS_CUDA(c, cudaMemsetAsync(r->tile_count + r->cap_tiles, 0, sizeof(uint32_t), c->stream));
         GS_TRY(dalloc(c, &r->bin_ranges, (size_t)r->cap_tiles + 2));      // bins <= tiles
@@ -655,6 +658,7 @@ static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     r->mark(5);
     gs_launch_tile_ranges(r->sorted_keys, (uint32_t)P, tiles, nullptr, r->ranges, st);
     r->mark(6);
+    r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
     gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
     r->mark(7);
     GS_LAUNCH_CHECK(c);
@@ -704,6 +708,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         r->mark(5);
         gs_launch_tile_ranges32(r->sorted_tiles, cap, d_total, tiles, r->ranges, st);
         r->mark(6);
+        r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
         gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
@@ -769,6 +774,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         GS_CUDA(c, cudaMemcpyAsync(c->h_pinned, r->meta, GS_META_COUNT * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->xfer_meta));
         GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
         r->mark(6);
+        r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
         gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);

@@ -66,14 +66,14 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                                                              const float4* __restrict__ rendered, const float4* __restrict__ gt,
                                                              int quantize, const uint32_t* __restrict__ last_idx,
                                                              const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
-                                                             float* __restrict__ acc) {
+                                                             const uint32_t* __restrict__ order, float* __restrict__ acc) {
     constexpr int NT = 256 / PPT, NW = NT / 32, K = (BB + NT - 1) / NT, NP = PPT / 2;
     __shared__ BwdEnt s_e[BB];
     __shared__ float s_acc[NW][BB * 9];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
     __shared__ uint32_t s_mask[NW][BB / 32];           // per warp region: which staged entries can reach it at all
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint2 range = ranges[tile];                                // :410-413
@@ -410,7 +410,7 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
     if (ntx * nty == 0) return;
 #define GS_BWD_LAUNCH(PPT)                                                                                          \
     blend_backward_kernel<PPT><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
-                                                                 last_idx, tfinal, O.tile_flags, acc)
+                                                                 last_idx, tfinal, O.tile_flags, O.tile_order, acc)
     if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4);
     else GS_BWD_LAUNCH(2);
 }

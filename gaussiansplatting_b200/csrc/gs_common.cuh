@@ -246,6 +246,7 @@ struct GsProjected {
     uint32_t* dkey;  // sortable depth bits (tiled_shaders.metal:773-774); 0xFFFFFFFF when cnt == 0
     uint32_t* offs;  // exclusive scan of cnt in emission order (Gaussian order, or depth order in hoisted mode); [n] = total
     uint32_t* tile_flags;  // per TILE: 1 if the forward walked a conic-degenerate entry (backward then redoes pass 1)
+    uint32_t* tile_order;  // per CTA of the blend kernels: the tile it takes (longest lists first), or nullptr = raster order
 };
 
 // Packed gradient buffer: 16 planes of stride `stride` floats:

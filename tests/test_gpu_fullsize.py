@@ -90,3 +90,34 @@ def test_backward_is_additive_over_views_at_full_size(gs, ctx, c2):
         assert np.count_nonzero(both["opacity"]) > n // 20
     finally:
         D.close(); gt.close()
+
+
+def test_blend_tile_order_changes_nothing(gs, ctx, c2):
+    """the blend CTAs take the tiles longest list first (tile_order_kernel, default) or in raster order: image,
+    lastContribIdx and per-tile lists are bit-identical, gradients agree to the atomic-order tolerance"""
+    gs.tune("sort_mode", 0)
+    R, G, img, u, n = c2["R"], c2["G"], c2["img"], c2["u"], c2["n"]
+    gti = gs.Image(ctx, c2["W"], c2["H"])
+    D = gs.Grads(ctx, n)
+    out = []
+    try:
+        for order in (1, 0):
+            gs.tune("tile_order", order)
+            R.forward(G, u, img)
+            image, last = img.download(), R.get(gs.RAST_LAST_IDX)
+            if not out:
+                gti.upload(np.ascontiguousarray(image[::-1]))       # a ground truth that differs from the render
+            R.backward(G, D, u, img, gti)
+            out.append((image, last, R.get(gs.RAST_SORTED_VALUES), D.download(n)))
+    finally:
+        gs.tune("tile_order", 1)
+        D.close(); gti.close()
+    a, b = out
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    assert np.abs(a[3]["position"]).max() > 0
+    for f in ("position", "opacity", "scale", "rotation", "sh"):
+        x, y = a[3][f].astype(np.float64), b[3][f].astype(np.float64)
+        fin = np.isfinite(x) & np.isfinite(y)
+        assert np.array_equal(np.isfinite(x), np.isfinite(y)), f
+        x, y = x[fin], y[fin]
+        assert np.all(np.abs(x - y) <= 1e-3 * np.maximum(np.abs(x), np.abs(y)) + 1e-5 * np.abs(y).max()), f

@@ -30,17 +30,28 @@ def short(name):
 
 
 def launches(path, first):
-    rows = list(csv.DictReader(l for l in open(path) if not l.startswith("==")))
+    raw = list(csv.DictReader(l for l in open(path) if not l.startswith("==")))
+    # one row per launch: a capture with several --metrics has one CSV line per (launch, metric)
+    rows, by_id = [], {}
+    for r in raw:
+        d = by_id.get(r["ID"])
+        if d is None:
+            d = by_id[r["ID"]] = {"Kernel Name": r["Kernel Name"], "Grid Size": r["Grid Size"]}
+            rows.append(d)
+        d[r["Metric Name"]] = float(r["Metric Value"].replace(",", ""))
+    dram = any("dram__bytes_read.sum" in r for r in rows)
     starts = [i for i, r in enumerate(rows) if first in r["Kernel Name"]]
     print(f"# launch list: {path} ({len(rows)} launches; steps start at `{first}`)\n")
     print("ncu per-launch times are cold-cache and serialised: compare SHARES, not absolutes.\n")
     for si, s in enumerate(starts):
         e = starts[si + 1] if si + 1 < len(starts) else len(rows)
-        tot = sum(float(r["Metric Value"]) for r in rows[s:e])
-        print(f"## step {si}: {e - s} launches, {tot / 1e3:.1f} us\n\n| kernel | grid | us | share |\n|---|---|---|---|")
+        tot = sum(r["gpu__time_duration.sum"] for r in rows[s:e])
+        extra = " DRAM read MB | DRAM write MB |" if dram else ""
+        print(f"## step {si}: {e - s} launches, {tot / 1e3:.1f} us\n\n| kernel | grid | us | share |{extra}\n|---|---|---|---|" + ("---|---|" if dram else ""))
         for r in rows[s:e]:
-            v = float(r["Metric Value"])
-            print(f"| {short(r['Kernel Name'])} | {r['Grid Size']} | {v / 1e3:.1f} | {100 * v / tot:.1f}% |")
+            v = r["gpu__time_duration.sum"]
+            x = f" {r['dram__bytes_read.sum'] / 1e6:.1f} | {r['dram__bytes_write.sum'] / 1e6:.1f} |" if dram else ""
+            print(f"| {short(r['Kernel Name'])} | {r['Grid Size']} | {v / 1e3:.1f} | {100 * v / tot:.1f}% |{x}")
         print()
 
 
