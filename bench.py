@@ -351,8 +351,9 @@ def run_ours(args):
     D.set_stat_mode(False)
     # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan + coarse emit + bin histogram
     # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk
-    # counts, bin scan + tile scan (one kernel), fill, blend fwd, blend bwd, per-Gaussian chain (memsets not counted)
-    launches_fb = 10 + passes + (2 if passes > 5 else 0)
+    # counts, bin scan + tile scan (one kernel), fill, tile order, blend fwd, blend bwd, per-Gaussian chain (memsets not
+    # counted); the ncu launch list of a frame is profiles/r1zc_launches_C2.md (+ tile_order_kernel since)
+    launches_fb = 11 + passes + (2 if passes > 5 else 0)
     out["gpu_launches"] = K * launches_fb
 
     if rank == 0:
@@ -393,11 +394,11 @@ def run_ours(args):
                         "frac": a / fp32_peak}
         dom = max((k for k in roofs), key=lambda k: stage[k])
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this workload
-        # (profiles/r1i_blend_counters.txt); None for a workload or kernel that was not captured
-        ncu_traffic = {"blend_bwd": 119.0e6, "blend_fwd": 42.4e6} if args.workload == "C2" else {}
+        # (profiles/r1zc_blend_counters.csv); None for a workload or kernel that was not captured
+        ncu_traffic = {"blend_bwd": 114.4e6, "blend_fwd": 45.9e6} if args.workload == "C2" else {}
         out["roofline"] = dict(roofs[dom], kernel=dom, traffic=ncu_traffic.get(dom), peak_kind=peak_kind,
                                note="algorithmic bytes/flops per SURVEY 8(d); fp32 peak = 2*128*148*sm_max_mhz; traffic = DRAM "
-                                    "bytes per launch from profiles/r1i_blend_counters.txt (ncu), an FP32-issue-bound kernel")
+                                    "bytes per launch from profiles/r1zc_blend_counters.csv (ncu), an FP32-issue-bound kernel")
         out["rooflines"] = roofs
         out["stage_ms"] = stage
         out["evals"] = {"E": E, "C": C, "pairs": P, "sort_passes": passes}

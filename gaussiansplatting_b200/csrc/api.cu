@@ -1249,7 +1249,7 @@ int gs_viewer_render(gs_viewer* v, gs_gaussians* g, const uint32_t* d_order, con
     if (tiles > v->cap_tiles) {
         GS_CUDA(c, cudaStreamSynchronize(st));
         cudaFree(v->ranges); v->ranges = nullptr; v->cap_tiles = 0;
-        GS_TRY(dalloc(c, &v->ranges, tiles));
+        GS_TRY(dalloc(c, &v->ranges, (size_t)tiles + (tiles + 1) / 2));   // ranges, then the draw CTAs' tile order (u32 each)
         v->cap_tiles = tiles;
     }
     v->W = W; v->H = H; v->ntx = ntx; v->nty = nty; v->n = n;
@@ -1276,8 +1276,10 @@ int gs_viewer_render(gs_viewer* v, gs_gaussians* g, const uint32_t* d_order, con
     gs_launch_tile_ranges32(v->sorted_tiles, cap, v->meta, tiles, v->ranges, st);
     const bool count = (flags & GS_VIEW_COUNT_FRAGMENTS) != 0;
     if (count) GS_CUDA(c, cudaMemsetAsync(v->counters, 0, 2 * sizeof(unsigned long long), st));
+    uint32_t* order = g_tile_order ? reinterpret_cast<uint32_t*>(v->ranges + v->cap_tiles) : nullptr;
+    if (order) gs_launch_tile_order(v->ranges, tiles, order, st);
     gs_launch_view_blend(v->rec, v->sorted_vals, v->ranges, W, H, ntx, nty, (flags & GS_VIEW_QUANTIZE_RGBA8) ? 1 : 0, out->px,
-                         count ? v->counters : nullptr, st);
+                         count ? v->counters : nullptr, order, st);
     GS_LAUNCH_CHECK(c);
     GS_TRY(image_after_use(out, st));
     return GS_OK;

@@ -305,6 +305,10 @@ void gs_launch_rebuild_keys64(const uint32_t* sorted_tiles, const uint32_t* sort
     if (n) rebuild_keys64_kernel<<<(n + 255) / 256, 256, 0, st>>>(sorted_tiles, sorted_vals, dkey, n, keys);
 }
 
+void gs_launch_tile_order(const uint2* ranges, uint32_t num_tiles, uint32_t* order, cudaStream_t st) {
+    if (num_tiles) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, num_tiles, order);
+}
+
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st) {
     if (ntx * nty == 0) return;

@@ -115,9 +115,12 @@ void gs_launch_view_splats(const GsParams& P, const float* V, const float* VP, f
 // draw position j is Gaussian order[j], its pairs start at offs[j]; writes are bounded by cap_pairs
 void gs_launch_view_emit(const uint4* bbox, const uint32_t* cnt, const uint32_t* order, const uint32_t* offs, uint32_t n,
                          uint32_t ntx, uint32_t* tiles, uint32_t* vals, uint32_t cap_pairs, cudaStream_t st);
-// counters (may be null): [0] += fragments shaded, [1] += fragments blended
+// order[b] = the tile CTA b of a per-tile blend kernel takes: tiles by descending list length (blend_fwd.cu)
+void gs_launch_tile_order(const uint2* ranges, uint32_t num_tiles, uint32_t* order, cudaStream_t st);
+// counters (may be null): [0] += fragments shaded, [1] += fragments blended; order (may be null): gs_launch_tile_order's
 void gs_launch_view_blend(const float4* rec, const uint32_t* vals, const uint2* ranges, uint32_t W, uint32_t H, uint32_t ntx,
-                          uint32_t nty, int quantize, float4* image, unsigned long long* counters, cudaStream_t st);
+                          uint32_t nty, int quantize, float4* image, unsigned long long* counters, const uint32_t* order,
+                          cudaStream_t st);
 void gs_launch_view_splats_to_wire(const float4* rec, const uint4* bbox, uint32_t n, void* out64, cudaStream_t st);
 
 // logging loss (0.8 L1 + 0.2 D-SSIM, mean over pixels): adds the sum over pixels to *total (zeroed by the caller)

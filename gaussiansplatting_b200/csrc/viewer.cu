@@ -182,10 +182,11 @@ __device__ __forceinline__ float quant8(float v) { return gs::fdiv(rintf(gs::fmu
 template <int QUANT, int COUNT>
 __global__ void __launch_bounds__(256) view_blend_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ vals,
                                                          const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
-                                                         float4* __restrict__ image, unsigned long long* __restrict__ counters) {
+                                                         float4* __restrict__ image, unsigned long long* __restrict__ counters,
+                                                         const uint32_t* __restrict__ order) {
     __shared__ float4 s_rec[256 * 3];
     __shared__ uint32_t s_mask[8][8];
-    const uint32_t tile = blockIdx.x;
+    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tx = tile % ntx, ty = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint32_t lx = (lane & 7u) + (warp & 1u) * 8u, ly = (lane >> 3) + (warp >> 1) * 4u;
@@ -289,14 +290,15 @@ void gs_launch_view_emit(const uint4* bbox, const uint32_t* cnt, const uint32_t*
     view_emit_kernel<<<(n + 255) / 256, 256, 0, st>>>(bbox, cnt, order, offs, n, ntx, tiles, vals, cap_pairs);
 }
 void gs_launch_view_blend(const float4* rec, const uint32_t* vals, const uint2* ranges, uint32_t W, uint32_t H, uint32_t ntx,
-                          uint32_t nty, int quantize, float4* image, unsigned long long* counters, cudaStream_t st) {
+                          uint32_t nty, int quantize, float4* image, unsigned long long* counters, const uint32_t* order,
+                          cudaStream_t st) {
     const uint32_t g = ntx * nty;
     if (counters) {
-        if (quantize) view_blend_kernel<1, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
-        else view_blend_kernel<0, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+        if (quantize) view_blend_kernel<1, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters, order);
+        else view_blend_kernel<0, 1><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters, order);
     } else {
-        if (quantize) view_blend_kernel<1, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
-        else view_blend_kernel<0, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters);
+        if (quantize) view_blend_kernel<1, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters, order);
+        else view_blend_kernel<0, 0><<<g, 256, 0, st>>>(rec, vals, ranges, W, H, ntx, image, counters, order);
     }
 }
 void gs_launch_view_splats_to_wire(const float4* rec, const uint4* bbox, uint32_t n, void* out64, cudaStream_t st) {

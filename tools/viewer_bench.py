@@ -25,12 +25,15 @@ def frame(i):
     V.render(G, S.sorted_indices, view_uniforms(u), img)
 
 
-for i in range(3):
-    frame(i)
-ctx.sync()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record(stream)
-for i in range(reps):
-    frame(i)
-e1.record(stream); e1.synchronize()
-print(f"{wl}: {e0.elapsed_time(e1) / reps:.3f} ms / viewer frame, {V.pair_count} pairs")
+for rep in range(2):
+    for order in (0, 1):                       # draw CTAs in raster order / longest tile list first (default)
+        gs.tune("tile_order", order)
+        for i in range(3):
+            frame(i)
+        ctx.sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(reps):
+            frame(i)
+        e1.record(stream); e1.synchronize()
+        print(f"{wl} tile_order={order}: {e0.elapsed_time(e1) / reps:.3f} ms / viewer frame, {V.pair_count} pairs")
