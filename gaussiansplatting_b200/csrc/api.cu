@@ -64,6 +64,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "sort_mode")) { gs_set_sort_mode(value); return GS_OK; }
     if (!strcmp(name, "sort_tiny_tiles")) { gs_tune_sort_tiny(value); return GS_OK; }
     if (!strcmp(name, "sort_hybrid")) { gs_tune_sort_hybrid(value); return GS_OK; }
+    if (!strcmp(name, "sort_even")) { gs_tune_sort_even(value); return GS_OK; }
     if (!strcmp(name, "emit_fused")) { g_emit_fused = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }

@@ -523,7 +523,26 @@ static inline int ceil_log2_u64(uint64_t n) { int l = 0; while ((1ull << l) < n)
 
 static inline bool rs_small(uint64_t n) { return n <= (uint64_t)RS_SMALL_TILE * 148 * GS_RS_CTAS; }
 static inline bool rs_tiny(uint64_t n) { return g_rs_tiny && n <= (uint64_t)RS_TINY_TILE * 148 * GS_RS_CTAS * 2; }
-static inline uint32_t rs_tile_elems(uint64_t n) { return rs_tiny(n) ? RS_TINY_TILE : rs_small(n) ? RS_SMALL_TILE : RS_BIG_TILE; }
+static int g_rs_even = 1;   // knob: 0 = 3072-pair tiles for every one-wave input
+// Items per thread.  An input whose tiles are all resident at once (one wave) takes as long as the SM that holds the most
+// elements: among the compiled tile sizes take the one with the smallest (CTAs on the fullest SM) x (tile size), e.g.
+// 1 M pairs: 326 tiles of 3072 put three CTAs on 30 SMs (9216 elements), 290 tiles of 3456 put two on each (6912).
+static inline int rs_ipt(uint64_t n) {
+    if (rs_tiny(n)) return 4;
+    if (!rs_small(n)) return GS_RS_BIG_IPT;
+    int best = 8;
+    if (g_rs_even) {
+        uint64_t best_cost = ~0ull;
+        for (int ipt : {8, 9, 10, 12}) {     // measured: 435 tiles of 2304 (three per SM, same product) are slower: 79 against 72 us
+            const uint64_t tiles = (n + (uint64_t)RS_THREADS * ipt - 1) / ((uint64_t)RS_THREADS * ipt);
+            if (tiles > 148ull * GS_RS_CTAS) continue;
+            const uint64_t cost = ((tiles + 147) / 148) * ipt;
+            if (cost < best_cost) { best_cost = cost; best = ipt; }
+        }
+    }
+    return best;
+}
+static inline uint32_t rs_tile_elems(uint64_t n) { return (uint32_t)RS_THREADS * (uint32_t)rs_ipt(n); }
 
 template <typename KeyT>
 int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n,
@@ -535,7 +554,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
         return 0;
     }
     // small inputs: 2048-pair tiles so that every tile is resident at once (one wave) instead of 1.x waves of 4096
-    const bool small = rs_small(n), tiny = rs_tiny(n);
+    const int ipt = rs_ipt(n);
     const uint32_t tile_elems = rs_tile_elems(n);
     const uint32_t tiles = (uint32_t)((n + tile_elems - 1) / tile_elems);
     const size_t status_bytes = (size_t)tiles * 256 * 4;
@@ -572,8 +591,10 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
 #define GS_RS_GO(IPT, B_, PLAN, GATE, SLOT0, DST0) launch_passes<KeyT, IPT, B_>(keys_in, vals_in, kbuf, vbuf, n, d_n, PLAN, pl, tiles, ghist, counters, status, agg2, groups, st, GATE, SLOT0, DST0)
 #define GS_RS_RUN(PLAN, GATE, SLOT0, DST0)                                                                    \
     do {                                                                                                      \
-        if (tiny) { if (ballot) GS_RS_GO(4, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(4, false, PLAN, GATE, SLOT0, DST0); }          \
-        else if (small) { if (ballot) GS_RS_GO(8, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(8, false, PLAN, GATE, SLOT0, DST0); }    \
+        if (ipt == 4) { if (ballot) GS_RS_GO(4, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(4, false, PLAN, GATE, SLOT0, DST0); }      \
+        else if (ipt == 8) { if (ballot) GS_RS_GO(8, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(8, false, PLAN, GATE, SLOT0, DST0); } \
+        else if (ipt == 9) { if (ballot) GS_RS_GO(9, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(9, false, PLAN, GATE, SLOT0, DST0); } \
+        else if (ipt == 10) { if (ballot) GS_RS_GO(10, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(10, false, PLAN, GATE, SLOT0, DST0); } \
         else { if (ballot) GS_RS_GO(GS_RS_BIG_IPT, true, PLAN, GATE, SLOT0, DST0); else GS_RS_GO(GS_RS_BIG_IPT, false, PLAN, GATE, SLOT0, DST0); } \
     } while (0)
     if (!hybrid) {
@@ -605,6 +626,7 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
 
 void gs_tune_sort_tiny(int v) { g_rs_tiny = v ? 1 : 0; }
 void gs_tune_sort_hybrid(int v) { g_rs_hybrid = v ? 1 : 0; }
+void gs_tune_sort_even(int v) { g_rs_even = v ? 1 : 0; }
 const uint32_t* gs_sort_flags(const void* scratch) { return (const uint32_t*)((const char*)scratch + RS_HIST_BYTES) + RS_FLAG_HYBRID; }
 const uint32_t* gs_sort_pass_histogram(const void* scratch, int pass) { return (const uint32_t*)scratch + (size_t)pass * 256; }
 

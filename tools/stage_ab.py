@@ -1,5 +1,5 @@
 """A/B of one gs_tune knob on the fwd+bwd frame (config C2 by default): per-stage device times with the knob at 0 and 1,
-alternating so clock drift shows up in both.  usage: python tools/stage_ab.py KNOB [workload] [frames]"""
+alternating so clock drift shows up in both.  usage: python tools/stage_ab.py KNOB [workload] [frames] [values, e.g. 0,1,2]"""
 import os
 import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -9,6 +9,7 @@ from gaussiansplatting_b200 import capi as gs, synth
 knob = sys.argv[1]
 wl = sys.argv[2] if len(sys.argv) > 2 else "C2"
 frames = int(sys.argv[3]) if len(sys.argv) > 3 else 20
+values = [int(x) for x in sys.argv[4].split(",")] if len(sys.argv) > 4 else [0, 1]
 n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
 ctx = gs.Context(0)
 stream = torch.cuda.ExternalStream(ctx.stream, device=0)
@@ -25,7 +26,7 @@ def frame(i):
     R.backward(G, D, cams[i % 64], img, gti)
 
 for rep in range(3):
-    for v in (0, 1):
+    for v in values:
         gs.tune(knob, v)
         for i in range(3):
             frame(i)
