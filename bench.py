@@ -351,9 +351,9 @@ def run_ours(args):
     D.set_stat_mode(False)
     # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan + coarse emit + bin histogram
     # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk
-    # counts, bin scan + tile scan (one kernel), fill, tile order, blend fwd, blend bwd, per-Gaussian chain (memsets not
-    # counted); the ncu launch list of a frame is profiles/r1zc_launches_C2.md (+ tile_order_kernel since)
-    launches_fb = 11 + passes + (2 if passes > 5 else 0)
+    # counts, bin scan + tile scan (one kernel), fill (its CTA 0 writes the blend tile order), blend fwd, blend bwd,
+    # per-Gaussian chain (memsets not counted); the ncu launch list of a frame is profiles/r1zf_launches_C2.md
+    launches_fb = 10 + passes + (2 if passes > 5 else 0)
     out["gpu_launches"] = K * launches_fb
 
     if rank == 0:

@@ -660,7 +660,7 @@ static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     gs_launch_tile_ranges(r->sorted_keys, (uint32_t)P, tiles, nullptr, r->ranges, st);
     r->mark(6);
     r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, st);
     r->mark(7);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
@@ -710,7 +710,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         gs_launch_tile_ranges32(r->sorted_tiles, cap, d_total, tiles, r->ranges, st);
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         if (attempt == 0) GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));   // the GPU is still busy with the kernels above
@@ -763,6 +763,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         uint32_t* lists = r->vbuf[bplan.num_passes ? (res ^ 1) : 0];
         r->mark(5);
         const uint32_t* bin_hist = bplan.num_passes == 1 ? gs_sort_pass_histogram(r->sort_scratch, 0) : nullptr;
+        r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;   // written by bin_fill's CTA 0
         if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
         gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
                              d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u,
@@ -776,7 +777,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));                   // the GPU is still busy with the kernels above

@@ -330,11 +330,15 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
     __shared__ uint32_t s_rect[CH], s_gid[CH];
     __shared__ gs::CullRec s_cull[CH];
     __shared__ uint32_t s_w[NWARP];
+    // with a tile order asked for, CTA 0 (first wave) computes it from the finished ranges while the others fill
+    const bool with_order = O.tile_order != nullptr;
+    if (with_order && blockIdx.x == 0) { gs::tile_order_cta<CH>(ranges, ntx * nty, O.tile_order); return; }
+    const uint32_t bid = with_order ? blockIdx.x - 1u : blockIdx.x, nblk = with_order ? gridDim.x - 1u : gridDim.x;
     s_off[CH + threadIdx.x] = 0xFFFFFFFFu;
     __syncthreads();
     const uint32_t total = cstart[nbins];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-    for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
+    for (uint32_t chunk = bid; chunk < total; chunk += nblk) {
         const ChunkCtx cc = locate_chunk(chunk, chunk_bin, cstart, bin_ranges);
         const uint32_t bx = cc.bin % nbx, by = cc.bin / nbx;
         unsigned long long mask = 0ull;
@@ -435,7 +439,7 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
     bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count, done, ranges, total_pairs, cap_pairs);
-    bin_fill_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+    bin_fill_kernel<<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
 }
 
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,

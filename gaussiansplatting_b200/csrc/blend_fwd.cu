@@ -84,38 +84,9 @@ constexpr int FB = 256;   // raw list entries staged per round
 // The walk is branch-free and keeps the thread's pixels two to a packed fp32 pair (FFMA2): a pixel that does not take an
 // entry runs the same instructions with alpha forced to 0, which leaves C and T bit-unchanged (x*0 + C, T*(1-0)); a
 // finished pixel has NaN coordinates, so every test on it fails.  Per half the operation sequence is the pinned one.
-// Launch order of the blend CTAs: tiles by descending list length (256 buckets of the frame's longest list, counting
-// sort in one CTA), so the long tiles start first and the last wave is made of short ones.  Results do not depend on
-// the order a tile is taken in (gradient atomics are unordered either way).
+// launch order of the blend CTAs (gs::tile_order_cta); the binned pipeline computes it inside bin_fill instead
 __global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restrict__ ranges, uint32_t nt, uint32_t* __restrict__ order) {
-    __shared__ uint32_t s_hist[256], s_ws[8], s_max;
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    if (tid < 256) s_hist[tid] = 0;
-    if (tid == 0) s_max = 0;
-    __syncthreads();
-    uint32_t m = 0;
-    for (uint32_t i = tid; i < nt; i += 1024) m = max(m, ranges[i].y);
-    m = __reduce_max_sync(0xFFFFFFFFu, m);
-    if (lane == 0 && m) atomicMax(&s_max, m);
-    __syncthreads();
-    const float sc = 255.0f / (float)max(s_max, 1u);
-    for (uint32_t i = tid; i < nt; i += 1024) atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u);
-    __syncthreads();
-    uint32_t v = 0, inc = 0;
-    if (tid < 256) {
-        v = s_hist[tid]; inc = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= (uint32_t)d) inc += t; }
-        if (lane == 31) s_ws[warp] = inc;
-    }
-    __syncthreads();
-    if (tid < 256) {
-        uint32_t pre = 0;
-        for (uint32_t w = 0; w < warp; w++) pre += s_ws[w];
-        s_hist[tid] = pre + inc - v;
-    }
-    __syncthreads();
-    for (uint32_t i = tid; i < nt; i += 1024) order[atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u)] = i;
+    gs::tile_order_cta<1024>(ranges, nt, order);
 }
 
 struct FwdEnt { float4 r0, r1; float b; uint32_t idx; uint32_t pad0, pad1; };   // 48 B: one base address, three LDS
@@ -310,12 +281,13 @@ void gs_launch_tile_order(const uint2* ranges, uint32_t num_tiles, uint32_t* ord
 }
 
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
-                             uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st) {
+                             uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, int order_ready,
+                             cudaStream_t st) {
     if (ntx * nty == 0) return;
 #define GS_FWD_LAUNCH(PPT)                                                                                            \
     blend_forward_kernel<PPT, false><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
                                                                        tfinal, O.tile_flags, O.tile_order, nullptr)
-    if (O.tile_order) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, ntx * nty, O.tile_order);
+    if (O.tile_order && !order_ready) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, ntx * nty, O.tile_order);
     if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4);
     else GS_FWD_LAUNCH(2);
 }

@@ -217,6 +217,42 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// Launch order of the per-tile blend kernels: order[b] = the tile CTA b takes, tiles by descending list length (256
+// buckets of the frame's longest list, counting sort by ONE CTA of NT threads), so the long tiles start first and the
+// last wave is made of short ones.  Results do not depend on the order (gradient atomics are unordered either way).
+template <int NT>
+__device__ __forceinline__ void tile_order_cta(const uint2* __restrict__ ranges, uint32_t nt, uint32_t* __restrict__ order) {
+    static_assert(NT >= 256 && NT % 32 == 0, "one thread per bucket");
+    __shared__ uint32_t s_hist[256], s_ws[8], s_max;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    if (tid < 256) s_hist[tid] = 0;
+    if (tid == 0) s_max = 0;
+    __syncthreads();
+    uint32_t m = 0;
+    for (uint32_t i = tid; i < nt; i += NT) m = max(m, ranges[i].y);
+    m = __reduce_max_sync(0xFFFFFFFFu, m);
+    if (lane == 0 && m) atomicMax(&s_max, m);
+    __syncthreads();
+    const float sc = 255.0f / (float)max(s_max, 1u);
+    for (uint32_t i = tid; i < nt; i += NT) atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u);
+    __syncthreads();
+    uint32_t v = 0, inc = 0;
+    if (tid < 256) {
+        v = s_hist[tid]; inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= (uint32_t)d) inc += t; }
+        if (lane == 31) s_ws[warp] = inc;
+    }
+    __syncthreads();
+    if (tid < 256) {
+        uint32_t pre = 0;
+        for (uint32_t w = 0; w < warp; w++) pre += s_ws[w];
+        s_hist[tid] = pre + inc - v;
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < nt; i += NT) order[atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u)] = i;
+}
+
 }  // namespace gs
 
 // ---------------------------------------------------------------------------------------------

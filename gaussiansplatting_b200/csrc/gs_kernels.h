@@ -69,7 +69,7 @@ void gs_launch_rebuild_keys64(const uint32_t* sorted_tiles, const uint32_t* sort
 
 // K6: forward blend.  image: W*H float4 RGBA; last_idx/tfinal: W*H.
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
-                             uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, cudaStream_t st);
+                             uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, int order_ready, cudaStream_t st);
 
 void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                            uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st);
