@@ -72,7 +72,7 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
     __shared__ float s_acc[NW][BB * 9];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
-    __shared__ uint32_t s_mask[NW][BB / 32];           // per warp region: which staged entries can reach it at all
+    __shared__ unsigned char s_reach[BB];              // per staged entry: which warp regions it can reach at all (bit w)
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
@@ -164,26 +164,22 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
         for (int q = 0; q < K; q++) {
             if (v[q] >> 31) continue;
             const uint32_t g = v[q];
-            s_e[slot].r0 = rec[3 * (size_t)g]; s_e[slot].r1 = rec[3 * (size_t)g + 1];
+            const float4 r0 = rec[3 * (size_t)g], r1 = rec[3 * (size_t)g + 1];
+            s_e[slot].r0 = r0; s_e[slot].r1 = r1;
             s_e[slot].b = rec[3 * (size_t)g + 2].x; s_e[slot].idx = lo + threadIdx.x * K + q; s_e[slot].gid = g;
-            slot++;
-        }
-        for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
-        __syncthreads();
-        // ---- per-region footprint masks: lane tests one staged entry against every warp's pixel rectangle
-        for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
-            const uint32_t sl = s0 + lane;
-            const bool valid = sl < total;
-            const gs::CullRec cr = gs::cull_rec(s_e[valid ? sl : 0u].r0, s_e[valid ? sl : 0u].r1);
+            // footprint against every warp's pixel rectangle, by the thread that staged the entry: bit w = it can reach warp w
+            const gs::CullRec cr = gs::cull_rec(r0, r1);
+            uint32_t reach = 0;
 #pragma unroll
             for (int w = 0; w < NW; w++) {
                 uint32_t rx, ry; float ex, ey;
                 gs::warp_region<PPT>((uint32_t)w, rx, ry, ex, ey);
-                const bool keep = valid && !gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey);
-                const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
-                if (lane == 0) s_mask[w][s0 >> 5] = m;
+                if (!gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey)) reach |= 1u << w;
             }
+            s_reach[slot] = (unsigned char)reach;
+            slot++;
         }
+        for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
         __syncthreads();
         if (wmax > lo) {
             // staged list indices ascend: entries at or beyond this warp's extent are of no interest to it
@@ -194,8 +190,8 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                 kend = a;
             }
             for (int wd = ((int)kend - 1) >> 5; wd >= 0; wd--) {      // :473 back to front, reachable entries only
-                uint32_t mk = s_mask[warp][wd];
-                if ((uint32_t)wd == (kend >> 5)) mk &= (1u << (kend & 31u)) - 1u;
+                const uint32_t sl = (uint32_t)wd * 32u + lane;
+                uint32_t mk = __ballot_sync(0xFFFFFFFFu, sl < kend && ((s_reach[sl] >> warp) & 1u));
                 const uint32_t wbase = ebase + (uint32_t)wd * 32u * (uint32_t)sizeof(BwdEnt);
                 while (mk) {
                     const int kb = 31 - __clz(mk);

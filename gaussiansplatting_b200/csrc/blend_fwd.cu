@@ -100,7 +100,7 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
     constexpr int NT = 256 / PPT, NW = NT / 32, K = FB / NT, NP = PPT / 2;
     __shared__ FwdEnt s_e[FB];
     __shared__ uint32_t s_w[NW];
-    __shared__ uint32_t s_mask[NW][FB / 32];          // per warp region: which staged entries can reach it at all
+    __shared__ unsigned char s_reach[FB];             // per staged entry: which warp regions it can reach at all (bit w)
     __shared__ uint32_t s_degen;
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
@@ -154,28 +154,24 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
             float4 r1 = rec[3 * (size_t)g + 1];
             if (__float_as_uint(r2.w) & 1u) { r1.y = 0.f; s_degen = 1u; }   // :350-351 conic-magnitude skip (forward only)
             s_e[slot].r0 = r0; s_e[slot].r1 = r1; s_e[slot].b = r2.x; s_e[slot].idx = range.x + base + threadIdx.x * K + q;
-            slot++;
-        }
-        __syncthreads();
-        // ---- per-region footprint masks: lane tests one staged entry against every warp's pixel rectangle
-        for (uint32_t s0 = warp * 32u; s0 < total; s0 += NT) {
-            const uint32_t sl = s0 + lane;
-            const bool valid = sl < total;
-            const gs::CullRec cr = gs::cull_rec(s_e[valid ? sl : 0u].r0, s_e[valid ? sl : 0u].r1);
+            // footprint against every warp's pixel rectangle, by the thread that staged the entry: bit w = it can reach warp w
+            const gs::CullRec cr = gs::cull_rec(r0, r1);
+            uint32_t reach = 0;
 #pragma unroll
             for (int w = 0; w < NW; w++) {
                 uint32_t rx, ry; float ex, ey;
                 gs::warp_region<PPT>((uint32_t)w, rx, ry, ex, ey);
-                const bool keep = valid && !gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey);
-                const uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
-                if (lane == 0) s_mask[w][s0 >> 5] = m;
+                if (!gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey)) reach |= 1u << w;
             }
+            s_reach[slot] = (unsigned char)reach;
+            slot++;
         }
         __syncthreads();
         if (wlive) {
             const uint32_t nwords = (total + 31u) >> 5;
             for (uint32_t wd = 0; wd < nwords && wlive; wd++) {      // :334, entries that can reach this warp's pixels only
-                uint32_t m = s_mask[warp][wd];
+                const uint32_t sl = wd * 32u + lane;
+                uint32_t m = __ballot_sync(0xFFFFFFFFu, sl < total && ((s_reach[sl] >> warp) & 1u));
                 const uint32_t wbase = ebase + wd * 32u * (uint32_t)sizeof(FwdEnt);
                 while (m) {
                     const uint32_t kb = (uint32_t)__ffs(m) - 1u;
