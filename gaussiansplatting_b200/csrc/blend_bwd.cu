@@ -23,7 +23,10 @@ namespace {
 #ifndef GS_BWD_PPT
 #define GS_BWD_PPT 2
 #endif
-constexpr int BB = 128;   // raw list entries staged per round
+#ifndef GS_BWD_BB
+#define GS_BWD_BB 128
+#endif
+constexpr int BB = GS_BWD_BB;   // raw list entries staged per round
 
 // sum of v[0..7] over the warp; afterwards lane L holds (in v[0]) the total of value ((L>>2)&7 bit-reversed order below)
 __device__ __forceinline__ float warp_reduce8_transposed(float v[8], uint32_t lane) {

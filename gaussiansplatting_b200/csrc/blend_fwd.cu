@@ -75,7 +75,10 @@ __global__ void rebuild_keys64_kernel(const uint32_t* __restrict__ tiles, const 
 #ifndef GS_FWD_PPT
 #define GS_FWD_PPT 2
 #endif
-constexpr int FB = 256;   // raw list entries staged per round
+#ifndef GS_FWD_FB
+#define GS_FWD_FB 128
+#endif
+constexpr int FB = GS_FWD_FB;   // raw list entries staged per round
 
 // K6.  PPT (2 or 4) pixels per thread, NT = 256/PPT threads per tile.  Each round a CTA reads FB consecutive entries of
 // the tile's sorted list, drops those flagged GS_CULL_BIT (pairs.cu: the splat cannot reach any pixel of this tile),
