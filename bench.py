@@ -394,11 +394,11 @@ def run_ours(args):
                         "frac": a / fp32_peak}
         dom = max((k for k in roofs), key=lambda k: stage[k])
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this workload
-        # (profiles/r1zc_blend_counters.csv); None for a workload or kernel that was not captured
-        ncu_traffic = {"blend_bwd": 114.4e6, "blend_fwd": 45.9e6} if args.workload == "C2" else {}
+        # (profiles/r1zf_blend_counters.csv); None for a workload or kernel that was not captured
+        ncu_traffic = {"blend_bwd": 114.7e6, "blend_fwd": 41.3e6} if args.workload == "C2" else {}
         out["roofline"] = dict(roofs[dom], kernel=dom, traffic=ncu_traffic.get(dom), peak_kind=peak_kind,
                                note="algorithmic bytes/flops per SURVEY 8(d); fp32 peak = 2*128*148*sm_max_mhz; traffic = DRAM "
-                                    "bytes per launch from profiles/r1zc_blend_counters.csv (ncu), an FP32-issue-bound kernel")
+                                    "bytes per launch from profiles/r1zf_blend_counters.csv (ncu), an FP32-issue-bound kernel")
         out["rooflines"] = roofs
         out["stage_ms"] = stage
         out["evals"] = {"E": E, "C": C, "pairs": P, "sort_passes": passes}
