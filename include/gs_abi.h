@@ -103,7 +103,15 @@ int gs_ctx_sync(gs_ctx*);                               /* waitUntilCompleted */
 const char* gs_last_error(gs_ctx*);                     /* ctx may be NULL: last creation error */
 void* gs_ctx_stream(gs_ctx*);
 int gs_version(void);
-/* process-wide tuning knobs for benchmarking kernel variants: "fwd_ppt" / "bwd_ppt" = pixels per thread (1, 2, 4) */
+/* process-wide knobs for benchmarking kernel variants; no knob changes a result, only how it is computed:
+ *   "fwd_ppt" / "bwd_ppt"  pixels per thread of the blend kernels (2, 4)
+ *   "sort_mode"            pair pipeline: 0 two-level binning (default), 1 literal 64-bit pair sort, 2 hoisted radix
+ *   "emit_fused"           1 (default) scan + coarse emit + bin histogram as one kernel
+ *   "tile_order"           1 (default) blend / viewer-draw CTAs take the tiles longest list first, 0 raster order
+ *   "sort_even"            1 (default) one-wave radix passes pick the tile size that evens out the CTAs per SM
+ *   "sort_hybrid"          1 (default) hybrid plan for full 64-bit sorts, 0 always the 8-pass LSD plan
+ *   "sort_tiny_tiles", "tile_sort_ballot", "sort_api_ballot"   ranking / tile-size experiments (off / as shipped)
+ * unknown names return GS_ERR_ARG */
 int gs_tune(const char* name, int value);
 
 /* raw device memory (MTL::Buffer with no typed role: sort inputs, positions) */
