@@ -234,7 +234,14 @@ __device__ __forceinline__ void tile_order_cta(const uint2* __restrict__ ranges,
     if (lane == 0 && m) atomicMax(&s_max, m);
     __syncthreads();
     const float sc = 255.0f / (float)max(s_max, 1u);
-    for (uint32_t i = tid; i < nt; i += NT) atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u);
+    for (uint32_t i = tid; i < nt; i += 4 * NT) {                 // four loads in flight: one CTA walks every tile
+        uint32_t c[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) c[u] = (i + u * NT < nt) ? ranges[i + u * NT].y : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (i + u * NT < nt) atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)c[u] * sc))], 1u);
+    }
     __syncthreads();
     uint32_t v = 0, inc = 0;
     if (tid < 256) {
@@ -250,7 +257,14 @@ __device__ __forceinline__ void tile_order_cta(const uint2* __restrict__ ranges,
         s_hist[tid] = pre + inc - v;
     }
     __syncthreads();
-    for (uint32_t i = tid; i < nt; i += NT) order[atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)ranges[i].y * sc))], 1u)] = i;
+    for (uint32_t i = tid; i < nt; i += 4 * NT) {
+        uint32_t c[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) c[u] = (i + u * NT < nt) ? ranges[i + u * NT].y : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (i + u * NT < nt) order[atomicAdd(&s_hist[255u - min(255u, (uint32_t)((float)c[u] * sc))], 1u)] = i + u * NT;
+    }
 }
 
 }  // namespace gs

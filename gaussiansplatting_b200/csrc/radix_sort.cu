@@ -48,11 +48,18 @@ __global__ void __launch_bounds__(256) radix_hist_kernel(const KeyT* __restrict_
     for (int i = threadIdx.x; i < 8 * 256; i += blockDim.x) (&sh[0][0])[i] = 0;
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const KeyT k = keys[i];
+    // four keys in flight per thread: on a one-wave input the kernel lasts as long as a thread's chain of dependent loads
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += 4 * stride) {
+        KeyT k[4];
 #pragma unroll
-        for (int p = 0; p < 8; p++)
-            if (p < np) atomicAdd(&sh[p][(uint32_t)(k >> pl.shift[p]) & pl.mask[p]], 1u);   // pl starts at pass p0 (static indices: no local copy)
+        for (int u = 0; u < 4; u++) k[u] = (i + u * stride < n) ? keys[i + u * stride] : (KeyT)0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (i + u * stride >= n) break;
+#pragma unroll
+            for (int p = 0; p < 8; p++)
+                if (p < np) atomicAdd(&sh[p][(uint32_t)(k[u] >> pl.shift[p]) & pl.mask[p]], 1u);   // pl starts at pass p0 (static indices: no local copy)
+        }
     }
     __syncthreads();
     for (int p = 0; p < np; p++)
