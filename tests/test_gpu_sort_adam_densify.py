@@ -325,3 +325,21 @@ def test_sort64_hybrid_full_size(gs, ctx, logn):
         assert np.array_equal(v, vals[order]) and not S.last_plan_hybrid
     finally:
         S.close()
+
+
+@pytest.mark.parametrize("n", [440_000, 700_000, 1_000_000, 1 << 20, 1_200_000, 1_360_000])
+def test_sort64_one_wave_tile_sizes_agree(gs, ctx, n):
+    """one-wave inputs pick their tile size per n (rs_ipt: 8 / 9 / 10 / 12 items x 384 threads, radix_sort.cu); every choice,
+    and the fixed 3072-pair tiles ("sort_even" 0), must give numpy's stable sort on keys with many ties"""
+    keys = rand_u64(n, n) & np.uint64(0x000000FF00FF0FFF)
+    vals = np.arange(n, dtype=np.uint32)
+    order = np.argsort(keys, kind="stable")
+    S = gs.Sort64(ctx, n)
+    try:
+        for even in (1, 0):
+            gs.tune("sort_even", even)
+            k, v = S.sort_host(keys, vals)
+            assert np.array_equal(v, vals[order]) and np.array_equal(k, keys[order]), even
+    finally:
+        gs.tune("sort_even", 1)
+        S.close()
