@@ -428,6 +428,65 @@ void orc_forward(const OrcProjected* proj, const uint32_t* sortedIdx, const OrcT
 }
 
 /* ------------------------------------------------------------------------------------------
+ * A8 (literal precision)  tiledForward as the Metal source types it — tiled_shaders.metal:325-370: colour, T, power, G
+ * and alpha are `half`.  Every half-typed operation is rounded to nearest-even _Float16 (g++'s native type); the
+ * float expression of the power (:354-356) is evaluated in fp32 in the source's order and then converted (:354
+ * `half(...)`); exp(half) is taken as fp32 libm expf rounded once to half (Apple's fast-math exp is not reproducible
+ * off-device; SURVEY note H).  Thresholds are the half literals: 0.0001h, -4.5h, 0.99h, half(1.0/255.0).
+ * This is NOT the graded mode (the graded mode is fp32, orc_forward): it exists to measure how far the reference's
+ * precision choice moves the image and lastContribIdx from the fp32 statement (reported in BASELINE.md).
+ * ---------------------------------------------------------------------------------------- */
+void orc_forward_half(const OrcProjected* proj, const uint32_t* sortedIdx, const OrcTileRange* ranges,
+                      const OrcUniforms* u, float* image, uint32_t* lastIdxOut, int threads) {
+    typedef _Float16 half;
+    const uint32_t W = (uint32_t)u->screenSize[0], H = (uint32_t)u->screenSize[1];
+    threads = set_threads(threads);
+    const half T_EPS_H = (half)0.0001f, PMIN_H = (half)-4.5f, AMAX_H = (half)0.99f, AMIN_H = (half)(1.0 / 255.0), ONE_H = (half)1.0f;
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 1)
+    for (int64_t tile = 0; tile < (int64_t)(u->numTilesX * u->numTilesY); tile++) {
+        uint32_t tX = (uint32_t)tile % u->numTilesX, tY = (uint32_t)tile / u->numTilesX;
+        const OrcTileRange range = ranges[tile];
+        for (uint32_t py = tY * TILE; py < std::min(H, (tY + 1) * TILE); py++)
+        for (uint32_t px = tX * TILE; px < std::min(W, (tX + 1) * TILE); px++) {
+            half col[3] = {(half)0.0f, (half)0.0f, (half)0.0f};    /* :325 */
+            half T = ONE_H;                                          /* :326 */
+            float pixx = (float)px + 0.5f, pixy = (float)py + 0.5f;
+            uint32_t lastIdx = 0; bool hasContrib = false;
+            for (uint32_t i = 0; i < range.count && T > T_EPS_H; i++) {   /* :334 */
+                uint32_t sortIdx = range.start + i;
+                uint32_t gIdx = sortedIdx[sortIdx];
+                if (gIdx >= u->numGaussians) continue;
+                const OrcProjected& p = proj[gIdx];
+                if (p.radius <= 0) continue;
+                float dx = pixx - p.screenPos[0], dy = pixy - p.screenPos[1];
+                float conicMag = (fabsf(p.conic[0]) + fabsf(p.conic[1])) + fabsf(p.conic[2]);
+                if (conicMag < 0.0001f) continue;
+                /* :354-356, fp32 in source order, then one conversion to half */
+                float pf = -0.5f * ((p.conic[0] * dx * dx + 2.0f * p.conic[1] * dx * dy) + p.conic[2] * dy * dy);
+                half power = (half)pf;
+                if (power > (half)0.0f || power < PMIN_H) continue;   /* :359 */
+                if (power != power) continue;
+                half G = (half)expf((float)power);                   /* :362 */
+                half alpha = (half)((half)p.opacity * G);            /* :363 */
+                if (alpha > AMAX_H) alpha = AMAX_H;
+                if (alpha < AMIN_H) continue;                        /* :366 */
+                for (int c = 0; c < 3; c++) {                        /* :369 color += half3(p.color) * alpha * T */
+                    half t1 = (half)((half)p.color[c] * alpha);
+                    half t2 = (half)(t1 * T);
+                    col[c] = (half)(col[c] + t2);
+                }
+                T = (half)(T * (half)(ONE_H - alpha));               /* :370 */
+                lastIdx = sortIdx; hasContrib = true;
+            }
+            size_t pix = (size_t)py * W + px;
+            for (int c = 0; c < 3; c++) image[pix * 4 + c] = (float)(half)(col[c] + (half)(ONE_H * T));   /* :377-378 */
+            image[pix * 4 + 3] = 1.0f;
+            lastIdxOut[pix] = hasContrib ? lastIdx : 0xFFFFFFFFu;
+        }
+    }
+}
+
+/* ------------------------------------------------------------------------------------------
  * A10  tiledBackward — tiled_shaders.metal:388-738.
  * rendered / gt: W*H*4 float RGBA.  quantize: SURVEY note G (RGBA8 render target): when set, the
  * rendered colour is rounded to 8 bits before sign(diff).
@@ -438,15 +497,21 @@ void orc_forward(const OrcProjected* proj, const uint32_t* sortedIdx, const OrcT
 namespace {
 struct GradAcc { double v[16]; };   /* pos3, opacity, scale3, rot4, shdc3, viewspace2 */
 }
-void orc_backward(const OrcGaussian* gaussians, const OrcProjected* proj, const uint32_t* sortedIdx,
+/* absOut / termCount (both optional, test diagnostics): per component the sum of |term| over the (pixel, Gaussian) terms the
+ * reference adds with float atomics in arbitrary order (:699-736), and the number of such terms per Gaussian.  A float
+ * accumulation of k terms in any order stays within k * 2^-24 * sum|term| of the exact sum: that is the per-component
+ * "atomic ordering" band the gradient tolerance of the GPU tests is tied to. */
+static void backward_impl(const OrcGaussian* gaussians, const OrcProjected* proj, const uint32_t* sortedIdx,
                   const OrcTileRange* ranges, const OrcUniforms* u, const uint32_t* lastContribIdx,
                   const float* rendered, const float* gt, int quantize,
-                  OrcGradients* grads, float* tfinalOut, int threads) {
+                  OrcGradients* grads, float* tfinalOut, int threads, OrcGradients* absOut, uint32_t* termCount) {
     const uint32_t W = (uint32_t)u->screenSize[0], H = (uint32_t)u->screenSize[1];
     const uint32_t n = u->numGaussians;
     threads = set_threads(threads);
     if (threads > 32) threads = 32;
-    std::vector<std::vector<GradAcc>> accs(threads);
+    std::vector<std::vector<GradAcc>> accs(threads), aaccs(threads);
+    std::vector<std::vector<uint32_t>> cnts(threads);
+    const bool wantAbs = absOut != nullptr || termCount != nullptr;
     const float fx = u->focalLength[0], fy = u->focalLength[1];
     M3 viewRot;                                           /* :558-562 */
     for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) viewRot.c[c][r] = u->viewMatrix[c * 4 + r];
@@ -461,6 +526,9 @@ void orc_backward(const OrcGaussian* gaussians, const OrcProjected* proj, const 
 #endif
         std::vector<GradAcc>& acc = accs[tid];
         acc.assign(n, GradAcc{});
+        std::vector<GradAcc>& aacc = aaccs[tid];
+        std::vector<uint32_t>& cnt = cnts[tid];
+        if (wantAbs) { aacc.assign(n, GradAcc{}); cnt.assign(n, 0u); }
 #pragma omp for schedule(dynamic, 1)
         for (int64_t tile = 0; tile < (int64_t)(u->numTilesX * u->numTilesY); tile++) {
             uint32_t tX = (uint32_t)tile % u->numTilesX, tY = (uint32_t)tile / u->numTilesX;
@@ -598,6 +666,13 @@ void orc_backward(const OrcGaussian* gaussians, const OrcProjected* proj, const 
                     A.v[7] += dq[0]; A.v[8] += dq[1]; A.v[9] += dq[2]; A.v[10] += dq[3];
                     A.v[11] += dL_dColor[0] * SH_C0; A.v[12] += dL_dColor[1] * SH_C0; A.v[13] += dL_dColor[2] * SH_C0;
                     A.v[14] += dLdS[0]; A.v[15] += dLdS[1];
+                    if (wantAbs) {
+                        GradAcc& B = aacc[gIdx];
+                        const float t16[16] = {dLdW[0], dLdW[1], dLdW[2], dL_dRawOpacity, dLogS[0], dLogS[1], dLogS[2], dq[0], dq[1], dq[2],
+                                               dq[3], dL_dColor[0] * SH_C0, dL_dColor[1] * SH_C0, dL_dColor[2] * SH_C0, dLdS[0], dLdS[1]};
+                        for (int k = 0; k < 16; k++) B.v[k] += fabs((double)t16[k]);
+                        cnt[gIdx]++;
+                    }
                 }
             }
         }
@@ -614,7 +689,34 @@ void orc_backward(const OrcGaussian* gaussians, const OrcProjected* proj, const 
         for (int k = 0; k < 4; k++) g.rotation[k] = (float)s[7 + k];
         g.sh[0] = (float)s[11]; g.sh[4] = (float)s[12]; g.sh[8] = (float)s[13];
         g.viewspace_grad_x = (float)s[14]; g.viewspace_grad_y = (float)s[15];
+        if (wantAbs) {
+            double a[16] = {0}; uint32_t c = 0;
+            for (int t = 0; t < threads; t++) if (!aaccs[t].empty()) { for (int k = 0; k < 16; k++) a[k] += aaccs[t][i].v[k]; c += cnts[t][i]; }
+            if (termCount) termCount[i] = c;
+            if (absOut) {
+                OrcGradients& o = absOut[i];
+                memset(&o, 0, sizeof(o));
+                o.position_x = (float)a[0]; o.position_y = (float)a[1]; o.position_z = (float)a[2];
+                o.opacity = (float)a[3];
+                o.scale_x = (float)a[4]; o.scale_y = (float)a[5]; o.scale_z = (float)a[6];
+                for (int k = 0; k < 4; k++) o.rotation[k] = (float)a[7 + k];
+                o.sh[0] = (float)a[11]; o.sh[4] = (float)a[12]; o.sh[8] = (float)a[13];
+                o.viewspace_grad_x = (float)a[14]; o.viewspace_grad_y = (float)a[15];
+            }
+        }
     }
+}
+void orc_backward(const OrcGaussian* gaussians, const OrcProjected* proj, const uint32_t* sortedIdx,
+                  const OrcTileRange* ranges, const OrcUniforms* u, const uint32_t* lastContribIdx,
+                  const float* rendered, const float* gt, int quantize,
+                  OrcGradients* grads, float* tfinalOut, int threads) {
+    backward_impl(gaussians, proj, sortedIdx, ranges, u, lastContribIdx, rendered, gt, quantize, grads, tfinalOut, threads, nullptr, nullptr);
+}
+void orc_backward_ex(const OrcGaussian* gaussians, const OrcProjected* proj, const uint32_t* sortedIdx,
+                     const OrcTileRange* ranges, const OrcUniforms* u, const uint32_t* lastContribIdx,
+                     const float* rendered, const float* gt, int quantize,
+                     OrcGradients* grads, float* tfinalOut, int threads, OrcGradients* absOut, uint32_t* termCount) {
+    backward_impl(gaussians, proj, sortedIdx, ranges, u, lastContribIdx, rendered, gt, quantize, grads, tfinalOut, threads, absOut, termCount);
 }
 
 /* ------------------------------------------------------------------------------------------

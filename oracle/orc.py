@@ -140,7 +140,10 @@ def forward(proj, sorted_vals, ranges, u, threads=1):
     return img, last, (int(stats[0]), int(stats[1]))
 
 
-def backward(g, proj, sorted_vals, ranges, u, last, rendered, gt, quantize=False, threads=1, want_tfinal=False):
+def backward(g, proj, sorted_vals, ranges, u, last, rendered, gt, quantize=False, threads=1, want_tfinal=False, want_abs=False):
+    """tiledBackward.  want_abs: also return (sum over the (pixel, Gaussian) terms of |term| per component, as a GRADIENTS
+    array, and the number of terms per Gaussian) -- the per-component band a float-atomic accumulation in arbitrary order
+    can move in, which the GPU gradient tolerance is tied to (oracle/parity.py)"""
     n = len(g)
     grads = np.zeros(n, GRADIENTS)
     W, H = int(u["screenSize"][0][0]), int(u["screenSize"][0][1])
@@ -148,9 +151,24 @@ def backward(g, proj, sorted_vals, ranges, u, last, rendered, gt, quantize=False
     sv = np.ascontiguousarray(sorted_vals, np.uint32)
     r = np.ascontiguousarray(rendered, np.float32)
     t = np.ascontiguousarray(gt, np.float32)
+    if want_abs:
+        ab, cnt = np.zeros(n, GRADIENTS), np.zeros(n, np.uint32)
+        lib().orc_backward_ex(_p(g), _p(proj), _p(sv), _p(ranges), _p(u), _p(last), _p(r), _p(t),
+                              C.c_int(int(quantize)), _p(grads), _p(tf), C.c_int(threads), _p(ab), _p(cnt))
+        return (grads, tf, ab, cnt) if want_tfinal else (grads, ab, cnt)
     lib().orc_backward(_p(g), _p(proj), _p(sv), _p(ranges), _p(u), _p(last), _p(r), _p(t),
                        C.c_int(int(quantize)), _p(grads), _p(tf), C.c_int(threads))
     return (grads, tf) if want_tfinal else grads
+
+
+def forward_half(proj, sorted_vals, ranges, u, threads=1):
+    """tiledForward with the Metal source's `half` typing emulated in _Float16 (SURVEY note H): (image, lastContribIdx)"""
+    W, H = int(u["screenSize"][0][0]), int(u["screenSize"][0][1])
+    img = np.zeros((H, W, 4), np.float32)
+    last = np.zeros((H, W), np.uint32)
+    sv = np.ascontiguousarray(sorted_vals, np.uint32)
+    lib().orc_forward_half(_p(proj), _p(sv), _p(ranges), _p(u), _p(img), _p(last), C.c_int(threads))
+    return img, last
 
 
 class AdamState:

@@ -32,8 +32,8 @@ def make_case(n, W, H, s0, seed, view, nviews, dens_iter):
     u = synth.make_camera(view, nviews, W, H, n)
     r = orc.render(g, u, threads=1)
     gt = orc.render(gt_g, u, threads=1)["image"]
-    grads, tf = orc.backward(g, r["proj"], r["svals"], r["ranges"], u, r["last"], r["image"], gt, threads=1,
-                             want_tfinal=True)
+    grads, tf, gabs, gterms = orc.backward(g, r["proj"], r["svals"], r["ranges"], u, r["last"], r["image"], gt, threads=1,
+                                           want_tfinal=True, want_abs=True)
     st = orc.AdamState(n)
     g1 = g.copy()
     orc.adam_step(g1, grads, st, LRS)
@@ -51,6 +51,7 @@ def make_case(n, W, H, s0, seed, view, nviews, dens_iter):
     return dict(gaussians=g, gt_gaussians=gt_g, uniforms=u, proj=r["proj"], keys=r["keys"], vals=r["vals"],
                 skeys=r["skeys"], svals=r["svals"], ranges=r["ranges"], image=r["image"], last=r["last"],
                 evals=np.array([r["E"], r["C"]], np.uint64), gt=gt, grads=grads, tfinal=tf,
+                grads_abs=gabs, grads_terms=gterms,      # per-component sum|term| and term count: the gradient tolerance band (oracle/parity.py)
                 adam_gaussians=g1, dens_in=g1d, dens_iter=np.uint32(dens_iter), adam_m=np.concatenate(st.m), adam_v=np.concatenate(st.v),
                 dens_accum=accum, dens_counts=counts, dens_accum_in=accum_d, dens_out=dens, dens_markers=markers,
                 dens_stats=dstats)

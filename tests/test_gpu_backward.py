@@ -1,40 +1,34 @@
 """GPU parity of the backward path (K7 + K8) through the C ABI against the CPU oracle.
 
-Bar (north_star): gradients within 1e-3 relative (atomic order differs).  The comparison is per component against
-the oracle's double-accumulated value: |a-b| <= 1e-3 * max(|a|,|b|) + atol, where atol = 1e-5 * (largest |value| of
-that parameter group) absorbs components that are the tiny remainder of large cancelling terms (their float
-accumulation noise is relative to the terms, not to the remainder).
+Bar (north_star): gradients within 1e-3 relative, "since atomic ordering differs".  Per component, against the oracle's
+double-accumulated value b:   |a-b| <= 1e-3 * max(|a|,|b|) + k * 2^-23 * sum|term|   where k and sum|term| are the
+component's OWN number of accumulated (pixel, Gaussian) terms and the sum of their magnitudes, both produced by the
+oracle (orc.backward(want_abs=True)): the band a float-atomic accumulation in arbitrary order (the reference,
+tiled_shaders.metal:699-736) can move in.  There is no group-wide floor.  oracle/parity.py holds the rule and reports, per
+parameter group, the worst PURE relative error and the fraction of components that need the band.
 """
 import numpy as np
 import pytest
 from gaussiansplatting_b200 import synth
+from oracle import parity
 
 pytestmark = pytest.mark.gpu
 
-GROUPS = ["position", "opacity", "scale", "rotation", "sh", "viewspace"]
+GROUPS = list(parity.GROUPS)
 
 
-def compare_grads(got, ref, rtol=1e-3, atol_rel=1e-5):
+def compare_grads(got, ref, absref, count):
     """components the oracle itself overflows on (inf/NaN: giant splats, denom^2 > FLT_MAX) must be non-finite on
     the GPU too; every finite component is held to the tolerance"""
-    worst = {}
-    for f in GROUPS:
-        a, b = got[f].astype(np.float64), ref[f].astype(np.float64)
-        fin = np.isfinite(b)
-        assert not np.isfinite(a[~fin]).any() or f == "viewspace", (f, "oracle non-finite but GPU finite")
-        a, b = a[fin], b[fin]
-        assert np.isfinite(a).all(), (f, "GPU non-finite where the oracle is finite")
-        scale = max(np.abs(b).max(), 1e-30) if b.size else 1.0
-        err = np.abs(a - b) - (rtol * np.maximum(np.abs(a), np.abs(b)) + atol_rel * scale)
-        worst[f] = float(err.max()) if err.size else 0.0
-        assert worst[f] <= 0, (f, worst[f], float(scale))
-    return worst
+    rep = parity.assert_grads(got, ref, absref, count)
+    print({f: (r["worst_pure_rel"], r["frac_over_rtol_pure"], r["frac_need_band"]) for f, r in rep.items()})
+    return rep
 
 
 def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False):
     ref = orc.render(g, u)
     gt = orc.render(gt_g, u)["image"]
-    ref_gr = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, quantize=quantize)
+    ref_gr = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, quantize=quantize, want_abs=True)
     G = gs.Gaussians(ctx, len(g)); G.upload(g)
     R = gs.Rasterizer(ctx, len(g))
     img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
@@ -58,9 +52,11 @@ def test_backward_parity(gs, ctx, orc, n, W, H, s0, seed):
     g = synth.make_scene(n, seed, s0)
     gt_g = synth.make_scene(n, seed ^ 0xA5A5, s0)
     u = synth.make_camera(1, 8, W, H, n)
-    got, ref = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
     assert np.abs(ref["opacity"]).max() > 0
-    compare_grads(got, ref)
+    rep = compare_grads(got, ref, ab, cnt)
+    # almost every component is inside the PURE 1e-3 relative bar; the band is for the cancelling remainder
+    assert all(r["frac_need_band"] < 0.02 for r in rep.values()), rep
     # SH-rest gradients are never written (tiled_shaders.metal:699-704)
     for k in (1, 2, 3, 5, 6, 7, 9, 10, 11):
         assert np.all(got["sh"][:, k] == 0)
@@ -72,8 +68,8 @@ def test_backward_quantized_and_saturated(gs, ctx, orc):
     g = synth.make_scene(n, 31, 0.03); g["opacity"] += 2.0
     gt_g = synth.make_scene(n, 32, 0.03)
     u = synth.make_camera(5, 8, W, H, n)
-    got, ref = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=True)
-    compare_grads(got, ref)
+    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=True)
+    compare_grads(got, ref, ab, cnt)
 
 
 def test_backward_degenerate_conic_tiles(gs, ctx, orc):
@@ -89,9 +85,9 @@ def test_backward_degenerate_conic_tiles(gs, ctx, orc):
     p = ref["proj"]
     mag = np.abs(p["conic"]).sum(1)
     assert ((mag < 1e-4) & (p["radius"] > 0)).sum() > 0, "fixture must contain conic-degenerate visible splats"
-    got, refg = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (refg, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
     assert np.isfinite(refg["scale"]).all()
-    compare_grads(got, refg)
+    compare_grads(got, refg, ab, cnt)
 
 
 def test_backward_nonfinite_pathology(gs, ctx, orc):
@@ -103,7 +99,7 @@ def test_backward_nonfinite_pathology(gs, ctx, orc):
     g["scale"][:150] = np.log(3.0)
     gt_g = synth.make_scene(n, 42, 0.02)
     u = synth.make_camera(2, 8, W, H, n)
-    got, refg = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (refg, _, _) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
     bad_ref = ~(np.isfinite(refg["position"][:, 0]) & np.isfinite(refg["opacity"]) & np.isfinite(refg["sh"][:, 0]))
     bad_got = ~(np.isfinite(got["position"][:, 0]) & np.isfinite(got["opacity"]) & np.isfinite(got["sh"][:, 0]))
     assert bad_ref.sum() > 100
@@ -119,26 +115,27 @@ def test_backward_accumulate_two_views(gs, ctx, orc):
     R = gs.Rasterizer(ctx, n)
     img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
     D = gs.Grads(ctx, n); D.set_stat_mode(True)
-    total = None
+    total = tabs = tcnt = None
     accum, count = np.zeros(n, np.float32), np.zeros(n, np.uint32)
     try:
         for v in range(2):
             u = synth.make_camera(v, 2, W, H, n)
             ref = orc.render(g, u)
             gt = orc.render(gt_g, u)["image"]
-            rg = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt)
+            rg, ab, cn = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, want_abs=True)
             orc.accumulate_gradients(rg, accum, count)
-            total = rg.copy() if total is None else total
-            if v:
+            if v == 0:
+                total, tabs, tcnt = rg.copy(), ab.copy(), cn.copy()
+            else:
                 for f in GROUPS:
                     total[f] = total[f] + rg[f]
+                    tabs[f] = tabs[f] + ab[f]
+                tcnt = tcnt + cn
             gti.upload(gt)
             R.forward(G, u, img)
             R.backward(G, D, u, img, gti, gs.GS_BWD_ACCUMULATE if v else 0)
         got = D.download(n)
-        for f in GROUPS[:-1]:
-            a, b = got[f].astype(np.float64), total[f].astype(np.float64)
-            assert np.all(np.abs(a - b) <= 1e-3 * np.maximum(np.abs(a), np.abs(b)) + 1e-5 * np.abs(b).max()), f
+        parity.assert_grads(got, total, tabs, tcnt, groups=GROUPS[:-1])
         # columns 14/15 = sum of per-view clamped norms, number of views counted
         assert np.array_equal(got["viewspace"][:, 1].astype(np.uint32), count)
         assert np.allclose(got["viewspace"][:, 0], accum, rtol=1e-3, atol=1e-6)

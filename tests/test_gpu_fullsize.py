@@ -1,16 +1,69 @@
-"""Full-size (BASELINE config 2: 1 M Gaussians, 1920x1080) checks through size-independent properties — the oracle needs
-seconds per frame at this size, so it is not run here:
+"""Full-size checks (BASELINE configs 2, 4, 5).
+
+(1) ORACLE PARITY AT THE MEASURED SIZES (test_oracle_parity_at_full_size): the CPU oracle runs the same frame on all host
+cores (about a second at C2, a few seconds at C4) and the CUDA path must give its sorted keys, per-tile lists, tile ranges
+and lastContribIdx bit for bit, its image within 1e-4, and (C2, C5 scene) its gradients within the 1e-3 relative bar of
+oracle/parity.py — at 8,160 / 32,400 tiles and 7 M / 48 M pairs, where the two-level binning, the tile-order CTA, the one-wave
+tile-size picker and the ticketed look-back take their large-input branches.
+
+(2) Size-independent properties:
   * the binned pipeline (default), the hoisted sort (depth passes on N Gaussians, tile passes on P pairs) and the full
     64-bit pair sort must give the SAME
     sorted keys, per-tile lists, tile ranges, lastContribIdx and image, bit for bit;
   * sortedness, permutation, range contiguity / coverage (the reference's own run-time checks, tiled_rasterizer.mm:577-636);
   * idempotence of forward; linearity of the backward accumulation over views; culled-pair marking never changes results.
 """
+import os
 import numpy as np
 import pytest
 from gaussiansplatting_b200 import synth
+from oracle import parity
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("wl,view,backward", [("C2", 3, True), ("C5", 1, True), ("C4", 7, False)])
+def test_oracle_parity_at_full_size(gs, ctx, orc, wl, view, backward):
+    """tiled_shaders.metal:102-794 + sort.metal:553-589 through the oracle against the CUDA path at BASELINE sizes"""
+    gs.tune("sort_mode", 0)
+    n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
+    s0, seed, orbit = synth.CONFIG_S0[wl], synth.CONFIG_SEED[wl], synth.CONFIG_ORBIT[wl]
+    th = len(os.sched_getaffinity(0))
+    g = synth.make_scene(n, seed, s0)
+    u = synth.make_camera(view, 64 if wl != "C5" else 16, W, H, n, orbit)
+    G = gs.Gaussians(ctx, n)
+    R = gs.Rasterizer(ctx, n)
+    img, gti = gs.Image(ctx, W, H), gs.Image(ctx, W, H)
+    D = gs.Grads(ctx, n) if backward else None
+    try:
+        gt = None
+        if backward:   # ground truth = another scene seed through this library (an input)
+            G.upload(synth.make_scene(n, seed ^ 0xA5A5, s0))
+            R.forward(G, u, gti)
+            gt = gti.download()
+        G.upload(g)
+        ref = orc.render(g, u, th)
+        R.forward(G, u, img)
+        got = ref_gr = ab = cnt = None
+        if backward:
+            ref_gr, ab, cnt = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, threads=th, want_abs=True)
+            R.backward(G, D, u, img, gti)
+            got = D.download(n)
+        p = parity.frame_parity(gs, R, img.download(), ref, got, ref_gr, ab, cnt, what=wl)
+        print({k: v for k, v in p.items() if k != "grad_groups"})
+        if backward:
+            print({f: (r["worst_pure_rel"], r["frac_over_rtol_pure"], r["frac_need_band"], r["n_fail"]) for f, r in p["grad_groups"].items()})
+        assert p["pairs"] > (5_000_000 if wl != "C5" else 1_000_000), "the fixture must be large"
+        assert p["keys_equal"] and p["lists_equal"] and p["ranges_equal"] and p["last_equal"], p
+        assert p["image_max_abs"] <= 1e-4
+        if backward:
+            assert p["grad_n_fail"] == 0, p["grad_groups"]
+            assert p["grad_frac_need_band"] < 0.02
+        assert R.count_evals() == (ref["E"], ref["C"])
+    finally:
+        for o in (D, gti, img, R, G):
+            if o is not None:
+                o.close()
 
 
 @pytest.fixture(scope="module", params=["C2", "C4"])

@@ -42,7 +42,7 @@ def test_cuda_reproduces_golden(gs, ctx, path):
         R.forward(G, u, img)
         R.backward(G, D, u, img, gti)
         got = D.download(n)
-        compare_grads(got, d["grads"])
+        compare_grads(got, d["grads"], d["grads_abs"], d["grads_terms"])
         # Adam on the ORACLE's gradients (so the comparison is exact, not 1e-3)
         D.upload(d["grads"])
         A.step(G, D, LRS)
