@@ -45,6 +45,7 @@ inline M3 m3_mul(const M3& A, const M3& B) {    /* (A*B)[col][row] = sum_k A[k][
             R.c[col][row] = (A.c[0][row] * B.c[col][0] + A.c[1][row] * B.c[col][1]) + A.c[2][row] * B.c[col][2];
     return R;
 }
+inline M3 m3_abs(const M3& A) { M3 R; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) R.c[i][j] = fabsf(A.c[i][j]); return R; }
 inline M3 m3_T(const M3& A) { M3 R; for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) R.c[i][j] = A.c[j][i]; return R; }
 inline void m3_mulv(const M3& A, const float v[3], float out[3]) { /* sum_c A[c]*v[c] */
     for (int r = 0; r < 3; r++) out[r] = (A.c[0][r] * v[0] + A.c[1][r] * v[1]) + A.c[2][r] * v[2];
@@ -497,10 +498,12 @@ void orc_forward_half(const OrcProjected* proj, const uint32_t* sortedIdx, const
 namespace {
 struct GradAcc { double v[16]; };   /* pos3, opacity, scale3, rot4, shdc3, viewspace2 */
 }
-/* absOut / termCount (both optional, test diagnostics): per component the sum of |term| over the (pixel, Gaussian) terms the
- * reference adds with float atomics in arbitrary order (:699-736), and the number of such terms per Gaussian.  A float
- * accumulation of k terms in any order stays within k * 2^-24 * sum|term| of the exact sum: that is the per-component
- * "atomic ordering" band the gradient tolerance of the GPU tests is tied to. */
+/* absOut / termCount (both optional, test diagnostics): per component the sum over the (pixel, Gaussian) terms the reference
+ * adds with float atomics in arbitrary order (:699-736) of the term's MAGNITUDE CHAIN (the chain evaluated on magnitudes with
+ * all-plus sums; equal to |term| where the term is a plain product, larger where the chain cancels internally), and the
+ * number of such terms per Gaussian.  A float accumulation of k terms in any order stays within k * 2^-24 * sum|term| of the
+ * exact sum, and each fp32-evaluated term carries a rounding error proportional to its magnitude chain: k * 2^-23 * this sum
+ * is the per-component band the gradient tolerance of the GPU tests is tied to (oracle/parity.py). */
 static void backward_impl(const OrcGaussian* gaussians, const OrcProjected* proj, const uint32_t* sortedIdx,
                   const OrcTileRange* ranges, const OrcUniforms* u, const uint32_t* lastContribIdx,
                   const float* rendered, const float* gt, int quantize,
@@ -667,9 +670,47 @@ static void backward_impl(const OrcGaussian* gaussians, const OrcProjected* proj
                     A.v[11] += dL_dColor[0] * SH_C0; A.v[12] += dL_dColor[1] * SH_C0; A.v[13] += dL_dColor[2] * SH_C0;
                     A.v[14] += dLdS[0]; A.v[15] += dLdS[1];
                     if (wantAbs) {
+                        /* magnitude chain: the SAME chain with every operand replaced by its magnitude and every sum taken
+                         * with all-plus signs, i.e. the quantity any fp32 evaluation of this term (the reference's included) has
+                         * its rounding error proportional to.  a_* >= |*| component-wise. */
                         GradAcc& B = aacc[gIdx];
-                        const float t16[16] = {dLdW[0], dLdW[1], dLdW[2], dL_dRawOpacity, dLogS[0], dLogS[1], dLogS[2], dq[0], dq[1], dq[2],
-                                               dq[3], dL_dColor[0] * SH_C0, dL_dColor[1] * SH_C0, dL_dColor[2] * SH_C0, dLdS[0], dLdS[1]};
+                        const float aG = fabsf(dL_dG);
+                        float aS[2] = { aG * (fabsf(gdx * p.conic[0]) + fabsf(gdy * p.conic[1])), aG * (fabsf(gdy * p.conic[2]) + fabsf(gdx * p.conic[1])) };
+                        float aV[3] = { aS[0] * fabsf(fx / z), aS[1] * fabsf(fy / z),
+                                        aS[0] * fabsf(fx * txtz / z) + aS[1] * fabsf(fy * tytz / z) };
+                        M3 aWt = m3_abs(viewRotT);
+                        float aW[3]; m3_mulv(aWt, aV, aW);
+                        float aC[3] = { fabsf(dLdConic[0]), fabsf(dLdConic[1]), fabsf(dLdConic[2]) };
+                        float adn = fabsf(denom) + fabsf(cov_a * cov_c);
+                        float aCov[3];
+                        aCov[0] = denom2inv * (cov_c * cov_c * aC[0] + 2.0f * fabsf(cov_b * cov_c) * aC[1] + adn * aC[2]);
+                        aCov[2] = denom2inv * (cov_a * cov_a * aC[2] + 2.0f * fabsf(cov_a * cov_b) * aC[1] + adn * aC[0]);
+                        aCov[1] = denom2inv * 2.0f * (fabsf(cov_b * cov_c) * aC[0] + (fabsf(denom) + 2.0f * cov_b * cov_b) * aC[1] + fabsf(cov_a * cov_b) * aC[2]);
+                        M3 aT = m3_mul(m3_abs(J), m3_abs(viewRot));
+                        M3 aCov2 = {{{aCov[0], aCov[1], 0}, {aCov[1], aCov[2], 0}, {0, 0, 0}}};
+                        M3 aCov3 = m3_mul(m3_mul(m3_T(aT), aCov2), aT);
+                        M3 aR = m3_abs(R);
+                        M3 aM = m3_mul(aR, S);
+                        M3 a2 = aCov3;
+                        for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) a2.c[c][r] = 2.0f * aCov3.c[c][r];
+                        M3 adM = m3_mul(a2, aM);
+                        M3 aRtdM = m3_mul(m3_T(aR), adM);
+                        float aLogS[3];
+                        for (int k = 0; k < 3; k++) aLogS[k] = aRtdM.c[k][k] * sc[k];
+                        M3 adR;
+                        for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) adR.c[c][r] = adM.c[c][r] * sc[c];
+                        M3 aD = m3_T(adR);
+                        const float ar = fabsf(rq), ax = fabsf(xq), ay = fabsf(yq), az = fabsf(zq);
+                        float adq[4];
+                        adq[0] = 2.0f * (az * (aD.c[0][1] + aD.c[1][0]) + ay * (aD.c[2][0] + aD.c[0][2]) + ax * (aD.c[1][2] + aD.c[2][1]));
+                        adq[1] = 2.0f * (ay * (aD.c[1][0] + aD.c[0][1]) + az * (aD.c[2][0] + aD.c[0][2]) + ar * (aD.c[1][2] + aD.c[2][1])
+                                         + 2.0f * ax * (aD.c[2][2] + aD.c[1][1]));
+                        adq[2] = 2.0f * (ax * (aD.c[1][0] + aD.c[0][1]) + ar * (aD.c[2][0] + aD.c[0][2]) + az * (aD.c[1][2] + aD.c[2][1])
+                                         + 2.0f * ay * (aD.c[2][2] + aD.c[0][0]));
+                        adq[3] = 2.0f * (ar * (aD.c[0][1] + aD.c[1][0]) + ax * (aD.c[2][0] + aD.c[0][2]) + ay * (aD.c[1][2] + aD.c[2][1])
+                                         + 2.0f * az * (aD.c[1][1] + aD.c[0][0]));
+                        const float t16[16] = {aW[0], aW[1], aW[2], dL_dRawOpacity, aLogS[0], aLogS[1], aLogS[2], adq[0], adq[1], adq[2],
+                                               adq[3], dL_dColor[0] * SH_C0, dL_dColor[1] * SH_C0, dL_dColor[2] * SH_C0, aS[0], aS[1]};
                         for (int k = 0; k < 16; k++) B.v[k] += fabs((double)t16[k]);
                         cnt[gIdx]++;
                     }
@@ -826,6 +867,11 @@ void orc_accumulate_gradients(const OrcGradients* grads, uint32_t n, float* accu
  * out must hold maxGaussians entries.  markers (optional, n) receives the final markers.
  * stats[3] = pruned, cloned, split.  Returns the new count.
  * ---------------------------------------------------------------------------------------- */
+/* Test hook (tests/test_oracle_ref.py only): draw the split direction from libc rand() in index order, literally as
+ * density_control.mm:440-442 does, instead of the counter-based generator (SURVEY note L).  With srand() called alike on
+ * both sides this makes orc_densify_apply comparable bit for bit with the reference's own object code (oracle/_ref). */
+static int g_split_rng_libc = 0;
+void orc_set_split_rng_libc(int on) { g_split_rng_libc = on; }
 static inline uint32_t split_rand_u32(uint32_t seed, uint32_t iteration, uint32_t parent, uint32_t comp) {
     uint64_t z = (((uint64_t)seed << 32) | iteration) + 0x9E3779B97F4A7C15ull * ((uint64_t)parent * 3 + comp + 1);
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -898,6 +944,7 @@ uint32_t orc_densify_apply(const OrcGaussian* in, uint32_t n, const float* accum
             for (int k = 0; k < 3; k++) sc[k] = orc_expf(orc_clamp(g.scale[k], -MAX_SCALE_LOG, MAX_SCALE_LOG));   /* :429-433 */
             float r[3];
             for (uint32_t k = 0; k < 3; k++) {            /* :440-442 with the counter-based generator */
+                if (g_split_rng_libc) { r[k] = ((float)rand() / RAND_MAX - 0.5f) * 2.0f; continue; }
                 uint32_t h = split_rand_u32(seed, iteration, i, k);
                 r[k] = ((float)(h >> 8) * (1.0f / 16777216.0f) - 0.5f) * 2.0f;
             }

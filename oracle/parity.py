@@ -7,8 +7,12 @@ Gradient bar (BASELINE.json north_star: "gradients must match to 1e-3 relative, 
 a = this library's component, b = the oracle's (accumulated in double), and the second summand is the component's own
 accumulation band: the reference adds k per-(pixel, Gaussian) terms with relaxed float atomics in arbitrary order
 (tiled_shaders.metal:699-736); any such order stays within k * 2^-24 * sum|term| of the exact sum, and two different
-orders within twice that.  k and sum|term| come from the oracle itself (orc.backward(want_abs=True)).  A component with
-no cancellation has sum|term| = |b| and k * 2^-23 <= 1e-3 for k < 8388, so the band only matters where terms cancel.
+orders within twice that.  k and sum|term| come from the oracle itself (orc.backward(want_abs=True)); "|term|" is the
+term's magnitude chain (gs_oracle.cpp: the same chain on magnitudes with all-plus sums), which equals |term| for the
+plain products (opacity, colour) and exceeds it where the chain itself cancels (conic -> cov2D -> cov3D -> scale /
+quaternion: median 20-50 x), because an fp32 evaluation of such a term -- the reference's own included -- is only
+accurate relative to that magnitude.  A component without cancellation has sum|term| = |b| and k * 2^-23 <= 1e-3 for
+k < 8388, so the band only matters where terms cancel.  There is no group-wide floor.
 grad_report() also states, per parameter group, the worst PURE relative error |a-b| / max(|a|,|b|), the fraction of
 components above 1e-3 pure relative, and the fraction that pass only thanks to the band.
 """
