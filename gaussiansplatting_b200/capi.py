@@ -171,6 +171,13 @@ def loss(ctx, rendered, ground_truth, lambda_dssim=0.2, quantize=False):
     return float(out.value)
 
 
+def loss_noalloc(ctx, rendered, ground_truth, d_out, lambda_dssim=0.2, quantize=False):
+    """gs_loss_compute_noalloc: the same loss with static scratch and no allocation; enqueues only, the mean loss is written to
+    the caller's DEVICE float at d_out (no counterpart in the reference; see include/gs_abi.h)"""
+    ctx.check(lib().gs_loss_compute_noalloc(ctx.h, rendered.h, ground_truth.h, C.c_float(lambda_dssim), C.c_int(1 if quantize else 0),
+                                            C.c_void_p(d_out)))
+
+
 class Image:
     def __init__(self, ctx, width, height):
         self.ctx, self.w, self.hgt = ctx, width, height

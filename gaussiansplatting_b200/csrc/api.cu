@@ -463,6 +463,25 @@ int gs_loss_compute(gs_ctx* c, gs_image* rendered, gs_image* gt, float lambda_ds
     return GS_OK;
 }
 
+// The same loss without any allocation (no counterpart in the reference; added for
+// callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).  Enqueues two
+// kernels on the context's stream and returns; the mean loss lands in *d_loss_out, ONE float of caller-owned DEVICE memory.
+// Scratch: the static device array of csrc/loss.cu (GS_LOSS_NOALLOC_MAX_TILES tiles of 16x16 pixels).
+int gs_loss_compute_noalloc(gs_ctx* c, gs_image* rendered, gs_image* gt, float lambda_dssim, int flags, float* d_loss_out) {
+    GS_SETDEV(c);
+    GS_ARG(c, rendered && gt && d_loss_out, "null argument");
+    GS_ARG(c, rendered->w == gt->w && rendered->h == gt->h, "image sizes differ");
+    GS_TRY(image_before_read(rendered, c->stream));
+    GS_TRY(image_before_read(gt, c->stream));
+    const char* msg = nullptr;
+    const int rc = gs_launch_loss_noalloc(c->device, rendered->px, gt->px, rendered->w, rendered->h, lambda_dssim,
+                                          (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, d_loss_out, c->stream, &msg);
+    if (rc != GS_OK) { c->err = msg ? msg : "gs_loss_compute_noalloc failed"; return rc; }
+    GS_TRY(image_after_use(rendered, c->stream));
+    GS_TRY(image_after_use(gt, c->stream));
+    return GS_OK;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------------

@@ -127,6 +127,10 @@ void gs_launch_view_splats_to_wire(const float4* rec, const uint4* bbox, uint32_
 // logging loss (0.8 L1 + 0.2 D-SSIM, mean over pixels): adds the sum over pixels to *total (zeroed by the caller)
 void gs_launch_loss(const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize, double* total,
                     cudaStream_t st);
+// allocation-free variant: per-tile partial sums in a static device array of GS_LOSS_NOALLOC_MAX_TILES doubles (loss.cu)
+#define GS_LOSS_NOALLOC_MAX_TILES 32768
+int gs_launch_loss_noalloc(int device, const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize,
+                           float* d_loss_out, cudaStream_t st, const char** err);
 
 // layout conversion between the reference's AoS wire structs and the device SoA
 void gs_launch_params_from_aos(const void* aos112, uint32_t n, GsParams P, cudaStream_t st);

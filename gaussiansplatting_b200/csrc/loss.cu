@@ -14,6 +14,9 @@ namespace {
 
 constexpr int LR = 5, LW = 11, LT = 16, LS = LT + 2 * LR;   // window radius / size, tile, staged side
 
+// PARTIAL = false: the tile's sum goes to one double atomic on *total (gs_loss_compute).  PARTIAL = true: it is stored in
+// total[tile] instead (gs_loss_compute_noalloc below: per-tile partial sums in static scratch, summed in a fixed order).
+template <bool PARTIAL>
 __global__ void __launch_bounds__(LT * LT) loss_kernel(const float4* __restrict__ rendered, const float4* __restrict__ gt,
                                                        uint32_t W, uint32_t H, float lambda, int quantize, double* __restrict__ total) {
     __shared__ float s_x[LS][LS + 1], s_y[LS][LS + 1], s_w[LW * LW];
@@ -79,7 +82,8 @@ __global__ void __launch_bounds__(LT * LT) loss_kernel(const float4* __restrict_
     if (threadIdx.x == 0) {
         double s = 0.0;
         for (int w = 0; w < LT * LT / 32; w++) s += s_red[w];
-        atomicAdd(total, s);                                       // reduceLoss: :344-358 (double, so the order does not show)
+        if (PARTIAL) total[blockIdx.y * gridDim.x + blockIdx.x] = s;
+        else atomicAdd(total, s);                                  // reduceLoss: :344-358 (double, so the order does not show)
     }
 }
 
@@ -88,5 +92,61 @@ __global__ void __launch_bounds__(LT * LT) loss_kernel(const float4* __restrict_
 void gs_launch_loss(const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize, double* total,
                     cudaStream_t st) {
     if (W == 0 || H == 0) return;
-    loss_kernel<<<dim3((W + LT - 1) / LT, (H + LT - 1) / LT), LT * LT, 0, st>>>(rendered, gt, W, H, lambda, quantize, total);
+    loss_kernel<false><<<dim3((W + LT - 1) / LT, (H + LT - 1) / LT), LT * LT, 0, st>>>(rendered, gt, W, H, lambda, quantize, total);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant (gs_loss_compute_noalloc, include/gs_abi.h).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+// harnesses that forbid it).  The scratch — one double per 16x16 tile — lives in a file-scope device array, so every GPU
+// that loads this library holds GS_LOSS_NOALLOC_MAX_TILES * 8 B = 256 KiB until exit.  Every call shares the array and it
+// keeps the last call's contents; nothing has to start at zero because each call overwrites the ntiles slots it then
+// reads.  Two calls that overlap on the GPU (different streams) race on it.
+// In host code `g_loss_partials` is only a host-side stand-in for the symbol, never a device address: the address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+// ---------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_loss_partials[GS_LOSS_NOALLOC_MAX_TILES];
+
+namespace {
+// one CTA: the partial sums in a fixed order (thread t takes slots t, t + 1024, ...; then a fixed tree), so the result does
+// not depend on the order in which the tiles finished; mean over the pixels, as MTLEngine::computeLoss returns it
+__global__ void __launch_bounds__(1024) loss_finish_kernel(const double* __restrict__ partials, uint32_t ntiles, double inv_pixels,
+                                                           float* __restrict__ out) {
+    __shared__ double s_sum[1024];
+    double s = 0.0;
+    for (uint32_t i = threadIdx.x; i < ntiles; i += 1024u) s += partials[i];
+    s_sum[threadIdx.x] = s;
+    __syncthreads();
+    for (uint32_t d = 512u; d >= 1u; d >>= 1) {
+        if (threadIdx.x < d) s_sum[threadIdx.x] += s_sum[threadIdx.x + d];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = (float)(s_sum[0] * inv_pixels);
+}
+constexpr int MAX_DEVICES = 64;
+double* g_partials_addr[MAX_DEVICES] = {};      // device address of g_loss_partials on each device, resolved on first use
+}  // namespace
+
+// Enqueues the two kernels on `st`; allocates nothing.  `device` must be the current device.  On failure returns a negative
+// GS_ERR_* code and points *err at a static message.
+int gs_launch_loss_noalloc(int device, const float4* rendered, const float4* gt, uint32_t W, uint32_t H, float lambda, int quantize,
+                           float* d_loss_out, cudaStream_t st, const char** err) {
+    if (!rendered || !gt || !d_loss_out) { *err = "bad argument: null pointer"; return -3; }
+    if (W == 0 || H == 0) { *err = "bad argument: empty image"; return -3; }
+    const uint32_t ntx = (W + LT - 1) / LT, nty = (H + LT - 1) / LT;
+    if ((uint64_t)ntx * nty > (uint64_t)GS_LOSS_NOALLOC_MAX_TILES) {
+        *err = "gs_loss_compute_noalloc: image exceeds the static scratch (GS_LOSS_NOALLOC_MAX_TILES 16x16 tiles); use gs_loss_compute";
+        return -5;
+    }
+    if (device < 0 || device >= MAX_DEVICES) { *err = "bad argument: device ordinal beyond 63"; return -3; }
+    if (!g_partials_addr[device]) {
+        double* p = nullptr;
+        if (cudaGetSymbolAddress((void**)&p, g_loss_partials) != cudaSuccess || !p) { *err = "cudaGetSymbolAddress(g_loss_partials) failed"; return -1; }
+        g_partials_addr[device] = p;
+    }
+    double* partials = g_partials_addr[device];
+    loss_kernel<true><<<dim3(ntx, nty), LT * LT, 0, st>>>(rendered, gt, W, H, lambda, quantize, partials);
+    loss_finish_kernel<<<1, 1024, 0, st>>>(partials, ntx * nty, 1.0 / ((double)W * (double)H), d_loss_out);
+    if (cudaGetLastError() != cudaSuccess) { *err = "gs_loss_compute_noalloc: kernel launch failed"; return -1; }
+    return 0;
 }

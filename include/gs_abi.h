@@ -188,6 +188,18 @@ void* gs_image_devptr(gs_image*);                                          /* fl
  * mean RGB, clamp to edge), mean over pixels.  Off the gradient path.  flags: GS_BWD_QUANTIZE_RGBA8 reads the rendered
  * image as the reference's RGBA8Unorm texture would hold it.  Synchronises. */
 int gs_loss_compute(gs_ctx*, gs_image* rendered, gs_image* ground_truth, float lambda_dssim, int flags, float* loss);
+/* The same loss for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Calls no cudaMalloc /
+ * cudaFree / allocating routine and does not synchronise: it enqueues two kernels on the context's stream and the mean loss
+ * is written to *d_loss_out, ONE float of caller-owned DEVICE memory (e.g. from gs_dev_alloc).  Its scratch — one double per
+ * 16x16 tile, summed in a fixed order, so the result is run-to-run deterministic — is a static device array of
+ * GS_LOSS_NOALLOC_MAX_TILES (32768) entries = 256 KiB that every GPU loading the library holds until exit: images of more
+ * tiles (beyond e.g. 4096x2048 or 3840x2160) are rejected with GS_ERR_CAPACITY.  All calls on a device share that array and it
+ * keeps the last call's contents (each call overwrites every slot it reads, nothing needs clearing): calls that overlap on the
+ * GPU, i.e. on different contexts / streams of one device, race.  The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress): make it once before starting a graph capture. */
+#define GS_LOSS_NOALLOC_MAX_TILES 32768
+int gs_loss_compute_noalloc(gs_ctx*, gs_image* rendered, gs_image* ground_truth, float lambda_dssim, int flags, float* d_loss_out);
 
 /* ---- TiledRasterizer (tiled_rasterizer.hpp:56-124) ------------------------------------------------------ */
 int gs_rast_create(gs_ctx*, uint32_t max_gaussians, gs_rast** out);
