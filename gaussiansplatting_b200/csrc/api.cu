@@ -1093,7 +1093,9 @@ struct gs_dp {
     gs_grads* bound = nullptr;
     float* bound_ptr = nullptr;
     uint32_t* my_flags = nullptr;       // 3 barriers x GS_MAX_PEERS words, written by the peers
-    uint32_t* d_err = nullptr;
+    uint32_t* d_err = nullptr;          // device word: set by a barrier that timed out, read by the reduce kernels (sticky)
+    uint32_t* h_err = nullptr;          // the same flag in mapped pinned host memory (polled without a stream synchronisation)
+    uint32_t* h_err_dev = nullptr;      // its device-side address
     uint32_t epoch = 0;
     bool connected = false;
     void* opened[2 * GS_MAX_PEERS] = {};
@@ -1112,6 +1114,8 @@ int gs_dp_create(gs_ctx* c, int rank, int world, gs_dp** out) {
     if (rc == GS_OK) rc = dalloc(c, &d->d_err, 1);
     if (rc == GS_OK && cudaMemset(d->my_flags, 0, 3 * GS_MAX_PEERS * sizeof(uint32_t)) != cudaSuccess) rc = GS_ERR_CUDA;
     if (rc == GS_OK && cudaMemset(d->d_err, 0, sizeof(uint32_t)) != cudaSuccess) rc = GS_ERR_CUDA;
+    if (rc == GS_OK && cudaHostAlloc((void**)&d->h_err, sizeof(uint32_t), cudaHostAllocMapped) != cudaSuccess) rc = GS_ERR_OOM;
+    if (rc == GS_OK) { *d->h_err = 0; if (cudaHostGetDevicePointer((void**)&d->h_err_dev, d->h_err, 0) != cudaSuccess) rc = GS_ERR_CUDA; }
     if (rc != GS_OK) { gs_dp_destroy(d); return rc; }
     *out = d;
     return GS_OK;
@@ -1121,6 +1125,7 @@ int gs_dp_destroy(gs_dp* d) {
     cudaSetDevice(d->c->device); cudaStreamSynchronize(d->c->stream);
     for (void* p : d->opened) if (p) cudaIpcCloseMemHandle(p);
     cudaFree(d->my_flags); cudaFree(d->d_err);
+    if (d->h_err) cudaFreeHost(d->h_err);
     delete d;
     return GS_OK;
 }
@@ -1162,8 +1167,11 @@ int gs_dp_allreduce_grads(gs_dp* d, gs_grads* g, uint32_t n) {
     GS_ARG(c, g == d->bound && g->g == d->bound_ptr, "the gradient buffer was reallocated after gs_dp_export");
     GS_ARG(c, n <= g->cap, "n");
     if (n == 0) return GS_OK;
+    // a barrier of an EARLIER call timed out (a rank fell more than 5 s behind or is gone): that call's sum was withheld and the
+    // step poisoned (peer_reduce.cu); report it before another step is built on replicas that no longer agree
+    if (*(volatile uint32_t*)d->h_err) { c->err = "peer all-reduce: a rank did not arrive within 5 s (an earlier gradient sum was withheld)"; return GS_ERR_NCCL; }
     d->epoch++;
-    gs_launch_peer_allreduce(d->peers, n, g->stride, d->epoch, d->d_err, c->stream);
+    gs_launch_peer_allreduce(d->peers, n, g->stride, d->epoch, d->d_err, d->h_err_dev, c->stream);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }

@@ -36,15 +36,23 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
-__global__ void dp_barrier_kernel(const __grid_constant__ GsPeerSet P, int slot, uint32_t epoch, uint32_t* __restrict__ err) {
+// err: device word the kernels of this stream read; host_err: the same flag in mapped pinned host memory, which the host polls
+// without a stream synchronisation (gs_dp_allreduce_grads / gs_dp_check return GS_ERR_NCCL once it is set).  Both are sticky.
+__global__ void dp_barrier_kernel(const __grid_constant__ GsPeerSet P, int slot, uint32_t epoch, uint32_t* __restrict__ err,
+                                  volatile uint32_t* __restrict__ host_err) {
     const int t = (int)threadIdx.x;
     if (t >= P.world) return;
     __threadfence_system();
     st_release_sys(P.flags[t] + slot * GS_MAX_PEERS + P.rank, epoch);                  // tell rank t that this rank is here
     const uint32_t* mine = P.flags[P.rank] + slot * GS_MAX_PEERS + t;                  // wait for rank t
+    if (*reinterpret_cast<volatile uint32_t*>(err)) return;   // already failed (sticky): the peers are told, nobody is waited for
     const unsigned long long t0 = globaltimer_ns();
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-        if (globaltimer_ns() - t0 > 5000000000ull) { atomicExch(err, 1u); break; }     // 5 s: a peer is gone
+        if (globaltimer_ns() - t0 > 5000000000ull) {                                   // 5 s: a peer is gone
+            atomicExch(err, 1u);
+            if (host_err) { *host_err = 1u; __threadfence_system(); }
+            break;
+        }
         __nanosleep(64);
     }
 }
@@ -53,10 +61,21 @@ __global__ void dp_barrier_kernel(const __grid_constant__ GsPeerSet P, int slot,
 __device__ __forceinline__ size_t vec_offset(uint32_t v, uint32_t n4, uint32_t stride4) { return (size_t)(v / n4) * stride4 + (v % n4); }
 
 template <int WORLD>
-__global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ GsPeerSet P, uint32_t n4, uint32_t stride4, uint32_t v0, uint32_t v1) {
+__global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ GsPeerSet P, uint32_t n4, uint32_t stride4, uint32_t v0, uint32_t v1,
+                                                        const uint32_t* __restrict__ err) {
     constexpr int U = WORLD <= 2 ? 4 : 2;                       // vectors per thread per round: U * (WORLD - 1) remote loads in flight
     const float4* own = reinterpret_cast<const float4*>(P.bufs[P.rank]);
     const uint32_t T = gridDim.x * blockDim.x;
+    if (*err) {
+        // A barrier of this or an earlier call timed out: the peers' buffers may be incomplete, so nothing is summed and no
+        // peer is written.  This rank's position-x gradients (plane 0) become NaN instead, which makes adamStep's guard
+        // (shaders.metal:567-570) skip every Gaussian: the step is lost on this rank, never applied with a partial sum, and the
+        // host sees GS_ERR_NCCL on its next gs_dp_allreduce_grads / gs_dp_check.
+        float4* mine = reinterpret_cast<float4*>(P.bufs[P.rank]);
+        const float qn = __int_as_float(0x7FC00000);
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += T) mine[i] = make_float4(qn, qn, qn, qn);
+        return;
+    }
     for (uint32_t vb = v0 + blockIdx.x * blockDim.x + threadIdx.x; vb < v1; vb += U * T) {
         float4 x[U][WORLD];
         size_t o[U];
@@ -82,20 +101,21 @@ __global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ 
 
 }  // namespace
 
-void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, cudaStream_t st) {
+void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
+                              cudaStream_t st) {
     const uint32_t n4 = (n + 3u) / 4u, stride4 = stride / 4u;
     const uint32_t V = 16u * n4;
     const uint32_t per = (V + (uint32_t)P.world - 1u) / (uint32_t)P.world;
     const uint32_t v0 = std::min(V, per * (uint32_t)P.rank), v1 = std::min(V, v0 + per);
     const int grid = 148 * 8;
-    dp_barrier_kernel<<<1, 32, 0, st>>>(P, 0, epoch, err);
+    dp_barrier_kernel<<<1, 32, 0, st>>>(P, 0, epoch, err, host_err);
     if (v1 > v0) {
         switch (P.world) {
-#define GS_DP_CASE(W) case W: dp_reduce_kernel<W><<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1); break;
+#define GS_DP_CASE(W) case W: dp_reduce_kernel<W><<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1, err); break;
             GS_DP_CASE(2) GS_DP_CASE(3) GS_DP_CASE(4) GS_DP_CASE(5) GS_DP_CASE(6) GS_DP_CASE(7) GS_DP_CASE(8)
 #undef GS_DP_CASE
         default: break;
         }
     }
-    dp_barrier_kernel<<<1, 32, 0, st>>>(P, 1, epoch, err);
+    dp_barrier_kernel<<<1, 32, 0, st>>>(P, 1, epoch, err, host_err);
 }

@@ -15,6 +15,7 @@
 //     through shared memory so global stores are digit-contiguous, and scatters keys then values;
 //   * tile ids are handed out by an atomic ticket so a tile only ever waits on tiles that already started.
 #include <climits>
+#include <atomic>
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
@@ -486,17 +487,27 @@ constexpr uint32_t RS_BIG_TILE = RS_THREADS * GS_RS_BIG_IPT, RS_SMALL_TILE = RS_
 constexpr size_t RS_HIST_BYTES = RS_MAX_PASSES * 256 * 4;
 constexpr size_t RS_CTR_BYTES = 64;
 
+// bit of the current device in the per-device "attribute already set" masks (an ordinal beyond 63 has no bit: it sets the
+// attribute on every launch, which is cheap and harmless)
+static inline uint64_t rs_device_bit() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < 64) ? (1ull << dev) : 0ull;
+}
+
 template <typename KeyT, int IPT, bool BALLOT>
 void launch_passes(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint32_t* vbuf[2], uint64_t n, const uint32_t* d_n,
                    const GsSortPlan& plan, const PassList& pl, uint32_t tiles, uint32_t* ghist, uint32_t* counters,
                    uint32_t* status, unsigned long long* agg2, size_t groups, cudaStream_t st, const uint32_t* gate = nullptr,
                    int slot0 = 0, int dst0 = 0) {
     const size_t smem = sizeof(OnesweepSmem<KeyT, IPT>);
-    static bool attr_set = false;
-    if (!attr_set) {
+    // cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute: one bit per device ordinal, per instantiation
+    static std::atomic<uint64_t> attr_set{0};
+    const uint64_t dev_bit = rs_device_bit();
+    if (!(attr_set.load(std::memory_order_acquire) & dev_bit)) {
         cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(onesweep_kernel<KeyT, IPT, BALLOT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
+        attr_set.fetch_or(dev_bit, std::memory_order_release);        // set after the calls: a racing thread repeats them (idempotent)
     }
     const KeyT* kin = keys_in;
     const uint32_t* vin = vals_in;
@@ -616,8 +627,12 @@ int sort_impl(const KeyT* keys_in, const uint32_t* vals_in, KeyT* kbuf[2], uint3
     hybrid_precheck_kernel<<<1, 256, 0, st>>>(ghist + top * 256, 1 << pre.bits[pre.num_passes - 1], n, counters);
     GS_RS_RUN(pre, nullptr, plan.num_passes, (pre.num_passes & 1) ? 1 : 0);   // ungated (a gated CTA pays one more global round trip before its ticket)
     if constexpr (sizeof(KeyT) == 8) {
-        static bool ls_attr = false;
-        if (!ls_attr) { cudaFuncSetAttribute(local_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem)); ls_attr = true; }
+        static std::atomic<uint64_t> ls_attr{0};                      // per device, as above
+        const uint64_t dev_bit = rs_device_bit();
+        if (!(ls_attr.load(std::memory_order_acquire) & dev_bit)) {
+            cudaFuncSetAttribute(local_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LocalSortSmem));
+            ls_attr.fetch_or(dev_bit, std::memory_order_release);
+        }
         const uint32_t chunks = (uint32_t)((n + LS_CH - 1) / LS_CH);
         local_sort_kernel<<<chunks, LS_THREADS, sizeof(LocalSortSmem), st>>>(reinterpret_cast<uint64_t*>(kbuf[1]), vbuf[1], n, T, B, counters);
     }
