@@ -115,7 +115,7 @@ public:
         if (!gpuSort) gpuSort = new GPURadixSort32(device, library, kOperatorCapacity);               // mtl_engine.mm:317
         if (!renderPipeline) renderPipeline = new SplatRenderPipeline(device, library, (uint32_t)kOperatorCapacity);
         if (!positionBuffer || positionsStale) { updatePositionBuffer(); positionsStale = false; }
-        const uint32_t* sortedIndices = gpuSort->sort(commandQueue, positionBuffer, uniforms.cameraPos, gaussianCount);
+        MTL::Buffer* sortedIndices = gpuSort->sort(commandQueue, positionBuffer, uniforms.cameraPos, gaussianCount);   // mtl_engine.mm:403
         renderPipeline->draw(commandQueue, gaussianBuffer, uniforms, sortedIndices, target);
     }
 
@@ -261,17 +261,17 @@ public:
         return st;
     }
 
-    std::vector<Gaussian> getGaussians() const {                                 // mtl_engine.hpp:51-53 (contents()) -> explicit download
-        std::vector<Gaussian> out(gaussianCount);
-        if (gaussianCount) gaussianBuffer->download(out.data(), gaussianCount * sizeof(Gaussian));
-        return out;
+    // mtl_engine.hpp:51-53, signature and body as the reference: Buffer::contents() is a host mirror refreshed from the device by
+    // the call (metal_shim.hpp), valid until the next contents() on the buffer or until densify replaces the buffer
+    const Gaussian* getGaussians() const {
+        return gaussianBuffer ? (const Gaussian*)gaussianBuffer->contents() : nullptr;
     }
+    size_t getGaussianCount() const { return gaussianCount; }                    // mtl_engine.hpp:54-56
 
     // ---- on-disk state ---------------------------------------------------------------------------------
-    // main.mm:483-489: PLYExporter::exportPLY(path, engine.getGaussians(), count) — the explicit download replaces contents()
+    // main.mm:483-489, verbatim: PLYExporter::exportPLY(path, engine.getGaussians(), engine.getGaussianCount())
     bool exportPLY(const std::string& path) const {
-        const std::vector<Gaussian> g = getGaussians();
-        return PLYExporter::exportPLY(path, g.data(), g.size());
+        return PLYExporter::exportPLY(path, getGaussians(), getGaussianCount());
     }
     // main.mm:383-389 (the --ply path): load_ply + loadGaussians; returns the number of Gaussians loaded (0 = failure)
     size_t loadPLY(const std::string& path, float extent) {
@@ -291,8 +291,8 @@ public:
         const uint64_t n = gaussianCount;
         const uint32_t version = 1, t = optimizer->getTimestep(), zero = 0;
         f.write("GSCK", 4); f.write((const char*)&version, 4); f.write((const char*)&n, 8); f.write((const char*)&t, 4); f.write((const char*)&zero, 4);
-        const std::vector<Gaussian> g = getGaussians();
-        f.write((const char*)g.data(), (std::streamsize)(n * sizeof(Gaussian)));
+        const Gaussian* g = getGaussians();
+        if (n) f.write((const char*)g, (std::streamsize)(n * sizeof(Gaussian)));
         static const int width[5] = {3, 3, 4, 1, 12};
         std::vector<float> buf;
         for (int group = 0; group < 5; group++)

@@ -5,9 +5,9 @@
 //   optimizer.hpp:23-61          AdamOptimizer              density_control.hpp:20-48  DensityController
 //   gradients.hpp:11-31          GaussianGradients          ply_loader.hpp:14-20  Gaussian
 // so that MTLEngine::trainStep / train (mtl_engine.mm:856-1221) call them unchanged.  Each body is a forwarding shell:
-// the pipeline states, scratch buffers and dispatch code of the .mm files live inside the library.  Errors: the
-// reference's methods return void and log to std::cerr; here a failing gs_* call throws std::runtime_error with
-// gs_last_error()'s text.
+// the pipeline states, scratch buffers and dispatch code of the .mm files live inside the library.  Errors: as in the
+// reference, the methods return void and a failing device call is logged to std::cerr (with gs_last_error()'s text) and
+// remembered in MTL::lastError(); MTL::setThrowOnError(true) turns that into std::runtime_error (metal_shim.hpp).
 #pragma once
 #include <vector>
 #include "metal_shim.hpp"
@@ -55,18 +55,25 @@ public:
     GPURadixSort64(MTL::Device* device, MTL::Library*, size_t maxElements) : device_(device) {
         MTL::gs_check(device->ctx(), gs_sort64_create(device->ctx(), maxElements, &s_), "GPURadixSort64");
     }
-    ~GPURadixSort64() { gs_sort64_destroy(s_); }
+    ~GPURadixSort64() { if (keys_) keys_->release(); if (vals_) vals_->release(); gs_sort64_destroy(s_); }
     // sort 64-bit keys with 32-bit values (stable, all 64 bits); keysIn / valuesIn are raw device buffers
     void sort(MTL::CommandQueue*, MTL::Buffer* keysIn, MTL::Buffer* valuesIn, size_t numElements) {
         MTL::gs_check(device_->ctx(), gs_sort64_sort(s_, (const uint64_t*)keysIn->devptr(), (const uint32_t*)valuesIn->devptr(),
                                                       numElements, 0, 64), "GPURadixSort64::sort");
+        n_ = numElements;
     }
-    // borrowed device pointers, valid until the next sort (gpu_sort.hpp:76-77 return the internal MTL::Buffers)
-    const uint64_t* getSortedKeys() { return gs_sort64_sorted_keys(s_); }
-    const uint32_t* getSortedValues() { return gs_sort64_sorted_values(s_); }
+    // gpu_sort.hpp:76-77: the sorter's internal result buffers, borrowed, valid until the next sort
+    MTL::Buffer* getSortedKeys() { return rewrap(keys_, gs_sort64_sorted_keys(s_), n_ * 8); }
+    MTL::Buffer* getSortedValues() { return rewrap(vals_, gs_sort64_sorted_values(s_), n_ * 4); }
 private:
+    MTL::Buffer* rewrap(MTL::Buffer*& slot, const void* p, size_t bytes) {
+        if (slot) slot->release();
+        return slot = device_->wrapBuffer(p, bytes);
+    }
     MTL::Device* device_;
     gs_sort64* s_ = nullptr;
+    size_t n_ = 0;
+    MTL::Buffer *keys_ = nullptr, *vals_ = nullptr;
 };
 
 // ---- GPURadixSort32 (gpu_sort.hpp:14-62): viewer depth order, far to near -----------------------------------------
@@ -75,17 +82,24 @@ public:
     GPURadixSort32(MTL::Device* device, MTL::Library*, size_t maxElements) : device_(device) {
         MTL::gs_check(device->ctx(), gs_sort32_create(device->ctx(), maxElements, &s_), "GPURadixSort32");
     }
-    ~GPURadixSort32() { gs_sort32_destroy(s_); }
-    // positionBuffer: float4 per Gaussian (updatePositionBuffer, mtl_engine.mm:1028-1036); returns the sorted indices
-    const uint32_t* sort(MTL::CommandQueue*, MTL::Buffer* positionBuffer, simd_float3 cameraPos, size_t numElements) {
+    ~GPURadixSort32() { if (idx_) idx_->release(); gs_sort32_destroy(s_); }
+    // positionBuffer: float4 per Gaussian (updatePositionBuffer, mtl_engine.mm:1028-1036).  Returns the sorted indices as the
+    // reference does (gpu_sort.hpp:19-22): the sorter's internal buffer, borrowed, valid until the next sort
+    MTL::Buffer* sort(MTL::CommandQueue*, MTL::Buffer* positionBuffer, simd_float3 cameraPos, size_t numElements) {
         const float cam[3] = {cameraPos.x, cameraPos.y, cameraPos.z};
         MTL::gs_check(device_->ctx(), gs_sort32_sort_depth(s_, positionBuffer->devptr(), cam, numElements), "GPURadixSort32::sort");
-        return gs_sort32_sorted_indices(s_);
+        n_ = numElements;
+        return getSortedIndices();
     }
-    const uint32_t* getSortedIndices() { return gs_sort32_sorted_indices(s_); }
+    MTL::Buffer* getSortedIndices() {                                        // gpu_sort.hpp:26
+        if (idx_) idx_->release();
+        return idx_ = device_->wrapBuffer(gs_sort32_sorted_indices(s_), n_ * 4);
+    }
 private:
     MTL::Device* device_;
     gs_sort32* s_ = nullptr;
+    size_t n_ = 0;
+    MTL::Buffer* idx_ = nullptr;
 };
 
 // ---- the viewer's draw call (MTLEngine::createPipeline + the render encoder of MTLEngine::render, mtl_engine.mm:337-375,575-605):
@@ -97,8 +111,8 @@ public:
     }
     ~SplatRenderPipeline() { gs_viewer_destroy(v_); }
     // drawPrimitives(TriangleStrip, 0, 4, gaussianCount) with vertex buffers (gaussians, uniforms, sortedIndices), :592-597
-    void draw(MTL::CommandQueue*, MTL::Buffer* gaussianBuffer, const Uniforms& uniforms, const uint32_t* sortedIndices, MTL::Texture* target) {
-        MTL::gs_check(device_->ctx(), gs_viewer_render(v_, gaussianBuffer->gaussians(), sortedIndices,
+    void draw(MTL::CommandQueue*, MTL::Buffer* gaussianBuffer, const Uniforms& uniforms, MTL::Buffer* sortedIndices, MTL::Texture* target) {
+        MTL::gs_check(device_->ctx(), gs_viewer_render(v_, gaussianBuffer->gaussians(), (const uint32_t*)sortedIndices->devptr(),
                                                        reinterpret_cast<const gs_view_uniforms*>(&uniforms), target->image(),
                                                        quantize_ ? GS_VIEW_QUANTIZE_RGBA8 : 0), "SplatRenderPipeline::draw");
     }

@@ -30,6 +30,9 @@ typedef struct {
 } gs_host_train_result;
 
 static char g_err[512];
+// this file's C entry points report failures as a status code + gs_host_last_error(): they run the shells in exception mode
+// (the shells' default is the reference's: log to std::cerr and carry on, metal_shim.hpp)
+static const bool g_throw_mode = (MTL::setThrowOnError(true), true);
 const char* gs_host_last_error(void) { return g_err; }
 
 // Trains `gaussians` on num_views views (poses: quats[4*v] wxyz + trans[3*v]); the ground truth of view v is the render
@@ -99,8 +102,8 @@ int gs_host_train(int device, const gs_gaussian* gaussians, uint32_t n, const gs
             if (res) res->views_exported = (uint32_t)w;
         }
         if (out) {
-            const std::vector<Gaussian> g = eng.getGaussians();
-            std::memcpy(out, g.data(), std::min<size_t>(g.size(), out_cap) * sizeof(Gaussian));
+            const Gaussian* g = eng.getGaussians();
+            if (g) std::memcpy(out, g, std::min<size_t>(eng.getGaussianCount(), out_cap) * sizeof(Gaussian));
         }
         for (auto& tv : eng.trainingImages) tv.texture->release();
         return 0;
@@ -187,8 +190,8 @@ int gs_host_sort64(int device, const uint64_t* keys, const uint32_t* vals, uint6
             sorter.sort(q, k, v, n);
             dev->waitUntilCompleted();
             if (n) {
-                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), keys_out, sorter.getSortedKeys(), n * 8), "download");
-                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), vals_out, sorter.getSortedValues(), n * 4), "download");
+                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), keys_out, sorter.getSortedKeys()->devptr(), n * 8), "download");
+                MTL::gs_check(dev->ctx(), gs_dev_download(dev->ctx(), vals_out, sorter.getSortedValues()->devptr(), n * 4), "download");
             }
             k->release(); v->release(); q->release();
         }

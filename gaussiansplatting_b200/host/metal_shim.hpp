@@ -6,15 +6,19 @@
 // signatures verbatim (tiled_rasterizer.hpp:59-75, gpu_sort.hpp:16-77, optimizer.hpp:26-61, density_control.hpp:22-48).
 // What differs, because a CUDA device is not unified memory:
 //   * a Buffer has a ROLE (raw bytes, the Gaussian model, the gradient buffer): the library keeps its own SoA layout on
-//     the device, so contents() does not exist — use upload()/download() with the reference's wire structs;
+//     the device.  contents() (102 call sites in the reference, e.g. getGaussians(), mtl_engine.hpp:51-53) returns a HOST
+//     MIRROR in the reference's wire layout, refreshed from the device by every call (a synchronising download); host
+//     writes reach the device only through didModifyRange() (metal-cpp's call for managed storage) or upload();
 //   * a Texture is an RGBA image on the device (float4 per pixel; RGBA8 transfers convert on the device);
 //   * Library carries nothing: the kernels are compiled into libgs_b200.so.
 #pragma once
 #include <cstddef>
 #include <cstdint>
 #include <cstdio>
+#include <iostream>
 #include <stdexcept>
 #include <string>
+#include <vector>
 #include "../../include/gs_abi.h"
 
 // ---- <simd/simd.h> stand-ins (size / alignment of Apple's types: float2 8/8, float3 16/16, float4 16/16, float4x4 64/16)
@@ -26,8 +30,20 @@ static_assert(sizeof(simd_float2) == 8 && sizeof(simd_float3) == 16 && sizeof(si
 
 namespace MTL {
 
-inline void gs_check(gs_ctx* c, int rc, const char* what) {
-    if (rc != GS_OK) throw std::runtime_error(std::string(what) + ": " + gs_last_error(c));
+// Error convention: the reference's host methods return void; on a failing device call they print to std::cerr
+// and carry on (mtl_engine.mm:178-181, gpu_sort.mm:167-176).  The shells do the same: a non-zero gs_* status is logged with
+// gs_last_error()'s text, remembered (lastError()) and the call returns.  Callers that prefer an exception (this repo's own C
+// entry points in gs_host_capi.cpp, which turn it into a status code for Python) switch it on with setThrowOnError(true).
+inline bool& throwOnErrorFlag() { static bool f = false; return f; }
+inline std::string& lastErrorText() { static std::string s; return s; }
+inline void setThrowOnError(bool on) { throwOnErrorFlag() = on; }
+inline const std::string& lastError() { return lastErrorText(); }
+inline bool gs_check(gs_ctx* c, int rc, const char* what) {
+    if (rc == GS_OK) return true;
+    lastErrorText() = std::string(what) + ": " + gs_last_error(c);
+    if (throwOnErrorFlag()) throw std::runtime_error(lastErrorText());
+    std::cerr << lastErrorText() << std::endl;
+    return false;
 }
 
 enum ResourceOptions { ResourceStorageModeShared = 0, ResourceStorageModePrivate = 1 };
@@ -57,6 +73,11 @@ public:
     // host <-> device with the reference's wire structs (Gaussian 112 B, GaussianGradients 112 B) or raw bytes
     void upload(const void* host, size_t bytes);
     void download(void* host, size_t bytes) const;
+    // MTL::Buffer::contents(): pointer to a host mirror of the buffer in the reference's layout (Gaussian[count] for the
+    // model, GaussianGradients[count] for gradients, the bytes of a raw buffer), refreshed from the device on every call.
+    void* contents();
+    // host edits made through contents() -> device (the whole buffer; Metal's managed-storage call takes a range)
+    void didModifyRange(size_t /*location*/ = 0, size_t /*length*/ = 0) { if (!mirror_.empty()) upload(mirror_.data(), mirror_.size()); }
     void release();
 private:
     friend class Device;
@@ -67,6 +88,8 @@ private:
     void* raw_ = nullptr;
     gs_gaussians* g_ = nullptr;
     gs_grads* gr_ = nullptr;
+    bool borrowed_ = false;            // wraps a device pointer owned by somebody else (e.g. a sorter's internal result buffer)
+    std::vector<unsigned char> mirror_;
 };
 
 class Texture {            // render target / ground-truth image (mtl_engine.mm:715-727, image_loader.mm:24)
@@ -105,6 +128,12 @@ public:
         gs_check(ctx_, gs_dev_alloc(ctx_, bytes, &b->raw_), "newBuffer");
         return b;
     }
+    // a Buffer handle over device memory that somebody else owns (gpu_sort.hpp:19-26,76-77 return the sorter's internal
+    // MTL::Buffers: borrowed, valid until the next sort); release() frees the handle only
+    Buffer* wrapBuffer(const void* devptr, size_t bytes) {
+        Buffer* b = new Buffer(); b->dev_ = this; b->bytes_ = bytes; b->raw_ = const_cast<void*>(devptr); b->borrowed_ = true;
+        return b;
+    }
     Buffer* newGaussianBuffer(const gs_gaussian* host, size_t count, size_t capacity = 0) {    // mtl_engine.mm:296-300
         Buffer* b = new Buffer(); b->dev_ = this; b->role_ = Buffer::Gaussians; b->bytes_ = count * sizeof(gs_gaussian);
         gs_check(ctx_, gs_gaussians_create(ctx_, (uint32_t)(capacity > count ? capacity : count), &b->g_), "newGaussianBuffer");
@@ -140,10 +169,17 @@ inline void Buffer::download(void* host, size_t bytes) const {
     else if (role_ == Gradients) gs_check(c, gs_grads_download(gr_, (gs_gradients*)host, (uint32_t)(bytes / sizeof(gs_gradients))), "download");
     else gs_check(c, gs_dev_download(c, host, raw_, bytes), "download");
 }
+inline void* Buffer::contents() {
+    size_t bytes = bytes_;
+    if (role_ == Gaussians) bytes = (size_t)gs_gaussians_count(g_) * sizeof(gs_gaussian);
+    mirror_.resize(bytes);
+    if (bytes) download(mirror_.data(), bytes);
+    return mirror_.data();
+}
 inline void Buffer::release() {
     if (g_) gs_gaussians_destroy(g_);
     if (gr_) gs_grads_destroy(gr_);
-    if (raw_) gs_dev_free(dev_->ctx(), raw_);
+    if (raw_ && !borrowed_) gs_dev_free(dev_->ctx(), raw_);
     delete this;
 }
 inline void Texture::replaceRegionRGBA8(const uint8_t* rgba) {
