@@ -461,33 +461,53 @@ class Bench:
         gbuf = vp.device_tensor(D) if dist is not None else None
         # the gradient sum: this library's own kernels over NVLink peer memory (gs_dp_*, csrc/peer_reduce.cu); NCCL's all-reduce on
         # the same buffer is timed beside it (--allreduce nccl makes it the headline instead)
-        PR = None
+        PR = SG = None
         if dist is not None:
             PR = gs.PeerReduce(ctx, rank, world)
             blobs = [None] * world
             dist.all_gather_object(blobs, PR.export(D))
             PR.connect(blobs)
+            # the same payload in symmetric, multicast-mapped memory: the sum runs in the NVSwitch (multimem.ld_reduce / multimem.st)
+            try:
+                SG = dp.SymmetricGrads(gs, ctx, dist, n5, local)
+                SG.grads.set_stat_mode(True)
+                if not SG.multicast:
+                    SG.close(); SG = None
+            except Exception as e:
+                out.setdefault("notes", []).append("no symmetric / multicast memory on this box: " + repr(e)[:160])
+                SG = None
+            ok = torch.tensor([1 if SG is not None else 0], device="cuda"); dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if not int(ok.item()) and SG is not None:
+                SG.close(); SG = None
 
         def make_train_step(views_per_step, reduce_impl):
+            Dg = SG.grads if reduce_impl == "nvls" else D
             def step(i):
                 mine = vp.views(i, views_per_step, NVT)
                 for k, v in enumerate(mine):
                     R.forward(G5, cams5[v], img)
-                    R.backward(G5, D, cams5[v], img, gts5[v], gs.GS_BWD_ACCUMULATE if k else 0)
+                    R.backward(G5, Dg, cams5[v], img, gts5[v], gs.GS_BWD_ACCUMULATE if k else 0)
                 if dist is not None:
                     if reduce_impl == "peer":
                         PR.allreduce(D, n5)              # enqueued on the ctx stream behind the backward kernels
+                    elif reduce_impl == "nvls":
+                        SG.reduce.allreduce(Dg, n5)
                     elif reduce_impl == "nccl":
                         with torch.cuda.stream(self.stream):  # NCCL orders itself after / before the ctx stream: no host sync
                             dist.all_reduce(gbuf)
-                Dn.accumulate(D, n5)
-                A5.step(G5, D, LRS)
+                Dn.accumulate(Dg, n5)
+                A5.step(G5, Dg, LRS)
             return step
 
-        main, alt = args.allreduce, ("nccl" if args.allreduce == "peer" else "peer")
+        main = args.allreduce
+        if main == "auto":
+            main = "nvls" if SG is not None else "peer"
+        if main == "nvls" and SG is None:
+            main = "peer"
+        alts = [a for a in ("nvls", "peer", "nccl") if a != main and (a != "nvls" or SG is not None)]
         runs = [("train", world, main), ("c5", 8, main)]
         if dist is not None:
-            runs += [("train_alt", world, alt), ("c5_alt", 8, alt), ("c5_noreduce", 8, "none")]
+            runs += [("c5_noreduce", 8, "none")] + [(f"c5_alt_{a}", 8, a) for a in alts] + [(f"train_alt_{a}", world, a) for a in alts[:1]]
         c5 = {}
         for name, vps, impl in runs:
             if vps % world:
@@ -519,34 +539,59 @@ class Bench:
             elif name == "c5_noreduce":
                 c5["allreduce_us_exposed"] = 1e3 * (c5["ms_per_step"] - ms / K)
             else:
-                out[f"{name.replace('_alt', '')}_{'iters' if name.startswith('train') else 'steps'}_per_s_{alt}_allreduce"] = 1e3 * K / ms
-                if name == "c5_alt":
-                    c5[f"steps_per_s_{alt}"] = 1e3 * K / ms
+                kind, a = name.split("_alt_")
+                out[f"{kind}_{'iters' if kind == 'train' else 'steps'}_per_s_{a}_allreduce"] = 1e3 * K / ms
+                if kind == "c5":
+                    c5[f"steps_per_s_{a}"] = 1e3 * K / ms
         if dist is not None:
-            # correctness of the peer-memory sum: the same per-rank inputs summed by NCCL, compared element for element
+            # correctness of this library's sums: the same per-rank inputs summed by NCCL, compared element for element
             G5.upload(g5_host)
             v0 = vp.views(0, world, NVT)[0]
-            R.forward(G5, cams5[v0], img); R.backward(G5, D, cams5[v0], img, gts5[v0])
-            ctx.sync()
-            mine_in = gbuf.clone()
-            want = mine_in.clone()
-            dist.all_reduce(want)
-            torch.cuda.synchronize()
-            PR.allreduce(D, n5); ctx.sync()
-            err = (gbuf - want).abs().max().item()
-            scale = want.abs().max().item()
-            fin = bool(torch.isfinite(gbuf).all().item() == torch.isfinite(want).all().item())
-            t = torch.tensor([err / max(scale, 1e-30)], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            PR.check()
-            out["allreduce"] = {"impl": main, "payload_bytes": 64 * n5, "max_abs_diff_vs_nccl_over_max": float(t.item()), "finite_pattern_equal": fin,
-                                "what": "peer = gs_dp_allreduce_grads (own kernels over NVLink peer memory: barrier, slice reduce in rank "
-                                        "order + store to every rank, barrier); nccl = torch.distributed.all_reduce on the same buffer; the "
-                                        "*_allreduce keys hold the other implementation's numbers; parity = one view per rank, both sums of "
-                                        "the same inputs"}
-            c5["allreduce_parity_max_rel"] = float(t.item())
+            par = {}
+            for impl in [main] + [a for a in alts if a != "nccl"]:
+                Dg = SG.grads if impl == "nvls" else D
+                gb = vp.device_tensor(Dg)
+                R.forward(G5, cams5[v0], img); R.backward(G5, Dg, cams5[v0], img, gts5[v0])
+                ctx.sync()
+                want = gb.clone()
+                dist.all_reduce(want)
+                torch.cuda.synchronize()
+                (SG.reduce if impl == "nvls" else PR).allreduce(Dg, n5); ctx.sync()
+                err = (gb - want).abs().max().item()
+                scale = want.abs().max().item()
+                t = torch.tensor([err / max(scale, 1e-30)], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                # every rank must hold the same bits
+                hs = [None] * world
+                dist.all_gather_object(hs, hashlib.sha1(gb.cpu().numpy().tobytes()).hexdigest())
+                par[impl] = {"max_abs_diff_vs_nccl_over_max": float(t.item()), "all_ranks_bit_equal": bool(all(h == hs[0] for h in hs))}
+                (SG.reduce if impl == "nvls" else PR).check()
+            # the collective alone: 20 back-to-back sums of the 64 MB payload behind a barrier (no compute in between), max over ranks
+            pure = {}
+            for impl in [main] + alts:
+                Dg = SG.grads if impl == "nvls" else D
+                gb = vp.device_tensor(Dg)
+                gb.zero_()
+
+                def one(i, impl=impl, Dg=Dg, gb=gb):
+                    if impl == "nccl":
+                        with torch.cuda.stream(self.stream):
+                            dist.all_reduce(gb)
+                    else:
+                        (SG.reduce if impl == "nvls" else PR).allreduce(Dg, n5)
+                for i in range(3):
+                    one(i)
+                pure[impl] = 1e3 * self.timed(one, 20) / 20
+            c5["allreduce_us"] = pure
+            out["allreduce"] = {"impl": main, "payload_bytes": 64 * n5, "parity": par, "us_per_call": pure,
+                                "what": "nvls = gs_dp_allreduce_grads on a symmetric multicast-mapped buffer (own kernel: multimem.ld_reduce in the "
+                                        "NVSwitch + multimem.st broadcast); peer = the same entry point over plain NVLink peer loads / stores, sums "
+                                        "in rank order; nccl = torch.distributed.all_reduce on the same buffer; parity = one view per rank, each "
+                                        "sum against NCCL's of the same inputs"}
+            c5["allreduce_parity_max_rel"] = par[main]["max_abs_diff_vs_nccl_over_max"]
+            c5["allreduce_ranks_bit_equal"] = par[main]["all_ranks_bit_equal"]
             c5["allreduce_impl"] = main
         out["config"]["c5"] = c5
-        for o in gts5 + [A5, G5] + ([PR] if PR is not None else []):
+        for o in gts5 + [A5, G5] + ([PR] if PR is not None else []) + ([SG] if SG is not None else []):
             o.close()
         Dn.set_scene_extent(synth.scene_extent(orbit))
         D.set_stat_mode(False)
@@ -810,7 +855,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline + parity leg")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 training loop")
     ap.add_argument("--no-c4", action="store_true", help="skip the config-4 render-only leg")
-    ap.add_argument("--allreduce", default="peer", choices=["peer", "nccl"], help="gradient sum of view-parallel training (N > 1)")
+    ap.add_argument("--allreduce", default="auto", choices=["auto", "nvls", "peer", "nccl"],
+                    help="gradient sum of view-parallel training (N > 1); auto = nvls where the box has multicast memory, else peer")
     ap.add_argument("--no-viewer", action="store_true", help="skip the viewer-frame line (SURVEY 8f-3)")
     ap.add_argument("--c3-epochs", type=int, default=100, help="epochs of 16 views for the config-3 loop")
     args = ap.parse_args()

@@ -134,10 +134,15 @@ class Gaussians:
 
 
 class Grads:
-    def __init__(self, ctx, capacity):
+    def __init__(self, ctx, capacity, external_ptr=None):
+        """external_ptr: device memory the caller owns (16 * capacity floats, capacity a multiple of 64), e.g. a symmetric
+        multicast-mapped allocation for the NVLS gradient sum (gs_grads_create_external)"""
         self.ctx = ctx
         self.h = C.c_void_p()
-        ctx.check(lib().gs_grads_create(ctx.h, C.c_uint32(capacity), C.byref(self.h)))
+        if external_ptr is None:
+            ctx.check(lib().gs_grads_create(ctx.h, C.c_uint32(capacity), C.byref(self.h)))
+        else:
+            ctx.check(lib().gs_grads_create_external(ctx.h, C.c_uint32(capacity), C.c_void_p(external_ptr), C.byref(self.h)))
 
     def zero(self, n):
         self.ctx.check(lib().gs_grads_zero(self.h, C.c_uint32(n)))
@@ -383,6 +388,13 @@ class PeerReduce:
         raw = b"".join(blobs)
         buf = (C.c_ubyte * len(raw)).from_buffer_copy(raw)
         self.ctx.check(lib().gs_dp_connect(self.h, buf))
+
+    def connect_ptrs(self, grads, peer_bufs, peer_flags, multicast_buf=None):
+        """gs_dp_connect_ptrs: pointers from a symmetric-memory rendezvous; multicast_buf != None -> in-switch (NVLS) sum"""
+        w = len(peer_bufs)
+        pb = (C.c_void_p * w)(*[C.c_void_p(int(p)) for p in peer_bufs])
+        pf = (C.c_void_p * w)(*[C.c_void_p(int(p)) for p in peer_flags])
+        self.ctx.check(lib().gs_dp_connect_ptrs(self.h, grads.h, pb, pf, C.c_void_p(int(multicast_buf)) if multicast_buf else None))
 
     def allreduce(self, grads, n):
         self.ctx.check(lib().gs_dp_allreduce_grads(self.h, grads.h, C.c_uint32(n)))

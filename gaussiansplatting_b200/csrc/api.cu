@@ -241,6 +241,7 @@ struct gs_grads {
     float* g = nullptr;         // 16 planes of `stride` floats
     uint32_t cap = 0, stride = 0;
     int stat_mode = 0;
+    bool external = false;      // g points into caller-owned memory (gs_grads_create_external): never freed, never regrown
     void* staging = nullptr;
     size_t staging_bytes = 0;
     GsGradPack view() const { GsGradPack G; G.g = g; G.stride = stride; return G; }
@@ -286,6 +287,7 @@ static int image_async_begin(gs_image* im, cudaStream_t* xfer) {
 static int grads_reserve(gs_grads* g, uint32_t n, bool exact = false) {
     if (n <= g->cap) return GS_OK;
     gs_ctx* c = g->c;
+    if (g->external) { c->err = "gradient buffer in caller-provided memory is too small (it cannot grow)"; return GS_ERR_CAPACITY; }
     GS_CUDA(c, cudaStreamSynchronize(c->stream));
     cudaFree(g->g); g->g = nullptr;
     g->cap = ((exact ? n : (uint32_t)(n * 1.25)) + 63u) & ~63u;
@@ -318,8 +320,24 @@ int gs_grads_destroy(gs_grads* g) {
     if (!g) return GS_OK;
     cudaSetDevice(g->c->device);
     cudaStreamSynchronize(g->c->stream);
-    cudaFree(g->g); cudaFree(g->staging);
+    if (!g->external) cudaFree(g->g);
+    cudaFree(g->staging);
     delete g;
+    return GS_OK;
+}
+// The gradient buffer in memory the CALLER owns: 16 planes of `capacity` floats at d_mem (capacity a multiple of 64, d_mem
+// 16-byte aligned).  For view-parallel training the caller passes a symmetric allocation that every rank of the node has
+// mapped and that has a multicast (NVLS) address, so that the per-Gaussian chain kernel writes the all-reduce payload in
+// place (gs_dp_connect_ptrs).  No counterpart in the reference (single device).
+int gs_grads_create_external(gs_ctx* c, uint32_t capacity, void* d_mem, gs_grads** out) {
+    GS_SETDEV(c);
+    GS_ARG(c, out && d_mem, "null argument");
+    GS_ARG(c, capacity >= 64u && capacity % 64u == 0u && ((uintptr_t)d_mem & 15u) == 0u, "capacity must be a multiple of 64 and the memory 16-byte aligned");
+    gs_grads* g = new (std::nothrow) gs_grads();
+    if (!g) return GS_ERR_OOM;
+    g->c = c; g->g = static_cast<float*>(d_mem); g->cap = capacity; g->stride = capacity; g->external = true;
+    if (cudaMemsetAsync(g->g, 0, (size_t)capacity * 16 * sizeof(float), c->stream) != cudaSuccess) { delete g; c->err = "cudaMemsetAsync on the caller's memory"; return GS_ERR_CUDA; }
+    *out = g;
     return GS_OK;
 }
 int gs_grads_zero(gs_grads* g, uint32_t n) {
@@ -1098,6 +1116,7 @@ struct gs_dp {
     uint32_t* h_err_dev = nullptr;      // its device-side address
     uint32_t epoch = 0;
     bool connected = false;
+    float* mc_buf = nullptr;            // multicast (NVLS) address of the ranks' gradient buffers, or null: plain peer loads / stores
     void* opened[2 * GS_MAX_PEERS] = {};
     GsPeerSet peers{};
 };
@@ -1160,6 +1179,27 @@ int gs_dp_connect(gs_dp* d, const void* blobs) {
     d->connected = true;
     return GS_OK;
 }
+// The same connection from pointers that are already valid in this process (a symmetric-memory rendezvous done by the caller,
+// e.g. torch.distributed._symmetric_memory): peer_bufs[q] = rank q's gradient buffer, peer_flags[q] = 3 * 8 zero-initialised
+// u32 flag words in rank q's memory, multicast_buf = the multicast address that maps ALL ranks' buffers (null = none).  With a
+// multicast address the sum runs in the NVSwitch: rank r issues multimem.ld_reduce over slice r (the switch adds the g copies)
+// and multimem.st broadcasts the result; per-GPU traffic drops from 2 (g-1)/g of the payload per direction to 1x.
+int gs_dp_connect_ptrs(gs_dp* d, gs_grads* g, void* const* peer_bufs, void* const* peer_flags, void* multicast_buf) {
+    gs_ctx* c = d->c; GS_SETDEV(c);
+    GS_ARG(c, g && g->g && peer_bufs && peer_flags, "null argument");
+    GS_ARG(c, peer_bufs[d->rank] == (void*)g->g, "peer_bufs[rank] must be this rank's gradient buffer");
+    d->peers.rank = d->rank; d->peers.world = d->world;
+    for (int q = 0; q < d->world; q++) {
+        GS_ARG(c, peer_bufs[q] && peer_flags[q], "null peer pointer");
+        d->peers.bufs[q] = static_cast<float*>(peer_bufs[q]); d->peers.flags[q] = static_cast<uint32_t*>(peer_flags[q]);
+    }
+    GS_CUDA(c, cudaMemsetAsync(peer_flags[d->rank], 0, 3 * GS_MAX_PEERS * sizeof(uint32_t), c->stream));
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));      // the caller runs a host barrier over the ranks before the first all-reduce
+    d->bound = g; d->bound_ptr = g->g;
+    d->mc_buf = static_cast<float*>(multicast_buf);
+    d->connected = true;
+    return GS_OK;
+}
 int gs_dp_allreduce_grads(gs_dp* d, gs_grads* g, uint32_t n) {
     gs_ctx* c = d->c; GS_SETDEV(c);
     if (d->world == 1) return GS_OK;
@@ -1171,7 +1211,7 @@ int gs_dp_allreduce_grads(gs_dp* d, gs_grads* g, uint32_t n) {
     // step poisoned (peer_reduce.cu); report it before another step is built on replicas that no longer agree
     if (*(volatile uint32_t*)d->h_err) { c->err = "peer all-reduce: a rank did not arrive within 5 s (an earlier gradient sum was withheld)"; return GS_ERR_NCCL; }
     d->epoch++;
-    gs_launch_peer_allreduce(d->peers, n, g->stride, d->epoch, d->d_err, d->h_err_dev, c->stream);
+    gs_launch_peer_allreduce(d->peers, d->mc_buf, n, g->stride, d->epoch, d->d_err, d->h_err_dev, c->stream);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
 }

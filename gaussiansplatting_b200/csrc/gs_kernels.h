@@ -175,7 +175,8 @@ void gs_launch_permute_moments(const float* src, uint32_t src_cap, float* dst, u
 // its 3 x GS_MAX_PEERS flag words, mapped into this process (q == rank: local memory)
 #define GS_MAX_PEERS 8
 struct GsPeerSet { float* bufs[GS_MAX_PEERS]; uint32_t* flags[GS_MAX_PEERS]; int rank, world; };
-void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
+// mc = multicast (NVLS) address of the ranks' buffers or null (plain peer loads / stores, sums in rank order)
+void gs_launch_peer_allreduce(const GsPeerSet& P, float* mc, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
                               cudaStream_t st);
 
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)

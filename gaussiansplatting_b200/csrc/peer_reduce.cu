@@ -99,9 +99,41 @@ __global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ 
     }
 }
 
+// NVLS variant: the NVSwitch adds.  Rank r owns slice r: multimem.ld_reduce on the multicast address returns the sum of the
+// g copies of a 16-byte vector (one switch-side reduction, fp32 accumulate), multimem.st writes it to all g copies.  Every
+// element is reduced exactly once and the one result is broadcast, so all ranks hold bit-identical sums; the order of the
+// additions inside the switch is the hardware's (the rank-ordered kernel above stays the mode whose order is specified).
+__global__ void __launch_bounds__(256) dp_reduce_mc_kernel(float4* __restrict__ mc, float4* __restrict__ own, uint32_t n4, uint32_t stride4,
+                                                           uint32_t v0, uint32_t v1, const uint32_t* __restrict__ err) {
+    constexpr int U = 4;
+    const uint32_t T = gridDim.x * blockDim.x;
+    if (*err) {                                                 // see dp_reduce_kernel: withhold the sum, poison the step
+        const float qn = __int_as_float(0x7FC00000);
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += T) own[i] = make_float4(qn, qn, qn, qn);
+        return;
+    }
+    for (uint32_t vb = v0 + blockIdx.x * blockDim.x + threadIdx.x; vb < v1; vb += U * T) {
+        float4 x[U];
+        float4* p[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const uint32_t v = vb + (uint32_t)u * T;
+            p[u] = mc + vec_offset(v < v1 ? v : vb, n4, stride4);
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(x[u].x), "=f"(x[u].y), "=f"(x[u].z), "=f"(x[u].w) : "l"(p[u]) : "memory");
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (vb + (uint32_t)u * T >= v1) break;
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                         :: "l"(p[u]), "f"(x[u].x), "f"(x[u].y), "f"(x[u].z), "f"(x[u].w) : "memory");
+        }
+    }
+}
+
 }  // namespace
 
-void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
+void gs_launch_peer_allreduce(const GsPeerSet& P, float* mc, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
                               cudaStream_t st) {
     const uint32_t n4 = (n + 3u) / 4u, stride4 = stride / 4u;
     const uint32_t V = 16u * n4;
@@ -109,7 +141,9 @@ void gs_launch_peer_allreduce(const GsPeerSet& P, uint32_t n, uint32_t stride, u
     const uint32_t v0 = std::min(V, per * (uint32_t)P.rank), v1 = std::min(V, v0 + per);
     const int grid = 148 * 8;
     dp_barrier_kernel<<<1, 32, 0, st>>>(P, 0, epoch, err, host_err);
-    if (v1 > v0) {
+    if (v1 > v0 && mc) {
+        dp_reduce_mc_kernel<<<148 * 4, 256, 0, st>>>(reinterpret_cast<float4*>(mc), reinterpret_cast<float4*>(P.bufs[P.rank]), n4, stride4, v0, v1, err);
+    } else if (v1 > v0) {
         switch (P.world) {
 #define GS_DP_CASE(W) case W: dp_reduce_kernel<W><<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1, err); break;
             GS_DP_CASE(2) GS_DP_CASE(3) GS_DP_CASE(4) GS_DP_CASE(5) GS_DP_CASE(6) GS_DP_CASE(7) GS_DP_CASE(8)

@@ -90,3 +90,34 @@ class ViewParallel:
         import torch
         ptr, nfl, _ = grads_handle.packed()
         return torch.as_tensor(CudaArrayView(ptr, nfl), device="cuda")
+
+
+class SymmetricGrads:
+    """The packed gradient buffer of view-parallel training in SYMMETRIC memory: every rank of the node maps every other rank's
+    buffer and the NVSwitch maps all of them at one multicast address, so that gs_dp_allreduce_grads can reduce in the
+    switch (multimem.ld_reduce / multimem.st, csrc/peer_reduce.cu).  torch.distributed._symmetric_memory does the plumbing
+    (allocation + handle exchange); the kernels are this library's.  use_multicast=False keeps the rank-ordered peer kernel
+    on the same pointers."""
+    FLAG_FLOATS = 64                      # 24 u32 flag words per rank live behind the 16 planes
+
+    def __init__(self, gs, ctx, dist, capacity, device, use_multicast=True):
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        self.capacity = (int(capacity) + 63) // 64 * 64
+        self.tensor = symm_mem.empty(16 * self.capacity + self.FLAG_FLOATS, dtype=torch.float32, device=torch.device("cuda", device))
+        self.tensor.zero_()
+        torch.cuda.synchronize(device)
+        self.handle = symm_mem.rendezvous(self.tensor, dist.group.WORLD.group_name)
+        rank, world = dist.get_rank(), dist.get_world_size()
+        bufs = [int(p) for p in self.handle.buffer_ptrs]
+        assert bufs[rank] == self.tensor.data_ptr()
+        flags = [p + 16 * self.capacity * 4 for p in bufs]
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        self.multicast = bool(mc) and use_multicast
+        self.grads = gs.Grads(ctx, self.capacity, external_ptr=bufs[rank])
+        self.reduce = gs.PeerReduce(ctx, rank, world)
+        self.reduce.connect_ptrs(self.grads, bufs, flags, mc if self.multicast else None)
+        dist.barrier()                    # every rank's flag words are zero before anybody signals
+
+    def close(self):
+        self.reduce.close(); self.grads.close()

@@ -135,6 +135,11 @@ int gs_gaussians_positions(gs_gaussians*, void* dptr_float4);
 
 /* ---- gradient buffer ------------------------------------------------------------------------------------ */
 int gs_grads_create(gs_ctx*, uint32_t capacity, gs_grads** out);
+/* The gradient buffer in CALLER-OWNED device memory: 16 planes of `capacity` floats at d_mem (capacity a multiple of 64, d_mem
+ * 16-byte aligned); zeroed here, never freed or regrown by the library (GS_ERR_CAPACITY where gs_grads_create's buffer would
+ * grow).  No counterpart in the reference (one device): it lets view-parallel training keep the all-reduce payload in a
+ * symmetric, multicast-mapped allocation that the NVSwitch can reduce in place (gs_dp_connect_ptrs). */
+int gs_grads_create_external(gs_ctx*, uint32_t capacity, void* d_mem, gs_grads** out);
 int gs_grads_destroy(gs_grads*);
 int gs_grads_zero(gs_grads*, uint32_t n);
 int gs_grads_upload(gs_grads*, const gs_gradients* host, uint32_t n);     /* SH-rest gradients must be 0 (never produced) */
@@ -163,6 +168,14 @@ int gs_dp_create(gs_ctx*, int rank, int world, gs_dp** out);
 int gs_dp_destroy(gs_dp*);
 int gs_dp_export(gs_dp*, gs_grads*, void* blob_out);
 int gs_dp_connect(gs_dp*, const void* blobs_in_rank_order);
+/* The same connection from pointers already valid in this process (a symmetric-memory rendezvous done by the caller, e.g.
+ * torch.distributed._symmetric_memory; replaces steps 2-3): peer_bufs[q] = rank q's gradient buffer (peer_bufs[rank] must be
+ * the buffer of `grads`), peer_flags[q] = 24 u32 flag words in rank q's memory (this rank's are zeroed here; run a host
+ * barrier over the ranks before the first all-reduce), multicast_buf = the multicast (NVLS) address mapping ALL ranks'
+ * buffers, or NULL.  With a multicast address gs_dp_allreduce_grads reduces IN THE NVSWITCH: rank r issues multimem.ld_reduce
+ * over slice r and multimem.st broadcasts the sum, so a GPU moves 1x the payload per direction instead of 2 (g-1)/g x; every
+ * rank still ends with bit-identical sums (one reduction per element, broadcast), in the switch's order of addition. */
+int gs_dp_connect_ptrs(gs_dp*, gs_grads* grads, void* const* peer_bufs, void* const* peer_flags, void* multicast_buf);
 int gs_dp_allreduce_grads(gs_dp*, gs_grads*, uint32_t n);
 int gs_dp_check(gs_dp*);
 

@@ -213,3 +213,62 @@ def test_one_process_two_devices_sort_on_both(gs):
         finally:
             S.close(); c.close()
         assert np.array_equal(k, keys[o]) and np.array_equal(v, vals[o]), dev
+
+
+def _nvls_worker(rank, world, port, n, steps, out_dir):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from gaussiansplatting_b200 import capi as gs, dp
+    ctx = gs.Context(rank)
+    res = {"multicast": False, "ok": True}
+    try:
+        SG = dp.SymmetricGrads(gs, ctx, dist, n, rank)
+        res["multicast"] = SG.multicast
+        for s in range(steps):
+            SG.grads.upload(_grads_for(rank + 10 * s, n))
+            dist.barrier()
+            SG.reduce.allreduce(SG.grads, n)
+            SG.reduce.check()
+            got = SG.grads.download(n)
+            for f in ("position", "opacity", "scale", "rotation", "sh", "viewspace"):
+                want = _grads_for(0 + 10 * s, n)[f].astype(np.float64)
+                for q in range(1, world):
+                    want = want + _grads_for(q + 10 * s, n)[f]
+                w32 = want.astype(np.float32)
+                # two ranks: one rounding, so the switch's sum IS float32(a + b); more ranks: its order of addition is unspecified
+                if world == 2:
+                    res["ok"] &= bool(np.array_equal(got[f], w32))
+                else:
+                    res["ok"] &= bool(np.all(np.abs(got[f] - want) <= 4e-7 * np.maximum(np.abs(want), 1.0) * world))
+        # a second buffer size through the same objects is not possible (external memory cannot grow): must be loud
+        try:
+            SG.grads.upload(_grads_for(0, SG.capacity + 64)); res["grow"] = "no error"
+        except gs.GsError as e:
+            res["grow"] = str(e)
+        SG.close()
+    except Exception as e:
+        res["error"] = repr(e)
+    np.save(os.path.join(out_dir, f"nvls_{rank}.npy"), np.array([repr(res)]))
+    ctx.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [1000, 250007])
+def test_nvls_allreduce_in_the_switch(tmp_path, n):
+    """gs_grads_create_external + gs_dp_connect_ptrs: the gradient sum by multimem.ld_reduce / multimem.st on a symmetric,
+    multicast-mapped buffer (plumbing: torch.distributed._symmetric_memory); every rank ends with the same bits"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    mp.spawn(_nvls_worker, args=(2, 29720 + (n % 7), n, 3, str(tmp_path)), nprocs=2, join=True)
+    res = [eval(str(np.load(tmp_path / f"nvls_{r}.npy")[0])) for r in range(2)]
+    if not res[0].get("multicast") and "error" not in res[0]:
+        pytest.skip("no multicast (NVLS) memory on this box")
+    for r in res:
+        assert "error" not in r, r
+        assert r["ok"] and "cannot grow" in r["grow"], r
