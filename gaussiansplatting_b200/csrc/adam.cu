@@ -81,6 +81,11 @@ __global__ void __launch_bounds__(256, 4) adam_kernel(GsParams P, GsGradPack G, 
             const float mag = gs::fsqrt(gs::fadd(gs::fadd(gs::fmul(up[0], up[0]), gs::fmul(up[1], up[1])), gs::fmul(up[2], up[2])));
             if (mag > 0.1f) { const float s = gs::fdiv(0.1f, mag); up[0] = gs::fmul(up[0], s); up[1] = gs::fmul(up[1], s); up[2] = gs::fmul(up[2], s); }
             const float n0 = gs::fsub(p[0][e], up[0]), n1 = gs::fsub(p[1][e], up[1]), n2 = gs::fsub(p[2][e], up[2]);
+            // INVARIANT the other 17 jobs of this launch rely on: they re-evaluate the whole-Gaussian skip predicate from position
+            // plane 0 (adam_skip4) while this job may already have stored the new position.  That is only sound because a
+            // stored x never flips the predicate: a position is accepted only if it is not NaN and |x| < 1e6 (so also finite),
+            // and the predicate tests exactly isnan / isinf / |x| > 1e6.  Whoever changes this acceptance test or the clamp must
+            // compute the predicate once from a snapshot instead.
             if (!isnan(n0) && !isnan(n1) && !isnan(n2) && fabsf(n0) < 1e6f && fabsf(n1) < 1e6f && fabsf(n2) < 1e6f) {
                 p[0][e] = n0; p[1][e] = n1; p[2][e] = n2;
             }

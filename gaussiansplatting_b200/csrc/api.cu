@@ -24,6 +24,7 @@ struct gs_ctx {
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
 static int g_tile_order = 1;                        // blend CTAs take the tiles longest list first (tile_order_kernel)
+static int g_depth_prehist = 1;      // K1 fills the depth sort's histograms (0: the sort runs its own histogram kernel)
 static int g_emit_fused = 1;                        // binned pipeline: scan + coarse emit + bin histogram as one kernel
 static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
 static void gs_set_sort_mode(int v);
@@ -66,6 +67,10 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "sort_hybrid")) { gs_tune_sort_hybrid(value); return GS_OK; }
     if (!strcmp(name, "sort_even")) { gs_tune_sort_even(value); return GS_OK; }
     if (!strcmp(name, "emit_fused")) { g_emit_fused = value ? 1 : 0; return GS_OK; }
+    if (!strcmp(name, "dp_mc_grid")) { gs_tune_dp_mc(0, value); return GS_OK; }
+    if (!strcmp(name, "dp_mc_threads")) { gs_tune_dp_mc(1, value); return GS_OK; }
+    if (!strcmp(name, "dp_mc_unroll")) { gs_tune_dp_mc(2, value); return GS_OK; }
+    if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     return GS_ERR_ARG;
@@ -542,6 +547,7 @@ struct gs_rast {
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
+    bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
     void mark(int i) { if (prof) cudaEventRecord(ev[i], c->stream); }
@@ -719,7 +725,8 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     while ((1u << tile_bits) < tiles) tile_bits++;
     // depth order of the Gaussians: keys = depth bits (bit 31 is always set: depth > 0.1), values = index
     const GsSortPlan dplan = gs_sort_plan(0, 31, ~0ull);
-    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, GS_SORT_HINT_DISTINCT, r->dsort_scratch, st);
+    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan,
+                                      GS_SORT_HINT_DISTINCT | (r->depth_prehist ? GS_SORT_HINT_PREHIST : 0), r->dsort_scratch, st);
     const uint32_t* perm = r->perm_buf[dres];
     r->mark(2);
     gs_launch_exclusive_scan(r->proj.cnt, perm, r->proj.offs, n, r->meta + GS_META_TOTAL_PAIRS, r->scan_scratch, st);
@@ -772,7 +779,8 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
     int bin_bits = 0;
     while ((1u << bin_bits) < nbins) bin_bits++;
     const GsSortPlan dplan = gs_sort_plan(0, 31, ~0ull);
-    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan, GS_SORT_HINT_DISTINCT, r->dsort_scratch, st);
+    const int dres = gs_launch_sort32(r->proj.dkey, r->iota, r->dk_buf, r->perm_buf, n, nullptr, dplan,
+                                      GS_SORT_HINT_DISTINCT | (r->depth_prehist ? GS_SORT_HINT_PREHIST : 0), r->dsort_scratch, st);
     const uint32_t* perm = r->perm_buf[dres];
     r->mark(2);
     uint32_t* d_coarse = r->meta + GS_META_COARSE_PAIRS;
@@ -851,8 +859,11 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     }
     r->mark(0);
     // the reference overrides numTilesX/Y/numGaussians from the texture size and live count (:308-311)
+    // binned / hoisted pipelines: K1 also fills the digit histograms of the depth sort that follows (its scratch is cleared here)
+    r->depth_prehist = (r->mode != 1 && g_depth_prehist && n > 0);
+    uint32_t* dhist = r->depth_prehist ? gs_sort_prepare(n, gs_sort_plan(0, 31, ~0ull), r->dsort_scratch, st) : nullptr;
     gs_launch_preprocess(g->view(), r->proj, u->viewMatrix, u->viewProjectionMatrix, u->screenSize[0], u->screenSize[1],
-                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->mode == 1 ? r->meta : nullptr, st);
+                         u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->mode == 1 ? r->meta : nullptr, dhist, st);
     r->mark(1);
     GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : r->mode == 2 ? forward_hoisted(r, g, u, out) : forward_binned(r, g, u, out));
     return image_after_use(out, st);
@@ -941,9 +952,9 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
             if (r->mode == 1) { src = which == GS_RAST_KEYS ? (const void*)r->keys_in : (const void*)r->vals_in; }
             else if (r->pairs) {
                 // hoisted mode never materialises the reference's pre-sort list: rebuild it (Gaussian order, u64 keys) on demand
-                GS_CUDA(c, cudaMalloc(&tmp[0], ((size_t)r->n + 1) * 4));
-                GS_CUDA(c, cudaMalloc(&tmp[1], r->pairs * 8));
-                GS_CUDA(c, cudaMalloc(&tmp[2], r->pairs * 4));
+                if (cudaMalloc(&tmp[0], ((size_t)r->n + 1) * 4) != cudaSuccess) { cudaGetLastError(); c->err = "cudaMalloc (inspection buffer)"; rc = GS_ERR_OOM; break; }
+                if (cudaMalloc(&tmp[1], r->pairs * 8) != cudaSuccess) { cudaGetLastError(); c->err = "cudaMalloc (inspection buffer)"; rc = GS_ERR_OOM; break; }
+                if (cudaMalloc(&tmp[2], r->pairs * 4) != cudaSuccess) { cudaGetLastError(); c->err = "cudaMalloc (inspection buffer)"; rc = GS_ERR_OOM; break; }
                 gs_launch_exclusive_scan(r->proj.cnt, nullptr, (uint32_t*)tmp[0], r->n, r->meta + GS_META_COUNT - 1, r->scan_scratch, st);
                 gs_launch_emit_pairs(r->proj, (const uint32_t*)tmp[0], r->n, r->ntx, (uint64_t*)tmp[1], (uint32_t*)tmp[2], (uint32_t)r->pairs, st);
                 src = which == GS_RAST_KEYS ? tmp[1] : tmp[2];
@@ -952,7 +963,7 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
         case GS_RAST_SORTED_KEYS:
             if (r->mode == 1) src = r->sorted_keys;
             else if (r->pairs) {
-                GS_CUDA(c, cudaMalloc(&tmp[0], r->pairs * 8));
+                if (cudaMalloc(&tmp[0], r->pairs * 8) != cudaSuccess) { cudaGetLastError(); c->err = "cudaMalloc (inspection buffer)"; rc = GS_ERR_OOM; break; }
                 if (r->mode == 0) gs_launch_rebuild_keys64_ranges(r->ranges, r->ntx * r->nty, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
                 else gs_launch_rebuild_keys64(r->sorted_tiles, r->sorted_vals, r->proj.dkey, (uint32_t)r->pairs, (uint64_t*)tmp[0], st);
                 src = tmp[0];
@@ -964,7 +975,7 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
         case GS_RAST_TFINAL: src = r->tfinal; need = (size_t)r->W * r->H * 4; break;
         default: GS_ARG(c, false, "which");
     }
-    if (bytes < need) { c->err = "bad argument: host buffer too small"; rc = GS_ERR_ARG; }
+    if (rc == GS_OK && bytes < need) { c->err = "bad argument: host buffer too small"; rc = GS_ERR_ARG; }
     if (rc == GS_OK && need && cudaMemcpyAsync(host, src, need, cudaMemcpyDeviceToHost, st) != cudaSuccess) { c->err = "cudaMemcpyAsync"; rc = GS_ERR_CUDA; }
     if (cudaStreamSynchronize(st) != cudaSuccess && rc == GS_OK) { c->err = "cudaStreamSynchronize"; rc = GS_ERR_CUDA; }
     for (void* t : tmp) cudaFree(t);
@@ -996,6 +1007,21 @@ struct sort_obj {
 };
 struct gs_sort64 : sort_obj<uint64_t> {};
 struct gs_sort32 : sort_obj<uint32_t> {};
+// getSortedKeys / getSortedValues hand out the sorter's own ping-pong buffers as borrowed pointers: fed straight back into sort()
+// (re-sorting a result) pass 0 would scatter into the buffer it reads and the hybrid plan's LSD fallback would start from
+// overwritten input.  true = [p, p + bytes) overlaps one of the sorter's internal buffers.
+template <typename S>
+static bool sort_input_aliases(const S* s, const void* p, size_t bytes, size_t key_bytes) {
+    if (!p || !bytes) return false;
+    const char* a = static_cast<const char*>(p);
+    for (int i = 0; i < 2; i++) {
+        const char* k = reinterpret_cast<const char*>(s->kbuf[i]);
+        const char* v = reinterpret_cast<const char*>(s->vbuf[i]);
+        if (k && a < k + (size_t)s->cap * key_bytes && k < a + bytes) return true;
+        if (v && a < v + (size_t)s->cap * 4 && v < a + bytes) return true;
+    }
+    return false;
+}
 
 template <typename S>
 static void sort_free(S* s) {
@@ -1042,6 +1068,8 @@ int gs_sort64_sort(gs_sort64* s, const uint64_t* d_keys, const uint32_t* d_vals,
     GS_ARG(c, (d_keys && d_vals) || n == 0, "null input");
     if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
     GS_TRY(sort_reserve(s, n, false));
+    GS_ARG(c, !sort_input_aliases(s, d_keys, n * 8, 8) && !sort_input_aliases(s, d_vals, n * 4, 8),
+           "input aliases the sorter's own result buffers (copy a previous result out before sorting it again)");
     const GsSortPlan plan = gs_sort_plan(begin_bit, end_bit, ~0ull);
     s->result = gs_launch_sort64(d_keys, d_vals, s->kbuf, s->vbuf, n, plan, g_sort_api_hint, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);
@@ -1079,6 +1107,8 @@ int gs_sort32_sort(gs_sort32* s, const uint32_t* d_keys, const uint32_t* d_vals,
     gs_ctx* c = s->c; GS_SETDEV(c);
     if (n >= (1ull << 30)) { c->err = "element count exceeds 2^30"; return GS_ERR_CAPACITY; }
     GS_TRY(sort_reserve(s, n, true));
+    GS_ARG(c, !sort_input_aliases(s, d_keys, n * 4, 4) && !sort_input_aliases(s, d_vals, n * 4, 4),
+           "input aliases the sorter's own result buffers (copy a previous result out before sorting it again)");
     const GsSortPlan plan = gs_sort_plan(0, 32, ~0ull);               // 4 passes x 8 bits, gpu_sort.hpp:34
     s->result = gs_launch_sort32(d_keys, d_vals, s->kbuf, s->vbuf, n, nullptr, plan, g_sort_api_hint, s->scratch, c->stream);
     GS_LAUNCH_CHECK(c);

@@ -10,7 +10,7 @@ enum { GS_META_TOTAL_PAIRS = 0, GS_META_KEY_OR = 1, GS_META_KEY_AND = 2, GS_META
 
 // K1 ------------------------------------------------------------------------------------------------
 void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* V, const float* VP, float sw, float sh,
-                          float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, cudaStream_t st);
+                          float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, uint32_t* depth_hist, cudaStream_t st);
 
 // K2: exclusive scan: out[j] = sum_{j'<j} in[perm ? perm[j'] : j']; out[n] and *total receive the sum (in == out allowed
 // when perm is null).  scratch: gs_scan_scratch_bytes(n).
@@ -179,6 +179,7 @@ struct GsPeerSet { float* bufs[GS_MAX_PEERS]; uint32_t* flags[GS_MAX_PEERS]; int
 void gs_launch_peer_allreduce(const GsPeerSet& P, float* mc, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
                               cudaStream_t st);
 
+void gs_tune_dp_mc(int which, int v);   // in-switch reduce: 0 grid, 1 threads per CTA, 2 vectors in flight per thread
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
 void gs_tune_fwd_ppt(int v);
 void gs_tune_bwd_ppt(int v);

@@ -103,9 +103,9 @@ __global__ void __launch_bounds__(256) dp_reduce_kernel(const __grid_constant__ 
 // g copies of a 16-byte vector (one switch-side reduction, fp32 accumulate), multimem.st writes it to all g copies.  Every
 // element is reduced exactly once and the one result is broadcast, so all ranks hold bit-identical sums; the order of the
 // additions inside the switch is the hardware's (the rank-ordered kernel above stays the mode whose order is specified).
-__global__ void __launch_bounds__(256) dp_reduce_mc_kernel(float4* __restrict__ mc, float4* __restrict__ own, uint32_t n4, uint32_t stride4,
+template <int U>
+__global__ void __launch_bounds__(512) dp_reduce_mc_kernel(float4* __restrict__ mc, float4* __restrict__ own, uint32_t n4, uint32_t stride4,
                                                            uint32_t v0, uint32_t v1, const uint32_t* __restrict__ err) {
-    constexpr int U = 4;
     const uint32_t T = gridDim.x * blockDim.x;
     if (*err) {                                                 // see dp_reduce_kernel: withhold the sum, poison the step
         const float qn = __int_as_float(0x7FC00000);
@@ -133,6 +133,14 @@ __global__ void __launch_bounds__(256) dp_reduce_mc_kernel(float4* __restrict__ 
 
 }  // namespace
 
+// launch shape of the in-switch reduce (gs_tune "dp_mc_grid" / "dp_mc_threads" / "dp_mc_unroll"; swept on 8 GPUs by tools/allreduce_probe.py)
+static int g_mc_grid = 148 * 4, g_mc_threads = 256, g_mc_unroll = 4;
+void gs_tune_dp_mc(int which, int v) {
+    if (which == 0 && v >= 1 && v <= 148 * 16) g_mc_grid = v;
+    if (which == 1 && v >= 32 && v <= 512 && v % 32 == 0) g_mc_threads = v;
+    if (which == 2 && (v == 1 || v == 2 || v == 4 || v == 8)) g_mc_unroll = v;
+}
+
 void gs_launch_peer_allreduce(const GsPeerSet& P, float* mc, uint32_t n, uint32_t stride, uint32_t epoch, uint32_t* err, uint32_t* host_err,
                               cudaStream_t st) {
     const uint32_t n4 = (n + 3u) / 4u, stride4 = stride / 4u;
@@ -142,7 +150,12 @@ void gs_launch_peer_allreduce(const GsPeerSet& P, float* mc, uint32_t n, uint32_
     const int grid = 148 * 8;
     dp_barrier_kernel<<<1, 32, 0, st>>>(P, 0, epoch, err, host_err);
     if (v1 > v0 && mc) {
-        dp_reduce_mc_kernel<<<148 * 4, 256, 0, st>>>(reinterpret_cast<float4*>(mc), reinterpret_cast<float4*>(P.bufs[P.rank]), n4, stride4, v0, v1, err);
+        float4* m4 = reinterpret_cast<float4*>(mc); float4* o4 = reinterpret_cast<float4*>(P.bufs[P.rank]);
+        const int g = g_mc_grid, t = g_mc_threads;
+        if (g_mc_unroll == 1) dp_reduce_mc_kernel<1><<<g, t, 0, st>>>(m4, o4, n4, stride4, v0, v1, err);
+        else if (g_mc_unroll == 2) dp_reduce_mc_kernel<2><<<g, t, 0, st>>>(m4, o4, n4, stride4, v0, v1, err);
+        else if (g_mc_unroll == 8) dp_reduce_mc_kernel<8><<<g, t, 0, st>>>(m4, o4, n4, stride4, v0, v1, err);
+        else dp_reduce_mc_kernel<4><<<g, t, 0, st>>>(m4, o4, n4, stride4, v0, v1, err);
     } else if (v1 > v0) {
         switch (P.world) {
 #define GS_DP_CASE(W) case W: dp_reduce_kernel<W><<<grid, 256, 0, st>>>(P, n4, stride4, v0, v1, err); break;

@@ -25,9 +25,21 @@ __device__ __forceinline__ float dot3(float a0, float b0, float a1, float b1, fl
     return gs::fadd(gs::fadd(gs::fmul(a0, b0), gs::fmul(a1, b1)), gs::fmul(a2, b2));
 }
 
+// dhist (optional): the digit histograms of the coming depth sort (4 passes over bits 0..30 of dkey, gs_sort_plan(0, 31)):
+// hist[p * 256 + d] += number of keys whose digit p is d.  The grid is persistent (a CTA strides over 256-Gaussian chunks), so a
+// CTA keeps its four 256-bin histograms in shared memory over all its chunks and flushes them once: the sort then runs with
+// GS_SORT_HINT_PREHIST, without its own clear + histogram kernel (one launch and one pass over the keys less per frame).
 __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected O, const __grid_constant__ Uni u,
-                                                         uint32_t* __restrict__ meta) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+                                                         uint32_t* __restrict__ meta, uint32_t* __restrict__ dhist) {
+    __shared__ uint32_t s_hist[4][256];
+    if (dhist) {
+#pragma unroll
+        for (int p = 0; p < 4; p++) s_hist[p][threadIdx.x] = 0u;
+        __syncthreads();
+    }
+    uint32_t acc_or = 0u, acc_and = 0xFFFFFFFFu;
+  for (uint32_t base = blockIdx.x * blockDim.x; base < u.n; base += gridDim.x * blockDim.x) {
+    const uint32_t i = base + threadIdx.x;
     const bool live = i < u.n;
     uint32_t count = 0, dkey = 0;
     if (live) {
@@ -141,14 +153,26 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
         O.bbox[i] = bb; O.aux[i] = ax; O.covc[i] = cc;
         O.cnt[i] = count;
         O.ccnt[i] = count ? ((bb.z >> 3) - (bb.x >> 3) + 1u) * ((bb.w >> 3) - (bb.y >> 3) + 1u) : 0u;
-        O.dkey[i] = count ? dkey : 0xFFFFFFFFu;
+        const uint32_t dk = count ? dkey : 0xFFFFFFFFu;
+        O.dkey[i] = dk;
+        if (dhist) {
+            atomicAdd(&s_hist[0][dk & 255u], 1u); atomicAdd(&s_hist[1][(dk >> 8) & 255u], 1u);
+            atomicAdd(&s_hist[2][(dk >> 16) & 255u], 1u); atomicAdd(&s_hist[3][(dk >> 24) & 127u], 1u);
+        }
+    }
+    if (count) { acc_or |= dkey; acc_and &= dkey; }
+  }
+    if (dhist) {
+        __syncthreads();
+#pragma unroll
+        for (int p = 0; p < 4; p++) { const uint32_t h = s_hist[p][threadIdx.x]; if (h) atomicAdd(&dhist[p * 256 + threadIdx.x], h); }
     }
     // depth-key OR / AND over Gaussians that emit pairs: digits whose bits never vary need no sort pass (only the literal
     // 64-bit pipeline reads them; two same-address atomics per warp are not free, so the other pipelines skip them)
     if (meta == nullptr) return;
     __shared__ uint32_t s_or[8], s_and[8];
-    const uint32_t kor = __reduce_or_sync(0xFFFFFFFFu, count ? dkey : 0u);
-    const uint32_t kand = __reduce_and_sync(0xFFFFFFFFu, count ? dkey : 0xFFFFFFFFu);
+    const uint32_t kor = __reduce_or_sync(0xFFFFFFFFu, acc_or);
+    const uint32_t kand = __reduce_and_sync(0xFFFFFFFFu, acc_and);
     if (gs::lane_id() == 0) { s_or[threadIdx.x >> 5] = kor; s_and[threadIdx.x >> 5] = kand; }
     __syncthreads();
     if (threadIdx.x == 0) {                                  // one pair of atomics per CTA (same-address atomics serialise)
@@ -163,10 +187,13 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
 }  // namespace
 
 void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* V, const float* VP, float sw, float sh,
-                          float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, cudaStream_t st) {
+                          float fx, float fy, uint32_t ntx, uint32_t nty, uint32_t n, uint32_t* meta, uint32_t* depth_hist, cudaStream_t st) {
     if (n == 0) return;
     Uni u;
     for (int k = 0; k < 16; k++) { u.V[k] = V[k]; u.VP[k] = VP[k]; }
     u.sw = sw; u.sh = sh; u.fx = fx; u.fy = fy; u.ntx = ntx; u.nty = nty; u.n = n;
-    preprocess_kernel<<<(n + 255) / 256, 256, 0, st>>>(P, O, u, meta);
+    // persistent grid when the histograms ride along (one flush of 4 x 256 bins per CTA); one chunk per CTA otherwise
+    const uint32_t chunks = (n + 255u) / 256u;
+    const uint32_t grid = depth_hist ? (chunks < 148u * 8u ? chunks : 148u * 8u) : chunks;
+    preprocess_kernel<<<grid, 256, 0, st>>>(P, O, u, meta, depth_hist);
 }

@@ -229,6 +229,9 @@ public:
                 const bool shouldDensify = totalIterations > S.densifyFromIter && totalIterations < S.densifyUntilIter &&
                                            totalIterations % S.densityControlInterval == 0;                   // :1112-1114
                 if (shouldDensify) {
+                    // apply() ends with a read-back of the new count (a stream drain, as the reference's CPU apply needs one): drain
+                    // the training steps still queued FIRST, so that densifySeconds is the event's own cost and not theirs
+                    device->waitUntilCompleted();
                     const auto d0 = std::chrono::high_resolution_clock::now();
                     const TrainingView& v = trainingImages[imgIdx];
                     const size_t oldCount = gaussianCount;

@@ -343,3 +343,25 @@ def test_sort64_one_wave_tile_sizes_agree(gs, ctx, n):
     finally:
         gs.tune("sort_even", 1)
         S.close()
+
+
+def test_sort_rejects_its_own_result_buffers_as_input(gs, ctx):
+    """getSortedKeys / getSortedValues are borrowed pointers into the sorter's ping-pong buffers; sorting them in
+    place would read what pass 0 overwrites, so it is an argument error (copy the result out first)"""
+    n = 5000
+    keys = synth.splitmix64(77, n, 1)
+    vals = np.arange(n, dtype=np.uint32)
+    S = gs.Sort64(ctx, n)
+    dk, dv = ctx.alloc(n * 8), ctx.alloc(n * 4)
+    try:
+        ctx.upload(dk, keys); ctx.upload(dv, vals)
+        S.sort(dk, dv, n); ctx.sync()
+        with pytest.raises(gs.GsError, match="aliases"):
+            S.sort(S.sorted_keys, dv, n)
+        with pytest.raises(gs.GsError, match="aliases"):
+            S.sort(dk, S.sorted_values, n)
+        S.sort(dk, dv, n); ctx.sync()                      # the sorter is still usable
+        o = np.argsort(keys, kind="stable")
+        assert np.array_equal(ctx.download(S.sorted_keys, n, np.uint64), keys[o])
+    finally:
+        ctx.free(dk); ctx.free(dv); S.close()

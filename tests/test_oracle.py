@@ -376,3 +376,26 @@ def test_logging_loss_against_an_independent_float64_statement(orc):
     assert abs(orc.loss(a, b, lambda_dssim=0.0) - l1.mean()) <= 1e-6
     aq = np.floor(np.clip(a, 0, 1) * 255 + 0.5).astype(np.float32) / 255
     assert abs(orc.loss(a, b, quantize=True) - orc.loss(aq, b)) <= 1e-7
+
+
+def test_half_precision_forward_mode_stays_close_to_the_graded_fp32_mode(orc):
+    """SURVEY note H: the Metal kernel blends in `half` (tiled_shaders.metal:325-370).  orc.forward_half emulates that typing
+    with _Float16; it is not graded, it quantifies how far the reference's precision choice moves the result: image within
+    ~1e-2 (half has 11 significant bits and the colour sum has up to hundreds of terms), lastContribIdx on almost all pixels"""
+    n, W, H = 2000, 160, 128
+    g = synth.make_scene(n, 103, 0.02)
+    u = synth.make_camera(5, 8, W, H, n)
+    r = orc.render(g, u)
+    img_h, last_h = orc.forward_half(r["proj"], r["svals"], r["ranges"], u)
+    d = np.abs(img_h - r["image"])[..., :3]
+    assert 1e-5 < d.max() < 2e-2 and d.mean() < 1e-3, (d.max(), d.mean())
+    assert (last_h != r["last"]).mean() < 0.01
+    assert np.all(img_h[..., 3] == 1) and img_h.min() >= 0 and img_h.max() <= 1.001
+    # a pixel without a contributor is exactly the white background (the half thresholds differ in the last bits from the
+    # fp32 ones, so a few pixels have a contributor in one mode only)
+    empty = last_h == 0xFFFFFFFF
+    assert empty.any() and np.all(img_h[empty][:, :3] == 1)
+    assert ((r["last"] == 0xFFFFFFFF) != empty).mean() < 0.01
+    # thread count does not matter
+    img2, last2 = orc.forward_half(r["proj"], r["svals"], r["ranges"], u, threads=4)
+    assert np.array_equal(img2, img_h) and np.array_equal(last2, last_h)

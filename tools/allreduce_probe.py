@@ -46,5 +46,39 @@ if rank == 0:
     ms = e0.elapsed_time(e1) / 20
     print(f"peer kernels: {ms * 1e3:.0f} us per 64 MB all-reduce, algbw {64e6 / ms / 1e6:.0f} GB/s", flush=True)
 dist.barrier()
+
+# ---- the in-switch (NVLS) sum on symmetric multicast memory, swept over the launch shape of its kernel
+from gaussiansplatting_b200 import dp
+try:
+    SG = dp.SymmetricGrads(gs, ctx, dist, n, local)
+except Exception as e:
+    SG = None
+    if rank == 0:
+        print("no symmetric memory:", repr(e)[:200], flush=True)
+if SG is not None and SG.multicast:
+    def time_nvls(reps=20):
+        for _ in range(3):
+            SG.reduce.allreduce(SG.grads, n)
+        ctx.sync(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            SG.reduce.allreduce(SG.grads, n)
+        b.record(stream); b.synchronize()
+        t = torch.tensor([a.elapsed_time(b) / reps], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    rows = []
+    for threads in (256, 512):
+        for unroll in (1, 2, 4, 8):
+            for grid in (16, 32, 64, 148, 296, 592, 1184):
+                gs.tune("dp_mc_threads", threads); gs.tune("dp_mc_unroll", unroll); gs.tune("dp_mc_grid", grid)
+                rows.append((time_nvls(10), threads, unroll, grid))
+    SG.reduce.check()
+    if rank == 0:
+        rows.sort()
+        for ms, threads, unroll, grid in rows[:12] + rows[-3:]:
+            print(f"nvls threads {threads} unroll {unroll} grid {grid}: {ms * 1e3:.0f} us, algbw {64e6 / ms / 1e6:.0f} GB/s", flush=True)
+    dist.barrier()
+    SG.close()
 pr.close(); D.close(); ctx.close()
 dist.destroy_process_group()
