@@ -133,8 +133,11 @@ __global__ void __launch_bounds__(512) dp_reduce_mc_kernel(float4* __restrict__ 
 
 }  // namespace
 
-// launch shape of the in-switch reduce (gs_tune "dp_mc_grid" / "dp_mc_threads" / "dp_mc_unroll"; swept on 8 GPUs by tools/allreduce_probe.py)
-static int g_mc_grid = 148 * 4, g_mc_threads = 256, g_mc_unroll = 4;
+// launch shape of the in-switch reduce (gs_tune "dp_mc_grid" / "dp_mc_threads" / "dp_mc_unroll").  Swept on 8 B200 by
+// tools/allreduce_probe.py (profiles/r2_allreduce_probe_8gpu.txt): 64 MB in 158-161 us for every shape with 16-148 CTAs, but
+// 490-770 us with 592-1184 CTAs x 8 vectors in flight -- the switch's multimem queues congest, so FEW requests in flight win:
+// 64 CTAs x 512 threads x 1 vector (512 KiB in flight per GPU).
+static int g_mc_grid = 64, g_mc_threads = 512, g_mc_unroll = 1;
 void gs_tune_dp_mc(int which, int v) {
     if (which == 0 && v >= 1 && v <= 148 * 16) g_mc_grid = v;
     if (which == 1 && v >= 32 && v <= 512 && v % 32 == 0) g_mc_threads = v;
