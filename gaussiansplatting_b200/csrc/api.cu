@@ -24,6 +24,7 @@ struct gs_ctx {
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
 static int g_tile_order = 1;                        // blend CTAs take the tiles longest list first (tile_order_kernel)
+static int g_side_bins = 1;          // bins-from-histogram kernel on the side stream, under the bin-sort pass
 static int g_depth_prehist = 1;      // K1 fills the depth sort's histograms (0: the sort runs its own histogram kernel)
 static int g_emit_fused = 1;                        // binned pipeline: scan + coarse emit + bin histogram as one kernel
 static int g_sort_api_hint = GS_SORT_HINT_DISTINCT; // GPURadixSort32/64 on caller keys: assume no structure
@@ -70,6 +71,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "dp_mc_grid")) { gs_tune_dp_mc(0, value); return GS_OK; }
     if (!strcmp(name, "dp_mc_threads")) { gs_tune_dp_mc(1, value); return GS_OK; }
     if (!strcmp(name, "dp_mc_unroll")) { gs_tune_dp_mc(2, value); return GS_OK; }
+    if (!strcmp(name, "side_bins")) { g_side_bins = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
     if (!strcmp(name, "sort_api_ballot")) { g_sort_api_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
@@ -544,6 +546,7 @@ struct gs_rast {
     const uint64_t* sorted_keys = nullptr;   // 64-bit mode: sorted keys
     cudaEvent_t ev_pairs = nullptr;     // recorded after the pair count landed in pinned memory
     cudaEvent_t ev_scan = nullptr;      // recorded on the compute stream after the scan (the copy-out stream waits on it)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // side-stream fork / join around the bins-from-histogram kernel
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
@@ -664,6 +667,8 @@ int gs_rast_destroy(gs_rast* r) {
     cudaFree(r->counters);
     if (r->ev_pairs) cudaEventDestroy(r->ev_pairs);
     if (r->ev_scan) cudaEventDestroy(r->ev_scan);
+    if (r->ev_fork) cudaEventDestroy(r->ev_fork);
+    if (r->ev_join) cudaEventDestroy(r->ev_join);
     for (int i = 0; i < GS_PROF_EVENTS; i++) if (r->ev[i]) cudaEventDestroy(r->ev[i]);
     delete r;
     return GS_OK;
@@ -801,18 +806,30 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
             gs_launch_emit_coarse_scan(r->proj, perm, n, r->ntx, bk_in, r->vals_in, cap, d_coarse, r->emit_scratch, bplan, ghist, st);
         } else gs_launch_emit_coarse(r->proj, perm, r->proj.offs, n, r->ntx, bk_in, r->vals_in, cap, st);
         r->mark(4);
+        // one-pass bin sort: its digit histogram IS the bin histogram and is final now, so the bins' runs and the chunk map are
+        // computed on the side stream while the sort pass runs (a one-CTA kernel off the critical path)
+        const bool side_bins = fused && bplan.num_passes == 1 && g_side_bins;
+        uint32_t* chunk_bin = r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 64;
+        if (side_bins) {
+            if (!r->ev_fork) { GS_CUDA(c, cudaEventCreateWithFlags(&r->ev_fork, cudaEventDisableTiming)); GS_CUDA(c, cudaEventCreateWithFlags(&r->ev_join, cudaEventDisableTiming)); }
+            GS_CUDA(c, cudaEventRecord(r->ev_fork, st));
+            GS_CUDA(c, cudaStreamWaitEvent(c->xfer_meta, r->ev_fork, 0));
+            gs_launch_bins_from_hist(gs_sort_pass_histogram(r->sort_scratch, 0), r->ntx, r->nty, r->bin_ranges, r->cstart, chunk_bin, c->xfer_meta);
+            GS_CUDA(c, cudaEventRecord(r->ev_join, c->xfer_meta));
+        }
         const int res = gs_launch_sort32(bk_in, r->vals_in, bk, r->vbuf, cap, d_coarse, bplan, g_tile_sort_hint | (fused ? GS_SORT_HINT_PREHIST : 0),
                                          r->sort_scratch, st);
+        if (side_bins) GS_CUDA(c, cudaStreamWaitEvent(st, r->ev_join, 0));
         const uint32_t* sorted_bins = bplan.num_passes ? bk[res] : bk_in;
         const uint32_t* cvals = bplan.num_passes ? r->vbuf[res] : r->vals_in;
         uint32_t* lists = r->vbuf[bplan.num_passes ? (res ^ 1) : 0];
         r->mark(5);
-        const uint32_t* bin_hist = bplan.num_passes == 1 ? gs_sort_pass_histogram(r->sort_scratch, 0) : nullptr;
+        const uint32_t* bin_hist = side_bins ? GS_BINS_READY : bplan.num_passes == 1 ? gs_sort_pass_histogram(r->sort_scratch, 0) : nullptr;
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;   // written by bin_fill's CTA 0
         if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
         gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
                              d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u,
-                             r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 64, r->tile_count + r->cap_tiles, st);
+                             chunk_bin, r->tile_count + r->cap_tiles, st);
         r->result = 0;
         r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;
         // the pair counts travel to the host on their own copy stream; the compute stream carries on with the blend

@@ -426,6 +426,14 @@ void gs_launch_emit_coarse_scan(const GsProjected& O, const uint32_t* perm, uint
                                                     status, status + blocks, ghist, dg);
 }
 
+// the bins' runs + chunk map from the coarse sort's digit histogram, as a launch of its own: it depends only on the histogram
+// (final once the emit kernel is done), so the caller runs it on a side stream while the bin-sort pass is in flight
+void gs_launch_bins_from_hist(const uint32_t* bin_hist, uint32_t ntx, uint32_t nty, uint2* bin_ranges, uint32_t* cstart, uint32_t* chunk_bin,
+                              cudaStream_t st) {
+    const uint32_t nbins = gs_bin_count(ntx, nty);
+    if (nbins) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
+}
+
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
                           uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* done, cudaStream_t st) {
@@ -435,7 +443,8 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     // sizes the grid from the previous frame's coarse count (one chunk per CTA: the chunk's dependent gathers of many
     // CTAs overlap), falling back to a persistent grid.
     const uint32_t grid = grid_chunks > 148u * 4u ? grid_chunks : 148u * 4u;
-    if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
+    if (bin_hist == GS_BINS_READY) {}                          // gs_launch_bins_from_hist already ran (side stream, under the bin sort)
+    else if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
     else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
     bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count, done, ranges, total_pairs, cap_pairs);

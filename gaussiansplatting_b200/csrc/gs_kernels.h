@@ -103,6 +103,9 @@ void gs_tune_sort_tiny(int v);
 const uint32_t* gs_sort_flags(const void* scratch);   // three words: hybrid plan admitted, local pass gave up, LSD plan ran
 void gs_tune_sort_hybrid(int v);
 void gs_tune_sort_even(int v);   // 1 (default): full 64-bit sorts may take the prefix-passes + local-pass plan (radix_sort.cu)
+#define GS_BINS_READY (reinterpret_cast<const uint32_t*>(uintptr_t(1)))   // bin_hist value: gs_launch_bins_from_hist already ran
+void gs_launch_bins_from_hist(const uint32_t* bin_hist, uint32_t ntx, uint32_t nty, uint2* bin_ranges, uint32_t* cstart, uint32_t* chunk_bin,
+                              cudaStream_t st);
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
                           uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* done, cudaStream_t st);

@@ -157,8 +157,15 @@ __global__ void __launch_bounds__(256) preprocess_kernel(GsParams P, GsProjected
         O.dkey[i] = dk;
         if (dhist) {
             atomicAdd(&s_hist[0][dk & 255u], 1u); atomicAdd(&s_hist[1][(dk >> 8) & 255u], 1u);
-            atomicAdd(&s_hist[2][(dk >> 16) & 255u], 1u); atomicAdd(&s_hist[3][(dk >> 24) & 127u], 1u);
+            atomicAdd(&s_hist[2][(dk >> 16) & 255u], 1u);
         }
+    }
+    if (dhist) {
+        // top digit (sign + exponent bits): a handful of distinct values per frame, so 256 same-address shared atomics per chunk
+        // would serialise; one atomic per distinct value and warp instead
+        const uint32_t d3 = live ? (((count ? dkey : 0xFFFFFFFFu) >> 24) & 127u) : 128u;
+        const uint32_t peers = __match_any_sync(0xFFFFFFFFu, d3);
+        if (d3 < 128u && (uint32_t)(__ffs(peers) - 1) == gs::lane_id()) atomicAdd(&s_hist[3][d3], (uint32_t)__popc(peers));
     }
     if (count) { acc_or |= dkey; acc_and &= dkey; }
   }
@@ -192,8 +199,19 @@ void gs_launch_preprocess(const GsParams& P, const GsProjected& O, const float* 
     Uni u;
     for (int k = 0; k < 16; k++) { u.V[k] = V[k]; u.VP[k] = VP[k]; }
     u.sw = sw; u.sh = sh; u.fx = fx; u.fy = fy; u.ntx = ntx; u.nty = nty; u.n = n;
-    // persistent grid when the histograms ride along (one flush of 4 x 256 bins per CTA); one chunk per CTA otherwise
+    // persistent grid when the histograms ride along (one flush of 4 x 256 bins per CTA); one chunk per CTA otherwise.  The grid is
+    // ONE balanced wave: with R resident CTAs on the device every CTA takes k = ceil(chunks / R) chunks and ceil(chunks / k) CTAs
+    // are launched, so no CTA waits for a second wave and none does a chunk more than its neighbours.
     const uint32_t chunks = (n + 255u) / 256u;
-    const uint32_t grid = depth_hist ? (chunks < 148u * 8u ? chunks : 148u * 8u) : chunks;
+    uint32_t grid = chunks;
+    if (depth_hist) {
+        int per_sm = 0, dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, preprocess_kernel, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+        const uint32_t R = (uint32_t)per_sm * (uint32_t)sms;
+        const uint32_t k = (chunks + R - 1u) / R;
+        grid = k ? (chunks + k - 1u) / k : 1u;
+    }
     preprocess_kernel<<<grid, 256, 0, st>>>(P, O, u, meta, depth_hist);
 }
