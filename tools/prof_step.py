@@ -1,5 +1,7 @@
 """Small driver for ncu: a few fwd+bwd(+Adam) steps of config C2 through the C ABI (no torch, no oracle).
-usage: python tools/prof_step.py [workload] [warm] [steps]"""
+usage: python tools/prof_step.py [workload] [warm] [steps] [noadam] [knob=value ...]
+(knobs go to gs_tune; capture the ordering kernels with side_bins=0: ncu restores device memory around every replayed pass of a
+kernel, which rolls back what a kernel running on the side stream wrote in the meantime)"""
 import os
 import sys
 import numpy as np
@@ -9,7 +11,10 @@ from gaussiansplatting_b200 import capi as gs, synth
 wl = sys.argv[1] if len(sys.argv) > 1 else "C2"
 warm = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 2
-adam = not (len(sys.argv) > 4 and sys.argv[4] == "noadam")
+adam = "noadam" not in sys.argv[4:]
+for a in sys.argv[4:]:
+    if "=" in a:
+        gs.tune(a.split("=")[0], int(a.split("=")[1]))
 n = synth.CONFIG_N[wl]; W, H = synth.CONFIG_RES[wl]
 ctx = gs.Context(0)
 G = gs.Gaussians(ctx, n); G.upload(synth.make_scene(n, synth.CONFIG_SEED[wl], synth.CONFIG_S0[wl]))
