@@ -29,8 +29,7 @@ __device__ __forceinline__ float adam_update(float gr, float& m, float& v, const
 // (float4 planes + renormalisation), jobs 2-4 scale, 5 opacity, 6-17 the SH planes.  A CTA then touches 7-13 streams of
 // 4 KB each instead of 152 streams of 1 KB (one-thread-per-Gaussian version: 2.0 TB/s), which is what DRAM pages want.
 // The third coupling is the reference's early return (a Gaussian with a non-finite gradient or position is skipped as a
-// whole, shaders.metal:567-576): every job re-evaluates that predicate from the four planes involved (16 B / Gaussian,
-// L2 hits after the first job).
+// whole, shaders.metal:567-576): adam_skip_kernel evaluates that predicate once per step into a byte per Gaussian.
 struct Skip4 { bool s[4]; };
 __device__ __forceinline__ Skip4 adam_skip4(const GsParams& P, const GsGradPack& G, size_t i4) {
     const float4 g0 = *reinterpret_cast<const float4*>(G.g + i4), g3 = *reinterpret_cast<const float4*>(G.g + 3 * (size_t)G.stride + i4),
@@ -44,6 +43,15 @@ __device__ __forceinline__ Skip4 adam_skip4(const GsParams& P, const GsGradPack&
                  isnan(d[e]) || isinf(d[e]) || fabsf(d[e]) > 1e6f;                                // :573-576
     return r;
 }
+// The predicate is taken ONCE per step, from a snapshot of the four planes it reads, into one byte per Gaussian (a 32-bit word
+// per thread of the main kernel): the 18 jobs then read 4 B instead of 64 B each, and no job can see a position that job 0 of
+// the same launch has already updated.
+__global__ void __launch_bounds__(256) adam_skip_kernel(GsParams P, GsGradPack G, uint32_t n, uint32_t* __restrict__ skipw) {
+    const size_t i4 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i4 >= n) return;
+    const Skip4 r = adam_skip4(P, G, i4);
+    skipw[i4 >> 2] = (r.s[0] ? 1u : 0u) | (r.s[1] ? 0x100u : 0u) | (r.s[2] ? 0x10000u : 0u) | (r.s[3] ? 0x1000000u : 0u);
+}
 __device__ __forceinline__ void ld4(const float* p, float (&v)[4]) { const float4 t = *reinterpret_cast<const float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
 __device__ __forceinline__ void st4(float* p, const float (&v)[4]) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
 
@@ -51,7 +59,8 @@ __device__ __forceinline__ void st4(float* p, const float (&v)[4]) { *reinterpre
 // identity and return at once.  clean[1] (preset to 1 by the host, read by the NEXT step): cleared by a job that had to
 // leave an out-of-range value behind because its Gaussian is skipped.
 __global__ void __launch_bounds__(256, 4) adam_kernel(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const __grid_constant__ AdamK k,
-                                                      const uint32_t* __restrict__ clean_in, uint32_t* __restrict__ clean_out) {
+                                                      const uint32_t* __restrict__ clean_in, uint32_t* __restrict__ clean_out,
+                                                      const uint32_t* __restrict__ skipw) {
     const size_t i4 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (i4 >= n) return;
     const uint32_t job = blockIdx.y;
@@ -59,7 +68,10 @@ __global__ void __launch_bounds__(256, 4) adam_kernel(GsParams P, GsGradPack G, 
     if (sh_rest && *clean_in) return;
     const size_t gs_ = G.stride, cap = P.cap, sc = S.cap;
     const float clip = 0.5f;                                          // shaders.metal:582
-    const Skip4 sk = adam_skip4(P, G, i4);
+    const uint32_t skw = skipw[i4 >> 2];
+    Skip4 sk;
+#pragma unroll
+    for (int e = 0; e < 4; e++) sk.s[e] = ((skw >> (8 * e)) & 0xFFu) != 0u;
     const bool full = i4 + 4 <= n;                                    // a partial last vector is handled element-wise on store
     bool live[4];
 #pragma unroll
@@ -81,11 +93,6 @@ __global__ void __launch_bounds__(256, 4) adam_kernel(GsParams P, GsGradPack G, 
             const float mag = gs::fsqrt(gs::fadd(gs::fadd(gs::fmul(up[0], up[0]), gs::fmul(up[1], up[1])), gs::fmul(up[2], up[2])));
             if (mag > 0.1f) { const float s = gs::fdiv(0.1f, mag); up[0] = gs::fmul(up[0], s); up[1] = gs::fmul(up[1], s); up[2] = gs::fmul(up[2], s); }
             const float n0 = gs::fsub(p[0][e], up[0]), n1 = gs::fsub(p[1][e], up[1]), n2 = gs::fsub(p[2][e], up[2]);
-            // INVARIANT the other 17 jobs of this launch rely on: they re-evaluate the whole-Gaussian skip predicate from position
-            // plane 0 (adam_skip4) while this job may already have stored the new position.  That is only sound because a
-            // stored x never flips the predicate: a position is accepted only if it is not NaN and |x| < 1e6 (so also finite),
-            // and the predicate tests exactly isnan / isinf / |x| > 1e6.  Whoever changes this acceptance test or the clamp must
-            // compute the predicate once from a snapshot instead.
             if (!isnan(n0) && !isnan(n1) && !isnan(n2) && fabsf(n0) < 1e6f && fabsf(n1) < 1e6f && fabsf(n2) < 1e6f) {
                 p[0][e] = n0; p[1][e] = n1; p[2][e] = n2;
             }
@@ -170,12 +177,13 @@ __global__ void accumulate_stats_kernel(GsGradPack G, int stat_mode, uint32_t n,
 }  // namespace
 
 void gs_launch_adam(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const float lrs[5], float beta1, float beta2,
-                    float eps, float bc1, float bc2, const uint32_t* clean_in, uint32_t* clean_out, cudaStream_t st) {
+                    float eps, float bc1, float bc2, const uint32_t* clean_in, uint32_t* clean_out, uint32_t* skip_words, cudaStream_t st) {
     if (n == 0) return;
     AdamK k;
     for (int i = 0; i < 5; i++) k.lr[i] = lrs[i];
     k.b1 = beta1; k.b2 = beta2; k.omb1 = 1.0f - beta1; k.omb2 = 1.0f - beta2; k.eps = eps; k.bc1 = bc1; k.bc2 = bc2;
-    adam_kernel<<<dim3((n + 1023) / 1024, 18), 256, 0, st>>>(P, G, S, n, k, clean_in, clean_out);
+    adam_skip_kernel<<<(n + 1023) / 1024, 256, 0, st>>>(P, G, n, skip_words);
+    adam_kernel<<<dim3((n + 1023) / 1024, 18), 256, 0, st>>>(P, G, S, n, k, clean_in, clean_out, skip_words);
 }
 
 void gs_launch_accumulate_stats(GsGradPack G, int stat_mode, uint32_t n, float* accum, uint32_t* count, cudaStream_t st) {

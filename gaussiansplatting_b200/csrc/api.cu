@@ -1444,6 +1444,8 @@ struct gs_adam {
     uint32_t num = 0;           // the reference's numGaussians (state covers [0, num))
     uint32_t timestep = 0;
     uint32_t* clean_flags = nullptr;   // device: two words, see gs_adam_step
+    uint32_t* skip_words = nullptr;    // one byte per Gaussian: the step's whole-Gaussian skip predicate (adam_skip_kernel)
+    uint32_t skip_cap = 0;
     uint32_t sh_clamped_n = 0;  // leading Gaussians whose non-DC SH planes went through the clamp since they were last written
     bool sh_rest_zero = true;   // moments of the nine non-DC SH planes are all +0 (they never receive a gradient; only an upload can change that)
     GsAdamState view() const {
@@ -1495,7 +1497,7 @@ int gs_adam_create(gs_ctx* c, uint32_t num, gs_adam** out) {
 int gs_adam_destroy(gs_adam* a) {
     if (!a) return GS_OK;
     cudaSetDevice(a->c->device); cudaStreamSynchronize(a->c->stream);
-    cudaFree(a->base); cudaFree(a->clean_flags); delete a;
+    cudaFree(a->base); cudaFree(a->clean_flags); cudaFree(a->skip_words); delete a;
     return GS_OK;
 }
 int gs_adam_reset(gs_adam* a) {                                        // optimizer.mm:80-93
@@ -1558,7 +1560,13 @@ int gs_adam_step(gs_adam* a, gs_gaussians* g, gs_grads* gr, const float lrs[5]) 
     const bool known = a->sh_rest_zero && !g->sh_rest_dirty && n <= a->sh_clamped_n;
     if (!known) GS_CUDA(c, cudaMemsetAsync(cin, 0, 4, c->stream));      // host-visible writers: force the nine jobs to run
     GS_CUDA(c, cudaMemsetAsync(cout, 1, 4, c->stream));                   // any non-zero word means clean
-    gs_launch_adam(g->view(), gr->view(), a->view(), n, lrs, beta1, beta2, eps, bc1, bc2, cin, cout, c->stream);
+    if (n > a->skip_cap) {
+        GS_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(a->skip_words); a->skip_words = nullptr;
+        a->skip_cap = std::max(a->cap, (n + 1023u) & ~1023u);
+        GS_TRY(dalloc(c, &a->skip_words, (size_t)a->skip_cap / 4 + 1));
+    }
+    gs_launch_adam(g->view(), gr->view(), a->view(), n, lrs, beta1, beta2, eps, bc1, bc2, cin, cout, a->skip_words, c->stream);
     GS_LAUNCH_CHECK(c);
     a->sh_clamped_n = std::max(a->sh_clamped_n, n);
     g->sh_rest_dirty = false;

@@ -153,7 +153,7 @@ struct GsAdamState {   // the reference's 10 moment buffers (optimizer.mm:34-60)
     uint32_t cap;
 };
 void gs_launch_adam(GsParams P, GsGradPack G, GsAdamState S, uint32_t n, const float lrs[5], float beta1, float beta2,
-                    float eps, float bc1, float bc2, const uint32_t* clean_in, uint32_t* clean_out, cudaStream_t st);
+                    float eps, float bc1, float bc2, const uint32_t* clean_in, uint32_t* clean_out, uint32_t* skip_words, cudaStream_t st);
 
 // A13 / K10-K11: density control ----------------------------------------------------------------------
 void gs_launch_accumulate_stats(GsGradPack G, int stat_mode, uint32_t n, float* accum, uint32_t* count, cudaStream_t st);
