@@ -652,11 +652,11 @@ class Bench:
                 out["config"]["c4"] = {"error": repr(e)[:200]}
         clocks = sampler.stop() if rank == 0 else {}    # sampled over every timed region above (fwd+bwd, e2e, training, C4)
         out["clocks"] = clocks
-        # kernels per fwd+bwd frame (binned pipeline): preprocess, depth histogram + 4 passes, scan + coarse emit + bin histogram
-        # (one kernel), the bin passes, bin runs (1 kernel from the histogram, 3 when the bin sort needed two passes), chunk
-        # counts, bin scan + tile scan (one kernel), fill (its CTA 0 writes the blend tile order), blend fwd, blend bwd,
-        # per-Gaussian chain (memsets not counted); the ncu launch list of a frame is under profiles/
-        launches_fb = 10 + passes + (2 if passes > 5 else 0)
+        # kernels per fwd+bwd frame (binned pipeline): preprocess (it also fills the depth sort's histograms), 4 depth passes, scan +
+        # coarse emit + bin histogram (one kernel), bins from the histogram (side stream), the bin passes (1; with two passes the
+        # run boundaries take 2 more kernels), chunk counts, bin scan + tile scan (one kernel), fill (its CTA 0 writes the blend
+        # tile order), blend fwd, blend bwd, per-Gaussian chain (memsets not counted): 14 at C2, profiles/r2_launches_C2.md
+        launches_fb = 9 + passes + (2 if passes > 5 else 0)
         out["gpu_launches"] = K * launches_fb
 
         if rank == 0:
