@@ -655,8 +655,9 @@ class Bench:
         # kernels per fwd+bwd frame (binned pipeline): preprocess (it also fills the depth sort's histograms), 4 depth passes, scan +
         # coarse emit + bin histogram (one kernel), bins from the histogram (side stream), the bin passes (1; with two passes the
         # run boundaries take 2 more kernels), chunk counts, bin scan + tile scan (one kernel), fill (its CTA 0 writes the blend
-        # tile order), blend fwd, blend bwd, per-Gaussian chain (memsets not counted): 14 at C2, profiles/r2_launches_C2.md
-        launches_fb = 9 + passes + (2 if passes > 5 else 0)
+        # tile order), blend fwd, blend bwd (two launches: the walk on the forward's visit words, then the pinned walk for the
+        # tiles the forward flagged), per-Gaussian chain (memsets not counted): 15 at C2, profiles/r2_launches_C2.md
+        launches_fb = 10 + passes + (2 if passes > 5 else 0)
         out["gpu_launches"] = K * launches_fb
 
         if rank == 0:

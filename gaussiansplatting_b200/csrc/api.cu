@@ -24,6 +24,7 @@ struct gs_ctx {
 static std::string g_create_err;
 static int g_tile_sort_hint = 0;                    // in-frame tile-id passes: match.any measured faster
 static int g_tile_order = 1;                        // blend CTAs take the tiles longest list first (tile_order_kernel)
+static int g_bwd_masks = 1;          // backward takes its per-slot decisions from the forward's visit words (0: re-derives them)
 static int g_side_bins = 1;          // bins-from-histogram kernel on the side stream, under the bin-sort pass
 static int g_depth_prehist = 1;      // K1 fills the depth sort's histograms (0: the sort runs its own histogram kernel)
 static int g_emit_fused = 1;                        // binned pipeline: scan + coarse emit + bin histogram as one kernel
@@ -71,6 +72,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "dp_mc_grid")) { gs_tune_dp_mc(0, value); return GS_OK; }
     if (!strcmp(name, "dp_mc_threads")) { gs_tune_dp_mc(1, value); return GS_OK; }
     if (!strcmp(name, "dp_mc_unroll")) { gs_tune_dp_mc(2, value); return GS_OK; }
+    if (!strcmp(name, "bwd_masks")) { g_bwd_masks = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "side_bins")) { g_side_bins = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
@@ -550,6 +552,9 @@ struct gs_rast {
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
+    // forward's visit words for the backward (blend_fwd.cu / blend_bwd.cu): 4 x uint2 per pair slot.  Allocated by the first
+    // backward call (render-only users never pay), regrown with the pair buffers; vis_valid = the last forward filled it.
+    uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false;
     bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
@@ -621,6 +626,19 @@ static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureB
     r->W = W; r->H = H; r->ntx = ntx; r->nty = nty;
     return GS_OK;
 }
+// the buffer the coming forward blend writes its visits to (null: none); marks them valid for the backward of this frame
+static uint2* rast_vis_for_forward(gs_rast* r) {
+    r->vis_valid = r->vis != nullptr && g_bwd_masks && gs_fwd_writes_visits() && r->vis_cap >= r->cap_pairs;
+    return r->vis_valid ? r->vis : nullptr;
+}
+static int rast_reserve_vis(gs_rast* r) {      // visit words for cap_pairs pair slots x 4 warps (32 B per pair slot)
+    if (r->vis && r->vis_cap >= r->cap_pairs) return GS_OK;
+    gs_ctx* c = r->c;
+    GS_CUDA(c, cudaStreamSynchronize(c->stream));
+    cudaFree(r->vis); r->vis = nullptr; r->vis_valid = false;
+    r->vis_cap = r->cap_pairs;
+    return dalloc(c, &r->vis, (size_t)r->vis_cap * 4);
+}
 static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapacity, tiled_rasterizer.mm:242-272 (no 100 M clamp: note C)
     if (need <= r->cap_pairs) return GS_OK;
     gs_ctx* c = r->c;
@@ -635,6 +653,7 @@ static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapac
     GS_CUDA(c, cudaMalloc(&r->sort_scratch, gs_sort_scratch_bytes(cap, 8)));
     GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * 65));    // 64 counts per chunk, then the chunk -> bin table
     r->cap_pairs = cap;
+    if (r->want_vis) GS_TRY(rast_reserve_vis(r));
     return GS_OK;
 }
 
@@ -664,7 +683,7 @@ int gs_rast_destroy(gs_rast* r) {
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); }
     cudaFree(r->ranges); cudaFree(r->proj.tile_flags); cudaFree(r->last_idx); cudaFree(r->tfinal); cudaFree(r->staging);
     cudaFree(r->tile_count); cudaFree(r->bin_ranges); cudaFree(r->cstart); cudaFree(r->chunk_counts);
-    cudaFree(r->counters);
+    cudaFree(r->counters); cudaFree(r->vis);
     if (r->ev_pairs) cudaEventDestroy(r->ev_pairs);
     if (r->ev_scan) cudaEventDestroy(r->ev_scan);
     if (r->ev_fork) cudaEventDestroy(r->ev_fork);
@@ -708,7 +727,7 @@ static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     gs_launch_tile_ranges(r->sorted_keys, (uint32_t)P, tiles, nullptr, r->ranges, st);
     r->mark(6);
     r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, st);
+    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), st);
     r->mark(7);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
@@ -759,7 +778,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         gs_launch_tile_ranges32(r->sorted_tiles, cap, d_total, tiles, r->ranges, st);
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         if (attempt == 0) GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));   // the GPU is still busy with the kernels above
@@ -839,7 +858,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, rast_vis_for_forward(r), st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));                   // the GPU is still busy with the kernels above
@@ -902,8 +921,10 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     if (!r->acc_clean) GS_CUDA(c, cudaMemsetAsync(r->acc, 0, (size_t)r->cap_g * 12 * sizeof(float), st));
     r->acc_clean = false;
     const uint32_t* svals = r->sorted_vals;
+    const bool masked = r->vis_valid && g_bwd_masks && gs_bwd_uses_visits();
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
-                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, st);
+                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, st);
+    if (!r->want_vis && g_bwd_masks) { r->want_vis = true; GS_TRY(rast_reserve_vis(r)); }   // a training caller: record visits from the next forward on
     r->mark(9);
     gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,
                                   gr->view(), gr->stat_mode, accumulate, st);

@@ -13,9 +13,13 @@
 #include "gs_kernels.h"
 
 #ifdef GS_BWD_MINB         // optional: minimum resident CTAs per SM asked of ptxas (register budget knob; measured: no gain)
-#define GS_BWD_BOUNDS(nt) __launch_bounds__(nt, GS_BWD_MINB)
+#define GS_BWD_BOUNDS(nt, masked) __launch_bounds__(nt, GS_BWD_MINB)
 #else
-#define GS_BWD_BOUNDS(nt) __launch_bounds__(nt)
+#ifndef GS_BWD_MASKED_MINB
+#define GS_BWD_MASKED_MINB 0   // 0 = unconstrained (66 registers, 7 CTAs per SM: 412 us at C2).  Measured: 8 -> 64 registers, 423 us;
+                               // 8 with rounds of 120 entries so that eight CTAs' shared memory fits as well: 420 us
+#endif
+#define GS_BWD_BOUNDS(nt, masked) __launch_bounds__(nt, (masked) ? GS_BWD_MASKED_MINB : 0)
 #endif
 
 namespace {
@@ -27,6 +31,10 @@ namespace {
 #define GS_BWD_BB 128
 #endif
 constexpr int BB = GS_BWD_BB;   // raw list entries staged per round
+#ifndef GS_BWD_BB_MASKED
+#define GS_BWD_BB_MASKED 128
+#endif
+constexpr int BBM = GS_BWD_BB_MASKED;   // the same for the masked variant, whose rounds also hold 32 B of visit words per entry
 
 // sum of v[0..7] over the warp; afterwards lane L holds (in v[0]) the total of value ((L>>2)&7 bit-reversed order below)
 __device__ __forceinline__ float warp_reduce8_transposed(float v[8], uint32_t lane) {
@@ -63,24 +71,36 @@ __device__ __forceinline__ uint32_t reduce8_index(uint32_t lane) {
 // does not take an entry runs the same instructions with alpha and G forced to 0, which leaves its T and accumulated
 // colour unchanged (T * rcp(1), 0*c + 1*acc) and adds exact zeros to the moments.
 struct BwdEnt { float4 r0, r1; float b; uint32_t idx, gid, pad; };   // 48 B: one base address, three LDS.128
-template <int PPT>
-__global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+// MASKED (PPT 2): the forward stored, for every (entry, warp) visit, which of the warp's 64 pixel slots took the entry
+// (blend_fwd.cu, `vis`).  The backward's decisions (:489, :495, the extent of the walk) are the forward's, so this variant takes
+// them from that word instead of re-deriving them: no pinned exp on the path (G by ex2.approx: gradients are graded at 1e-3),
+// no range / threshold compares, no vote, and a visit in which no slot took the entry is skipped before its record is loaded.
+// Tiles in which the forward skipped a conic-degenerate entry that the reference's backward does not skip (note I, tile_flags)
+// are left to the pinned variant, launched behind this one with only_flagged = 1.
+__device__ __forceinline__ float ex2_approx(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+template <int PPT, bool MASKED>
+__global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                              const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                              const float4* __restrict__ rendered, const float4* __restrict__ gt,
                                                              int quantize, const uint32_t* __restrict__ last_idx,
                                                              const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
-                                                             const uint32_t* __restrict__ order, float* __restrict__ acc) {
-    constexpr int NT = 256 / PPT, NW = NT / 32, K = (BB + NT - 1) / NT, NP = PPT / 2;
-    __shared__ BwdEnt s_e[BB];
-    __shared__ float s_acc[NW][BB * 9];
+                                                             const uint32_t* __restrict__ order, float* __restrict__ acc,
+                                                             const uint2* __restrict__ vis, int only_flagged) {
+    constexpr int RB = MASKED ? BBM : BB;
+    constexpr int NT = 256 / PPT, NW = NT / 32, K = (RB + NT - 1) / NT, NP = PPT / 2;
+    static_assert(!MASKED || PPT == 2, "the forward records its visits for two pixels per thread only");
+    __shared__ BwdEnt s_e[RB];
+    __shared__ uint2 s_vis[MASKED ? RB : 1][NW];
+    __shared__ float s_acc[NW][RB * 9];
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
-    __shared__ unsigned char s_reach[BB];              // per staged entry: which warp regions it can reach at all (bit w)
+    __shared__ unsigned char s_reach[RB];              // per staged entry: which warp regions it can reach at all (bit w)
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint2 range = ranges[tile];                                // :410-413
     const bool redo = tile_flags[tile] != 0u;
+    if (MASKED ? redo : (only_flagged && !redo)) return;             // CTA-uniform: each tile belongs to exactly one of the two launches
     const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e);
 
     gs::f32x2 X2[NP], Y2[NP], T2[NP], dr2[NP], dg2[NP], db2[NP], ar2[NP], ag2[NP], ab2[NP];
@@ -151,7 +171,7 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
     float* my_acc = s_acc[warp];
     const gs::f32x2 one2 = gs::bc2(1.0f);
     for (uint32_t hi = bmax; hi > 0;) {
-        const uint32_t lo = hi > (uint32_t)BB ? hi - BB : 0u;
+        const uint32_t lo = hi > (uint32_t)RB ? hi - RB : 0u;
         const uint32_t cntraw = hi - lo;
         // ---- stage (compacting out culled pairs, list order kept) and clear this warp's moment rows
         uint32_t v[K], nl = 0;
@@ -180,6 +200,12 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                 if (!gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey)) reach |= 1u << w;
             }
             s_reach[slot] = (unsigned char)reach;
+            if (MASKED) {                                            // the four warps' words of this entry: 32 contiguous bytes
+                const uint4* vp = reinterpret_cast<const uint4*>(vis + ((size_t)range.x + lo + threadIdx.x * K + q) * 4u);
+                const uint4 v01 = vp[0], v23 = vp[1];
+                s_vis[slot][0] = make_uint2(v01.x, v01.y); s_vis[slot][1] = make_uint2(v01.z, v01.w);
+                s_vis[slot][2] = make_uint2(v23.x, v23.y); s_vis[slot][3] = make_uint2(v23.z, v23.w);
+            }
             slot++;
         }
         for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
@@ -194,7 +220,9 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
             }
             for (int wd = ((int)kend - 1) >> 5; wd >= 0; wd--) {      // :473 back to front, reachable entries only
                 const uint32_t sl = (uint32_t)wd * 32u + lane;
-                uint32_t mk = __ballot_sync(0xFFFFFFFFu, sl < kend && ((s_reach[sl] >> warp) & 1u));
+                bool want = sl < kend && ((s_reach[sl] >> warp) & 1u);
+                if (MASKED) { if (want) { const uint2 vm = s_vis[sl][warp]; want = (vm.x | vm.y) != 0u; } }
+                uint32_t mk = __ballot_sync(0xFFFFFFFFu, want);
                 const uint32_t wbase = ebase + (uint32_t)wd * 32u * (uint32_t)sizeof(BwdEnt);
                 while (mk) {
                     const int kb = 31 - __clz(mk);
@@ -212,9 +240,19 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                     for (int p = 0; p < NP; p++) {
                         const gs::f32x2 dx = gs::fsub2(X2[p], sx), dy = gs::fsub2(Y2[p], sy);   // :483
                         const gs::f32x2 pw2 = gs::blend_power2(Ah, Bn, Ch, dx, dy);
+                        float pw[2], al[2], G[2];
+                        if (MASKED) {
+                            const uint2 vm = s_vis[wd * 32 + kb][warp];
+                            float t0, t1;
+                            gs::up2(gs::fmul2(pw2, gs::bc2(GS_LOG2E)), t0, t1);
+                            G[0] = ex2_approx(t0); G[1] = ex2_approx(t1);                      // :492
+                            const bool c0 = (vm.x >> lane) & 1u, c1 = (vm.y >> lane) & 1u;     // the forward's decision for this slot
+                            al[0] = c0 ? fminf(b.y * G[0], GS_ALPHA_MAX) : 0.0f; al[1] = c1 ? fminf(b.y * G[1], GS_ALPHA_MAX) : 0.0f;
+                            G[0] = c0 ? G[0] : 0.0f; G[1] = c1 ? G[1] : 0.0f;
+                            anyc = true;
+                        } else {
                         const gs::f32x2 G2 = gs::exp_blend2(pw2);                             // :492
                         const gs::f32x2 a2 = gs::fmul2(op, G2);
-                        float pw[2], al[2], G[2];
                         gs::up2(pw2, pw[0], pw[1]); gs::up2(a2, al[0], al[1]); gs::up2(G2, G[0], G[1]);
 #pragma unroll
                         for (int h = 0; h < 2; h++) {
@@ -223,6 +261,7 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                             al[h] = ch ? al[h] : 0.0f;
                             G[h] = ch ? G[h] : 0.0f;
                             anyc |= ch;
+                        }
                         }
                         const gs::f32x2 alpha = gs::pk2(al[0], al[1]), Gq = gs::pk2(G[0], G[1]);
                         const gs::f32x2 om = gs::fsub2(one2, alpha);
@@ -249,7 +288,7 @@ __global__ void GS_BWD_BOUNDS(256 / PPT) blend_backward_kernel(const float4* __r
                             m2[6] = gs::ffma2(qx, dx, m2[6]); m2[7] = gs::ffma2(qx, dy, m2[7]); m2[8] = gs::ffma2(qy, dy, m2[8]);
                         }
                     }
-                    if (!__any_sync(0xFFFFFFFFu, anyc)) continue;
+                    if (!MASKED) { if (!__any_sync(0xFFFFFFFFu, anyc)) continue; }
                     float v8[8], v9;
 #pragma unroll
                     for (int i = 0; i < 9; i++) {
@@ -405,14 +444,16 @@ void gs_tune_bwd_ppt(int v) { if (v == 2 || v == 4) g_bwd_ppt = v; }
 
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
-                              const uint32_t* last_idx, const float* tfinal, float* acc, cudaStream_t st) {
+                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, cudaStream_t st) {
     if (ntx * nty == 0) return;
-#define GS_BWD_LAUNCH(PPT)                                                                                          \
-    blend_backward_kernel<PPT><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
-                                                                 last_idx, tfinal, O.tile_flags, O.tile_order, acc)
-    if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4);
-    else GS_BWD_LAUNCH(2);
+#define GS_BWD_LAUNCH(PPT, MASKED, ONLY)                                                                            \
+    blend_backward_kernel<PPT, MASKED><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
+                                                                         last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis, ONLY)
+    if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false, 0);
+    else if (vis) { GS_BWD_LAUNCH(2, true, 0); GS_BWD_LAUNCH(2, false, 1); }   // recorded visits; flagged tiles by the pinned variant
+    else GS_BWD_LAUNCH(2, false, 0);
 }
+bool gs_bwd_uses_visits() { return g_bwd_ppt == 2; }
 
 void gs_launch_preprocess_backward(const GsParams& P, const GsProjected& O, float* acc, const float* V, float fx,
                                    float fy, uint32_t n, GsGradPack G, int stat_mode, int accumulate, cudaStream_t st) {

@@ -93,17 +93,24 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restric
 }
 
 struct FwdEnt { float4 r0, r1; float b; uint32_t idx; uint32_t pad0, pad1; };   // 48 B: one base address, three LDS
-template <int PPT, bool COUNT>
+// vis (optional, PPT 2 only): for every STAGED list entry four 64-bit words, one per warp, "which of the warp's 64 pixel slots
+// took the entry" (two ballots: slot j = 0 / 1 of every lane; zero = the warp never took it), at vis[entry * 4 + warp].  A warp
+// keeps its word in shared memory; the CTA writes a round's words out once, 32 contiguous bytes per entry.  The backward
+// walk takes its per-slot decisions from these words instead of re-deriving them (blend_bwd.cu).  Entries behind the round in
+// which the whole tile finished are never staged and get no words: no pixel's lastContribIdx lies beyond that round.
+template <int PPT, bool COUNT, bool VIS>
 __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
                                                             float4* __restrict__ image, uint32_t* __restrict__ last_idx,
                                                             float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags,
                                                             const uint32_t* __restrict__ order,
-                                                            unsigned long long* __restrict__ counters) {
+                                                            unsigned long long* __restrict__ counters, uint2* __restrict__ vis) {
     constexpr int NT = 256 / PPT, NW = NT / 32, K = FB / NT, NP = PPT / 2;
     __shared__ FwdEnt s_e[FB];
     __shared__ uint32_t s_w[NW];
     __shared__ unsigned char s_reach[FB];             // per staged entry: which warp regions it can reach at all (bit w)
+    static_assert(!VIS || (PPT == 2 && !COUNT), "visit words are recorded by the two-pixel blend only");
+    __shared__ uint2 s_vis[VIS ? FB : 1][NW];   // this round's visit words (zero = the warp did not take the entry)
     __shared__ uint32_t s_degen;
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
@@ -111,6 +118,9 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
     const uint2 range = ranges[tile];                                // :320-323
     if (threadIdx.x == 0) s_degen = 0;
     const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e);
+    // this warp's column of s_vis as a warp-uniform address (the broadcast tells the compiler so: no per-thread register, no
+    // special-register read inside the walk)
+    const uint32_t vbase = (uint32_t)__cvta_generic_to_shared(s_vis) + __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0) * (uint32_t)sizeof(uint2);
 
     uint32_t px[PPT], py[PPT], last[PPT];
     float Tp[PPT];
@@ -136,8 +146,19 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
         T2[p] = gs::pk2(t0[0], t0[1]); Cr2[p] = gs::bc2(0.f); Cg2[p] = gs::bc2(0.f); Cb2[p] = gs::bc2(0.f);
     }
     bool wlive = __any_sync(0xFFFFFFFFu, live);      // warp-uniform: some pixel of this warp still walks
+    constexpr bool rec_vis = VIS;   // a kernel of its own: the render-only frame keeps the walk without the two votes and the store
+    uint32_t prev_total = 0;                          // staged entries of the previous round, whose visit words are still in s_vis
     for (uint32_t base = 0; base < range.y; base += FB) {
-        if (__syncthreads_and(!wlive)) break;
+        const bool all_done = __syncthreads_and(!wlive);
+        if (rec_vis) {                                // the previous round's words: 32 contiguous bytes per entry, one thread each
+            for (uint32_t k = threadIdx.x; k < prev_total; k += NT) {
+                uint4* dst = reinterpret_cast<uint4*>(vis + (size_t)s_e[k].idx * 4u);
+                dst[0] = make_uint4(s_vis[k][0].x, s_vis[k][0].y, s_vis[k][1].x, s_vis[k][1].y);
+                dst[1] = make_uint4(s_vis[k][2].x, s_vis[k][2].y, s_vis[k][3].x, s_vis[k][3].y);
+            }
+            prev_total = 0;
+        }
+        if (all_done) break;
         // ---- stage: drop culled pairs, keep list order
         const uint32_t cntraw = min((uint32_t)FB, range.y - base);
         uint32_t v[K], nl = 0;
@@ -167,9 +188,14 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
                 if (!gs::box_cannot_contribute(cr, (float)(tX * 16u + rx) + 0.5f, (float)(tY * 16u + ry) + 0.5f, ex, ey)) reach |= 1u << w;
             }
             s_reach[slot] = (unsigned char)reach;
+            if (rec_vis) {
+#pragma unroll
+                for (int w = 0; w < NW; w++) s_vis[slot][w] = make_uint2(0u, 0u);
+            }
             slot++;
         }
         __syncthreads();
+        prev_total = total;
         if (wlive) {
             const uint32_t nwords = (total + 31u) >> 5;
             for (uint32_t wd = 0; wd < nwords && wlive; wd++) {      // :334, entries that can reach this warp's pixels only
@@ -187,6 +213,7 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
                     const gs::f32x2 sx = gs::bc2(a.x), sy = gs::bc2(a.y), Ah = gs::bc2(a.z), Bn = gs::bc2(a.w), Ch = gs::bc2(b.x),
                                     op = gs::bc2(b.y), cr = gs::bc2(b.z), cg = gs::bc2(b.w), cb = gs::bc2(c.x);
                     bool alive = false;
+                    bool took0 = false, took1 = false;
 #pragma unroll
                     for (int p = 0; p < NP; p++) {
                         const gs::f32x2 dx = gs::fsub2(X2[p], sx), dy = gs::fsub2(Y2[p], sy);   // :347
@@ -203,6 +230,7 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
                             c2[h] = (To[h] > GS_T_EPS) && (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);
                             al[h] = c2[h] ? al[h] : 0.0f;
                         }
+                        if (p == 0) { took0 = c2[0]; took1 = c2[1]; }
                         const gs::f32x2 alpha = gs::pk2(al[0], al[1]);
                         const gs::f32x2 w2 = gs::fmul2(alpha, T2[p]);                          // :369
                         Cr2[p] = gs::ffma2(cr, w2, Cr2[p]); Cg2[p] = gs::ffma2(cg, w2, Cg2[p]); Cb2[p] = gs::ffma2(cb, w2, Cb2[p]);
@@ -217,9 +245,21 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
                             alive |= Tn[h] > GS_T_EPS;                                        // :334 loop condition
                         }
                     }
+                    if (rec_vis) {
+                        const uint32_t m0 = __ballot_sync(0xFFFFFFFFu, took0), m1 = __ballot_sync(0xFFFFFFFFu, took1);
+                        // every lane stores the same word to the same address: one shared-memory transaction, no lane predicate
+                        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(vbase + (wd * 32u + kb) * (uint32_t)(NW * sizeof(uint2))), "r"(m0), "r"(m1) : "memory");
+                    }
                     if (!__any_sync(0xFFFFFFFFu, alive)) { wlive = false; break; }
                 }
             }
+        }
+    }
+    if (rec_vis && __syncthreads_or(prev_total != 0u)) {   // the last round's words (the loop ended by exhausting the list)
+        for (uint32_t k = threadIdx.x; k < prev_total; k += NT) {
+            uint4* dst = reinterpret_cast<uint4*>(vis + (size_t)s_e[k].idx * 4u);
+            dst[0] = make_uint4(s_vis[k][0].x, s_vis[k][0].y, s_vis[k][1].x, s_vis[k][1].y);
+            dst[1] = make_uint4(s_vis[k][2].x, s_vis[k][2].y, s_vis[k][3].x, s_vis[k][3].y);
         }
     }
     float Tf[PPT], Cr[PPT], Cg[PPT], Cb[PPT];
@@ -257,6 +297,7 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
 
 static int g_fwd_ppt = GS_FWD_PPT;
 void gs_tune_fwd_ppt(int v) { if (v == 2 || v == 4) g_fwd_ppt = v; }
+bool gs_fwd_writes_visits() { return g_fwd_ppt == 2; }
 
 void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* /*lb*/,
                            uint2* ranges, cudaStream_t st) {
@@ -281,20 +322,21 @@ void gs_launch_tile_order(const uint2* ranges, uint32_t num_tiles, uint32_t* ord
 
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, int order_ready,
-                             cudaStream_t st) {
+                             uint2* vis, cudaStream_t st) {
     if (ntx * nty == 0) return;
-#define GS_FWD_LAUNCH(PPT)                                                                                            \
-    blend_forward_kernel<PPT, false><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
-                                                                       tfinal, O.tile_flags, O.tile_order, nullptr)
+#define GS_FWD_LAUNCH(PPT, VIS)                                                                                       \
+    blend_forward_kernel<PPT, false, VIS><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
+                                                                            tfinal, O.tile_flags, O.tile_order, nullptr, vis)
     if (O.tile_order && !order_ready) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, ntx * nty, O.tile_order);
-    if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4);
-    else GS_FWD_LAUNCH(2);
+    if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4, false);
+    else if (vis) GS_FWD_LAUNCH(2, true);
+    else GS_FWD_LAUNCH(2, false);
 }
 
 // counts E (entries visited) and C (contributing evaluations) of the forward walk; counters[2] zeroed by the caller
 void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                            uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st) {
     if (ntx * nty == 0) return;
-    blend_forward_kernel<2, true><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
-                                                             O.tile_flags, nullptr, counters);
+    blend_forward_kernel<2, true, false><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
+                                                             O.tile_flags, nullptr, counters, nullptr);
 }
