@@ -281,6 +281,10 @@ class Rasterizer:
     def sort_passes(self):
         return int(lib().gs_rast_sort_passes(self.h))
 
+    @property
+    def backward_used_visits(self):
+        return bool(lib().gs_rast_backward_used_visits(self.h))
+
     def get(self, which):
         P = self.pair_count
         shape, dt = {RAST_PROJECTED: (self._n, PROJECTED), RAST_KEYS: (P, np.uint64), RAST_VALUES: (P, np.uint32),

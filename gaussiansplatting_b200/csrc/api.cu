@@ -554,7 +554,7 @@ struct gs_rast {
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
     // forward's visit words for the backward (blend_fwd.cu / blend_bwd.cu): 4 x uint2 per pair slot.  Allocated by the first
     // backward call (render-only users never pay), regrown with the pair buffers; vis_valid = the last forward filled it.
-    uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false;
+    uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false, bwd_used_vis = false;
     bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
@@ -922,6 +922,7 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     r->acc_clean = false;
     const uint32_t* svals = r->sorted_vals;
     const bool masked = r->vis_valid && g_bwd_masks && gs_bwd_uses_visits();
+    r->bwd_used_vis = masked;
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
                              (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, st);
     if (!r->want_vis && g_bwd_masks) { r->want_vis = true; GS_TRY(rast_reserve_vis(r)); }   // a training caller: record visits from the next forward on
@@ -1026,6 +1027,7 @@ int gs_rast_get(gs_rast* r, int which, void* host, size_t bytes) {
 uint64_t gs_rast_pair_count(const gs_rast* r) { return r->pairs; }
 uint64_t gs_rast_coarse_pair_count(const gs_rast* r) { return r->mode == 0 ? r->coarse_hint : 0; }
 int gs_rast_sort_passes(const gs_rast* r) { return r->passes; }
+int gs_rast_backward_used_visits(const gs_rast* r) { return r->bwd_used_vis ? 1 : 0; }
 
 }  // extern "C"
 

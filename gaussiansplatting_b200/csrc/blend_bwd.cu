@@ -76,16 +76,16 @@ struct BwdEnt { float4 r0, r1; float b; uint32_t idx, gid, pad; };   // 48 B: on
 // them from that word instead of re-deriving them: no pinned exp on the path (G by ex2.approx: gradients are graded at 1e-3),
 // no range / threshold compares, no vote, and a visit in which no slot took the entry is skipped before its record is loaded.
 // Tiles in which the forward skipped a conic-degenerate entry that the reference's backward does not skip (note I, tile_flags)
-// are left to the pinned variant, launched behind this one with only_flagged = 1.
+// are left to the pinned variant (blend_backward_flagged_kernel, launched behind this one).
 __device__ __forceinline__ float ex2_approx(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// one tile's walk by one CTA of 256 / PPT threads (the body of both kernels below); redo = the tile is flagged
 template <int PPT, bool MASKED>
-__global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
-                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
-                                                             const float4* __restrict__ rendered, const float4* __restrict__ gt,
-                                                             int quantize, const uint32_t* __restrict__ last_idx,
-                                                             const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
-                                                             const uint32_t* __restrict__ order, float* __restrict__ acc,
-                                                             const uint2* __restrict__ vis, int only_flagged) {
+__device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const bool redo, const float4* __restrict__ rec,
+                                                    const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W,
+                                                    uint32_t H, uint32_t ntx, const float4* __restrict__ rendered,
+                                                    const float4* __restrict__ gt, int quantize, const uint32_t* __restrict__ last_idx,
+                                                    const float* __restrict__ tfinal, float* __restrict__ acc,
+                                                    const uint2* __restrict__ vis) {
     constexpr int RB = MASKED ? BBM : BB;
     constexpr int NT = 256 / PPT, NW = NT / 32, K = (RB + NT - 1) / NT, NP = PPT / 2;
     static_assert(!MASKED || PPT == 2, "the forward records its visits for two pixels per thread only");
@@ -95,12 +95,9 @@ __global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const flo
     __shared__ uint32_t s_w[NW];
     __shared__ uint32_t s_wmax[NW];
     __shared__ unsigned char s_reach[RB];              // per staged entry: which warp regions it can reach at all (bit w)
-    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     const uint2 range = ranges[tile];                                // :410-413
-    const bool redo = tile_flags[tile] != 0u;
-    if (MASKED ? redo : (only_flagged && !redo)) return;             // CTA-uniform: each tile belongs to exactly one of the two launches
     const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e);
 
     gs::f32x2 X2[NP], Y2[NP], T2[NP], dr2[NP], dg2[NP], db2[NP], ar2[NP], ag2[NP], ab2[NP];
@@ -317,6 +314,45 @@ __global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const flo
     }
 }
 
+template <int PPT, bool MASKED>
+__global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
+                                                             const float4* __restrict__ rendered, const float4* __restrict__ gt,
+                                                             int quantize, const uint32_t* __restrict__ last_idx,
+                                                             const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
+                                                             const uint32_t* __restrict__ order, float* __restrict__ acc,
+                                                             const uint2* __restrict__ vis) {
+    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
+    const bool redo = tile_flags[tile] != 0u;
+    if (MASKED && redo) return;                                      // CTA-uniform: left to blend_backward_flagged_kernel
+    blend_backward_tile<PPT, MASKED>(tile, redo, rec, svals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal, acc, vis);
+}
+
+// The flagged tiles behind a masked launch, by the pinned walk.  They are rare (none in most frames), so the grid is not one
+// CTA per tile: a CTA reads the flags of 256 / PPT consecutive tiles with one coalesced load, leaves at once when none is set
+// (3 us for the whole launch instead of the 10 us that 8160 CTAs need to start and return), and otherwise walks its flagged
+// tiles one after another.
+template <int PPT>
+__global__ void __launch_bounds__(256 / PPT) blend_backward_flagged_kernel(const float4* __restrict__ rec, const uint32_t* __restrict__ svals,
+                                                             const uint2* __restrict__ ranges, uint32_t W, uint32_t H, uint32_t ntx,
+                                                             uint32_t ntiles, const float4* __restrict__ rendered,
+                                                             const float4* __restrict__ gt, int quantize,
+                                                             const uint32_t* __restrict__ last_idx, const float* __restrict__ tfinal,
+                                                             const uint32_t* __restrict__ tile_flags, float* __restrict__ acc) {
+    constexpr int NT = 256 / PPT;
+    __shared__ unsigned char s_flag[NT];
+    const uint32_t t = blockIdx.x * NT + threadIdx.x;
+    const bool f = t < ntiles && tile_flags[t] != 0u;
+    s_flag[threadIdx.x] = f ? 1 : 0;
+    if (!__syncthreads_or(f)) return;
+    for (uint32_t i = 0; i < (uint32_t)NT; i++) {
+        if (!s_flag[i]) continue;                                    // CTA-uniform
+        blend_backward_tile<PPT, false>(blockIdx.x * NT + i, true, rec, svals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal,
+                                        acc, nullptr);
+        __syncthreads();
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // K8: per-Gaussian tail of tiledBackward (:517-736) applied to the nine moments.  HBM-bound (196 B/Gaussian).
 // Not pinned arithmetic: gradients are graded at 1e-3 relative.
@@ -446,12 +482,15 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
                               const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, cudaStream_t st) {
     if (ntx * nty == 0) return;
-#define GS_BWD_LAUNCH(PPT, MASKED, ONLY)                                                                            \
+#define GS_BWD_LAUNCH(PPT, MASKED)                                                                                  \
     blend_backward_kernel<PPT, MASKED><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
-                                                                         last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis, ONLY)
-    if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false, 0);
-    else if (vis) { GS_BWD_LAUNCH(2, true, 0); GS_BWD_LAUNCH(2, false, 1); }   // recorded visits; flagged tiles by the pinned variant
-    else GS_BWD_LAUNCH(2, false, 0);
+                                                                         last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis)
+    if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false);
+    else if (vis) {                                  // recorded visits; flagged tiles by the pinned variant
+        GS_BWD_LAUNCH(2, true);
+        blend_backward_flagged_kernel<2><<<(ntx * nty + 127u) / 128u, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, ntx * nty, rendered, gt,
+                                                                                    quantize, last_idx, tfinal, O.tile_flags, acc);
+    } else GS_BWD_LAUNCH(2, false);
 }
 bool gs_bwd_uses_visits() { return g_bwd_ppt == 2; }
 

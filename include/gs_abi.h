@@ -245,6 +245,9 @@ int gs_rast_count_evals(gs_rast*, uint64_t* E, uint64_t* C);
 uint64_t gs_rast_pair_count(const gs_rast*);
 uint64_t gs_rast_coarse_pair_count(const gs_rast*);                      /* (8x8-tile bin, Gaussian) pairs of the last forward in the default binned pipeline; 0 in the sort pipelines */
 int gs_rast_sort_passes(const gs_rast*);                /* digit passes the last forward ran */
+/* 1 if the last backward took its per-pixel decisions from the visit words the forward recorded (every backward of a
+ * rasterizer but its first, gs_tune "bwd_masks" = 1), 0 if it re-derived them (diagnostic of this library; no counterpart) */
+int gs_rast_backward_used_visits(const gs_rast*);
 
 /* ---- GPURadixSort64 / GPURadixSort32 (gpu_sort.hpp:14-107) ---------------------------------------------- */
 int gs_sort64_create(gs_ctx*, uint64_t max_elements, gs_sort64** out);

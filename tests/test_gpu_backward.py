@@ -25,7 +25,28 @@ def compare_grads(got, ref, absref, count):
     return rep
 
 
-def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False):
+@pytest.fixture(params=["pinned", "visits"], autouse=True)
+def walk(request, gs):
+    """every test of this file runs twice: with the backward walk that re-derives its decisions (gs_tune "bwd_masks" = 0; also the
+    only one a rasterizer's FIRST backward can take) and with the walk on the visit words the forward recorded (every later frame
+    of a training caller)"""
+    gs.tune("bwd_masks", 1 if request.param == "visits" else 0)
+    yield request.param
+    gs.tune("bwd_masks", 1)
+
+
+def run_backward(gs, R, G, D, u, img, gti, flags, walk):
+    """forward + backward in the requested walk; the visits walk needs one earlier backward on the rasterizer (it allocates the
+    words) and is asserted to have been taken"""
+    if walk == "visits":
+        R.forward(G, u, img)
+        R.backward(G, D, u, img, gti, flags)
+    R.forward(G, u, img)
+    R.backward(G, D, u, img, gti, flags)
+    assert R.backward_used_visits == (walk == "visits")
+
+
+def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False, walk="pinned"):
     ref = orc.render(g, u)
     gt = orc.render(gt_g, u)["image"]
     ref_gr = orc.backward(g, ref["proj"], ref["svals"], ref["ranges"], u, ref["last"], ref["image"], gt, quantize=quantize, want_abs=True)
@@ -35,8 +56,7 @@ def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False):
     gti.upload(gt)
     D = gs.Grads(ctx, len(g))
     try:
-        R.forward(G, u, img)
-        R.backward(G, D, u, img, gti, gs.GS_BWD_QUANTIZE_RGBA8 if quantize else 0)
+        run_backward(gs, R, G, D, u, img, gti, gs.GS_BWD_QUANTIZE_RGBA8 if quantize else 0, walk)
         got = D.download(len(g))
     finally:
         D.close(); gti.close(); img.close(); R.close(); G.close()
@@ -48,11 +68,11 @@ def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False):
     (2000, 100, 70, 0.03, 8),
     (10000, 256, 256, 0.012, synth.CONFIG_SEED["C1"]),
 ])
-def test_backward_parity(gs, ctx, orc, n, W, H, s0, seed):
+def test_backward_parity(gs, ctx, orc, n, W, H, s0, seed, walk):
     g = synth.make_scene(n, seed, s0)
     gt_g = synth.make_scene(n, seed ^ 0xA5A5, s0)
     u = synth.make_camera(1, 8, W, H, n)
-    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, walk=walk)
     assert np.abs(ref["opacity"]).max() > 0
     rep = compare_grads(got, ref, ab, cnt)
     # almost every component is inside the PURE 1e-3 relative bar; the band is for the cancelling remainder
@@ -62,17 +82,17 @@ def test_backward_parity(gs, ctx, orc, n, W, H, s0, seed):
         assert np.all(got["sh"][:, k] == 0)
 
 
-def test_backward_quantized_and_saturated(gs, ctx, orc):
+def test_backward_quantized_and_saturated(gs, ctx, orc, walk):
     """RGBA8 render-target mode (note G) on a dense scene where many pixels hit the T < 1e-4 cut (note I)"""
     n, W, H = 6000, 128, 96
     g = synth.make_scene(n, 31, 0.03); g["opacity"] += 2.0
     gt_g = synth.make_scene(n, 32, 0.03)
     u = synth.make_camera(5, 8, W, H, n)
-    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=True)
+    got, (ref, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=True, walk=walk)
     compare_grads(got, ref, ab, cnt)
 
 
-def test_backward_degenerate_conic_tiles(gs, ctx, orc):
+def test_backward_degenerate_conic_tiles(gs, ctx, orc, walk):
     """giant splats whose conic magnitude is < 1e-4 are skipped by the forward but not by the backward's first
     pass (note I): exercises the per-tile recompute path"""
     n, W, H = 3000, 256, 256
@@ -85,12 +105,12 @@ def test_backward_degenerate_conic_tiles(gs, ctx, orc):
     p = ref["proj"]
     mag = np.abs(p["conic"]).sum(1)
     assert ((mag < 1e-4) & (p["radius"] > 0)).sum() > 0, "fixture must contain conic-degenerate visible splats"
-    got, (refg, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (refg, ab, cnt) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, walk=walk)
     assert np.isfinite(refg["scale"]).all()
     compare_grads(got, refg, ab, cnt)
 
 
-def test_backward_nonfinite_pathology(gs, ctx, orc):
+def test_backward_nonfinite_pathology(gs, ctx, orc, walk):
     """150 opaque giants: the reference's second pass divides T by (1-alpha) for entries its first pass never
     multiplied in (note I), T overflows and the gradients of ~1/3 of the scene become inf/NaN.  The CUDA path must
     be non-finite for (at least) the same Gaussians so that Adam's NaN guard (shaders.metal:567-570) skips them."""
@@ -99,7 +119,7 @@ def test_backward_nonfinite_pathology(gs, ctx, orc):
     g["scale"][:150] = np.log(3.0)
     gt_g = synth.make_scene(n, 42, 0.02)
     u = synth.make_camera(2, 8, W, H, n)
-    got, (refg, _, _) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H)
+    got, (refg, _, _) = fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, walk=walk)
     bad_ref = ~(np.isfinite(refg["position"][:, 0]) & np.isfinite(refg["opacity"]) & np.isfinite(refg["sh"][:, 0]))
     bad_got = ~(np.isfinite(got["position"][:, 0]) & np.isfinite(got["opacity"]) & np.isfinite(got["sh"][:, 0]))
     assert bad_ref.sum() > 100

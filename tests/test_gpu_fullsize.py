@@ -59,6 +59,15 @@ def test_oracle_parity_at_full_size(gs, ctx, orc, wl, view, backward):
         if backward:
             assert p["grad_n_fail"] == 0, p["grad_groups"]
             assert p["grad_frac_need_band"] < 0.02
+            # the same frame again: from a rasterizer's second backward on, the walk runs on the forward's visit words
+            assert not R.backward_used_visits
+            R.forward(G, u, img)
+            R.backward(G, D, u, img, gti)
+            assert R.backward_used_visits
+            p2 = parity.frame_parity(gs, R, img.download(), ref, D.download(n), ref_gr, ab, cnt, what=wl + " (visit words)")
+            print({k: v for k, v in p2.items() if k != "grad_groups"})
+            assert p2["lists_equal"] and p2["last_equal"] and p2["image_max_abs"] <= 1e-4
+            assert p2["grad_n_fail"] == 0, p2["grad_groups"]
         assert R.count_evals() == (ref["E"], ref["C"])
     finally:
         for o in (D, gti, img, R, G):

@@ -43,6 +43,12 @@ def test_cuda_reproduces_golden(gs, ctx, path):
         R.backward(G, D, u, img, gti)
         got = D.download(n)
         compare_grads(got, d["grads"], d["grads_abs"], d["grads_terms"])
+        assert not R.backward_used_visits            # a rasterizer's first backward re-derives the walk's decisions ...
+        R.forward(G, u, img)
+        R.backward(G, D, u, img, gti)
+        assert R.backward_used_visits                # ... every later one takes them from the forward's visit words
+        assert np.array_equal(R.get(gs.RAST_LAST_IDX), d["last"]) and np.abs(img.download() - d["image"]).max() <= 1e-4
+        compare_grads(D.download(n), d["grads"], d["grads_abs"], d["grads_terms"])
         # Adam on the ORACLE's gradients (so the comparison is exact, not 1e-3)
         D.upload(d["grads"])
         A.step(G, D, LRS)
