@@ -207,10 +207,10 @@ __device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const b
         }
         for (uint32_t i = lane; i < total * 9u; i += 32u) my_acc[i] = 0.f;
         __syncthreads();
-        if (wmax > lo) {
+        if (MASKED || wmax > lo) {                                   // MASKED: a zero visit word says "not this warp's entry"
             // staged list indices ascend: entries at or beyond this warp's extent are of no interest to it
             uint32_t kend = total;
-            if (wmax < hi) {
+            if (!MASKED && wmax < hi) {
                 uint32_t a = 0, b = total;
                 while (a < b) { const uint32_t m = (a + b) >> 1; if (s_e[m].idx < wmax) a = m + 1; else b = m; }
                 kend = a;
@@ -222,8 +222,14 @@ __device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const b
                 uint32_t mk = __ballot_sync(0xFFFFFFFFu, want);
                 const uint32_t wbase = ebase + (uint32_t)wd * 32u * (uint32_t)sizeof(BwdEnt);
                 while (mk) {
-                    const int kb = 31 - __clz(mk);
-                    mk &= ~(1u << kb);
+                    int kb;
+                    if (MASKED) {                                    // bfind = the position of the highest set bit in one instruction
+                        asm("bfind.u32 %0, %1;" : "=r"(kb) : "r"(mk));
+                        mk ^= 1u << kb;
+                    } else {
+                        kb = 31 - __clz(mk);
+                        mk &= ~(1u << kb);
+                    }
                     const uint32_t addr = wbase + (uint32_t)kb * (uint32_t)sizeof(BwdEnt);
                     const float4 a = gs::lds128(addr);
                     const float4 b = gs::lds128(addr + 16u);
@@ -297,8 +303,15 @@ __device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const b
 #pragma unroll
                     for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
                     const int k = wd * 32 + kb;
-                    if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
-                    if (lane == 1u) my_acc[k * 9 + 8] = v9;
+                    if (MASKED) {
+                        // the four lanes of a group hold the same sum, all lanes the same v9: unpredicated stores to the same
+                        // words (one transaction) leave the predicate registers to the lane bits of the butterfly
+                        my_acc[k * 9 + reduce8_index(lane)] = tot;
+                        my_acc[k * 9 + 8] = v9;
+                    } else {
+                        if ((lane & 3u) == 0u) my_acc[k * 9 + reduce8_index(lane)] = tot;
+                        if (lane == 1u) my_acc[k * 9 + 8] = v9;
+                    }
                 }
             }
         }
