@@ -73,6 +73,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "dp_mc_threads")) { gs_tune_dp_mc(1, value); return GS_OK; }
     if (!strcmp(name, "dp_mc_unroll")) { gs_tune_dp_mc(2, value); return GS_OK; }
     if (!strcmp(name, "bwd_masks")) { g_bwd_masks = value ? 1 : 0; return GS_OK; }
+    if (!strcmp(name, "bwd_warp")) { gs_tune_bwd_warp(value); return GS_OK; }
     if (!strcmp(name, "side_bins")) { g_side_bins = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }

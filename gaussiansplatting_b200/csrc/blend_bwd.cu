@@ -367,6 +367,154 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_flagged_kernel(const
 }
 
 // ---------------------------------------------------------------------------------------------------
+// K7, warp-autonomous walk on the forward's visit words (gs_tune "bwd_warp" = 1).
+// In the CTA-cooperative kernels above the four warps of a tile meet at three barriers per round of 128 entries, and the
+// warp with the most visits of a round keeps the other three waiting (ncu: the barrier is the largest stall of the kernel,
+// 22 % of the warps' time).  With the visit words a warp does not need the CTA: word (entry, warp) says whether the entry
+// concerns the warp at all.  Each warp walks its own extent of the tile's list back to front in chunks of 32 entries: lane i
+// reads entry i's pair value and the warp's word of it (the next chunk's are in flight while this one is walked), the lanes
+// whose word is not zero gather their records into the warp's 1.5 KB of shared memory, and the warp visits them highest
+// first.  The nine moments of a visit go to the per-Gaussian rows with global float reductions straight from the registers
+// (no shared accumulator, no flush pass): about as many reductions as the cooperative kernel issues, since an entry is
+// visited by two warps on average and the cooperative kernel flushes every staged entry's nine moments per tile.  No
+// __syncthreads anywhere: a warp whose pixels took nothing leaves at once.
+struct WEnt { float4 r0, r1; float b; uint32_t gid, vx, vy; };   // 48 B: three LDS.128 per visit (record, id, visit word)
+#ifndef GS_BWD_WARP_MINB
+#define GS_BWD_WARP_MINB 8
+#endif
+__global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_kernel(
+    const float4* __restrict__ rec, const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W, uint32_t H,
+    uint32_t ntx, const float4* __restrict__ rendered, const float4* __restrict__ gt, int quantize,
+    const uint32_t* __restrict__ last_idx, const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
+    const uint32_t* __restrict__ order, float* __restrict__ acc, const uint2* __restrict__ vis) {
+    __shared__ __align__(16) WEnt s_e[4][32];
+    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
+    if (tile_flags[tile] != 0u) return;                              // left to blend_backward_flagged_kernel
+    const uint32_t tX = tile % ntx, tY = tile / ntx;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint2 range = ranges[tile];                                // :410-413
+    gs::f32x2 X2, Y2, T2, dr2, dg2, db2, ar2, ag2, ab2;
+    uint32_t emax = 0;
+    {
+        float pxf[2], pyf[2], T[2], dr[2], dg[2], db[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            uint32_t x, y;
+            gs::tile_pixel<2>(warp, lane, h, x, y);
+            const uint32_t px = tX * 16u + x, py = tY * 16u + y;
+            pxf[h] = (float)px + 0.5f; pyf[h] = (float)py + 0.5f;        // :416
+            T[h] = 1.0f; dr[h] = 0.f; dg[h] = 0.f; db[h] = 0.f;
+            if (px < W && py < H) {
+                const size_t pix = (size_t)py * W + px;
+                const uint32_t li = last_idx[pix];                       // :404-407
+                if (li != 0xFFFFFFFFu) {
+                    emax = max(emax, min(li + 1u, range.x + range.y) - range.x);    // :427
+                    const float4 r = rendered[pix], t = gt[pix];         // :418-423
+                    float rr[3] = {r.x, r.y, r.z};
+                    const float tt[3] = {t.x, t.y, t.z};
+                    float sg[3];
+#pragma unroll
+                    for (int c = 0; c < 3; c++) {
+                        if (quantize) rr[c] = floorf(gs::clampf(rr[c], 0.f, 1.f) * 255.0f + 0.5f) / 255.0f;
+                        const float diff = rr[c] - tt[c];
+                        sg[c] = (diff > 0.f) ? (1.0f / 3.0f) : ((diff < 0.f) ? (-1.0f / 3.0f) : 0.f);
+                    }
+                    dr[h] = sg[0]; dg[h] = sg[1]; db[h] = sg[2];
+                    T[h] = tfinal[pix];
+                }
+            }
+        }
+        X2 = gs::pk2(pxf[0], pxf[1]); Y2 = gs::pk2(pyf[0], pyf[1]); T2 = gs::pk2(T[0], T[1]);
+        dr2 = gs::pk2(dr[0], dr[1]); dg2 = gs::pk2(dg[0], dg[1]); db2 = gs::pk2(db[0], db[1]);
+        ar2 = gs::bc2(1.0f); ag2 = gs::bc2(1.0f); ab2 = gs::bc2(1.0f);   // accum_rec starts at the white background :468-470
+    }
+    const uint32_t wmax = __reduce_max_sync(0xFFFFFFFFu, emax);      // this warp's extent of the list
+    if (wmax == 0u) return;
+    const uint32_t wu = __shfl_sync(0xFFFFFFFFu, warp, 0);           // the warp index as a value the compiler knows to be uniform
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e) + wu * (32u * (uint32_t)sizeof(WEnt));
+    WEnt* const me = &s_e[wu][lane];
+    const uint32_t* const sv = svals + range.x;
+    const uint2* const vw = vis + (size_t)range.x * 4u + wu;         // this warp's word of list entry i: vw[4 * i]
+    const uint32_t lanebit = 1u << lane, ridx = reduce8_index(lane);
+    const gs::f32x2 one2 = gs::bc2(1.0f);
+    // chunks of 32 list entries, back to front, cut at multiples of 32 so that the 128-byte loads of the pair values are aligned
+    uint32_t lo = (wmax - 1u) & ~31u;
+    uint32_t v_n = GS_CULL_BIT;
+    uint2 w_n = make_uint2(0u, 0u);
+    if (lo + lane < wmax) { v_n = sv[lo + lane]; w_n = vw[(size_t)(lo + lane) * 4u]; }
+    for (;;) {
+        const uint32_t v = v_n;
+        const uint2 w = w_n;
+        const bool more = lo != 0u;
+        if (more) { lo -= 32u; v_n = sv[lo + lane]; w_n = vw[(size_t)(lo + lane) * 4u]; }   // in flight while this chunk is walked
+        // a culled pair was never staged by the forward and has no word (GS_CULL_BIT, pairs.cu); a zero word = not this warp's entry
+        const bool has = !(v >> 31) && (w.x | w.y) != 0u;
+        uint32_t mk = __ballot_sync(0xFFFFFFFFu, has);
+        if (mk) {
+            if (has) {
+                const uint32_t g = v & GS_ID_MASK;
+                me->r0 = rec[3 * (size_t)g]; me->r1 = rec[3 * (size_t)g + 1];
+                me->b = rec[3 * (size_t)g + 2].x; me->gid = g; me->vx = w.x; me->vy = w.y;
+            }
+            __syncwarp();
+            while (mk) {                                             // :473 back to front
+                int kb;
+                asm("bfind.u32 %0, %1;" : "=r"(kb) : "r"(mk));
+                mk ^= 1u << kb;
+                const uint32_t addr = ebase + (uint32_t)kb * (uint32_t)sizeof(WEnt);
+                const float4 a = gs::lds128(addr);
+                const float4 b = gs::lds128(addr + 16u);
+                const float4 c = gs::lds128(addr + 32u);
+                const gs::f32x2 sx = gs::bc2(a.x), sy = gs::bc2(a.y), Ah = gs::bc2(a.z), Bn = gs::bc2(a.w), Ch = gs::bc2(b.x),
+                                cr = gs::bc2(b.z), cg = gs::bc2(b.w), cb = gs::bc2(c.x);
+                const gs::f32x2 dx = gs::fsub2(X2, sx), dy = gs::fsub2(Y2, sy);   // :483
+                const gs::f32x2 pw2 = gs::blend_power2(Ah, Bn, Ch, dx, dy);
+                float t0, t1, al[2], G[2];
+                gs::up2(gs::fmul2(pw2, gs::bc2(GS_LOG2E)), t0, t1);
+                G[0] = ex2_approx(t0); G[1] = ex2_approx(t1);                      // :492
+                const bool c0 = (__float_as_uint(c.z) & lanebit) != 0u, c1 = (__float_as_uint(c.w) & lanebit) != 0u;   // the forward's decisions
+                al[0] = c0 ? fminf(b.y * G[0], GS_ALPHA_MAX) : 0.0f; al[1] = c1 ? fminf(b.y * G[1], GS_ALPHA_MAX) : 0.0f;
+                G[0] = c0 ? G[0] : 0.0f; G[1] = c1 ? G[1] : 0.0f;
+                const gs::f32x2 alpha = gs::pk2(al[0], al[1]), Gq = gs::pk2(G[0], G[1]);
+                const gs::f32x2 om = gs::fsub2(one2, alpha);
+                float om0, om1;
+                gs::up2(om, om0, om1);
+                const gs::f32x2 Tn = gs::fmul2(T2, gs::pk2(gs::rcp_approx(fmaxf(om0, 0.0001f)), gs::rcp_approx(fmaxf(om1, 0.0001f))));   // :498
+                T2 = Tn;
+                const gs::f32x2 w2 = gs::fmul2(alpha, Tn);                             // :500
+                gs::f32x2 s2 = gs::fmul2(dr2, gs::fsub2(cr, ar2));
+                s2 = gs::ffma2(dg2, gs::fsub2(cg, ag2), s2);
+                s2 = gs::ffma2(db2, gs::fsub2(cb, ab2), s2);
+                const gs::f32x2 dLdA = gs::fmul2(Tn, s2);                              // :510
+                ar2 = gs::ffma2(alpha, cr, gs::fmul2(om, ar2));                        // :514
+                ag2 = gs::ffma2(alpha, cg, gs::fmul2(om, ag2));
+                ab2 = gs::ffma2(alpha, cb, gs::fmul2(om, ab2));
+                const gs::f32x2 q = gs::fmul2(dLdA, Gq);
+                const gs::f32x2 qx = gs::fmul2(q, dx), qy = gs::fmul2(q, dy);
+                gs::f32x2 m2[9];
+                m2[0] = gs::fmul2(dr2, w2); m2[1] = gs::fmul2(dg2, w2); m2[2] = gs::fmul2(db2, w2); m2[3] = q;
+                m2[4] = qx; m2[5] = qy; m2[6] = gs::fmul2(qx, dx); m2[7] = gs::fmul2(qx, dy); m2[8] = gs::fmul2(qy, dy);
+                float v8[8], v9;
+#pragma unroll
+                for (int i = 0; i < 9; i++) {
+                    float l, h;
+                    gs::up2(m2[i], l, h);
+                    if (i < 8) v8[i] = l + h; else v9 = l + h;
+                }
+                const float tot = warp_reduce8_transposed(v8, lane);
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
+                float* const row = acc + (size_t)__float_as_uint(c.y) * 12u;
+                if ((lane & 3u) == 0u && tot != 0.f) atomicAdd(row + ridx, tot);
+                if (lane == 1u && v9 != 0.f) atomicAdd(row + 8, v9);
+            }
+            __syncwarp();
+        }
+        if (!more) break;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // K8: per-Gaussian tail of tiledBackward (:517-736) applied to the nine moments.  HBM-bound (196 B/Gaussian).
 // Not pinned arithmetic: gradients are graded at 1e-3 relative.
 // ---------------------------------------------------------------------------------------------------
@@ -489,7 +637,9 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(GsParams P, Gs
 }  // namespace
 
 static int g_bwd_ppt = GS_BWD_PPT;
+static int g_bwd_warp = 1;   // masked walk: 1 = warp-autonomous kernel, 0 = CTA-cooperative rounds
 void gs_tune_bwd_ppt(int v) { if (v == 2 || v == 4) g_bwd_ppt = v; }
+void gs_tune_bwd_warp(int v) { g_bwd_warp = v ? 1 : 0; }
 
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
@@ -500,7 +650,10 @@ void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals,
                                                                          last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis)
     if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false);
     else if (vis) {                                  // recorded visits; flagged tiles by the pinned variant
-        GS_BWD_LAUNCH(2, true);
+        if (g_bwd_warp)
+            blend_backward_warp_kernel<<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal,
+                                                                  O.tile_flags, O.tile_order, acc, vis);
+        else GS_BWD_LAUNCH(2, true);
         blend_backward_flagged_kernel<2><<<(ntx * nty + 127u) / 128u, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, ntx * nty, rendered, gt,
                                                                                     quantize, last_idx, tfinal, O.tile_flags, acc);
     } else GS_BWD_LAUNCH(2, false);
