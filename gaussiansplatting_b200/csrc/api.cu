@@ -74,6 +74,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "dp_mc_unroll")) { gs_tune_dp_mc(2, value); return GS_OK; }
     if (!strcmp(name, "bwd_masks")) { g_bwd_masks = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "bwd_warp")) { gs_tune_bwd_warp(value); return GS_OK; }
+    if (!strcmp(name, "fwd_warp")) { gs_tune_fwd_warp(value); return GS_OK; }
     if (!strcmp(name, "side_bins")) { g_side_bins = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }
@@ -555,7 +556,7 @@ struct gs_rast {
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
     // forward's visit words for the backward (blend_fwd.cu / blend_bwd.cu): 4 x uint2 per pair slot.  Allocated by the first
     // backward call (render-only users never pay), regrown with the pair buffers; vis_valid = the last forward filled it.
-    uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false, bwd_used_vis = false;
+    uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false, bwd_used_vis = false, vis_warp_extent = false;
     bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
@@ -630,6 +631,7 @@ static int rast_reserve_image(gs_rast* r, uint32_t W, uint32_t H) {   // ensureB
 // the buffer the coming forward blend writes its visits to (null: none); marks them valid for the backward of this frame
 static uint2* rast_vis_for_forward(gs_rast* r) {
     r->vis_valid = r->vis != nullptr && g_bwd_masks && gs_fwd_writes_visits() && r->vis_cap >= r->cap_pairs;
+    r->vis_warp_extent = gs_fwd_words_end_with_the_warp();
     return r->vis_valid ? r->vis : nullptr;
 }
 static int rast_reserve_vis(gs_rast* r) {      // visit words for cap_pairs pair slots x 4 warps (32 B per pair slot)
@@ -925,7 +927,7 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     const bool masked = r->vis_valid && g_bwd_masks && gs_bwd_uses_visits();
     r->bwd_used_vis = masked;
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
-                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, st);
+                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, r->vis_warp_extent ? 1 : 0, st);
     if (!r->want_vis && g_bwd_masks) { r->want_vis = true; GS_TRY(rast_reserve_vis(r)); }   // a training caller: record visits from the next forward on
     r->mark(9);
     gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,

@@ -380,7 +380,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_flagged_kernel(const
 // __syncthreads anywhere: a warp whose pixels took nothing leaves at once.
 struct WEnt { float4 r0, r1; float b; uint32_t gid, vx, vy; };   // 48 B: three LDS.128 per visit (record, id, visit word)
 #ifndef GS_BWD_WARP_MINB
-#define GS_BWD_WARP_MINB 8
+#define GS_BWD_WARP_MINB 8   // 60 registers; measured flat from 7 to 10 CTAs per SM (385-395 us at C2): the kernel is issue-bound
 #endif
 __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_kernel(
     const float4* __restrict__ rec, const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W, uint32_t H,
@@ -643,14 +643,15 @@ void gs_tune_bwd_warp(int v) { g_bwd_warp = v ? 1 : 0; }
 
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
-                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, cudaStream_t st) {
+                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, int vis_warp_extent,
+                              cudaStream_t st) {
     if (ntx * nty == 0) return;
 #define GS_BWD_LAUNCH(PPT, MASKED)                                                                                  \
     blend_backward_kernel<PPT, MASKED><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
                                                                          last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis)
     if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false);
     else if (vis) {                                  // recorded visits; flagged tiles by the pinned variant
-        if (g_bwd_warp)
+        if (g_bwd_warp || vis_warp_extent)
             blend_backward_warp_kernel<<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal,
                                                                   O.tile_flags, O.tile_order, acc, vis);
         else GS_BWD_LAUNCH(2, true);

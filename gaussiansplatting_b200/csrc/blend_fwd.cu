@@ -293,10 +293,143 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
     if (threadIdx.x == 0) tile_flags[tile] = s_degen;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// K6, warp-autonomous walk (gs_tune "fwd_warp" = 1).  In the kernel above the four warps of a tile stage rounds of 128
+// entries together and meet at a barrier per round; a warp whose pixels are saturated, or which has few visits in a
+// round, waits for the others (ncu: the barrier is the kernel's largest stall).  Here a warp walks the tile's list on its own,
+// 32 entries at a time: lane i reads entry i's pair value (the next chunk's is in flight), gathers its record, tests its
+// footprint against the warp's 8x8 pixels and, if it can reach them, puts it into the warp's 1.5 KB of shared memory; the
+// warp then visits those entries in list order and stops as soon as its own 64 pixels are done.  The records are read by all
+// four warps of the tile (L1 serves the repeats).  VIS: the lane that holds entry kb keeps the visit's two ballots and stores
+// the warp's word of its entry after the chunk (zero if the warp did not take it); words exist up to the end of the chunk in
+// which the warp stopped, which covers every lastContribIdx of its pixels -- the extent the warp-autonomous backward reads.
+// Arithmetic and order of a pixel's walk are those of the kernel above: images and lastContribIdx are bit-identical.
+#ifndef GS_FWD_WARP_MINB
+#define GS_FWD_WARP_MINB 10
+#endif
+template <bool VIS>
+__global__ void __launch_bounds__(128, GS_FWD_WARP_MINB) blend_forward_warp_kernel(
+    const float4* __restrict__ rec, const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W, uint32_t H,
+    uint32_t ntx, float4* __restrict__ image, uint32_t* __restrict__ last_idx, float* __restrict__ tfinal,
+    uint32_t* __restrict__ tile_flags, const uint32_t* __restrict__ order, uint2* __restrict__ vis) {
+    __shared__ __align__(16) FwdEnt s_e[4][32];
+    const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
+    const uint32_t tX = tile % ntx, tY = tile / ntx;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    const uint2 range = ranges[tile];                                // :320-323
+    if (threadIdx.x == 0) tile_flags[tile] = 0u;
+    __syncthreads();          // the only barrier: the clear of the tile's flag is ordered before any warp's set (end of kernel)
+    uint32_t px[2], py[2], last[2];
+    float Tp[2];
+    gs::f32x2 X2, Y2, T2, Cr2 = gs::bc2(0.f), Cg2 = gs::bc2(0.f), Cb2 = gs::bc2(0.f);
+    bool live = false;
+    {
+        float xf[2], yf[2], t0[2];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            uint32_t x, y;
+            gs::tile_pixel<2>(warp, lane, h, x, y);
+            px[h] = tX * 16u + x; py[h] = tY * 16u + y;
+            const bool in = px[h] < W && py[h] < H;
+            xf[h] = (float)px[h] + 0.5f; yf[h] = (float)py[h] + 0.5f;   // :328
+            t0[h] = in ? 1.0f : 0.0f;                                   // a pixel outside the image never walks (T = 0 <= eps)
+            Tp[h] = 1.0f; last[h] = 0xFFFFFFFFu;
+            live |= in;
+        }
+        X2 = gs::pk2(xf[0], xf[1]); Y2 = gs::pk2(yf[0], yf[1]); T2 = gs::pk2(t0[0], t0[1]);
+    }
+    bool wlive = __any_sync(0xFFFFFFFFu, live);      // warp-uniform: some pixel of this warp still walks
+    const uint32_t wu = __shfl_sync(0xFFFFFFFFu, warp, 0);           // the warp index as a value the compiler knows to be uniform
+    const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e) + wu * (32u * (uint32_t)sizeof(FwdEnt));
+    FwdEnt* const me = &s_e[wu][lane];
+    uint32_t rx, ry;
+    float ex, ey;
+    gs::warp_region<2>(wu, rx, ry, ex, ey);
+    const float bx0 = (float)(tX * 16u + rx) + 0.5f, by0 = (float)(tY * 16u + ry) + 0.5f;
+    const uint32_t* const sv = svals + range.x;
+    bool degen = false;
+    uint32_t v_n = lane < range.y ? sv[lane] : GS_CULL_BIT;
+    for (uint32_t base = 0; base < range.y && wlive; base += 32u) {
+        const uint32_t v = v_n;
+        v_n = base + 32u + lane < range.y ? sv[base + 32u + lane] : GS_CULL_BIT;   // in flight while this chunk is walked
+        bool reach = false;
+        if (!(v >> 31)) {                                            // a culled pair can never contribute (pairs.cu)
+            const float4 r0 = rec[3 * (size_t)v], r2 = rec[3 * (size_t)v + 2];
+            float4 r1 = rec[3 * (size_t)v + 1];
+            if (__float_as_uint(r2.w) & 1u) { r1.y = 0.f; degen = true; }   // :350-351 conic-magnitude skip (forward only)
+            reach = !gs::box_cannot_contribute(gs::cull_rec(r0, r1), bx0, by0, ex, ey);
+            if (reach) { me->r0 = r0; me->r1 = r1; me->b = r2.x; me->idx = range.x + base + lane; }
+        }
+        uint32_t m = __ballot_sync(0xFFFFFFFFu, reach);
+        uint32_t w0 = 0u, w1 = 0u;                                   // VIS: the warp's visit word of this lane's entry
+        __syncwarp();
+        while (m) {                                                  // :334 in list order
+            const uint32_t kb = (uint32_t)__ffs(m) - 1u;
+            m &= m - 1u;
+            const uint32_t addr = ebase + kb * (uint32_t)sizeof(FwdEnt);
+            const float4 a = gs::lds128(addr);
+            const float4 b = gs::lds128(addr + 16u);
+            const float2 c = gs::lds64(addr + 32u);
+            const uint32_t idx = __float_as_uint(c.y);
+            const gs::f32x2 sx = gs::bc2(a.x), sy = gs::bc2(a.y), Ah = gs::bc2(a.z), Bn = gs::bc2(a.w), Ch = gs::bc2(b.x),
+                            op = gs::bc2(b.y), cr = gs::bc2(b.z), cg = gs::bc2(b.w), cb = gs::bc2(c.x);
+            const gs::f32x2 dx = gs::fsub2(X2, sx), dy = gs::fsub2(Y2, sy);   // :347
+            const gs::f32x2 pw2 = gs::blend_power2(Ah, Bn, Ch, dx, dy);
+            const gs::f32x2 G2 = gs::exp_blend2(pw2);                             // :362
+            const gs::f32x2 a2 = gs::fmul2(op, G2);                               // :363
+            float pw[2], al[2], Tn[2], To[2];
+            gs::up2(pw2, pw[0], pw[1]); gs::up2(a2, al[0], al[1]); gs::up2(T2, To[0], To[1]);
+            bool c2[2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                al[h] = fminf(al[h], GS_ALPHA_MAX);
+                // :334 (the pixel still walks: T > 1e-4), :359, :366
+                c2[h] = (To[h] > GS_T_EPS) && (pw[h] <= 0.0f) && !(pw[h] < -4.5f) && !(al[h] < GS_ALPHA_MIN);
+                al[h] = c2[h] ? al[h] : 0.0f;
+            }
+            const gs::f32x2 alpha = gs::pk2(al[0], al[1]);
+            const gs::f32x2 w2 = gs::fmul2(alpha, T2);                          // :369
+            Cr2 = gs::ffma2(cr, w2, Cr2); Cg2 = gs::ffma2(cg, w2, Cg2); Cb2 = gs::ffma2(cb, w2, Cb2);
+            T2 = gs::fmul2(T2, gs::fsub2(gs::bc2(1.0f), alpha));            // :370
+            gs::up2(T2, Tn[0], Tn[1]);
+            bool alive = false;
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                Tp[h] = c2[h] ? To[h] : Tp[h];
+                last[h] = c2[h] ? idx : last[h];                                  // :372
+                alive |= Tn[h] > GS_T_EPS;                                        // :334 loop condition
+            }
+            if (VIS) {
+                const uint32_t m0 = __ballot_sync(0xFFFFFFFFu, c2[0]), m1 = __ballot_sync(0xFFFFFFFFu, c2[1]);
+                if (lane == kb) { w0 = m0; w1 = m1; }
+            }
+            if (!__any_sync(0xFFFFFFFFu, alive)) { wlive = false; break; }
+        }
+        if (VIS) { if (!(v >> 31)) vis[(size_t)(range.x + base + lane) * 4u + wu] = make_uint2(w0, w1); }
+        __syncwarp();
+    }
+    if (degen) tile_flags[tile] = 1u;
+    float Tf[2], Cr[2], Cg[2], Cb[2];
+    gs::up2(T2, Tf[0], Tf[1]); gs::up2(Cr2, Cr[0], Cr[1]); gs::up2(Cg2, Cg[0], Cg[1]); gs::up2(Cb2, Cb[0], Cb[1]);
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+        if (px[j] < W && py[j] < H) {
+            const size_t pix = (size_t)py[j] * W + px[j];
+            image[pix] = make_float4(gs::fadd(Cr[j], Tf[j]), gs::fadd(Cg[j], Tf[j]), gs::fadd(Cb[j], Tf[j]), 1.0f);   // :377-384 white background
+            last_idx[pix] = last[j];                                  // :382
+            tfinal[pix] = (Tf[j] < GS_T_EPS) ? Tp[j] : Tf[j];         // as in blend_forward_kernel
+        }
+    }
+}
+
 }  // namespace
 
 static int g_fwd_ppt = GS_FWD_PPT;
+static int g_fwd_warp = 1;   // 1 = warp-autonomous forward walk, 0 = CTA-cooperative rounds
 void gs_tune_fwd_ppt(int v) { if (v == 2 || v == 4) g_fwd_ppt = v; }
+void gs_tune_fwd_warp(int v) { g_fwd_warp = v ? 1 : 0; }
+// the visit words of the warp-autonomous forward end with each warp's own walk: only the warp-autonomous backward may read them
+bool gs_fwd_words_end_with_the_warp() { return g_fwd_ppt == 2 && g_fwd_warp; }
 bool gs_fwd_writes_visits() { return g_fwd_ppt == 2; }
 
 void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* /*lb*/,
@@ -328,7 +461,11 @@ void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, 
     blend_forward_kernel<PPT, false, VIS><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
                                                                             tfinal, O.tile_flags, O.tile_order, nullptr, vis)
     if (O.tile_order && !order_ready) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, ntx * nty, O.tile_order);
+#define GS_FWD_WARP_LAUNCH(VIS)                                                                                       \
+    blend_forward_warp_kernel<VIS><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, tfinal, \
+                                                               O.tile_flags, O.tile_order, vis)
     if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4, false);
+    else if (g_fwd_warp) { if (vis) GS_FWD_WARP_LAUNCH(true); else GS_FWD_WARP_LAUNCH(false); }
     else if (vis) GS_FWD_LAUNCH(2, true);
     else GS_FWD_LAUNCH(2, false);
 }

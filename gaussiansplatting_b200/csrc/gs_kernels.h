@@ -80,7 +80,8 @@ void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, co
 //   acc[12i+4..5] = sum q*dx, q*dy            acc[12i+6..8] = sum q*dx^2, q*dx*dy, q*dy^2
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
-                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, cudaStream_t st);
+                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, int vis_warp_extent,
+                              cudaStream_t st);
 
 // K8: per-Gaussian chain: moments -> parameter gradients, written to (accumulate = 0) or added into the packed gradient
 // planes; clears the moment rows it consumed
@@ -187,6 +188,8 @@ void gs_tune_dp_mc(int which, int v);   // in-switch reduce: 0 grid, 1 threads p
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
 void gs_tune_fwd_ppt(int v);
 bool gs_fwd_writes_visits();   // the forward variant in use records its (entry, warp) visits (PPT 2)
+void gs_tune_fwd_warp(int v);  // forward blend: 1 = warp-autonomous walk, 0 = CTA-cooperative rounds
+bool gs_fwd_words_end_with_the_warp();
 void gs_tune_bwd_warp(int v);  // masked backward: 1 = warp-autonomous walk, 0 = CTA-cooperative rounds
 bool gs_bwd_uses_visits();     // the backward variant in use can consume them (PPT 2)
 void gs_tune_bwd_ppt(int v);
