@@ -425,11 +425,16 @@ __global__ void __launch_bounds__(128, GS_FWD_WARP_MINB) blend_forward_warp_kern
 }  // namespace
 
 static int g_fwd_ppt = GS_FWD_PPT;
-static int g_fwd_warp = 1;   // 1 = warp-autonomous forward walk, 0 = CTA-cooperative rounds
+// forward walk: 0 = CTA-cooperative rounds, 1 = warp-autonomous when the frame records visit words (training), cooperative for
+// render-only frames, 2 = warp-autonomous always.  Measured on one B200 (profiles/r2_fwd_warp_ab.txt): training forward 227 ->
+// 215 us at C2, 447 -> 387 us on a C5 view; render-only 435 -> 409 us on a C5 view and 272 -> 251 us at C3 (dense lists, many
+// saturated pixels), but 599 -> 609 us at C4 and 211 -> 214 us at C2 (tiny splats: an entry reaches one warp of four and the
+// per-chunk footprint tests weigh more than the barriers did), hence 1.
+static int g_fwd_warp = 1;
 void gs_tune_fwd_ppt(int v) { if (v == 2 || v == 4) g_fwd_ppt = v; }
-void gs_tune_fwd_warp(int v) { g_fwd_warp = v ? 1 : 0; }
+void gs_tune_fwd_warp(int v) { if (v >= 0 && v <= 2) g_fwd_warp = v; }
 // the visit words of the warp-autonomous forward end with each warp's own walk: only the warp-autonomous backward may read them
-bool gs_fwd_words_end_with_the_warp() { return g_fwd_ppt == 2 && g_fwd_warp; }
+bool gs_fwd_words_end_with_the_warp() { return g_fwd_ppt == 2 && g_fwd_warp != 0; }
 bool gs_fwd_writes_visits() { return g_fwd_ppt == 2; }
 
 void gs_launch_tile_ranges(const uint64_t* sorted_keys, uint32_t num_pairs, uint32_t num_tiles, uint32_t* /*lb*/,
@@ -465,7 +470,8 @@ void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, 
     blend_forward_warp_kernel<VIS><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, tfinal, \
                                                                O.tile_flags, O.tile_order, vis)
     if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4, false);
-    else if (g_fwd_warp) { if (vis) GS_FWD_WARP_LAUNCH(true); else GS_FWD_WARP_LAUNCH(false); }
+    else if (vis && g_fwd_warp) GS_FWD_WARP_LAUNCH(true);
+    else if (g_fwd_warp == 2) GS_FWD_WARP_LAUNCH(false);
     else if (vis) GS_FWD_LAUNCH(2, true);
     else GS_FWD_LAUNCH(2, false);
 }
