@@ -9,6 +9,15 @@ from gaussiansplatting_b200 import synth
 
 pytestmark = pytest.mark.gpu
 
+@pytest.fixture(params=["rounds", "warps"], autouse=True)
+def forward_walk(request, gs):
+    """every test of this file runs with both forward blend kernels: the CTA-cooperative rounds (the default of a render-only
+    frame) and the warp-autonomous walk (gs_tune "fwd_warp" = 2; the default of a frame that records visit words)"""
+    gs.tune("fwd_warp", 2 if request.param == "warps" else 0)
+    yield request.param
+    gs.tune("fwd_warp", 1)
+
+
 FLOAT_FIELDS = ["screenPos", "conic", "depth", "opacity", "color", "radius", "viewPos_xy", "cov2D"]
 UINT_FIELDS = ["tileMinX", "tileMinY", "tileMaxX", "tileMaxY"]
 
