@@ -73,13 +73,19 @@ def ncu_traffic(kernel_substr):
             continue
         ir, iw = rows[0].index("dram__bytes_read.sum"), rows[0].index("dram__bytes_write.sum")
         unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        it = rows[0].index("gpu__time_duration.sum") if "gpu__time_duration.sum" in rows[0] else None
+        best = None                                   # several kernels may match (the flagged-tile pass): the longest launch
         for r in rows[2:]:
             if r and kernel_substr in r[0]:
                 try:
-                    return (float(r[ir]) * unit.get(rows[1][ir], 1.0) + float(r[iw]) * unit.get(rows[1][iw], 1.0),
-                            os.path.relpath(path, ROOT))
+                    t = float(r[it]) if it is not None else 0.0
+                    b = float(r[ir]) * unit.get(rows[1][ir], 1.0) + float(r[iw]) * unit.get(rows[1][iw], 1.0)
                 except (ValueError, IndexError):
-                    pass
+                    continue
+                if best is None or t > best[0]:
+                    best = (t, b)
+        if best is not None:
+            return best[1], os.path.relpath(path, ROOT)
     return None, None
 
 
