@@ -111,6 +111,13 @@ int gs_version(void);
  *   "sort_even"            1 (default) one-wave radix passes pick the tile size that evens out the CTAs per SM
  *   "sort_hybrid"          1 (default) hybrid plan for full 64-bit sorts, 0 always the 8-pass LSD plan
  *   "sort_tiny_tiles", "tile_sort_ballot", "sort_api_ballot"   ranking / tile-size experiments (off / as shipped)
+ *   "depth_prehist"        1 (default) the projection kernel fills the depth sort's digit histograms
+ *   "side_bins"            1 (default) the bins-from-histogram kernel runs on a side stream under the bin pass
+ *   "bwd_masks"            1 (default) a training forward records its visit words and the backward walks on them
+ *   "bwd_warp"             1 (default) that backward is the warp-autonomous kernel, 0 the CTA-cooperative one
+ *   "fwd_warp"             forward blend: 0 CTA-cooperative rounds, 1 (default) warp-autonomous when the frame records
+ *                          visit words, 2 warp-autonomous always
+ *   "dp_mc_grid", "dp_mc_threads", "dp_mc_unroll"   launch shape of the in-switch gradient sum
  * unknown names return GS_ERR_ARG */
 int gs_tune(const char* name, int value);
 
