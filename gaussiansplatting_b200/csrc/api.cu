@@ -75,6 +75,7 @@ int gs_tune(const char* name, int value) {
     if (!strcmp(name, "bwd_masks")) { g_bwd_masks = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "bwd_warp")) { gs_tune_bwd_warp(value); return GS_OK; }
     if (!strcmp(name, "fwd_warp")) { gs_tune_fwd_warp(value); return GS_OK; }
+    if (!strcmp(name, "pair_cull")) { gs_tune_pair_cull(value); return GS_OK; }
     if (!strcmp(name, "side_bins")) { g_side_bins = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "depth_prehist")) { g_depth_prehist = value ? 1 : 0; return GS_OK; }
     if (!strcmp(name, "tile_sort_ballot")) { g_tile_sort_hint = value ? GS_SORT_HINT_DISTINCT : 0; return GS_OK; }

@@ -319,6 +319,7 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restri
 // word of every tile (which lanes cover it) and from those the slot of each warp's first covering entry.
 // Phase B (one thread per PAIR, so large splats do not unbalance a warp): owner entry by fixed-step search over the
 // scanned pair counts, tile from the rectangle, rank = popc of the ballot word below the owner's lane.
+template <bool CULL>
 __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
                                                       const uint32_t* __restrict__ cstart, const uint32_t* __restrict__ chunk_bin,
                                                       uint32_t nbins, uint32_t nbx, uint32_t ntx,
@@ -328,7 +329,7 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
     __shared__ uint32_t s_base[NWARP][64];                     // slot of the warp's first covering entry per tile
     __shared__ uint32_t s_off[2 * CH];                         // exclusive scan of the entries' pair counts; [CH..] = sentinel
     __shared__ uint32_t s_rect[CH], s_gid[CH];
-    __shared__ gs::CullRec s_cull[CH];
+    __shared__ gs::CullRec s_cull[CULL ? CH : 1];
     __shared__ uint32_t s_w[NWARP];
     // with a tile order asked for, CTA 0 (first wave) computes it from the finished ranges while the others fill
     const bool with_order = O.tile_order != nullptr;
@@ -351,7 +352,7 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
             np = r.w * r.h;
             s_rect[threadIdx.x] = r.x0 | (r.y0 << 4) | (r.w << 8) | ((0x10000u / r.w + 1u) << 12);   // x0, y0 < 8, w <= 8, 17-bit reciprocal
             s_gid[threadIdx.x] = g;
-            s_cull[threadIdx.x] = gs::cull_rec(O.rec[3 * (size_t)g], O.rec[3 * (size_t)g + 1]);
+            if (CULL) s_cull[threadIdx.x] = gs::cull_rec(O.rec[3 * (size_t)g], O.rec[3 * (size_t)g + 1]);
         }
         uint32_t npairs;
         const uint32_t ex = gs::cta_excl_scan<NWARP>(np, s_w, &npairs);
@@ -380,7 +381,8 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
             const uint32_t ew = e >> 5, el = e & 31u;
             const uint32_t slot = s_base[ew][t] + __popc(s_ball[ew][t] & ((1u << el) - 1u));
             const uint32_t tx = bx * BT + lx, ty = by * BT + ly;
-            const bool cull = gs::box_cannot_contribute(s_cull[e], (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
+            bool cull = false;
+            if (CULL) cull = gs::box_cannot_contribute(s_cull[e], (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
             if (slot < cap_pairs) out_vals[slot] = s_gid[e] | (cull ? GS_CULL_BIT : 0u);
         }
         __syncthreads();
@@ -399,6 +401,10 @@ __global__ void __launch_bounds__(256) rebuild_keys64_ranges_kernel(const uint2*
 }
 
 }  // namespace
+
+// 1 = the fill evaluates the per-(tile, Gaussian) cull bit (GS_CULL_BIT); 0 = no pair is ever marked
+static int g_pair_cull = 0;
+void gs_tune_pair_cull(int v) { g_pair_cull = v ? 1 : 0; }
 
 uint32_t gs_bin_count(uint32_t ntx, uint32_t nty) { return ((ntx + BT - 1u) / BT) * ((nty + BT - 1u) / BT); }
 uint32_t gs_bin_nbx(uint32_t ntx) { return (ntx + BT - 1u) / BT; }
@@ -448,7 +454,8 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
     bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count, done, ranges, total_pairs, cap_pairs);
-    bin_fill_kernel<<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+    if (g_pair_cull) bin_fill_kernel<true><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+    else bin_fill_kernel<false><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
 }
 
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,

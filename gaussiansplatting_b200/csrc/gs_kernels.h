@@ -188,6 +188,7 @@ void gs_tune_dp_mc(int which, int v);   // in-switch reduce: 0 grid, 1 threads p
 // tuning knobs (gs_tune in the C ABI): pixels per thread of the blend kernels (1, 2 or 4)
 void gs_tune_fwd_ppt(int v);
 bool gs_fwd_writes_visits();   // the forward variant in use records its (entry, warp) visits (PPT 2)
+void gs_tune_pair_cull(int v);  // binned pipeline: 1 = bin_fill evaluates the tile-level cull bit, 0 = never set
 void gs_tune_fwd_warp(int v);  // forward blend: 1 = warp-autonomous walk, 0 = CTA-cooperative rounds
 bool gs_fwd_words_end_with_the_warp();
 void gs_tune_bwd_warp(int v);  // masked backward: 1 = warp-autonomous walk, 0 = CTA-cooperative rounds

@@ -117,6 +117,8 @@ int gs_version(void);
  *   "bwd_warp"             1 (default) that backward is the warp-autonomous kernel, 0 the CTA-cooperative one
  *   "fwd_warp"             forward blend: 0 CTA-cooperative rounds, 1 (default) warp-autonomous when the frame records
  *                          visit words, 2 warp-autonomous always
+ *   "pair_cull"            binned pipeline: 1 the expansion marks (tile, Gaussian) pairs that cannot contribute (bit 31 of the
+ *                          list value), 0 (default) it does not: the blend kernels' per-warp footprint test does the work
  *   "dp_mc_grid", "dp_mc_threads", "dp_mc_unroll"   launch shape of the in-switch gradient sum
  * unknown names return GS_ERR_ARG */
 int gs_tune(const char* name, int value);

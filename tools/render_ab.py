@@ -17,6 +17,8 @@ G = gs.Gaussians(ctx, n); G.upload(synth.make_scene(n, synth.CONFIG_SEED[wl], sy
 R = gs.Rasterizer(ctx, n)
 img = gs.Image(ctx, W, H)
 cams = [synth.make_camera(v, 64, W, H, n, synth.CONFIG_ORBIT[wl]) for v in range(64)]
+for kv in os.environ.get("GS_TUNE", "").split():       # fixed knobs for the whole run, e.g. GS_TUNE="fwd_warp=2"
+    gs.tune(kv.split("=")[0], int(kv.split("=")[1]))
 for rep in range(3):
     for v in values:
         gs.tune(knob, v)
