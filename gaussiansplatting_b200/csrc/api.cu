@@ -655,7 +655,7 @@ static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapac
     GS_TRY(dalloc(c, &r->vals_in, cap));
     for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->kbuf[i], cap)); GS_TRY(dalloc(c, &r->vbuf[i], cap)); }
     GS_CUDA(c, cudaMalloc(&r->sort_scratch, gs_sort_scratch_bytes(cap, 8)));
-    GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * 65));    // 64 counts per chunk, then the chunk -> bin table
+    GS_TRY(dalloc(c, &r->chunk_counts, gs_bin_max_chunks(cap, GS_MAX_BINS) * (65 + 512)));    // 64 counts per chunk, then the chunk -> bin table, then 8 x 64 coverage words per chunk
     r->cap_pairs = cap;
     if (r->want_vis) GS_TRY(rast_reserve_vis(r));
     return GS_OK;
@@ -852,7 +852,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         if (!bin_hist) gs_launch_tile_ranges32(sorted_bins, cap, d_coarse, nbins, r->bin_ranges, st);
         gs_launch_bin_expand(r->proj, cvals, bin_hist, r->bin_ranges, r->ntx, r->nty, r->cstart, r->chunk_counts, r->tile_count, r->ranges,
                              d_total, lists, cap, r->coarse_hint ? (uint32_t)(r->coarse_hint / 256 * 9 / 8) + nbins + 1u : 0u,
-                             chunk_bin, r->tile_count + r->cap_tiles, st);
+                             chunk_bin, r->chunk_counts + gs_bin_max_chunks(r->cap_pairs, GS_MAX_BINS) * 65, r->tile_count + r->cap_tiles, st);
         r->result = 0;
         r->sorted_tiles = nullptr; r->sorted_keys = nullptr; r->sorted_vals = lists;
         // the pair counts travel to the host on their own copy stream; the compute stream carries on with the blend

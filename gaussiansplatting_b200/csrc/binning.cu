@@ -218,31 +218,37 @@ __device__ __forceinline__ BinRect bin_rect(const uint4 bb, uint32_t bx, uint32_
     return r;
 }
 
-// count: chunk_counts[chunk][t] = entries of the chunk covering local tile t.  Every entry covers a RECTANGLE of the
-// bin's 8x8 tiles, so it adds +1/-1 at the four corners of a 9x9 difference grid (shared-memory atomics, four per entry
-// whatever its size) and 64 threads take the 2-D prefix sum.  Grid-stride over the chunks.
+// count: chunk_counts[chunk][t] = entries of the chunk covering local tile t, and chunk_words[chunk][warp][t] = WHICH of the
+// warp's 32 entries cover it.  Every entry covers a rectangle of the bin's 8x8 tiles = a 64-bit mask; two 32x32 bit-matrix
+// transposes across the warp turn the 32 masks into the 64 words "which lanes cover tile t" (five shfl.bfly rounds each).  The
+// words are stored (2 KB per chunk, coalesced) so that the fill kernel neither gathers the rectangles again nor searches for a
+// pair's owner; the counts are their popcounts summed over the chunk's eight warps.  Grid-stride over the chunks.
 __global__ void __launch_bounds__(CH) bin_count_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
                                                        const uint32_t* __restrict__ cstart, const uint32_t* __restrict__ chunk_bin,
-                                                       uint32_t nbins, uint32_t nbx, uint32_t* __restrict__ chunk_counts) {
-    __shared__ int s_diff[9][9];
+                                                       uint32_t nbins, uint32_t nbx, uint32_t* __restrict__ chunk_counts,
+                                                       uint32_t* __restrict__ chunk_words) {
+    __shared__ uint32_t s_cnt[NWARP][64];
     const uint32_t total = cstart[nbins];
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     for (uint32_t chunk = blockIdx.x; chunk < total; chunk += gridDim.x) {
         const ChunkCtx cc = locate_chunk(chunk, chunk_bin, cstart, bin_ranges);
-        if (threadIdx.x < 81u) (&s_diff[0][0])[threadIdx.x] = 0;
-        __syncthreads();
+        unsigned long long mask = 0ull;
         if (threadIdx.x < cc.count) {
             const uint32_t g = cvals[cc.first + threadIdx.x];
             const BinRect r = bin_rect(O.bbox[g], cc.bin % nbx, cc.bin / nbx);
-            atomicAdd(&s_diff[r.y0][r.x0], 1); atomicAdd(&s_diff[r.y0][r.x0 + r.w], -1);
-            atomicAdd(&s_diff[r.y0 + r.h][r.x0], -1); atomicAdd(&s_diff[r.y0 + r.h][r.x0 + r.w], 1);
+            const unsigned long long row = (unsigned long long)(((1u << r.w) - 1u) << r.x0);               // < 256: one byte per tile row
+            mask = row * ((0x0101010101010101ull >> (8u * (8u - r.h))) << (8u * r.y0));                     // rows y0 .. y0 + h - 1
         }
+        const uint32_t w0 = warp_transpose32((uint32_t)mask, lane), w1 = warp_transpose32((uint32_t)(mask >> 32), lane);
+        uint32_t* wd = chunk_words + ((size_t)chunk * NWARP + warp) * 64u;
+        wd[lane] = w0; wd[lane + 32u] = w1;
+        s_cnt[warp][lane] = __popc(w0); s_cnt[warp][lane + 32u] = __popc(w1);
         __syncthreads();
         if (threadIdx.x < 64u) {
-            const uint32_t tx = threadIdx.x & 7u, ty = threadIdx.x >> 3;
-            int sum = 0;
-            for (uint32_t y = 0; y <= ty; y++)
-                for (uint32_t x = 0; x <= tx; x++) sum += s_diff[y][x];
-            chunk_counts[(size_t)chunk * 64u + threadIdx.x] = (uint32_t)sum;
+            uint32_t sum = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < NWARP; w++) sum += s_cnt[w][threadIdx.x];
+            chunk_counts[(size_t)chunk * 64u + threadIdx.x] = sum;
         }
         __syncthreads();
     }
@@ -315,77 +321,103 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restri
 }
 
 // fill: every (entry, covered tile) of the chunk is stored at start[tile] + prefix over earlier chunks + rank in the chunk.
-// Phase A (one thread per entry): rectangle, footprint record and pair count into shared memory; per warp the ballot
-// word of every tile (which lanes cover it) and from those the slot of each warp's first covering entry.
-// Phase B (one thread per PAIR, so large splats do not unbalance a warp): owner entry by fixed-step search over the
-// scanned pair counts, tile from the rectangle, rank = popc of the ballot word below the owner's lane.
+// bin_count left the chunk's 8 x 64 coverage words ("which of warp w's 32 entries cover tile t").  Lane l of warp w takes the
+// words of tiles l and l + 32 for ITS warp's entries and walks their set bits in ascending order (entry order = depth order),
+// writing the entries' Gaussian ids into a shared-memory image of the chunk's output: tile runs back to back, inside a run
+// the warps' entries in warp order (offsets from the popcounts).  Then warp w copies the runs of tiles 8w .. 8w+7 to the tiles'
+// lists, lanes over consecutive slots: coalesced stores.  Round 1 assigned one thread per pair (a search for the owner entry
+// and a per-pair cull test: 168 instructions per pair) and every lane of a store instruction hit a different tile's list --
+// 18 sectors per instruction, 56 M four-byte sector writes at C4, which is what bounded the kernel once the cull test had
+// gone.  A chunk with more than FILL_CAP pairs (large splats) writes straight to the lists instead.  CULL keeps the cull bit
+// (gs_tune "pair_cull").
+constexpr uint32_t FILL_CAP = 4096;
 template <bool CULL>
 __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint32_t* __restrict__ cvals, const uint2* __restrict__ bin_ranges,
                                                       const uint32_t* __restrict__ cstart, const uint32_t* __restrict__ chunk_bin,
                                                       uint32_t nbins, uint32_t nbx, uint32_t ntx,
                                                       uint32_t nty, const uint32_t* __restrict__ chunk_prefix,
+                                                      const uint32_t* __restrict__ chunk_words,
                                                       const uint2* __restrict__ ranges, uint32_t* __restrict__ out_vals, uint32_t cap_pairs) {
-    __shared__ uint32_t s_ball[NWARP][64];                     // ballot word per (warp, tile)
-    __shared__ uint32_t s_base[NWARP][64];                     // slot of the warp's first covering entry per tile
-    __shared__ uint32_t s_off[2 * CH];                         // exclusive scan of the entries' pair counts; [CH..] = sentinel
-    __shared__ uint32_t s_rect[CH], s_gid[CH];
+    __shared__ uint32_t s_cnt[NWARP][64];                      // popcounts, then their exclusive prefix over the warps
+    __shared__ uint32_t s_toff[65];                            // chunk-local start of each tile's run; [64] = pairs of the chunk
+    __shared__ uint32_t s_tcnt[64], s_gbase[64];
+    __shared__ uint32_t s_gid[CH];
+    __shared__ uint32_t s_out[FILL_CAP];
     __shared__ gs::CullRec s_cull[CULL ? CH : 1];
-    __shared__ uint32_t s_w[NWARP];
     // with a tile order asked for, CTA 0 (first wave) computes it from the finished ranges while the others fill
     const bool with_order = O.tile_order != nullptr;
     if (with_order && blockIdx.x == 0) { gs::tile_order_cta<CH>(ranges, ntx * nty, O.tile_order); return; }
     const uint32_t bid = with_order ? blockIdx.x - 1u : blockIdx.x, nblk = with_order ? gridDim.x - 1u : gridDim.x;
-    s_off[CH + threadIdx.x] = 0xFFFFFFFFu;
-    __syncthreads();
     const uint32_t total = cstart[nbins];
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     for (uint32_t chunk = bid; chunk < total; chunk += nblk) {
         const ChunkCtx cc = locate_chunk(chunk, chunk_bin, cstart, bin_ranges);
         const uint32_t bx = cc.bin % nbx, by = cc.bin / nbx;
-        unsigned long long mask = 0ull;
-        uint32_t np = 0;
+        const uint32_t* wd = chunk_words + ((size_t)chunk * NWARP + warp) * 64u;
+        const uint32_t word[2] = {wd[lane], wd[lane + 32u]};
         if (threadIdx.x < cc.count) {
             const uint32_t g = cvals[cc.first + threadIdx.x];
-            const BinRect r = bin_rect(O.bbox[g], bx, by);
-            const unsigned long long row = (unsigned long long)(((1u << r.w) - 1u) << r.x0);               // < 256: one byte per tile row
-            mask = row * ((0x0101010101010101ull >> (8u * (8u - r.h))) << (8u * r.y0));                     // rows y0 .. y0 + h - 1
-            np = r.w * r.h;
-            s_rect[threadIdx.x] = r.x0 | (r.y0 << 4) | (r.w << 8) | ((0x10000u / r.w + 1u) << 12);   // x0, y0 < 8, w <= 8, 17-bit reciprocal
             s_gid[threadIdx.x] = g;
             if (CULL) s_cull[threadIdx.x] = gs::cull_rec(O.rec[3 * (size_t)g], O.rec[3 * (size_t)g + 1]);
         }
-        uint32_t npairs;
-        const uint32_t ex = gs::cta_excl_scan<NWARP>(np, s_w, &npairs);
-        s_off[threadIdx.x] = threadIdx.x < cc.count ? ex : 0xFFFFFFFFu;
-        s_ball[warp][lane] = warp_transpose32((uint32_t)mask, lane);                // lane t: which lanes cover tile t
-        s_ball[warp][lane + 32u] = warp_transpose32((uint32_t)(mask >> 32), lane);
+        s_cnt[warp][lane] = __popc(word[0]); s_cnt[warp][lane + 32u] = __popc(word[1]);
         __syncthreads();
-        if (threadIdx.x < 64u) {
+        if (threadIdx.x < 64u) {                               // two warps: per tile the warps' prefix, then the scan over the tiles
             const uint32_t t = threadIdx.x;
+            uint32_t run = 0;
+#pragma unroll
+            for (uint32_t w = 0; w < NWARP; w++) { const uint32_t c = s_cnt[w][t]; s_cnt[w][t] = run; run += c; }
+            s_tcnt[t] = run;
             const uint32_t tx = bx * BT + (t & 7u), ty = by * BT + (t >> 3);
-            uint32_t run = (tx < ntx && ty < nty) ? ranges[ty * ntx + tx].x + chunk_prefix[(size_t)chunk * 64u + t] : 0u;
+            s_gbase[t] = (tx < ntx && ty < nty) ? ranges[ty * ntx + tx].x + chunk_prefix[(size_t)chunk * 64u + t] : 0u;
+            uint32_t inc = run;
 #pragma unroll
-            for (uint32_t w = 0; w < NWARP; w++) { s_base[w][t] = run; run += __popc(s_ball[w][t]); }
+            for (uint32_t d = 1; d < 32u; d <<= 1) { const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= d) inc += o; }
+            if (t == 31u) s_toff[64] = inc;                    // first half's total, parked
+            s_toff[t] = inc - run;
         }
         __syncthreads();
-        for (uint32_t j = threadIdx.x; j < npairs; j += CH) {
-            uint32_t e = 0;
+        if (threadIdx.x >= 32u && threadIdx.x < 64u) s_toff[threadIdx.x] += s_toff[64];
+        __syncthreads();
+        if (threadIdx.x == 63u) s_toff[64] = s_toff[63] + s_tcnt[63];
+        __syncthreads();
+        const bool staged = !CULL && s_toff[64] <= FILL_CAP;   // CTA-uniform
 #pragma unroll
-            for (uint32_t sft = CH / 2; sft >= 1u; sft >>= 1) { if (s_off[e + sft] <= j) e += sft; }
-            const uint32_t k = j - s_off[e];                   // < 64
-            const uint32_t rc = s_rect[e];
-            const uint32_t w = (rc >> 8) & 0xFu;
-            const uint32_t row = (k * (rc >> 12)) >> 16;       // k / w for k < 64, w <= 8 (reciprocal 65536/w + 1, exact in that range)
-            const uint32_t lx = (rc & 0xFu) + (k - row * w), ly = ((rc >> 4) & 0xFu) + row;
-            const uint32_t t = ly * 8u + lx;
-            const uint32_t ew = e >> 5, el = e & 31u;
-            const uint32_t slot = s_base[ew][t] + __popc(s_ball[ew][t] & ((1u << el) - 1u));
-            const uint32_t tx = bx * BT + lx, ty = by * BT + ly;
-            bool cull = false;
-            if (CULL) cull = gs::box_cannot_contribute(s_cull[e], (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
-            if (slot < cap_pairs) out_vals[slot] = s_gid[e] | (cull ? GS_CULL_BIT : 0u);
+        for (uint32_t hh = 0; hh < 2u; hh++) {
+            const uint32_t t = lane + 32u * hh;
+            uint32_t wv = word[hh];
+            if (wv == 0u) continue;
+            if (staged) {
+                uint32_t pos = s_toff[t] + s_cnt[warp][t];
+                while (wv) {
+                    const uint32_t e = warp * 32u + (uint32_t)__ffs(wv) - 1u;
+                    wv &= wv - 1u;
+                    s_out[pos++] = s_gid[e];
+                }
+            } else {
+                const uint32_t tx = bx * BT + (t & 7u), ty = by * BT + (t >> 3);
+                uint32_t slot = s_gbase[t] + s_cnt[warp][t];
+                while (wv) {
+                    const uint32_t e = warp * 32u + (uint32_t)__ffs(wv) - 1u;
+                    wv &= wv - 1u;
+                    bool cull = false;
+                    if (CULL) cull = gs::box_cannot_contribute(s_cull[e], (float)(tx * GS_TILE) + 0.5f, (float)(ty * GS_TILE) + 0.5f, 15.0f, 15.0f);
+                    if (slot < cap_pairs) out_vals[slot] = s_gid[e] | (cull ? GS_CULL_BIT : 0u);
+                    slot++;
+                }
+            }
         }
         __syncthreads();
+        if (staged) {
+#pragma unroll 1
+            for (uint32_t q = 0; q < 8u; q++) {
+                const uint32_t t = warp * 8u + q;
+                const uint32_t cnt = s_tcnt[t], off = s_toff[t], gb = s_gbase[t];
+                for (uint32_t k = lane; k < cnt; k += 32u)
+                    if (gb + k < cap_pairs) out_vals[gb + k] = s_out[off + k];
+            }
+            __syncthreads();
+        }
     }
 }
 
@@ -442,7 +474,8 @@ void gs_launch_bins_from_hist(const uint32_t* bin_hist, uint32_t ntx, uint32_t n
 
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
-                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* done, cudaStream_t st) {
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* chunk_words, uint32_t* done,
+                          cudaStream_t st) {
     const uint32_t nbx = gs_bin_nbx(ntx), nbins = gs_bin_count(ntx, nty);
     if (nbins == 0) return;
     // The number of chunks lives on the device; the chunk kernels stride over it, so any grid is correct.  The caller
@@ -452,10 +485,10 @@ void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uin
     if (bin_hist == GS_BINS_READY) {}                          // gs_launch_bins_from_hist already ran (side stream, under the bin sort)
     else if (bin_hist) bins_from_hist_kernel<<<1, 256, 0, st>>>(bin_hist, nbins, bin_ranges, cstart, chunk_bin);
     else chunk_map_kernel<<<1, 1024, 0, st>>>(bin_ranges, nbins, cstart, chunk_bin);
-    bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts);
+    bin_count_kernel<<<grid, CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, chunk_counts, chunk_words);
     bin_scan_kernel<<<nbins, 1024, 0, st>>>(cstart, nbx, ntx, nty, chunk_counts, tile_count, done, ranges, total_pairs, cap_pairs);
-    if (g_pair_cull) bin_fill_kernel<true><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
-    else bin_fill_kernel<false><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, ranges, out_vals, cap_pairs);
+    if (g_pair_cull) bin_fill_kernel<true><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, chunk_words, ranges, out_vals, cap_pairs);
+    else bin_fill_kernel<false><<<grid + (O.tile_order ? 1u : 0u), CH, 0, st>>>(O, cvals, bin_ranges, cstart, chunk_bin, nbins, nbx, ntx, nty, chunk_counts, chunk_words, ranges, out_vals, cap_pairs);
 }
 
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,

@@ -110,7 +110,8 @@ void gs_launch_bins_from_hist(const uint32_t* bin_hist, uint32_t ntx, uint32_t n
                               cudaStream_t st);
 void gs_launch_bin_expand(const GsProjected& O, const uint32_t* cvals, const uint32_t* bin_hist, uint2* bin_ranges, uint32_t ntx, uint32_t nty,
                           uint32_t* cstart, uint32_t* chunk_counts, uint32_t* tile_count, uint2* ranges, uint32_t* total_pairs,
-                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* done, cudaStream_t st);
+                          uint32_t* out_vals, uint32_t cap_pairs, uint32_t grid_chunks, uint32_t* chunk_bin, uint32_t* chunk_words, uint32_t* done,
+                          cudaStream_t st);
 void gs_launch_rebuild_keys64_ranges(const uint2* ranges, uint32_t ntiles, const uint32_t* sorted_vals, const uint32_t* dkey,
                                      uint32_t n, uint64_t* keys, cudaStream_t st);
 
