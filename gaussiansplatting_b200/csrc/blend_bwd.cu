@@ -435,7 +435,8 @@ __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_ker
     WEnt* const me = &s_e[wu][lane];
     const uint32_t* const sv = svals + range.x;
     const uint2* const vw = vis + (size_t)range.x * 4u + wu;         // this warp's word of list entry i: vw[4 * i]
-    const uint32_t lanebit = 1u << lane, ridx = reduce8_index(lane);
+    const uint32_t lanebit = 1u << lane, ridx = lane == 1u ? 8u : reduce8_index(lane);
+    const bool writer = (lane & 3u) == 0u || lane == 1u;
     const gs::f32x2 one2 = gs::bc2(1.0f);
     // chunks of 32 list entries, back to front, cut at multiples of 32 so that the 128-byte loads of the pair values are aligned
     uint32_t lo = (wmax - 1u) & ~31u;
@@ -504,9 +505,10 @@ __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_ker
                 const float tot = warp_reduce8_transposed(v8, lane);
 #pragma unroll
                 for (int d = 16; d >= 1; d >>= 1) v9 += __shfl_xor_sync(0xFFFFFFFFu, v9, d);
+                // one reduction instruction for all nine moments: lanes 0, 4, .., 28 carry the eight transposed sums, lane 1 the ninth
                 float* const row = acc + (size_t)__float_as_uint(c.y) * 12u;
-                if ((lane & 3u) == 0u && tot != 0.f) atomicAdd(row + ridx, tot);
-                if (lane == 1u && v9 != 0.f) atomicAdd(row + 8, v9);
+                const float val = lane == 1u ? v9 : tot;
+                if (writer && val != 0.f) atomicAdd(row + ridx, val);
             }
             __syncwarp();
         }
