@@ -555,7 +555,7 @@ struct gs_rast {
     // optional per-stage CUDA-event timing (replaces the reference's chrono prints, tiled_rasterizer.mm:639-671)
     bool prof = false;
     bool acc_clean = false;       // the moment buffer is all-zero (K8 clears what K7 wrote)
-    // forward's visit words for the backward (blend_fwd.cu / blend_bwd.cu): 4 x uint2 per pair slot.  Allocated by the first
+    // forward's visit words for the backward (blend_fwd.cu / blend_bwd.cu): four planes (one per warp) of vis_cap uint2 words.  Allocated by the first
     // backward call (render-only users never pay), regrown with the pair buffers; vis_valid = the last forward filled it.
     uint2* vis = nullptr; uint64_t vis_cap = 0; bool want_vis = false, vis_valid = false, bwd_used_vis = false, vis_warp_extent = false;
     bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
@@ -731,7 +731,7 @@ static int forward_pairs64(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
     gs_launch_tile_ranges(r->sorted_keys, (uint32_t)P, tiles, nullptr, r->ranges, st);
     r->mark(6);
     r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), st);
+    gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), (size_t)r->vis_cap, st);
     r->mark(7);
     GS_LAUNCH_CHECK(c);
     return GS_OK;
@@ -782,7 +782,7 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
         gs_launch_tile_ranges32(r->sorted_tiles, cap, d_total, tiles, r->ranges, st);
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 0, rast_vis_for_forward(r), (size_t)r->vis_cap, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         if (attempt == 0) GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));   // the GPU is still busy with the kernels above
@@ -862,7 +862,7 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, rast_vis_for_forward(r), st);
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, rast_vis_for_forward(r), (size_t)r->vis_cap, st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));                   // the GPU is still busy with the kernels above
@@ -928,7 +928,7 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     const bool masked = r->vis_valid && g_bwd_masks && gs_bwd_uses_visits();
     r->bwd_used_vis = masked;
     gs_launch_blend_backward(r->proj, svals, r->ranges, r->W, r->H, r->ntx, r->nty, rendered->px, gt->px,
-                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, r->vis_warp_extent ? 1 : 0, st);
+                             (flags & GS_BWD_QUANTIZE_RGBA8) ? 1 : 0, r->last_idx, r->tfinal, r->acc, masked ? r->vis : nullptr, (size_t)r->vis_cap, r->vis_warp_extent ? 1 : 0, st);
     if (!r->want_vis && g_bwd_masks) { r->want_vis = true; GS_TRY(rast_reserve_vis(r)); }   // a training caller: record visits from the next forward on
     r->mark(9);
     gs_launch_preprocess_backward(g->view(), r->proj, r->acc, u->viewMatrix, u->focalLength[0], u->focalLength[1], n,

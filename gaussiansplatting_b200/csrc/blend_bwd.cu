@@ -85,7 +85,7 @@ __device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const b
                                                     uint32_t H, uint32_t ntx, const float4* __restrict__ rendered,
                                                     const float4* __restrict__ gt, int quantize, const uint32_t* __restrict__ last_idx,
                                                     const float* __restrict__ tfinal, float* __restrict__ acc,
-                                                    const uint2* __restrict__ vis) {
+                                                    const uint2* __restrict__ vis, size_t vstride) {
     constexpr int RB = MASKED ? BBM : BB;
     constexpr int NT = 256 / PPT, NW = NT / 32, K = (RB + NT - 1) / NT, NP = PPT / 2;
     static_assert(!MASKED || PPT == 2, "the forward records its visits for two pixels per thread only");
@@ -198,10 +198,8 @@ __device__ __forceinline__ void blend_backward_tile(const uint32_t tile, const b
             }
             s_reach[slot] = (unsigned char)reach;
             if (MASKED) {                                            // the four warps' words of this entry: 32 contiguous bytes
-                const uint4* vp = reinterpret_cast<const uint4*>(vis + ((size_t)range.x + lo + threadIdx.x * K + q) * 4u);
-                const uint4 v01 = vp[0], v23 = vp[1];
-                s_vis[slot][0] = make_uint2(v01.x, v01.y); s_vis[slot][1] = make_uint2(v01.z, v01.w);
-                s_vis[slot][2] = make_uint2(v23.x, v23.y); s_vis[slot][3] = make_uint2(v23.z, v23.w);
+#pragma unroll
+                for (int w = 0; w < NW; w++) s_vis[slot][w] = vis[(size_t)w * vstride + range.x + lo + threadIdx.x * K + q];
             }
             slot++;
         }
@@ -334,11 +332,11 @@ __global__ void GS_BWD_BOUNDS(256 / PPT, MASKED) blend_backward_kernel(const flo
                                                              int quantize, const uint32_t* __restrict__ last_idx,
                                                              const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
                                                              const uint32_t* __restrict__ order, float* __restrict__ acc,
-                                                             const uint2* __restrict__ vis) {
+                                                             const uint2* __restrict__ vis, size_t vstride) {
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const bool redo = tile_flags[tile] != 0u;
     if (MASKED && redo) return;                                      // CTA-uniform: left to blend_backward_flagged_kernel
-    blend_backward_tile<PPT, MASKED>(tile, redo, rec, svals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal, acc, vis);
+    blend_backward_tile<PPT, MASKED>(tile, redo, rec, svals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal, acc, vis, vstride);
 }
 
 // The flagged tiles behind a masked launch, by the pinned walk.  They are rare (none in most frames), so the grid is not one
@@ -361,7 +359,7 @@ __global__ void __launch_bounds__(256 / PPT) blend_backward_flagged_kernel(const
     for (uint32_t i = 0; i < (uint32_t)NT; i++) {
         if (!s_flag[i]) continue;                                    // CTA-uniform
         blend_backward_tile<PPT, false>(blockIdx.x * NT + i, true, rec, svals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal,
-                                        acc, nullptr);
+                                        acc, nullptr, 0);
         __syncthreads();
     }
 }
@@ -386,7 +384,7 @@ __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_ker
     const float4* __restrict__ rec, const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W, uint32_t H,
     uint32_t ntx, const float4* __restrict__ rendered, const float4* __restrict__ gt, int quantize,
     const uint32_t* __restrict__ last_idx, const float* __restrict__ tfinal, const uint32_t* __restrict__ tile_flags,
-    const uint32_t* __restrict__ order, float* __restrict__ acc, const uint2* __restrict__ vis) {
+    const uint32_t* __restrict__ order, float* __restrict__ acc, const uint2* __restrict__ vis, size_t vstride) {
     __shared__ __align__(16) WEnt s_e[4][32];
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     if (tile_flags[tile] != 0u) return;                              // left to blend_backward_flagged_kernel
@@ -434,7 +432,7 @@ __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_ker
     const uint32_t ebase = (uint32_t)__cvta_generic_to_shared(s_e) + wu * (32u * (uint32_t)sizeof(WEnt));
     WEnt* const me = &s_e[wu][lane];
     const uint32_t* const sv = svals + range.x;
-    const uint2* const vw = vis + (size_t)range.x * 4u + wu;         // this warp's word of list entry i: vw[4 * i]
+    const uint2* const vw = vis + (size_t)wu * vstride + range.x;     // this warp's plane: its word of list entry i is vw[i]
     const uint32_t lanebit = 1u << lane, ridx = lane == 1u ? 8u : reduce8_index(lane);
     const bool writer = (lane & 3u) == 0u || lane == 1u;
     const gs::f32x2 one2 = gs::bc2(1.0f);
@@ -442,12 +440,12 @@ __global__ void __launch_bounds__(128, GS_BWD_WARP_MINB) blend_backward_warp_ker
     uint32_t lo = (wmax - 1u) & ~31u;
     uint32_t v_n = GS_CULL_BIT;
     uint2 w_n = make_uint2(0u, 0u);
-    if (lo + lane < wmax) { v_n = sv[lo + lane]; w_n = vw[(size_t)(lo + lane) * 4u]; }
+    if (lo + lane < wmax) { v_n = sv[lo + lane]; w_n = vw[lo + lane]; }
     for (;;) {
         const uint32_t v = v_n;
         const uint2 w = w_n;
         const bool more = lo != 0u;
-        if (more) { lo -= 32u; v_n = sv[lo + lane]; w_n = vw[(size_t)(lo + lane) * 4u]; }   // in flight while this chunk is walked
+        if (more) { lo -= 32u; v_n = sv[lo + lane]; w_n = vw[lo + lane]; }   // in flight while this chunk is walked
         // a culled pair was never staged by the forward and has no word (GS_CULL_BIT, pairs.cu); a zero word = not this warp's entry
         const bool has = !(v >> 31) && (w.x | w.y) != 0u;
         uint32_t mk = __ballot_sync(0xFFFFFFFFu, has);
@@ -645,17 +643,17 @@ void gs_tune_bwd_warp(int v) { g_bwd_warp = v ? 1 : 0; }
 
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
-                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, int vis_warp_extent,
+                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, size_t vstride, int vis_warp_extent,
                               cudaStream_t st) {
     if (ntx * nty == 0) return;
 #define GS_BWD_LAUNCH(PPT, MASKED)                                                                                  \
     blend_backward_kernel<PPT, MASKED><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, \
-                                                                         last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis)
+                                                                         last_idx, tfinal, O.tile_flags, O.tile_order, acc, vis, vstride)
     if (g_bwd_ppt == 4) GS_BWD_LAUNCH(4, false);
     else if (vis) {                                  // recorded visits; flagged tiles by the pinned variant
         if (g_bwd_warp || vis_warp_extent)
             blend_backward_warp_kernel<<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, rendered, gt, quantize, last_idx, tfinal,
-                                                                  O.tile_flags, O.tile_order, acc, vis);
+                                                                  O.tile_flags, O.tile_order, acc, vis, vstride);
         else GS_BWD_LAUNCH(2, true);
         blend_backward_flagged_kernel<2><<<(ntx * nty + 127u) / 128u, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, ntx * nty, rendered, gt,
                                                                                     quantize, last_idx, tfinal, O.tile_flags, acc);

@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(const uint2* __restric
 }
 
 struct FwdEnt { float4 r0, r1; float b; uint32_t idx; uint32_t pad0, pad1; };   // 48 B: one base address, three LDS
-// vis (optional, PPT 2 only): for every STAGED list entry four 64-bit words, one per warp, "which of the warp's 64 pixel slots
+// vis (optional, PPT 2 only; four planes of `vstride` words, one per warp: word (w, entry) at vis[w * vstride + entry], so that
+// a warp's words of consecutive entries are contiguous): for every STAGED list entry four 64-bit words, one per warp, "which of the warp's 64 pixel slots
 // took the entry" (two ballots: slot j = 0 / 1 of every lane; zero = the warp never took it), at vis[entry * 4 + warp].  A warp
 // keeps its word in shared memory; the CTA writes a round's words out once, 32 contiguous bytes per entry.  The backward
 // walk takes its per-slot decisions from these words instead of re-deriving them (blend_bwd.cu).  Entries behind the round in
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
                                                             float4* __restrict__ image, uint32_t* __restrict__ last_idx,
                                                             float* __restrict__ tfinal, uint32_t* __restrict__ tile_flags,
                                                             const uint32_t* __restrict__ order,
-                                                            unsigned long long* __restrict__ counters, uint2* __restrict__ vis) {
+                                                            unsigned long long* __restrict__ counters, uint2* __restrict__ vis, size_t vstride) {
     constexpr int NT = 256 / PPT, NW = NT / 32, K = FB / NT, NP = PPT / 2;
     __shared__ FwdEnt s_e[FB];
     __shared__ uint32_t s_w[NW];
@@ -152,9 +153,8 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
         const bool all_done = __syncthreads_and(!wlive);
         if (rec_vis) {                                // the previous round's words: 32 contiguous bytes per entry, one thread each
             for (uint32_t k = threadIdx.x; k < prev_total; k += NT) {
-                uint4* dst = reinterpret_cast<uint4*>(vis + (size_t)s_e[k].idx * 4u);
-                dst[0] = make_uint4(s_vis[k][0].x, s_vis[k][0].y, s_vis[k][1].x, s_vis[k][1].y);
-                dst[1] = make_uint4(s_vis[k][2].x, s_vis[k][2].y, s_vis[k][3].x, s_vis[k][3].y);
+#pragma unroll
+                for (int w = 0; w < NW; w++) vis[(size_t)w * vstride + s_e[k].idx] = s_vis[k][w];
             }
             prev_total = 0;
         }
@@ -257,9 +257,8 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
     }
     if (rec_vis && __syncthreads_or(prev_total != 0u)) {   // the last round's words (the loop ended by exhausting the list)
         for (uint32_t k = threadIdx.x; k < prev_total; k += NT) {
-            uint4* dst = reinterpret_cast<uint4*>(vis + (size_t)s_e[k].idx * 4u);
-            dst[0] = make_uint4(s_vis[k][0].x, s_vis[k][0].y, s_vis[k][1].x, s_vis[k][1].y);
-            dst[1] = make_uint4(s_vis[k][2].x, s_vis[k][2].y, s_vis[k][3].x, s_vis[k][3].y);
+#pragma unroll
+            for (int w = 0; w < NW; w++) vis[(size_t)w * vstride + s_e[k].idx] = s_vis[k][w];
         }
     }
     float Tf[PPT], Cr[PPT], Cg[PPT], Cb[PPT];
@@ -311,7 +310,7 @@ template <bool VIS>
 __global__ void __launch_bounds__(128, GS_FWD_WARP_MINB) blend_forward_warp_kernel(
     const float4* __restrict__ rec, const uint32_t* __restrict__ svals, const uint2* __restrict__ ranges, uint32_t W, uint32_t H,
     uint32_t ntx, float4* __restrict__ image, uint32_t* __restrict__ last_idx, float* __restrict__ tfinal,
-    uint32_t* __restrict__ tile_flags, const uint32_t* __restrict__ order, uint2* __restrict__ vis) {
+    uint32_t* __restrict__ tile_flags, const uint32_t* __restrict__ order, uint2* __restrict__ vis, size_t vstride) {
     __shared__ __align__(16) FwdEnt s_e[4][32];
     const uint32_t tile = order ? order[blockIdx.x] : blockIdx.x;
     const uint32_t tX = tile % ntx, tY = tile / ntx;
@@ -405,7 +404,7 @@ __global__ void __launch_bounds__(128, GS_FWD_WARP_MINB) blend_forward_warp_kern
             }
             if (!__any_sync(0xFFFFFFFFu, alive)) { wlive = false; break; }
         }
-        if (VIS) { if (!(v >> 31)) vis[(size_t)(range.x + base + lane) * 4u + wu] = make_uint2(w0, w1); }
+        if (VIS) { if (!(v >> 31)) vis[(size_t)wu * vstride + range.x + base + lane] = make_uint2(w0, w1); }   // 256 contiguous bytes per chunk
         __syncwarp();
     }
     if (degen) tile_flags[tile] = 1u;
@@ -460,15 +459,15 @@ void gs_launch_tile_order(const uint2* ranges, uint32_t num_tiles, uint32_t* ord
 
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, int order_ready,
-                             uint2* vis, cudaStream_t st) {
+                             uint2* vis, size_t vstride, cudaStream_t st) {
     if (ntx * nty == 0) return;
 #define GS_FWD_LAUNCH(PPT, VIS)                                                                                       \
     blend_forward_kernel<PPT, false, VIS><<<ntx * nty, 256 / PPT, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, \
-                                                                            tfinal, O.tile_flags, O.tile_order, nullptr, vis)
+                                                                            tfinal, O.tile_flags, O.tile_order, nullptr, vis, vstride)
     if (O.tile_order && !order_ready) tile_order_kernel<<<1, 1024, 0, st>>>(ranges, ntx * nty, O.tile_order);
 #define GS_FWD_WARP_LAUNCH(VIS)                                                                                       \
     blend_forward_warp_kernel<VIS><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, image, last_idx, tfinal, \
-                                                               O.tile_flags, O.tile_order, vis)
+                                                               O.tile_flags, O.tile_order, vis, vstride)
     if (g_fwd_ppt == 4) GS_FWD_LAUNCH(4, false);
     else if (vis && g_fwd_warp) GS_FWD_WARP_LAUNCH(true);
     else if (g_fwd_warp == 2) GS_FWD_WARP_LAUNCH(false);
@@ -481,5 +480,5 @@ void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, co
                            uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st) {
     if (ntx * nty == 0) return;
     blend_forward_kernel<2, true, false><<<ntx * nty, 128, 0, st>>>(O.rec, sorted_vals, ranges, W, H, ntx, nullptr, nullptr, nullptr,
-                                                             O.tile_flags, nullptr, counters, nullptr);
+                                                             O.tile_flags, nullptr, counters, nullptr, 0);
 }

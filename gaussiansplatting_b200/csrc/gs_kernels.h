@@ -70,7 +70,7 @@ void gs_launch_rebuild_keys64(const uint32_t* sorted_tiles, const uint32_t* sort
 // K6: forward blend.  image: W*H float4 RGBA; last_idx/tfinal: W*H.
 void gs_launch_blend_forward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                              uint32_t ntx, uint32_t nty, float4* image, uint32_t* last_idx, float* tfinal, int order_ready,
-                             uint2* vis, cudaStream_t st);
+                             uint2* vis, size_t vstride, cudaStream_t st);
 
 void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                            uint32_t ntx, uint32_t nty, unsigned long long* counters, cudaStream_t st);
@@ -80,7 +80,7 @@ void gs_launch_blend_count(const GsProjected& O, const uint32_t* sorted_vals, co
 //   acc[12i+4..5] = sum q*dx, q*dy            acc[12i+6..8] = sum q*dx^2, q*dx*dy, q*dy^2
 void gs_launch_blend_backward(const GsProjected& O, const uint32_t* sorted_vals, const uint2* ranges, uint32_t W, uint32_t H,
                               uint32_t ntx, uint32_t nty, const float4* rendered, const float4* gt, int quantize,
-                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, int vis_warp_extent,
+                              const uint32_t* last_idx, const float* tfinal, float* acc, const uint2* vis, size_t vstride, int vis_warp_extent,
                               cudaStream_t st);
 
 // K8: per-Gaussian chain: moments -> parameter gradients, written to (accumulate = 0) or added into the packed gradient

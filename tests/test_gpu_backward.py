@@ -25,25 +25,27 @@ def compare_grads(got, ref, absref, count):
     return rep
 
 
-@pytest.fixture(params=["pinned", "visits"], autouse=True)
+@pytest.fixture(params=["pinned", "visits", "visits-rounds"], autouse=True)
 def walk(request, gs):
     """every test of this file runs twice: with the backward walk that re-derives its decisions (gs_tune "bwd_masks" = 0; also the
-    only one a rasterizer's FIRST backward can take) and with the walk on the visit words the forward recorded (every later frame
-    of a training caller)"""
-    gs.tune("bwd_masks", 1 if request.param == "visits" else 0)
+    only one a rasterizer's FIRST backward can take), with the walk on the visit words the forward recorded (every later frame
+    of a training caller; warp-autonomous kernels) and with the CTA-cooperative kernels on such words"""
+    gs.tune("bwd_masks", 0 if request.param == "pinned" else 1)
+    rounds = request.param == "visits-rounds"       # the CTA-cooperative pair of kernels instead of the warp-autonomous one
+    gs.tune("fwd_warp", 0 if rounds else 1); gs.tune("bwd_warp", 0 if rounds else 1)
     yield request.param
-    gs.tune("bwd_masks", 1)
+    gs.tune("bwd_masks", 1); gs.tune("fwd_warp", 1); gs.tune("bwd_warp", 1)
 
 
 def run_backward(gs, R, G, D, u, img, gti, flags, walk):
     """forward + backward in the requested walk; the visits walk needs one earlier backward on the rasterizer (it allocates the
     words) and is asserted to have been taken"""
-    if walk == "visits":
+    if walk != "pinned":
         R.forward(G, u, img)
         R.backward(G, D, u, img, gti, flags)
     R.forward(G, u, img)
     R.backward(G, D, u, img, gti, flags)
-    assert R.backward_used_visits == (walk == "visits")
+    assert R.backward_used_visits == (walk != "pinned")
 
 
 def fwd_bwd(gs, ctx, orc, g, gt_g, u, W, H, quantize=False, walk="pinned"):
