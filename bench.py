@@ -269,7 +269,7 @@ class Bench:
         outs = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
         mine = dp.render_views_for_rank(num_views, self.world, self.rank) * reps
         cams = {v: synth.make_camera(v, num_views, W, H, n, orbit) for v in set(mine)}
-        for v in mine[:3]:
+        for v in sorted(set(mine)) + mine[:3]:        # one untimed forward per distinct view sizes the pair buffers (see run())
             R.forward(G, cams[v], imgs[0])
         ctx.sync()
         ms_dev = self.timed(lambda i: R.forward(G, cams[mine[i]], imgs[i % 2]), len(mine))
@@ -423,6 +423,11 @@ class Bench:
             R.forward(G, view(i), img)
             R.backward(G, D, view(i), img, gti)
 
+        # The pair buffers (and the visit words behind them) grow on demand, as the reference's do (ensurePairsCapacity,
+        # tiled_rasterizer.mm:242-272): a view with more pairs than any before it costs a reallocation and a redone frame, once.
+        # One untimed forward per distinct view of the timed loop takes those one-off events out of the timed region.
+        for v in sorted({(i * world + rank) % NV for i in range(K)}):
+            R.forward(G, cams[v], img)
         for i in range(Wm):
             fwd_bwd(i)
         sampler = ClockSampler(local)       # rank 0 only: eight nvidia-smi pollers on one box disturb the launch path of every rank
@@ -439,7 +444,8 @@ class Bench:
                "data": "synthetic",
                "config": {"workload": workload_string(args.workload), "pairs": pairs,
                           "parallelism": f"views sharded over {world} GPU(s), no data-path collective for fwd+bwd (config.c5 holds the step with the gradient all-reduce)",
-                          "l2": "per-step working set (~0.6 GB: params, records, pair buffers, images) exceeds the 126 MB L2"},
+                          "l2": "per-step working set (~0.6 GB: params, records, pair buffers, images) exceeds the 126 MB L2",
+                          "sizing": "one untimed forward per distinct view before the warm-up: on-demand growth of the pair buffers is a one-off reallocation, not a step"},
                "ms_per_step_stats": spread(per_step)}
 
         # ---- end to end through the C ABI with host buffers: every step copies that step's ground truth (pinned RGBA8) and

@@ -650,7 +650,9 @@ static int rast_reserve_pairs(gs_rast* r, uint64_t need) {   // ensurePairsCapac
     cudaFree(r->keys_in); cudaFree(r->vals_in); cudaFree(r->sort_scratch); cudaFree(r->chunk_counts);
     for (int i = 0; i < 2; i++) { cudaFree(r->kbuf[i]); cudaFree(r->vbuf[i]); r->kbuf[i] = nullptr; r->vbuf[i] = nullptr; }
     r->keys_in = nullptr; r->vals_in = nullptr; r->sort_scratch = nullptr; r->chunk_counts = nullptr;
-    const uint64_t cap = std::max<uint64_t>(need, (uint64_t)(r->cap_pairs * 1.5));
+    // an eighth of headroom over the request: the next view of an orbit rarely has exactly as many pairs, and every growth event
+    // costs a stream drain, a dozen reallocations and a redone frame
+    const uint64_t cap = std::max<uint64_t>(need + need / 8, (uint64_t)(r->cap_pairs * 1.5));
     GS_TRY(dalloc(c, &r->keys_in, cap));
     GS_TRY(dalloc(c, &r->vals_in, cap));
     for (int i = 0; i < 2; i++) { GS_TRY(dalloc(c, &r->kbuf[i], cap)); GS_TRY(dalloc(c, &r->vbuf[i], cap)); }
