@@ -323,9 +323,9 @@ __global__ void __launch_bounds__(1024) bin_scan_kernel(const uint32_t* __restri
 // fill: every (entry, covered tile) of the chunk is stored at start[tile] + prefix over earlier chunks + rank in the chunk.
 // bin_count left the chunk's 8 x 64 coverage words ("which of warp w's 32 entries cover tile t").  Lane l of warp w takes the
 // words of tiles l and l + 32 for ITS warp's entries and walks their set bits in ascending order (entry order = depth order),
-// writing the entries' Gaussian ids into a shared-memory image of the chunk's output: tile runs back to back, inside a run
-// the warps' entries in warp order (offsets from the popcounts).  Then warp w copies the runs of tiles 8w .. 8w+7 to the tiles'
-// lists, lanes over consecutive slots: coalesced stores.  Round 1 assigned one thread per pair (a search for the owner entry
+// writing (Gaussian id, destination slot) into a shared-memory image of the chunk's output: tile runs back to back, inside a
+// run the warps' entries in warp order (offsets from the popcounts).  Then the CTA copies the image out, thread k the k-th
+// pair: consecutive threads hit consecutive slots of a tile's list -- coalesced stores, five instructions per pair.  Round 1 assigned one thread per pair (a search for the owner entry
 // and a per-pair cull test: 168 instructions per pair) and every lane of a store instruction hit a different tile's list --
 // 18 sectors per instruction, 56 M four-byte sector writes at C4, which is what bounded the kernel once the cull test had
 // gone.  A chunk with more than FILL_CAP pairs (large splats) writes straight to the lists instead.  CULL keeps the cull bit
@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
     __shared__ uint32_t s_toff[65];                            // chunk-local start of each tile's run; [64] = pairs of the chunk
     __shared__ uint32_t s_tcnt[64], s_gbase[64];
     __shared__ uint32_t s_gid[CH];
-    __shared__ uint32_t s_out[FILL_CAP];
+    __shared__ uint2 s_out[FILL_CAP];                          // (Gaussian id, destination slot) of the chunk's pairs, tile runs back to back
     __shared__ gs::CullRec s_cull[CULL ? CH : 1];
     // with a tile order asked for, CTA 0 (first wave) computes it from the finished ranges while the others fill
     const bool with_order = O.tile_order != nullptr;
@@ -388,11 +388,11 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
             uint32_t wv = word[hh];
             if (wv == 0u) continue;
             if (staged) {
-                uint32_t pos = s_toff[t] + s_cnt[warp][t];
+                uint32_t pos = s_toff[t] + s_cnt[warp][t], dst = s_gbase[t] + s_cnt[warp][t];
                 while (wv) {
                     const uint32_t e = warp * 32u + (uint32_t)__ffs(wv) - 1u;
                     wv &= wv - 1u;
-                    s_out[pos++] = s_gid[e];
+                    s_out[pos++] = make_uint2(s_gid[e], dst++);
                 }
             } else {
                 const uint32_t tx = bx * BT + (t & 7u), ty = by * BT + (t >> 3);
@@ -408,13 +408,11 @@ __global__ void __launch_bounds__(CH) bin_fill_kernel(GsProjected O, const uint3
             }
         }
         __syncthreads();
-        if (staged) {
-#pragma unroll 1
-            for (uint32_t q = 0; q < 8u; q++) {
-                const uint32_t t = warp * 8u + q;
-                const uint32_t cnt = s_tcnt[t], off = s_toff[t], gb = s_gbase[t];
-                for (uint32_t k = lane; k < cnt; k += 32u)
-                    if (gb + k < cap_pairs) out_vals[gb + k] = s_out[off + k];
+        if (staged) {                                          // consecutive threads = consecutive slots of a tile's run (but at the run ends)
+            const uint32_t npairs = s_toff[64];
+            for (uint32_t k = threadIdx.x; k < npairs; k += CH) {
+                const uint2 o = s_out[k];
+                if (o.y < cap_pairs) out_vals[o.y] = o.x;
             }
             __syncthreads();
         }
