@@ -201,7 +201,10 @@ __global__ void __launch_bounds__(256 / PPT, GS_FWD_MINB) blend_forward_kernel(c
             for (uint32_t wd = 0; wd < nwords && wlive; wd++) {      // :334, entries that can reach this warp's pixels only
                 const uint32_t sl = wd * 32u + lane;
                 uint32_t m = __ballot_sync(0xFFFFFFFFu, sl < total && ((s_reach[sl] >> warp) & 1u));
-                const uint32_t wbase = ebase + wd * 32u * (uint32_t)sizeof(FwdEnt);
+                uint32_t wbase = ebase + wd * 32u * (uint32_t)sizeof(FwdEnt);
+                // opaque to the compiler: otherwise it re-derives the shared window's base from %cluster_ctaid inside the visit loop
+                // (five uniform-datapath instructions per visit, which still take issue slots)
+                asm volatile("" : "+r"(wbase));
                 while (m) {
                     const uint32_t kb = (uint32_t)__ffs(m) - 1u;
                     m &= m - 1u;
