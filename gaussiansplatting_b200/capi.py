@@ -281,6 +281,10 @@ class Rasterizer:
     def sort_passes(self):
         return int(lib().gs_rast_sort_passes(self.h))
 
+    def set_overlap(self, on=True):
+        """the ordering stage on a high-priority side stream (see gs_rast_set_overlap: for alternating two rasterizers)"""
+        self.ctx.check(lib().gs_rast_set_overlap(self.h, C.c_int(1 if on else 0)))
+
     @property
     def backward_used_visits(self):
         return bool(lib().gs_rast_backward_used_visits(self.h))

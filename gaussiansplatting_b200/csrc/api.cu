@@ -561,6 +561,13 @@ struct gs_rast {
     bool depth_prehist = false;   // this frame's K1 filled the depth sort's digit histograms (GS_SORT_HINT_PREHIST)
     cudaEvent_t ev[GS_PROF_EVENTS] = {};
     unsigned long long* counters = nullptr;
+    // gs_rast_set_overlap: the stages before the blend run on `ord` (a high-priority stream of this rasterizer) instead of the context
+    // stream.  ev_ord = "ordering done" (the context stream waits on it before the blend), ev_free = position of the context stream
+    // at the end of this rasterizer's last forward / backward call: from there on its buffers may be overwritten.
+    cudaStream_t ord = nullptr;
+    cudaEvent_t ev_ord = nullptr, ev_free = nullptr;
+    bool free_valid = false;
+    cudaStream_t ord_stream() const { return (ord && mode == 0 && !prof) ? ord : c->stream; }
     void mark(int i) { if (prof) cudaEventRecord(ev[i], c->stream); }
 };
 
@@ -694,6 +701,9 @@ int gs_rast_destroy(gs_rast* r) {
     if (r->ev_scan) cudaEventDestroy(r->ev_scan);
     if (r->ev_fork) cudaEventDestroy(r->ev_fork);
     if (r->ev_join) cudaEventDestroy(r->ev_join);
+    if (r->ev_ord) cudaEventDestroy(r->ev_ord);
+    if (r->ev_free) cudaEventDestroy(r->ev_free);
+    if (r->ord) cudaStreamDestroy(r->ord);
     for (int i = 0; i < GS_PROF_EVENTS; i++) if (r->ev[i]) cudaEventDestroy(r->ev[i]);
     delete r;
     return GS_OK;
@@ -803,7 +813,8 @@ static int forward_hoisted(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs
 // lists and ranges as the other two modes; no sort over the P pairs.
 static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image* out) {
     gs_ctx* c = r->c;
-    cudaStream_t st = c->stream;
+    cudaStream_t blend_st = c->stream;
+    cudaStream_t st = r->ord_stream();                                // everything up to the expansion; the blend stays on the context stream
     const uint32_t n = r->n, W = r->W, H = r->H;
     const uint32_t tiles = r->ntx * r->nty, nbins = gs_bin_count(r->ntx, r->nty);
     int bin_bits = 0;
@@ -864,7 +875,11 @@ static int forward_binned(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_
         GS_CUDA(c, cudaEventRecord(r->ev_pairs, c->xfer_meta));
         r->mark(6);
         r->proj.tile_order = g_tile_order ? r->proj.tile_flags + r->cap_tiles : nullptr;
-        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, rast_vis_for_forward(r), (size_t)r->vis_cap, st);
+        if (st != blend_st) {                                         // the lists are final: hand over to the context stream
+            GS_CUDA(c, cudaEventRecord(r->ev_ord, st));
+            GS_CUDA(c, cudaStreamWaitEvent(blend_st, r->ev_ord, 0));
+        }
+        gs_launch_blend_forward(r->proj, r->sorted_vals, r->ranges, W, H, r->ntx, r->nty, out->px, r->last_idx, r->tfinal, 1, rast_vis_for_forward(r), (size_t)r->vis_cap, blend_st);
         r->mark(7);
         GS_LAUNCH_CHECK(c);
         GS_CUDA(c, cudaEventSynchronize(r->ev_pairs));                   // the GPU is still busy with the kernels above
@@ -895,6 +910,9 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
     GS_TRY(rast_reserve_image(r, W, H));
     r->n = n; r->pairs = 0; r->passes = 0; r->mode = g_sort_mode;
     if (r->mode == 0 && gs_bin_count(r->ntx, r->nty) > GS_MAX_BINS) r->mode = 2;
+    cudaStream_t blend_st = st;
+    st = r->ord_stream();
+    if (st != blend_st && r->free_valid) GS_CUDA(c, cudaStreamWaitEvent(st, r->ev_free, 0));   // this rasterizer's buffers are free from there on
     if (r->mode == 1) {   // meta: key OR = 0, key AND = ~0 (the totals are plain stores of the scans)
         GS_CUDA(c, cudaMemsetAsync(r->meta, 0, 2 * sizeof(uint32_t), st));
         GS_CUDA(c, cudaMemsetAsync(r->meta + GS_META_KEY_AND, 0xFF, sizeof(uint32_t), st));
@@ -908,7 +926,36 @@ int gs_rast_forward(gs_rast* r, gs_gaussians* g, const gs_uniforms* u, gs_image*
                          u->focalLength[0], u->focalLength[1], r->ntx, r->nty, n, r->mode == 1 ? r->meta : nullptr, dhist, st);
     r->mark(1);
     GS_TRY(r->mode == 1 ? forward_pairs64(r, g, u, out) : r->mode == 2 ? forward_hoisted(r, g, u, out) : forward_binned(r, g, u, out));
-    return image_after_use(out, st);
+    if (r->ord) { GS_CUDA(c, cudaEventRecord(r->ev_free, blend_st)); r->free_valid = true; }
+    return image_after_use(out, blend_st);
+}
+
+// Opt-in: run this rasterizer's stages BEFORE the blend (projection, depth sort, coarse pairs, bin sort, expansion) on a
+// high-priority stream of its own.  They are latency-bound one-wave kernels; the blend kernels are issue-bound and fill the
+// GPU.  A caller that alternates TWO rasterizers over independent frames (render-only views, or fwd+bwd frames of one parameter
+// set) then gets frame i+1's ordering stage under frame i's blend: the side stream only waits for the end of the SAME
+// rasterizer's previous call, the context stream waits for the side stream before the blend.  Contract: work queued on the
+// context stream that WRITES the Gaussians (upload, Adam, densify) after this rasterizer's last forward / backward is not
+// waited for -- call gs_rast_set_overlap(r, 1) again after such work (it re-arms the wait at the stream's current position),
+// or leave overlap off (the default: one stream, the order of the calls).  No counterpart in the reference (one command queue).
+int gs_rast_set_overlap(gs_rast* r, int on) {
+    gs_ctx* c = r->c; GS_SETDEV(c);
+    if (on) {
+        if (!r->ord) {
+            int lo = 0, hi = 0;
+            GS_CUDA(c, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            GS_CUDA(c, cudaStreamCreateWithPriority(&r->ord, cudaStreamNonBlocking, hi));
+            GS_CUDA(c, cudaEventCreateWithFlags(&r->ev_ord, cudaEventDisableTiming));
+            GS_CUDA(c, cudaEventCreateWithFlags(&r->ev_free, cudaEventDisableTiming));
+        }
+        GS_CUDA(c, cudaEventRecord(r->ev_free, c->stream));
+        r->free_valid = true;
+    } else if (r->ord) {
+        GS_CUDA(c, cudaStreamSynchronize(r->ord));
+        GS_CUDA(c, cudaStreamDestroy(r->ord)); r->ord = nullptr;
+        cudaEventDestroy(r->ev_ord); cudaEventDestroy(r->ev_free); r->ev_ord = r->ev_free = nullptr; r->free_valid = false;
+    }
+    return GS_OK;
 }
 
 int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniforms* u, gs_image* rendered, gs_image* gt, int flags) {
@@ -938,6 +985,7 @@ int gs_rast_backward(gs_rast* r, gs_gaussians* g, gs_grads* gr, const gs_uniform
     r->acc_clean = true;                                              // K8 cleared every row K7 touched
     r->mark(10);
     GS_LAUNCH_CHECK(c);
+    if (r->ord) { GS_CUDA(c, cudaEventRecord(r->ev_free, st)); r->free_valid = true; }
     GS_TRY(image_after_use(rendered, st));
     GS_TRY(image_after_use(gt, st));
     return GS_OK;

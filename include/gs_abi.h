@@ -254,6 +254,11 @@ int gs_rast_count_evals(gs_rast*, uint64_t* E, uint64_t* C);
 uint64_t gs_rast_pair_count(const gs_rast*);
 uint64_t gs_rast_coarse_pair_count(const gs_rast*);                      /* (8x8-tile bin, Gaussian) pairs of the last forward in the default binned pipeline; 0 in the sort pipelines */
 int gs_rast_sort_passes(const gs_rast*);                /* digit passes the last forward ran */
+/* Opt-in: the stages before the blend run on a high-priority stream of this rasterizer, so that a caller alternating two
+ * rasterizers over independent frames gets frame i+1's ordering stage under frame i's blend.  Writes to the Gaussians queued on
+ * the context stream after this rasterizer's last call are NOT waited for: call again after such work (re-arms the wait), or
+ * leave it off (default).  No counterpart in the reference (one command queue). */
+int gs_rast_set_overlap(gs_rast*, int on);
 /* 1 if the last backward took its per-pixel decisions from the visit words the forward recorded (every backward of a
  * rasterizer but its first, gs_tune "bwd_masks" = 1), 0 if it re-derived them (diagnostic of this library; no counterpart) */
 int gs_rast_backward_used_visits(const gs_rast*);
