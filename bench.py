@@ -922,6 +922,7 @@ class Bench:
                "steps": c4["views"], "warmup": 3, "ms_per_step": c4["ms_per_frame_per_gpu"], "higher_is_better": True, "scaling": "strong",
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": c4["workload"], "pairs": c4["pairs"], "two_in_flight": c4["two_in_flight"],
+                          "how": c4["how"], "frames_per_s_one_rasterizer": c4["frames_per_s_one_rasterizer"],
                           "parallelism": f"views dealt v mod {self.world}, no communication (BASELINE config 4; mtl_engine.mm:1224-1306)"},
                "e2e": {"value": c4["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": 240, "d2h_bytes_per_step": W * H * 4,
                        "what": "every frame's RGBA8 pixels read back to pinned host memory on the copy-out stream, wall clock"},

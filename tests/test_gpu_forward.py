@@ -141,3 +141,37 @@ def test_tfinal_matches_backward_first_pass(gs, ctx, orc):
         assert np.array_equal(got[m], tf[m])
     finally:
         img.close(); R.close(); G.close()
+
+
+def test_overlap_mode_changes_nothing(gs, ctx, orc):
+    """gs_rast_set_overlap: two rasterizers alternating over independent frames, the stages before the blend on a side stream;
+    every frame's image and lastContribIdx stay those of the one-stream run (and of the oracle for the first view)"""
+    n, W, H = 20000, 320, 200
+    g = synth.make_scene(n, 77, 0.02)
+    G = gs.Gaussians(ctx, n); G.upload(g)
+    Rs = [gs.Rasterizer(ctx, n), gs.Rasterizer(ctx, n)]
+    imgs = [gs.Image(ctx, W, H), gs.Image(ctx, W, H)]
+    cams = [synth.make_camera(v, 8, W, H, n) for v in range(8)]
+    try:
+        want = []
+        for v in range(8):
+            Rs[0].forward(G, cams[v], imgs[0])
+            want.append((imgs[0].download().copy(), Rs[0].get(gs.RAST_LAST_IDX).copy()))
+        ref = orc.render(g, cams[0])
+        assert np.array_equal(want[0][0], ref["image"]) and np.array_equal(want[0][1], ref["last"])
+        for R in Rs:
+            R.set_overlap(True)
+        for rep in range(3):
+            for v in range(0, 8, 2):                     # two frames in flight, then look at both
+                Rs[0].forward(G, cams[v], imgs[0])
+                Rs[1].forward(G, cams[v + 1], imgs[1])
+                for k in range(2):
+                    assert np.array_equal(imgs[k].download(), want[v + k][0]), (rep, v, k)
+                    assert np.array_equal(Rs[k].get(gs.RAST_LAST_IDX), want[v + k][1]), (rep, v, k)
+        for R in Rs:
+            R.set_overlap(False)
+        Rs[1].forward(G, cams[3], imgs[1])
+        assert np.array_equal(imgs[1].download(), want[3][0])
+    finally:
+        for o in imgs + Rs + [G]:
+            o.close()
