@@ -645,6 +645,37 @@ class Bench:
                 out[f"{kind}_{'iters' if kind == 'train' else 'steps'}_per_s_{a}_allreduce"] = 1e3 * K / ms
                 if kind == "c5":
                     c5[f"steps_per_s_{a}"] = 1e3 * K / ms
+        # One GPU only: the 8 views of a step share one parameter set, so two rasterizers can alternate over them with
+        # gs_rast_set_overlap (view k+1's stages before the blend under view k's blend kernels), re-armed after every Adam step.
+        # Reported beside the plain figure; the multi-GPU runs keep one rasterizer per rank (one view per rank at 8 GPUs).
+        if dist is None:
+            try:
+                Rb = gs.Rasterizer(ctx, n5)
+                for v in range(NVT):
+                    Rb.forward(G5, cams5[v], img)                         # sizes its pair buffers
+                Rb.forward(G5, cams5[0], img); Rb.backward(G5, D, cams5[0], img, gts5[0])   # its visit words exist from here on
+                Rs5 = [R, Rb]
+
+                def step_ov(i):
+                    for k, v in enumerate(vp.views(i, 8, NVT)):
+                        Rs5[k % 2].forward(G5, cams5[v], img)
+                        Rs5[k % 2].backward(G5, D, cams5[v], img, gts5[v], gs.GS_BWD_ACCUMULATE if k else 0)
+                    Dn.accumulate(D, n5)
+                    A5.step(G5, D, LRS)
+                    for Rx in Rs5:
+                        Rx.set_overlap(True)                              # re-arm: the next forwards wait for this Adam step
+                G5.upload(g5_host); A5.reset(); Dn.reset_accumulator(n5)
+                for Rx in Rs5:
+                    Rx.set_overlap(True)
+                for i in range(3):
+                    step_ov(i)
+                ms = self.timed(step_ov, K, collective=False)
+                c5["steps_per_s_two_rasterizers_overlapped"] = 1e3 * K / ms
+                for Rx in Rs5:
+                    Rx.set_overlap(False)
+                Rb.close()
+            except Exception as e:
+                c5["steps_per_s_two_rasterizers_overlapped"] = "failed: " + repr(e)[:120]
         if dist is not None:
             # correctness of this library's sums: the same per-rank inputs summed by NCCL, compared element for element
             G5.upload(g5_host)
