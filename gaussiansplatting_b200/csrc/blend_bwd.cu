@@ -6,9 +6,15 @@
 // accumulates those nine moments
 //     m0..2 = sum dLdp_c * w      m3 = sum q      m4,5 = sum q*dx, q*dy      m6,7,8 = sum q*dx^2, q*dx*dy, q*dy^2
 // (w = alpha*T, q = dL/dalpha * G), reduced across the warp by a transposed butterfly (14 shuffles for 9
-// values), across the CTA's warps in shared memory, and flushed with one global float atomic per
-// (tile, Gaussian, moment); K8 then applies the chain once per Gaussian.  The decisions (power, G, alpha
-// tests) use the pinned arithmetic so K7 walks exactly the entries the oracle walks.
+// values); K8 then applies the chain once per Gaussian.  Three walks share that arithmetic:
+//   blend_backward_warp_kernel     the default from a rasterizer's second backward on: every warp walks its own extent of the
+//                                  list on the visit words the forward recorded (its decisions per pixel slot), the moments of
+//                                  a visit go to the per-Gaussian rows as one global float reduction instruction
+//   blend_backward_kernel<2,true>  the same words, CTA-cooperative rounds (gs_tune "bwd_warp" = 0)
+//   blend_backward_kernel<.,false> the pinned walk: re-derives the decisions (power, G, alpha tests in the pinned arithmetic, so
+//                                  it walks exactly the entries the oracle walks), sums the warps' moments in shared memory and
+//                                  flushes one atomic per (tile, Gaussian, moment); a rasterizer's first backward, and through
+//                                  blend_backward_flagged_kernel the tiles the forward flagged (conic-degenerate entries)
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 

@@ -1,10 +1,15 @@
 // blend_fwd.cu — K5 tile ranges (buildTileRanges, sort.metal:553-589) and K6 the per-tile front-to-back
 // alpha blend (tiledForward, tiled_shaders.metal:307-385; graded fp32 mode, SURVEY note H).
 //
-// K6: one CTA per 16x16 tile, one thread per pixel, each warp an 8x4 pixel patch.  The tile's sorted list is
-// staged through shared memory 256 entries at a time (one 48-B record gather per thread, then broadcast
-// LDS.128 in the inner loop).  FP32-issue bound; all arithmetic is the pinned sequence of gs_common.cuh, so the
-// image, lastContribIdx and T_final are bit-identical to the oracle.
+// K6: one CTA of 128 threads per 16x16 tile, two pixels per thread held as one packed fp32 pair (FFMA2), each warp an 8x8
+// pixel region.  Two kernels share the visit arithmetic:
+//   blend_forward_kernel        the four warps stage the tile's sorted list through shared memory 128 entries at a time (one
+//                               48-B record gather per thread, footprint bits per warp region, broadcast LDS.128 in the walk);
+//                               the default of a render-only frame
+//   blend_forward_warp_kernel   every warp walks the list on its own, 32 entries at a time, and stops with its own 64 pixels;
+//                               the default of a training frame, where it also records the visit words the backward walks on
+// Issue-bound (FP32 pipe close behind); all arithmetic is the pinned sequence of gs_common.cuh, so the image, lastContribIdx
+// and T_final are bit-identical to the oracle from either kernel.
 #include "gs_common.cuh"
 #include "gs_kernels.h"
 
